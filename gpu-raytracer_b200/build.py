@@ -1,0 +1,85 @@
+"""Builds gpu-raytracer_b200/libokrt.so (the C-ABI library of include/okrt.h) in-tree.
+
+Host builders are compiled with g++ (-ffp-contract=off), the device side with nvcc for sm_100a only
+(-gencode arch=compute_100a,code=sm_100a -lineinfo, -fmad=false: see csrc/okrt_kernels.cuh for why).
+nvcc cross-compiles without a GPU; the resulting .so travels to the GPU box with the repo snapshot.
+"""
+import os
+import shutil
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+CSRC = os.path.join(HERE, "csrc")
+OUT = os.path.join(HERE, "libokrt.so")
+OBJ = os.path.join(HERE, "_obj")
+
+HOST_SOURCES = ["okrt_host.cpp", "okrt_accel.cpp"]
+DEVICE_SOURCES = ["okrt_device.cu"]
+HEADERS = ["okrt_internal.h", "okrt_accel.h", "okrt_kernels.cuh", "okrt_math.cuh"]
+
+
+def _nvcc():
+    for cand in (os.environ.get("NVCC"), shutil.which("nvcc"), "/usr/local/cuda/bin/nvcc"):
+        if cand and os.path.exists(cand):
+            return cand
+    raise RuntimeError("nvcc not found")
+
+
+def _host_cxx():
+    # the image exports CXX=/opt/gcc/bin/g++ (a wrapper without libgomp specs); the system g++ is what nvcc uses
+    for cand in ("/usr/bin/g++", shutil.which("g++")):
+        if cand and os.path.exists(cand):
+            return cand
+    raise RuntimeError("g++ not found")
+
+
+def _stale(target, deps):
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(d) > t for d in deps)
+
+
+def build_library(force=False, verbose=False, extra_nvcc=()):
+    os.makedirs(OBJ, exist_ok=True)
+    inc = ["-I" + os.path.join(ROOT, "include"), "-I" + CSRC]
+    common_deps = [os.path.join(ROOT, "include", "okrt.h")] + [os.path.join(CSRC, h) for h in HEADERS]
+    objs = []
+    for src in HOST_SOURCES:
+        s = os.path.join(CSRC, src)
+        o = os.path.join(OBJ, src + ".o")
+        objs.append(o)
+        if force or _stale(o, [s] + common_deps):
+            cmd = [_host_cxx(), "-std=c++17", "-O2", "-ffp-contract=off", "-fno-fast-math", "-fPIC", "-pthread",
+                   "-fvisibility=hidden", "-Wall", "-c", s, "-o", o] + inc
+            if verbose:
+                print(" ".join(cmd))
+            subprocess.run(cmd, check=True)
+    for src in DEVICE_SOURCES:
+        s = os.path.join(CSRC, src)
+        o = os.path.join(OBJ, src + ".o")
+        objs.append(o)
+        if force or _stale(o, [s] + common_deps):
+            cmd = [_nvcc(), "-ccbin", _host_cxx(), "-std=c++17", "-O3", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
+                   "-fmad=false", "-prec-div=true", "-prec-sqrt=true", "-ftz=false",
+                   "-Xcompiler", "-fPIC,-ffp-contract=off,-fvisibility=hidden", "-Xptxas", "-v",
+                   "-c", s, "-o", o] + inc + list(extra_nvcc)
+            if verbose:
+                print(" ".join(cmd))
+            res = subprocess.run(cmd, check=True, capture_output=True, text=True)
+            with open(os.path.join(OBJ, src + ".ptxas.log"), "w") as f:
+                f.write(res.stderr)
+            if verbose:
+                print(res.stderr)
+    if force or _stale(OUT, objs):
+        cmd = [_nvcc(), "-ccbin", _host_cxx(), "-shared", "-o", OUT] + objs + ["-lpthread"]
+        if verbose:
+            print(" ".join(cmd))
+        subprocess.run(cmd, check=True)
+    return OUT
+
+
+if __name__ == "__main__":
+    print(build_library(force="--force" in sys.argv, verbose=True))

@@ -1,0 +1,252 @@
+/*
+ * okrt_accel.cpp — builds the device acceleration layout described in okrt_accel.h from the
+ * reference-format arrays handed to okrt_set_* (t0 Triangle, t2 BvhNode, t5 OctTreeNode, t7 Mesh;
+ * resources/shaders/GPU-Structs.hlsli:95-98,113-125,159-179).  Host C++, runs once per scene change.
+ */
+#include "okrt_accel.h"
+
+#include <algorithm>
+#include <cfloat>
+#include <cmath>
+#include <cstring>
+#include <functional>
+#include <string>
+#include <unordered_map>
+
+namespace okrt {
+namespace {
+
+inline float bitsToFloat(uint32_t u) { float f; std::memcpy(&f, &u, 4); return f; }
+
+struct Builder {
+    const okrt_triangle* tris; uint32_t numTris;
+    const okrt_bvh_node* nodes; uint32_t numNodes;
+    FastLayout& out;
+    uint32_t deepestPair = 0;     /* pair-node levels below a mesh root (for the fast stack bound) */
+    uint32_t deepestLeafLevel = 0;/* reference node levels (for the exact stack bound) */
+    bool failed = false;
+
+    uint32_t newPair()
+    {
+        const uint32_t idx = (uint32_t)(out.nodes.size() / 4);
+        out.nodes.resize(out.nodes.size() + 4, Float4{0, 0, 0, 0});
+        return idx;
+    }
+    void setChild(uint32_t pair, int which, const okrt_aabb& box, uint32_t ref)
+    {
+        Float4* q = &out.nodes[(size_t)pair * 4];
+        q[which * 2 + 0].x = box.min[0]; q[which * 2 + 0].y = box.min[1]; q[which * 2 + 0].z = box.min[2];
+        q[which * 2 + 1].x = box.max[0]; q[which * 2 + 1].y = box.max[1]; q[which * 2 + 1].z = box.max[2];
+        if (which == 0) q[0].w = bitsToFloat(ref); else q[1].w = bitsToFloat(ref);
+    }
+    bool fail(const std::string& why) { if (!failed) out.error = why; failed = true; return false; }
+
+    /* child reference for triangles [start, start+count) bounded by `box` */
+    uint32_t leafRef(uint32_t start, uint32_t count, const okrt_aabb& box, uint32_t level, uint32_t pairLevel)
+    {
+        if (count == 0) return kRefNone;
+        if ((uint64_t)start + count > numTris || start >= kMaxTriIndex) { fail("BVH leaf references triangles out of range"); return kRefNone; }
+        if (count <= kMaxLeafTris) return kRefTriLeaf | ((count - 1u) << 27) | start;
+        /* oversized leaf: chain of pair nodes that repeat the leaf's box */
+        const uint32_t p = newPair();
+        deepestPair = std::max(deepestPair, pairLevel + 1);
+        const uint32_t head = kRefTriLeaf | ((kMaxLeafTris - 1u) << 27) | start;
+        setChild(p, 0, box, head);
+        const uint32_t rest = leafRef(start + kMaxLeafTris, count - kMaxLeafTris, box, level, pairLevel + 1);
+        setChild(p, 1, box, rest);
+        return p;
+    }
+
+    uint32_t convert(uint32_t nodeIdx, uint32_t level, uint32_t pairLevel)
+    {
+        if (failed) return kRefNone;
+        if (nodeIdx >= numNodes) { fail("BVH child index out of range"); return kRefNone; }
+        if (level > 4096) { fail("BVH deeper than 4096 levels (cycle?)"); return kRefNone; }
+        const okrt_bvh_node& n = nodes[nodeIdx];
+        if (n.firstChildIdx == OKRT_INVALID_UINT) {
+            deepestLeafLevel = std::max(deepestLeafLevel, level);
+            const uint32_t count = (n.triEnd >= n.triStart && n.triStart != OKRT_INVALID_UINT) ? n.triEnd - n.triStart : 0u;
+            return leafRef(n.triStart, count, n.boundingBox, level, pairLevel);
+        }
+        if ((uint64_t)n.firstChildIdx + 1 >= numNodes) { fail("BVH child index out of range"); return kRefNone; }
+        const uint32_t p = newPair();
+        deepestPair = std::max(deepestPair, pairLevel + 1);
+        const uint32_t r0 = convert(n.firstChildIdx, level + 1, pairLevel + 1);
+        const uint32_t r1 = convert(n.firstChildIdx + 1, level + 1, pairLevel + 1);
+        setChild(p, 0, nodes[n.firstChildIdx].boundingBox, r0);
+        setChild(p, 1, nodes[n.firstChildIdx + 1].boundingBox, r1);
+        return p;
+    }
+};
+
+struct TopLeaf { double lo[3], hi[3]; uint32_t record; };
+
+inline float roundDown(double v) { float f = (float)v; return (double)f > v ? std::nextafterf(f, -INFINITY) : f; }
+inline float roundUp(double v) { float f = (float)v; return (double)f < v ? std::nextafterf(f, INFINITY) : f; }
+
+} // namespace
+
+bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh_node* nodes, uint32_t numNodes,
+                     const okrt_mesh_instance* instances, uint32_t numInstances,
+                     const okrt_octree_node* octNodes, uint32_t numOctNodes, FastLayout& out)
+{
+    out = FastLayout();
+
+    /* triangles: 3 x float4 */
+    out.tris.resize((size_t)numTris * 3);
+    for (uint32_t t = 0; t < numTris; t++)
+        for (int v = 0; v < 3; v++)
+            out.tris[(size_t)t * 3 + v] = Float4{tris[t].position[v][0], tris[t].position[v][1], tris[t].position[v][2], 0.f};
+
+    /* oct-tree: parents, reachability, reference stack bound */
+    out.octParent.assign(numOctNodes, 0xFFFFFFFFu);
+    std::vector<uint8_t> reachable(numOctNodes, 0);
+    if (numOctNodes) {
+        std::vector<uint32_t> stack{0u};
+        size_t maxOcc = 1, visited = 0;
+        while (!stack.empty()) {
+            const uint32_t n = stack.back(); stack.pop_back();
+            if (reachable[n]) { out.error = "oct-tree node reachable twice"; return false; }
+            reachable[n] = 1;
+            if (++visited > numOctNodes) { out.error = "oct-tree cycle"; return false; }
+            const okrt_octree_node& on = octNodes[n];
+            for (uint32_t c = 0; c < on.numChildren; c++) {
+                const uint64_t ci = (uint64_t)on.firstChildIdx + c;
+                if (ci >= numOctNodes) { out.error = "oct-tree child index out of range"; return false; }
+                out.octParent[ci] = n;
+                stack.push_back((uint32_t)ci);
+            }
+            maxOcc = std::max(maxOcc, stack.size());
+        }
+        out.exactOctDepth = (uint32_t)maxOcc;
+    }
+
+    /* which (reachable) oct-tree node lists each instance */
+    std::vector<uint32_t> instOct(numInstances, 0xFFFFFFFFu);
+    for (uint32_t n = 0; n < numOctNodes; n++) {
+        if (!reachable[n]) continue;
+        const okrt_octree_node& on = octNodes[n];
+        if (on.meshesStartIdx == OKRT_INVALID_UINT || on.meshesEndIdx == OKRT_INVALID_UINT) continue;
+        if (on.meshesEndIdx > numInstances && on.meshesStartIdx < on.meshesEndIdx) { out.error = "oct-tree node lists instances out of range"; return false; }
+        for (uint32_t i = on.meshesStartIdx; i < on.meshesEndIdx; i++) {
+            if (instOct[i] != 0xFFFFFFFFu) { out.error = "instance listed by two oct-tree nodes"; return false; }
+            instOct[i] = n;
+        }
+    }
+
+    /* bottom level: one conversion per distinct BVH root */
+    Builder b{tris, numTris, nodes, numNodes, out};
+    std::unordered_map<uint32_t, uint32_t> rootRefOf;
+    std::vector<TopLeaf> leaves;
+    for (uint32_t i = 0; i < numInstances; i++) {
+        if (instOct[i] == 0xFFFFFFFFu) continue;                 /* never visited by the reference either */
+        const okrt_mesh_instance& inst = instances[i];
+        if (inst.bvhNodeStartIdx >= numNodes) { out.error = "instance bvhNodeStartIdx out of range"; return false; }
+        auto it = rootRefOf.find(inst.bvhNodeStartIdx);
+        uint32_t rootRef;
+        if (it == rootRefOf.end()) {
+            const uint32_t before = b.deepestPair;
+            b.deepestPair = 0;
+            rootRef = b.convert(inst.bvhNodeStartIdx, 0, 0);
+            if (b.failed) return false;
+            b.deepestPair = std::max(before, b.deepestPair);
+            rootRefOf.emplace(inst.bvhNodeStartIdx, rootRef);
+        } else rootRef = it->second;
+        if (rootRef == kRefNone) continue;                       /* empty mesh */
+
+        const okrt_aabb& rb = nodes[inst.bvhNodeStartIdx].boundingBox;
+        const float* T = inst.transformMatrix;
+        const float* Ti = inst.inverseTransformMatrix;
+        bool finite = true;
+        for (int k = 0; k < 3; k++) finite = finite && std::isfinite(rb.min[k]) && std::isfinite(rb.max[k]) && rb.min[k] <= rb.max[k];
+        for (int k = 0; k < 16; k++) finite = finite && std::isfinite(T[k]) && std::isfinite(Ti[k]);
+        if (!finite) continue;                                   /* the reference's box test can never pass */
+
+        /* rigidity: (T3x3)^T (T3x3) == I within 1e-4 — otherwise local and world distances differ and
+         * the reference's local-vs-world culling (RaytracerCS.hlsl:285) is order dependent */
+        for (int a = 0; a < 3; a++)
+            for (int c = 0; c < 3; c++) {
+                double d = 0;
+                for (int r = 0; r < 3; r++) d += (double)T[r * 4 + a] * (double)T[r * 4 + c];
+                if (std::fabs(d - (a == c ? 1.0 : 0.0)) > 1e-4) out.allRigid = false;
+            }
+        static const float I16[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
+        bool identity = true;
+        for (int k = 0; k < 16; k++) identity = identity && T[k] == I16[k] && Ti[k] == I16[k];
+
+        const uint32_t rec = (uint32_t)(out.instances.size() / 8);
+        out.instances.resize(out.instances.size() + 8);
+        Float4* r = &out.instances[(size_t)rec * 8];
+        for (int row = 0; row < 3; row++) r[row] = Float4{Ti[row * 4 + 0], Ti[row * 4 + 1], Ti[row * 4 + 2], Ti[row * 4 + 3]};
+        for (int row = 0; row < 3; row++) r[3 + row] = Float4{T[row * 4 + 0], T[row * 4 + 1], T[row * 4 + 2], rb.min[row]};
+        r[6] = Float4{rb.max[0], rb.max[1], rb.max[2], bitsToFloat(identity ? 1u : 0u)};
+        r[7] = Float4{bitsToFloat(rootRef), bitsToFloat(instOct[i]), bitsToFloat(i), 0.f};
+
+        /* world box of the root box, padded: the top level only has to be conservative */
+        TopLeaf leaf; leaf.record = rec;
+        for (int k = 0; k < 3; k++) { leaf.lo[k] = DBL_MAX; leaf.hi[k] = -DBL_MAX; }
+        for (int corner = 0; corner < 8; corner++) {
+            const double v[3] = {(corner & 1) ? rb.max[0] : rb.min[0], (corner & 2) ? rb.max[1] : rb.min[1], (corner & 4) ? rb.max[2] : rb.min[2]};
+            for (int row = 0; row < 3; row++) {
+                const double p = (double)T[row * 4 + 0] * v[0] + (double)T[row * 4 + 1] * v[1] + (double)T[row * 4 + 2] * v[2] + (double)T[row * 4 + 3];
+                leaf.lo[row] = std::min(leaf.lo[row], p); leaf.hi[row] = std::max(leaf.hi[row], p);
+            }
+        }
+        double diag = 0, mag = 0;
+        for (int k = 0; k < 3; k++) { diag += (leaf.hi[k] - leaf.lo[k]) * (leaf.hi[k] - leaf.lo[k]); mag = std::max(mag, std::max(std::fabs(leaf.lo[k]), std::fabs(leaf.hi[k]))); }
+        const double pad = 1e-4 * std::sqrt(diag) + 1e-5 * mag + 1e-6;
+        for (int k = 0; k < 3; k++) { leaf.lo[k] -= pad; leaf.hi[k] += pad; }
+        leaves.push_back(leaf);
+    }
+    out.exactBvhDepth = b.deepestLeafLevel + 1;
+
+    /* top level: median split on the widest centroid axis, one instance per leaf */
+    uint32_t topDepth = 0;
+    std::function<uint32_t(size_t, size_t, uint32_t, okrt_aabb&)> buildTop = [&](size_t lo, size_t hi, uint32_t level, okrt_aabb& box) -> uint32_t {
+        double bl[3] = {DBL_MAX, DBL_MAX, DBL_MAX}, bh[3] = {-DBL_MAX, -DBL_MAX, -DBL_MAX};
+        double cl[3] = {DBL_MAX, DBL_MAX, DBL_MAX}, ch[3] = {-DBL_MAX, -DBL_MAX, -DBL_MAX};
+        for (size_t i = lo; i < hi; i++)
+            for (int k = 0; k < 3; k++) {
+                bl[k] = std::min(bl[k], leaves[i].lo[k]); bh[k] = std::max(bh[k], leaves[i].hi[k]);
+                const double c = 0.5 * (leaves[i].lo[k] + leaves[i].hi[k]);
+                cl[k] = std::min(cl[k], c); ch[k] = std::max(ch[k], c);
+            }
+        for (int k = 0; k < 3; k++) { box.min[k] = roundDown(bl[k]); box.max[k] = roundUp(bh[k]); }
+        if (hi - lo == 1) return kRefInstance | leaves[lo].record;
+        int axis = 0;
+        if (ch[1] - cl[1] > ch[axis] - cl[axis]) axis = 1;
+        if (ch[2] - cl[2] > ch[axis] - cl[axis]) axis = 2;
+        const size_t mid = lo + (hi - lo) / 2;
+        std::nth_element(leaves.begin() + (ptrdiff_t)lo, leaves.begin() + (ptrdiff_t)mid, leaves.begin() + (ptrdiff_t)hi,
+                         [axis](const TopLeaf& a, const TopLeaf& c) { return a.lo[axis] + a.hi[axis] < c.lo[axis] + c.hi[axis]; });
+        const uint32_t p = b.newPair();
+        topDepth = std::max(topDepth, level + 1);
+        okrt_aabb b0, b1;
+        const uint32_t r0 = buildTop(lo, mid, level + 1, b0);
+        const uint32_t r1 = buildTop(mid, hi, level + 1, b1);
+        b.setChild(p, 0, b0, r0);
+        b.setChild(p, 1, b1, r1);
+        return p;
+    };
+    if (!leaves.empty()) {
+        okrt_aabb rootBox;
+        out.topRef = buildTop(0, leaves.size(), 0, rootBox);
+        if ((out.topRef & kRefTagMask) == kRefInstance) {
+            /* single instance: wrap it in a pair node so the kernel always starts at an interior node */
+            const uint32_t p = b.newPair();
+            okrt_aabb empty; for (int k = 0; k < 3; k++) { empty.min[k] = FLT_MAX; empty.max[k] = -FLT_MAX; }
+            b.setChild(p, 0, rootBox, out.topRef);
+            b.setChild(p, 1, empty, kRefNone);
+            out.topRef = p;
+            topDepth = 1;
+        }
+    }
+    if ((out.nodes.size() / 4) >= (1u << 30) || (out.instances.size() / 8) >= (1u << 30)) { out.error = "scene too large for 30-bit references"; return false; }
+
+    /* fast stack: one deferred sibling per level in each tree, plus the instance-exit marker */
+    out.maxStackDepth = topDepth + b.deepestPair + 2;
+    if (b.failed) return false;
+    return true;
+}
+
+} // namespace okrt

@@ -1,0 +1,72 @@
+/*
+ * okrt_accel.h — device-side acceleration layout ("fast layout") built at upload time from the
+ * reference's canonical arrays (BvhNode 36 B, Triangle 36 B, Mesh 232 B, OctTreeNode 48 B).
+ *
+ * Child-pair node, 64 B, 16 B aligned, four LDG.128 per visit (BASELINE.json north_star: "node layout
+ * re-packed into ... 16B-aligned AABB pairs for vectorised LDG.128 loads"):
+ *     q0 = { c0.min.x, c0.min.y, c0.min.z, bits(ref0) }
+ *     q1 = { c0.max.x, c0.max.y, c0.max.z, bits(ref1) }
+ *     q2 = { c1.min.x, c1.min.y, c1.min.z, 0 }
+ *     q3 = { c1.max.x, c1.max.y, c1.max.z, 0 }
+ * The box floats are bit copies of the reference node boxes (BLAS) so that the slab test gives the
+ * reference's distNear/distFar exactly.  A child reference is one 32-bit word:
+ *     00 nnnnn...   interior: index of a child-pair node
+ *     10 ccc sssss  triangle leaf: count-1 (3 bits, <= 8 triangles), first triangle (27 bits)
+ *     11 iiiii...   instance leaf (top level only): index into the instance-record array
+ * Leaves with more than 8 triangles (possible when the SAH refuses to split or maxDepth is hit) are
+ * chained through extra pair nodes that repeat the leaf's box.
+ *
+ * Triangle: 48 B = three float4 {p.xyz, 0}; positions are bit copies (E1/E2 are formed in the kernel
+ * exactly as GPU-Utilities.hlsli:124 does).
+ *
+ * Instance record: 128 B = eight float4
+ *     r0..r2  rows 0..2 of inverseTransformMatrix           (world -> local)
+ *     r3..r5  rows 0..2 of transformMatrix, .w = root box min (local -> world for directions)
+ *     r6      root box max.xyz, .w = bits(flags)  (bit0: transform is exactly identity)
+ *     r7      bits{ rootRef, octNodeIdx, instanceIdx (reference order), 0 }
+ * The top-level tree over instance world boxes replaces the reference's oct-tree walk for CULLING
+ * only; every oct-tree box the reference would test on the way to an instance is still tested (with
+ * its arithmetic) before the instance is entered, so hit/miss decisions are unchanged.
+ */
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+#include "okrt.h"
+
+namespace okrt {
+
+constexpr uint32_t kRefTagMask = 0xC0000000u;
+constexpr uint32_t kRefInterior = 0x00000000u;
+constexpr uint32_t kRefTriLeaf = 0x80000000u;
+constexpr uint32_t kRefInstance = 0xC0000000u;
+constexpr uint32_t kRefNone = 0xFFFFFFFFu;        /* empty scene / empty child */
+constexpr uint32_t kMaxLeafTris = 8;
+constexpr uint32_t kMaxTriIndex = (1u << 27);
+constexpr uint32_t kFastStackCapacity = 64;       /* entries; validated against tree depth at upload */
+constexpr uint32_t kExactBvhStackCapacity = 64;   /* reference: 50, RaytracerCS.hlsl:249 */
+constexpr uint32_t kExactOctStackCapacity = 32;   /* reference: 20, RaytracerCS.hlsl:244 */
+
+struct Float4 { float x, y, z, w; };
+
+struct FastLayout {
+    std::vector<Float4> nodes;          /* 4 per pair node */
+    std::vector<Float4> tris;           /* 3 per triangle */
+    std::vector<Float4> instances;      /* 8 per instance record, top-level order */
+    std::vector<uint32_t> octParent;    /* parent index per oct-tree node (root: 0xFFFFFFFF) */
+    uint32_t topRef = kRefNone;         /* reference to the top-level root (interior or instance leaf) */
+    uint32_t maxStackDepth = 0;         /* worst-case fast-stack occupancy */
+    uint32_t exactBvhDepth = 0;         /* worst-case reference BVH stack occupancy */
+    uint32_t exactOctDepth = 0;         /* worst-case reference oct-tree stack occupancy */
+    bool allRigid = true;               /* every instance transform has unit scale */
+    std::string error;
+};
+
+/* Returns false (and sets out.error) if the scene cannot be laid out. */
+bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris,
+                     const okrt_bvh_node* nodes, uint32_t numNodes,
+                     const okrt_mesh_instance* instances, uint32_t numInstances,
+                     const okrt_octree_node* octNodes, uint32_t numOctNodes,
+                     FastLayout& out);
+
+} // namespace okrt

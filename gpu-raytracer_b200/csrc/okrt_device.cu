@@ -1,0 +1,578 @@
+/*
+ * okrt_device.cu — the renderer object behind the C ABI (include/okrt.h): device buffers for the
+ * reference's binding table, the re-packed acceleration layout, launch of the path-trace kernel.
+ * Replaces RayTracer::{initiate, render, updateBuffers, onResize, resetAccumulation}
+ * (source/Graphics/RayTracer.cpp:60-118,219-260,434-501; RayTracer.h:197-211) and GPUStorage
+ * (source/Graphics/GPUStorage.cpp:27-50) with cudaMalloc-backed buffers on one stream per handle.
+ *
+ * There is no CPU fallback: without a CUDA device okrt_create fails with OKRT_ERR_NO_DEVICE.
+ */
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "okrt.h"
+#include "okrt_accel.h"
+#include "okrt_internal.h"
+#include "okrt_kernels.cuh"
+
+using namespace okrt;
+
+namespace {
+
+struct CudaError { cudaError_t code; const char* what; };
+
+#define OKRT_CUDA(call)                                                                      \
+    do {                                                                                     \
+        cudaError_t e__ = (call);                                                            \
+        if (e__ != cudaSuccess) {                                                            \
+            setError(std::string(#call) + ": " + cudaGetErrorString(e__));                   \
+            return OKRT_ERR_CUDA;                                                            \
+        }                                                                                    \
+    } while (0)
+
+/* GPUStorage equivalent: initiate / updateRaw with re-allocation when the element count changes */
+struct DeviceBuffer {
+    void* ptr = nullptr;
+    size_t bytes = 0;
+    uint32_t count = 0;
+
+    int upload(const void* host, uint32_t n, size_t elemBytes, cudaStream_t stream)
+    {
+        const size_t need = (size_t)n * elemBytes;
+        if (need != bytes) {
+            if (ptr) { cudaFree(ptr); ptr = nullptr; bytes = 0; }
+            if (need) OKRT_CUDA(cudaMalloc(&ptr, need));
+            bytes = need;
+        }
+        count = n;
+        if (need) {
+            OKRT_CUDA(cudaMemcpyAsync(ptr, host, need, cudaMemcpyHostToDevice, stream));
+            OKRT_CUDA(cudaStreamSynchronize(stream));         /* caller's array may be freed on return */
+        }
+        return OKRT_OK;
+    }
+    void release() { if (ptr) cudaFree(ptr); ptr = nullptr; bytes = 0; count = 0; }
+};
+
+struct TextureArray {
+    cudaArray_t array = nullptr;
+    cudaTextureObject_t object = 0;
+    uint32_t width = 0, height = 0, layers = 0;
+
+    void release()
+    {
+        if (object) cudaDestroyTextureObject(object);
+        if (array) cudaFreeArray(array);
+        object = 0; array = nullptr; width = height = layers = 0;
+    }
+    int upload(const uint8_t* rgba8, uint32_t w, uint32_t h, uint32_t n, cudaStream_t stream)
+    {
+        release();
+        if (!w || !h || !n) return OKRT_OK;
+        cudaChannelFormatDesc desc = cudaCreateChannelDesc<uchar4>();
+        OKRT_CUDA(cudaMalloc3DArray(&array, &desc, make_cudaExtent(w, h, n), cudaArrayLayered));
+        cudaMemcpy3DParms p;
+        std::memset(&p, 0, sizeof(p));
+        p.srcPtr = make_cudaPitchedPtr(const_cast<uint8_t*>(rgba8), (size_t)w * 4, w, h);
+        p.dstArray = array;
+        p.extent = make_cudaExtent(w, h, n);
+        p.kind = cudaMemcpyHostToDevice;
+        OKRT_CUDA(cudaMemcpy3DAsync(&p, stream));
+        OKRT_CUDA(cudaStreamSynchronize(stream));
+        cudaResourceDesc res;
+        std::memset(&res, 0, sizeof(res));
+        res.resType = cudaResourceTypeArray;
+        res.res.array.array = array;
+        cudaTextureDesc td;
+        std::memset(&td, 0, sizeof(td));
+        td.addressMode[0] = td.addressMode[1] = td.addressMode[2] = cudaAddressModeClamp;
+        td.filterMode = cudaFilterModePoint;                  /* filtering is done in float32 in the kernel */
+        td.readMode = cudaReadModeElementType;
+        td.normalizedCoords = 0;
+        OKRT_CUDA(cudaCreateTextureObject(&object, &res, &td, nullptr));
+        width = w; height = h; layers = n;
+        return OKRT_OK;
+    }
+};
+
+} // namespace
+
+struct okrt_renderer {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t evStart = nullptr, evStop = nullptr;
+    uint32_t width = 0, height = 0;
+
+    DeviceBuffer triPos, triInfo, bvhNodes, octNodes, spheres, instances, dirLights, pointLights, spotLights;
+    TextureArray textures, environment;
+    DeviceBuffer fastNodes, fastTris, fastInstances, octParent;
+
+    /* host copies needed to (re)build the fast layout */
+    std::vector<okrt_triangle> hTris;
+    std::vector<okrt_bvh_node> hNodes;
+    std::vector<okrt_mesh_instance> hInstances;
+    std::vector<okrt_octree_node> hOct;
+    bool layoutDirty = true;
+    uint32_t topRef = kRefNone;
+    bool allRigid = true;
+    uint32_t fastStackNeed = 0, exactBvhNeed = 0, exactOctNeed = 0;
+
+    float4* accumulation = nullptr;
+    uchar4* result = nullptr;
+    okrt_aov* aov = nullptr;
+    unsigned long long* counters = nullptr;     /* 4 x u64 on device */
+
+    okrt_render_data rd;
+    okrt_options opt;
+    uint64_t launches = 0;
+    float lastRenderMs = 0.f;
+};
+
+namespace {
+
+int allocateImages(okrt_renderer* r)
+{
+    const size_t n = (size_t)r->width * r->height;
+    if (r->accumulation) cudaFree(r->accumulation);
+    if (r->result) cudaFree(r->result);
+    if (r->aov) cudaFree(r->aov);
+    r->accumulation = nullptr; r->result = nullptr; r->aov = nullptr;
+    OKRT_CUDA(cudaMalloc(&r->accumulation, n * sizeof(float4)));
+    OKRT_CUDA(cudaMalloc(&r->result, n * sizeof(uchar4)));
+    OKRT_CUDA(cudaMemsetAsync(r->accumulation, 0, n * sizeof(float4), r->stream));
+    clearResultKernel<<<(unsigned)((n + 255) / 256), 256, 0, r->stream>>>(r->result, n);
+    r->launches++;
+    OKRT_CUDA(cudaGetLastError());
+    return OKRT_OK;
+}
+
+int ensureAov(okrt_renderer* r)
+{
+    if (r->aov) return OKRT_OK;
+    const size_t n = (size_t)r->width * r->height;
+    OKRT_CUDA(cudaMalloc(&r->aov, n * sizeof(okrt_aov)));
+    OKRT_CUDA(cudaMemsetAsync(r->aov, 0, n * sizeof(okrt_aov), r->stream));
+    return OKRT_OK;
+}
+
+int rebuildLayout(okrt_renderer* r)
+{
+    FastLayout fl;
+    if (!buildFastLayout(r->hTris.data(), (uint32_t)r->hTris.size(), r->hNodes.data(), (uint32_t)r->hNodes.size(),
+                         r->hInstances.data(), (uint32_t)r->hInstances.size(), r->hOct.data(), (uint32_t)r->hOct.size(), fl)) {
+        setError("scene rejected: " + fl.error);
+        return OKRT_ERR_INVALID_ARGUMENT;
+    }
+    if (fl.maxStackDepth > kFastStackCapacity || fl.exactBvhDepth > kExactBvhStackCapacity || fl.exactOctDepth > kExactOctStackCapacity) {
+        char msg[256];
+        std::snprintf(msg, sizeof(msg), "traversal stack would overflow: fast %u/%u, bvh %u/%u, oct-tree %u/%u",
+                      fl.maxStackDepth, kFastStackCapacity, fl.exactBvhDepth, kExactBvhStackCapacity, fl.exactOctDepth, kExactOctStackCapacity);
+        setError(msg);
+        return OKRT_ERR_CAPACITY;
+    }
+    int rc;
+    if ((rc = r->fastNodes.upload(fl.nodes.data(), (uint32_t)fl.nodes.size(), sizeof(Float4), r->stream))) return rc;
+    if ((rc = r->fastTris.upload(fl.tris.data(), (uint32_t)fl.tris.size(), sizeof(Float4), r->stream))) return rc;
+    if ((rc = r->fastInstances.upload(fl.instances.data(), (uint32_t)fl.instances.size(), sizeof(Float4), r->stream))) return rc;
+    if ((rc = r->octParent.upload(fl.octParent.data(), (uint32_t)fl.octParent.size(), sizeof(uint32_t), r->stream))) return rc;
+    r->topRef = fl.topRef;
+    r->allRigid = fl.allRigid;
+    r->fastStackNeed = fl.maxStackDepth; r->exactBvhNeed = fl.exactBvhDepth; r->exactOctNeed = fl.exactOctDepth;
+    r->layoutDirty = false;
+    return OKRT_OK;
+}
+
+DeviceScene sceneView(const okrt_renderer* r)
+{
+    DeviceScene s;
+    std::memset(&s, 0, sizeof(s));
+    s.triPos = (const float*)r->triPos.ptr;
+    s.triInfo = (const float*)r->triInfo.ptr;
+    s.bvhNodes = (const okrt_bvh_node*)r->bvhNodes.ptr;
+    s.textures = r->textures.object;
+    s.environment = r->environment.object;
+    s.octNodes = (const okrt_octree_node*)r->octNodes.ptr;
+    s.spheres = (const okrt_sphere*)r->spheres.ptr;
+    s.instances = (const okrt_mesh_instance*)r->instances.ptr;
+    s.dirLights = (const okrt_directional_light*)r->dirLights.ptr;
+    s.pointLights = (const okrt_point_light*)r->pointLights.ptr;
+    s.spotLights = (const okrt_spot_light*)r->spotLights.ptr;
+    s.numTris = r->triPos.count; s.numBvhNodes = r->bvhNodes.count; s.numOctNodes = r->octNodes.count;
+    s.numSpheres = r->spheres.count; s.numInstances = r->instances.count;
+    s.numDirLights = r->dirLights.count; s.numPointLights = r->pointLights.count; s.numSpotLights = r->spotLights.count;
+    s.texSize = r->textures.width; s.texLayers = r->textures.layers;
+    s.envW = r->environment.width; s.envH = r->environment.height;
+    s.fastNodes = (const float4*)r->fastNodes.ptr;
+    s.fastTris = (const float4*)r->fastTris.ptr;
+    s.fastInstances = (const float4*)r->fastInstances.ptr;
+    s.octParent = (const uint32_t*)r->octParent.ptr;
+    s.topRef = r->topRef;
+    return s;
+}
+
+void coveredExtent(const okrt_renderer* r, uint32_t& cw, uint32_t& ch)
+{
+    /* [Q9] Dispatch(W/16, H/9) x numthreads(16,9) — RayTracer.cpp:256 */
+    cw = r->opt.coverAllPixels ? r->width : 16u * (r->width / 16u);
+    ch = r->opt.coverAllPixels ? r->height : 9u * (r->height / 9u);
+}
+
+int launchFrame(okrt_renderer* r)
+{
+    /* updateBuffers: the counter advances before the constants are uploaded (RayTracer.cpp:489) */
+    r->rd.numAccumulationFrames += r->rd.accumulationEnabled;
+    r->rd.textureDims[0] = r->width; r->rd.textureDims[1] = r->height;
+
+    FrameParams fp;
+    std::memset(&fp, 0, sizeof(fp));
+    fp.rd = r->rd;
+    fp.maxBounces = r->opt.maxBounces;
+    /* sample sharding: local frame k (1-based) draws the seed of global frame offset + (k-1)*stride + 1 */
+    const uint32_t localFrame = r->rd.numAccumulationFrames;
+    fp.seedFrame = r->rd.accumulationEnabled ? r->opt.frameOffset + (localFrame - 1u) * r->opt.frameStride + 1u : r->opt.frameOffset;
+    /* scaled instances make the reference's local-vs-world culling order dependent; debug heat maps
+     * display the reference's own visit counters: both need the reference visiting order */
+    fp.traversal = (r->opt.traversal == OKRT_TRAVERSAL_EXACT || !r->allRigid || r->rd.debugMode != 0u) ? OKRT_TRAVERSAL_EXACT : OKRT_TRAVERSAL_FAST;
+    coveredExtent(r, fp.coveredW, fp.coveredH);
+    fp.accumulation = r->accumulation;
+    fp.result = r->result;
+    fp.aov = r->opt.writeAov ? r->aov : nullptr;
+    fp.counters = r->counters;
+
+    uint32_t rows = r->height;
+    fp.shardCount = 1; fp.shardRank = 0; fp.bandRows = kTileH;
+    if (r->opt.shardMode == OKRT_SHARD_TILE && r->opt.shardCount > 1u) {
+        fp.shardCount = r->opt.shardCount; fp.shardRank = r->opt.shardRank;
+        fp.bandRows = r->opt.shardBandRows ? r->opt.shardBandRows : 8u;
+        const uint32_t bands = (r->height + fp.bandRows - 1u) / fp.bandRows;
+        const uint32_t mine = bands / fp.shardCount + ((bands % fp.shardCount) > fp.shardRank ? 1u : 0u);
+        rows = mine * fp.bandRows;
+    }
+    /* the reference clears the whole target to (0.2,0.4,0.6,1) every frame (RayTracer.cpp:227-228) and then
+     * overwrites every covered pixel; uncovered pixels [Q9] are cleared once, when the images are created
+     * or the coverage option changes, and never written afterwards */
+    if (rows == 0) return OKRT_OK;
+    const dim3 grid((r->width + kTileW - 1) / kTileW, (rows + kTileH - 1) / kTileH, 1);
+    pathTraceKernel<<<grid, kTileW * kTileH, 0, r->stream>>>(sceneView(r), fp);
+    r->launches++;
+    OKRT_CUDA(cudaGetLastError());
+    return OKRT_OK;
+}
+
+int checkHandle(const okrt_renderer* r, const char* fn)
+{
+    if (!r) { setError(std::string(fn) + ": null renderer"); return OKRT_ERR_INVALID_ARGUMENT; }
+    cudaError_t e = cudaSetDevice(r->device);
+    if (e != cudaSuccess) { setError(std::string(fn) + ": cudaSetDevice: " + cudaGetErrorString(e)); return OKRT_ERR_CUDA; }
+    return OKRT_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+int okrt_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+int okrt_create(int device, uint32_t width, uint32_t height, okrt_renderer** out)
+{
+    if (!out || !width || !height) { setError("okrt_create: bad argument"); return OKRT_ERR_INVALID_ARGUMENT; }
+    *out = nullptr;
+    const int n = okrt_device_count();
+    if (n <= 0) { setError("okrt_create: no CUDA device visible; this library has no CPU path"); return OKRT_ERR_NO_DEVICE; }
+    if (device < 0 || device >= n) { setError("okrt_create: device index out of range"); return OKRT_ERR_INVALID_ARGUMENT; }
+    OKRT_CUDA(cudaSetDevice(device));
+    okrt_renderer* r = new okrt_renderer();
+    r->device = device; r->width = width; r->height = height;
+    okrt_render_data_default(&r->rd);
+    okrt_options_default(&r->opt);
+    r->rd.textureDims[0] = width; r->rd.textureDims[1] = height;
+    cudaError_t e;
+    if ((e = cudaStreamCreateWithFlags(&r->stream, cudaStreamNonBlocking)) != cudaSuccess ||
+        (e = cudaEventCreate(&r->evStart)) != cudaSuccess || (e = cudaEventCreate(&r->evStop)) != cudaSuccess ||
+        (e = cudaMalloc(&r->counters, 4 * sizeof(unsigned long long))) != cudaSuccess ||
+        (e = cudaMemsetAsync(r->counters, 0, 4 * sizeof(unsigned long long), r->stream)) != cudaSuccess) {
+        setError(std::string("okrt_create: ") + cudaGetErrorString(e));
+        okrt_destroy(r);
+        return OKRT_ERR_CUDA;
+    }
+    const int rc = allocateImages(r);
+    if (rc) { okrt_destroy(r); return rc; }
+    *out = r;
+    return OKRT_OK;
+}
+
+void okrt_destroy(okrt_renderer* r)
+{
+    if (!r) return;
+    cudaSetDevice(r->device);
+    if (r->stream) cudaStreamSynchronize(r->stream);
+    r->triPos.release(); r->triInfo.release(); r->bvhNodes.release(); r->octNodes.release(); r->spheres.release();
+    r->instances.release(); r->dirLights.release(); r->pointLights.release(); r->spotLights.release();
+    r->fastNodes.release(); r->fastTris.release(); r->fastInstances.release(); r->octParent.release();
+    r->textures.release(); r->environment.release();
+    if (r->accumulation) cudaFree(r->accumulation);
+    if (r->result) cudaFree(r->result);
+    if (r->aov) cudaFree(r->aov);
+    if (r->counters) cudaFree(r->counters);
+    if (r->evStart) cudaEventDestroy(r->evStart);
+    if (r->evStop) cudaEventDestroy(r->evStop);
+    if (r->stream) cudaStreamDestroy(r->stream);
+    delete r;
+}
+
+int okrt_resize(okrt_renderer* r, uint32_t width, uint32_t height)
+{
+    int rc = checkHandle(r, "okrt_resize"); if (rc) return rc;
+    if (!width || !height) { setError("okrt_resize: zero extent"); return OKRT_ERR_INVALID_ARGUMENT; }
+    OKRT_CUDA(cudaStreamSynchronize(r->stream));
+    r->width = width; r->height = height;
+    r->rd.textureDims[0] = width; r->rd.textureDims[1] = height;
+    r->rd.numAccumulationFrames = 0u;                        /* onResize -> resetAccumulation, RayTracer.cpp:494-501 */
+    return allocateImages(r);
+}
+
+int okrt_set_triangles(okrt_renderer* r, const okrt_triangle* pos, const okrt_triangle_info* info, uint32_t n)
+{
+    int rc = checkHandle(r, "okrt_set_triangles"); if (rc) return rc;
+    if (n && (!pos || !info)) { setError("okrt_set_triangles: null array"); return OKRT_ERR_INVALID_ARGUMENT; }
+    if ((rc = r->triPos.upload(pos, n, sizeof(okrt_triangle), r->stream))) return rc;
+    if ((rc = r->triInfo.upload(info, n, sizeof(okrt_triangle_info), r->stream))) return rc;
+    r->hTris.assign(pos, pos + n);
+    r->layoutDirty = true;
+    return OKRT_OK;
+}
+
+int okrt_set_bvh_nodes(okrt_renderer* r, const okrt_bvh_node* nodes, uint32_t n)
+{
+    int rc = checkHandle(r, "okrt_set_bvh_nodes"); if (rc) return rc;
+    if (n && !nodes) { setError("okrt_set_bvh_nodes: null array"); return OKRT_ERR_INVALID_ARGUMENT; }
+    if ((rc = r->bvhNodes.upload(nodes, n, sizeof(okrt_bvh_node), r->stream))) return rc;
+    r->hNodes.assign(nodes, nodes + n);
+    r->layoutDirty = true;
+    return OKRT_OK;
+}
+
+int okrt_set_textures(okrt_renderer* r, const uint8_t* rgba8, uint32_t size, uint32_t layers)
+{
+    int rc = checkHandle(r, "okrt_set_textures"); if (rc) return rc;
+    if (size && layers && !rgba8) { setError("okrt_set_textures: null array"); return OKRT_ERR_INVALID_ARGUMENT; }
+    return r->textures.upload(rgba8, size, size, layers, r->stream);
+}
+
+int okrt_set_environment_map(okrt_renderer* r, const uint8_t* faces6, uint32_t faceW, uint32_t faceH)
+{
+    int rc = checkHandle(r, "okrt_set_environment_map"); if (rc) return rc;
+    if (faceW && faceH && !faces6) { setError("okrt_set_environment_map: null array"); return OKRT_ERR_INVALID_ARGUMENT; }
+    return r->environment.upload(faces6, faceW, faceH, (faceW && faceH) ? 6u : 0u, r->stream);
+}
+
+int okrt_set_octree(okrt_renderer* r, const okrt_octree_node* nodes, uint32_t n)
+{
+    int rc = checkHandle(r, "okrt_set_octree"); if (rc) return rc;
+    if (n && !nodes) { setError("okrt_set_octree: null array"); return OKRT_ERR_INVALID_ARGUMENT; }
+    if ((rc = r->octNodes.upload(nodes, n, sizeof(okrt_octree_node), r->stream))) return rc;
+    r->hOct.assign(nodes, nodes + n);
+    r->layoutDirty = true;
+    return OKRT_OK;
+}
+
+int okrt_set_spheres(okrt_renderer* r, const okrt_sphere* spheres, uint32_t n)
+{
+    int rc = checkHandle(r, "okrt_set_spheres"); if (rc) return rc;
+    if (n && !spheres) { setError("okrt_set_spheres: null array"); return OKRT_ERR_INVALID_ARGUMENT; }
+    return r->spheres.upload(spheres, n, sizeof(okrt_sphere), r->stream);
+}
+
+int okrt_set_mesh_instances(okrt_renderer* r, const okrt_mesh_instance* inst, uint32_t n)
+{
+    int rc = checkHandle(r, "okrt_set_mesh_instances"); if (rc) return rc;
+    if (n && !inst) { setError("okrt_set_mesh_instances: null array"); return OKRT_ERR_INVALID_ARGUMENT; }
+    if ((rc = r->instances.upload(inst, n, sizeof(okrt_mesh_instance), r->stream))) return rc;
+    r->hInstances.assign(inst, inst + n);
+    r->layoutDirty = true;
+    return OKRT_OK;
+}
+
+int okrt_set_directional_lights(okrt_renderer* r, const okrt_directional_light* l, uint32_t n)
+{
+    int rc = checkHandle(r, "okrt_set_directional_lights"); if (rc) return rc;
+    if (n && !l) { setError("okrt_set_directional_lights: null array"); return OKRT_ERR_INVALID_ARGUMENT; }
+    return r->dirLights.upload(l, n, sizeof(okrt_directional_light), r->stream);
+}
+
+int okrt_set_point_lights(okrt_renderer* r, const okrt_point_light* l, uint32_t n)
+{
+    int rc = checkHandle(r, "okrt_set_point_lights"); if (rc) return rc;
+    if (n && !l) { setError("okrt_set_point_lights: null array"); return OKRT_ERR_INVALID_ARGUMENT; }
+    return r->pointLights.upload(l, n, sizeof(okrt_point_light), r->stream);
+}
+
+int okrt_set_spot_lights(okrt_renderer* r, const okrt_spot_light* l, uint32_t n)
+{
+    int rc = checkHandle(r, "okrt_set_spot_lights"); if (rc) return rc;
+    if (n && !l) { setError("okrt_set_spot_lights: null array"); return OKRT_ERR_INVALID_ARGUMENT; }
+    return r->spotLights.upload(l, n, sizeof(okrt_spot_light), r->stream);
+}
+
+int okrt_set_render_data(okrt_renderer* r, const okrt_render_data* rd)
+{
+    if (!r || !rd) { setError("okrt_set_render_data: null argument"); return OKRT_ERR_INVALID_ARGUMENT; }
+    r->rd = *rd;
+    r->rd.textureDims[0] = r->width; r->rd.textureDims[1] = r->height;
+    return OKRT_OK;
+}
+
+int okrt_get_render_data(const okrt_renderer* r, okrt_render_data* out)
+{
+    if (!r || !out) { setError("okrt_get_render_data: null argument"); return OKRT_ERR_INVALID_ARGUMENT; }
+    *out = r->rd;
+    return OKRT_OK;
+}
+
+int okrt_set_options(okrt_renderer* r, const okrt_options* o)
+{
+    if (!r || !o) { setError("okrt_set_options: null argument"); return OKRT_ERR_INVALID_ARGUMENT; }
+    if (o->traversal > OKRT_TRAVERSAL_EXACT || o->shardMode > OKRT_SHARD_TILE) { setError("okrt_set_options: unknown mode"); return OKRT_ERR_INVALID_ARGUMENT; }
+    if (o->shardMode == OKRT_SHARD_TILE && (o->shardCount == 0u || o->shardRank >= o->shardCount)) { setError("okrt_set_options: shardRank/shardCount"); return OKRT_ERR_INVALID_ARGUMENT; }
+    if (o->shardBandRows % kTileH) { setError("okrt_set_options: shardBandRows must be a multiple of 8"); return OKRT_ERR_INVALID_ARGUMENT; }
+    const bool coverageChanged = (r->opt.coverAllPixels != 0u) != (o->coverAllPixels != 0u);
+    r->opt = *o;
+    if (coverageChanged) {
+        const size_t n = (size_t)r->width * r->height;
+        if (cudaSetDevice(r->device) == cudaSuccess) {
+            clearResultKernel<<<(unsigned)((n + 255) / 256), 256, 0, r->stream>>>(r->result, n);
+            r->launches++;
+        }
+    }
+    if (r->opt.frameStride == 0u) r->opt.frameStride = 1u;
+    if (r->opt.shardCount == 0u) r->opt.shardCount = 1u;
+    return OKRT_OK;
+}
+
+int okrt_render_frames(okrt_renderer* r, uint32_t frames)
+{
+    int rc = checkHandle(r, "okrt_render"); if (rc) return rc;
+    if (r->layoutDirty && (rc = rebuildLayout(r))) return rc;
+    if (r->opt.writeAov && (rc = ensureAov(r))) return rc;
+    OKRT_CUDA(cudaEventRecord(r->evStart, r->stream));
+    for (uint32_t f = 0; f < frames; f++)
+        if ((rc = launchFrame(r))) return rc;
+    OKRT_CUDA(cudaEventRecord(r->evStop, r->stream));
+    return OKRT_OK;
+}
+
+int okrt_render(okrt_renderer* r) { return okrt_render_frames(r, 1u); }
+
+int okrt_sync(okrt_renderer* r)
+{
+    int rc = checkHandle(r, "okrt_sync"); if (rc) return rc;
+    OKRT_CUDA(cudaStreamSynchronize(r->stream));
+    return OKRT_OK;
+}
+
+int okrt_toggle_accumulation(okrt_renderer* r, int enable)
+{
+    int rc = checkHandle(r, "okrt_toggle_accumulation"); if (rc) return rc;
+    r->rd.accumulationEnabled = enable ? 1u : 0u;
+    return okrt_reset_accumulation(r);
+}
+
+int okrt_reset_accumulation(okrt_renderer* r)
+{
+    int rc = checkHandle(r, "okrt_reset_accumulation"); if (rc) return rc;
+    r->rd.numAccumulationFrames = 0u;
+    OKRT_CUDA(cudaMemsetAsync(r->accumulation, 0, (size_t)r->width * r->height * sizeof(float4), r->stream));
+    return OKRT_OK;
+}
+
+uint32_t okrt_get_num_accumulation_frames(const okrt_renderer* r) { return r ? r->rd.numAccumulationFrames : 0u; }
+
+int okrt_read_result(okrt_renderer* r, uint8_t* outRgba8)
+{
+    int rc = checkHandle(r, "okrt_read_result"); if (rc) return rc;
+    if (!outRgba8) { setError("okrt_read_result: null output"); return OKRT_ERR_INVALID_ARGUMENT; }
+    OKRT_CUDA(cudaMemcpyAsync(outRgba8, r->result, (size_t)r->width * r->height * 4, cudaMemcpyDeviceToHost, r->stream));
+    OKRT_CUDA(cudaStreamSynchronize(r->stream));
+    return OKRT_OK;
+}
+
+int okrt_read_accumulation(okrt_renderer* r, float* outRgba32f)
+{
+    int rc = checkHandle(r, "okrt_read_accumulation"); if (rc) return rc;
+    if (!outRgba32f) { setError("okrt_read_accumulation: null output"); return OKRT_ERR_INVALID_ARGUMENT; }
+    OKRT_CUDA(cudaMemcpyAsync(outRgba32f, r->accumulation, (size_t)r->width * r->height * 16, cudaMemcpyDeviceToHost, r->stream));
+    OKRT_CUDA(cudaStreamSynchronize(r->stream));
+    return OKRT_OK;
+}
+
+int okrt_read_aov(okrt_renderer* r, okrt_aov* out)
+{
+    int rc = checkHandle(r, "okrt_read_aov"); if (rc) return rc;
+    if (!out) { setError("okrt_read_aov: null output"); return OKRT_ERR_INVALID_ARGUMENT; }
+    if (!r->aov) { setError("okrt_read_aov: render with options.writeAov = 1 first"); return OKRT_ERR_STATE; }
+    OKRT_CUDA(cudaMemcpyAsync(out, r->aov, (size_t)r->width * r->height * sizeof(okrt_aov), cudaMemcpyDeviceToHost, r->stream));
+    OKRT_CUDA(cudaStreamSynchronize(r->stream));
+    return OKRT_OK;
+}
+
+int okrt_write_accumulation(okrt_renderer* r, const float* rgba32f, uint32_t numAccumulationFrames)
+{
+    int rc = checkHandle(r, "okrt_write_accumulation"); if (rc) return rc;
+    if (!rgba32f) { setError("okrt_write_accumulation: null input"); return OKRT_ERR_INVALID_ARGUMENT; }
+    OKRT_CUDA(cudaMemcpyAsync(r->accumulation, rgba32f, (size_t)r->width * r->height * 16, cudaMemcpyHostToDevice, r->stream));
+    OKRT_CUDA(cudaStreamSynchronize(r->stream));
+    r->rd.numAccumulationFrames = numAccumulationFrames;
+    return OKRT_OK;
+}
+
+int okrt_resolve(okrt_renderer* r, uint32_t totalFrames)
+{
+    int rc = checkHandle(r, "okrt_resolve"); if (rc) return rc;
+    const size_t n = (size_t)r->width * r->height;
+    uint32_t cw, ch;
+    coveredExtent(r, cw, ch);
+    resolveKernel<<<(unsigned)((n + 255) / 256), 256, 0, r->stream>>>(r->accumulation, r->result, n, (float)totalFrames, r->width, cw, ch);
+    r->launches++;
+    OKRT_CUDA(cudaGetLastError());
+    return OKRT_OK;
+}
+
+void* okrt_accumulation_device_ptr(okrt_renderer* r) { return r ? (void*)r->accumulation : nullptr; }
+void* okrt_result_device_ptr(okrt_renderer* r) { return r ? (void*)r->result : nullptr; }
+void* okrt_cuda_stream(okrt_renderer* r) { return r ? (void*)r->stream : nullptr; }
+
+int okrt_get_stats(okrt_renderer* r, okrt_stats* out)
+{
+    int rc = checkHandle(r, "okrt_get_stats"); if (rc) return rc;
+    if (!out) { setError("okrt_get_stats: null output"); return OKRT_ERR_INVALID_ARGUMENT; }
+    unsigned long long h[4] = {0, 0, 0, 0};
+    OKRT_CUDA(cudaMemcpyAsync(h, r->counters, sizeof(h), cudaMemcpyDeviceToHost, r->stream));
+    OKRT_CUDA(cudaStreamSynchronize(r->stream));
+    std::memset(out, 0, sizeof(*out));
+    out->raySegments = h[0]; out->fallbackSegments = h[1]; out->pixelsTraced = h[2];
+    out->kernelLaunches = r->launches;
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, r->evStart, r->evStop) == cudaSuccess) r->lastRenderMs = ms; else cudaGetLastError();
+    out->lastRenderMs = r->lastRenderMs;
+    return OKRT_OK;
+}
+
+int okrt_reset_stats(okrt_renderer* r)
+{
+    int rc = checkHandle(r, "okrt_reset_stats"); if (rc) return rc;
+    OKRT_CUDA(cudaMemsetAsync(r->counters, 0, 4 * sizeof(unsigned long long), r->stream));
+    r->launches = 0;
+    return OKRT_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,754 @@
+/*
+ * okrt_kernels.cuh — sm_100a device code of the path tracer.
+ *
+ * Replaces resources/shaders/RaytracerCS.hlsl + GPU-Utilities.hlsli.  Arithmetic contract: every
+ * float32 operation that decides a result (slab test, Moeller-Trumbore, world-distance conversion,
+ * hit resolve, BSDF sampling, accumulation) is evaluated with the reference's expression order and
+ * individually rounded (-fmad=false), so that a hit is (triangle, u, v, distance) bit-for-bit what
+ * the scalar restatement of the HLSL computes.  What is free to change — and does — is the ORDER in
+ * which boxes and triangles are visited and the hierarchy used for culling; see traverseFast().
+ */
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+
+#include "okrt.h"
+#include "okrt_accel.h"
+#include "okrt_math.cuh"
+
+namespace okrt {
+
+/* ------------------------------------------------------------------ shim */
+struct V3 { float x, y, z; };
+struct V2 { float x, y; };
+
+__device__ __forceinline__ V3 v3(float x, float y, float z) { V3 r; r.x = x; r.y = y; r.z = z; return r; }
+__device__ __forceinline__ V3 v3(const float* p) { return v3(p[0], p[1], p[2]); }
+__device__ __forceinline__ V3 operator+(V3 a, V3 b) { return v3(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ V3 operator-(V3 a, V3 b) { return v3(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ V3 operator*(V3 a, V3 b) { return v3(a.x * b.x, a.y * b.y, a.z * b.z); }
+__device__ __forceinline__ V3 operator*(V3 a, float s) { return v3(a.x * s, a.y * s, a.z * s); }
+__device__ __forceinline__ V3 operator*(float s, V3 a) { return v3(s * a.x, s * a.y, s * a.z); }
+__device__ __forceinline__ V3 operator-(V3 a) { return v3(-a.x, -a.y, -a.z); }
+__device__ __forceinline__ float dot(V3 a, V3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
+__device__ __forceinline__ V3 cross(V3 a, V3 b) { return v3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
+__device__ __forceinline__ float length(V3 a) { return sqrtf(dot(a, a)); }
+__device__ __forceinline__ V3 normalize(V3 a) { const float inv = 1.0f / sqrtf(dot(a, a)); return a * inv; }
+__device__ __forceinline__ float lerp1(float a, float b, float s) { return a + s * (b - a); }
+__device__ __forceinline__ V3 lerp3(V3 a, V3 b, float s) { return v3(lerp1(a.x, b.x, s), lerp1(a.y, b.y, s), lerp1(a.z, b.z, s)); }
+__device__ __forceinline__ V3 reflect(V3 i, V3 n) { const float d2 = 2.0f * dot(i, n); return i - n * d2; }
+__device__ __forceinline__ float saturate(float x) { return fminf(fmaxf(x, 0.0f), 1.0f); }
+
+#define OKRT_FLT_MAX 3.402823466e+38F
+#define OKRT_PI 3.14159265f
+
+/* [Q1] the 16 floats are row-major M; mul(float4(v,w), M_hlsl) == M * v */
+__device__ __forceinline__ V3 mulPoint(V3 v, const float* m)
+{
+    return v3(((v.x * m[0] + v.y * m[1]) + v.z * m[2]) + m[3],
+              ((v.x * m[4] + v.y * m[5]) + v.z * m[6]) + m[7],
+              ((v.x * m[8] + v.y * m[9]) + v.z * m[10]) + m[11]);
+}
+__device__ __forceinline__ V3 mulDir(V3 v, const float* m)
+{
+    return v3((v.x * m[0] + v.y * m[1]) + v.z * m[2],
+              (v.x * m[4] + v.y * m[5]) + v.z * m[6],
+              (v.x * m[8] + v.y * m[9]) + v.z * m[10]);
+}
+__device__ __forceinline__ V3 mulPointRows(V3 v, float4 r0, float4 r1, float4 r2)
+{
+    return v3(((v.x * r0.x + v.y * r0.y) + v.z * r0.z) + r0.w,
+              ((v.x * r1.x + v.y * r1.y) + v.z * r1.z) + r1.w,
+              ((v.x * r2.x + v.y * r2.y) + v.z * r2.z) + r2.w);
+}
+__device__ __forceinline__ V3 mulDirRows(V3 v, float4 r0, float4 r1, float4 r2)
+{
+    return v3((v.x * r0.x + v.y * r0.y) + v.z * r0.z,
+              (v.x * r1.x + v.y * r1.y) + v.z * r1.z,
+              (v.x * r2.x + v.y * r2.y) + v.z * r2.z);
+}
+
+/* ------------------------------------------------------------ scene view */
+struct DeviceScene {
+    /* reference-format buffers (binding table t0..t10) */
+    const float* triPos;                      /* t0: 9 floats per triangle */
+    const float* triInfo;                     /* t1: 33 floats per triangle */
+    const okrt_bvh_node* bvhNodes;            /* t2 */
+    cudaTextureObject_t textures;             /* t3: layered 2D, uchar4, point fetch */
+    cudaTextureObject_t environment;          /* t4: 6-layer 2D, uchar4, point fetch */
+    const okrt_octree_node* octNodes;         /* t5 */
+    const okrt_sphere* spheres;               /* t6 */
+    const okrt_mesh_instance* instances;      /* t7 */
+    const okrt_directional_light* dirLights;  /* t8 */
+    const okrt_point_light* pointLights;      /* t9 */
+    const okrt_spot_light* spotLights;        /* t10 */
+    uint32_t numTris, numBvhNodes, numOctNodes, numSpheres, numInstances, numDirLights, numPointLights, numSpotLights;
+    uint32_t texSize, texLayers, envW, envH;
+    /* fast layout */
+    const float4* fastNodes;
+    const float4* fastTris;
+    const float4* fastInstances;
+    const uint32_t* octParent;
+    uint32_t topRef;
+    uint32_t pad0;
+};
+
+struct FrameParams {
+    okrt_render_data rd;                      /* b0 */
+    uint32_t maxBounces;
+    uint32_t seedFrame;                       /* numAccumulationFrames as used by the seed [Q3] */
+    uint32_t traversal;
+    uint32_t coveredW, coveredH;              /* [Q9] */
+    uint32_t bandRows, shardRank, shardCount; /* tile sharding: row band b belongs to rank b % shardCount */
+    float4* accumulation;                     /* u1 */
+    uchar4* result;                           /* u0 */
+    okrt_aov* aov;                            /* optional */
+    unsigned long long* counters;             /* [0] segments, [1] fallback segments, [2] pixels */
+};
+
+/* ------------------------------------------------------------------- RNG */
+__device__ __forceinline__ uint32_t pcgHash(uint32_t& seed)           /* GPU-Utilities.hlsli:18-25 [F7] */
+{
+    seed *= 747796405u + 2891336453u;
+    seed = ((seed >> ((seed >> 28u) + 4u)) ^ seed) * 277803737u;
+    seed = (seed >> 22u) ^ seed;
+    return seed;
+}
+__device__ __forceinline__ float randomFloat(uint32_t& seed)          /* :51-54; (float)UINT_MAX == 2^32 */
+{
+    return __uint2float_rn(pcgHash(seed)) / 4294967296.0f;
+}
+__device__ __forceinline__ float randomNormal(uint32_t& seed)         /* :56-62 */
+{
+    const float theta = (2 * OKRT_PI) * randomFloat(seed);
+    const float rho = sqrtf(-2 * okm::log_(randomFloat(seed)));
+    return rho * okm::cos_(theta);
+}
+__device__ __forceinline__ V3 getRandomVector(uint32_t& seed)         /* :64-70 */
+{
+    const float x = randomNormal(seed);
+    const float y = randomNormal(seed);
+    const float z = randomNormal(seed);
+    return normalize(v3(x, y, z));
+}
+__device__ __forceinline__ V2 randomPointInCircle(uint32_t& seed)     /* :72-78 */
+{
+    const float angle = randomFloat(seed) * 2.f * OKRT_PI;
+    const float c = okm::cos_(angle), s = okm::sin_(angle);
+    const float r = sqrtf(randomFloat(seed));
+    V2 o; o.x = c * r; o.y = s * r;
+    return o;
+}
+__device__ __forceinline__ float clampedDot(V3 v, V3 u) { return fmaxf(dot(v, u), 0.f); }
+
+__device__ __forceinline__ V3 refractCustom(V3 direction, V3 normal, float refractionRatio)   /* :85-93 */
+{
+    const float cosTheta = fminf(dot(-direction, normal), 1.f);
+    const V3 perp = refractionRatio * (direction + cosTheta * normal);
+    const float lenSq = dot(perp, perp);
+    const V3 parallel = -sqrtf(fabsf(1.f - lenSq)) * normal;
+    return perp + parallel;
+}
+
+/* ----------------------------------------------------------- intersection */
+__device__ __forceinline__ float rayAndSphere(V3 o, V3 d, V3 c, float radius)   /* :98-114 [Q15] */
+{
+    const V3 rayToSphere = c - o;
+    const float distToClosestPoint = dot(rayToSphere, d);
+    const float magSq = dot(rayToSphere, rayToSphere);
+    const float rSq = radius * radius;
+    if (distToClosestPoint < 0.f && magSq > rSq) return -1.f;
+    const float sideA = magSq - distToClosestPoint * distToClosestPoint;
+    if (sideA > rSq) return -1.f;
+    const float sideB = sqrtf(rSq - sideA);
+    return magSq > rSq ? distToClosestPoint - sideB : distToClosestPoint + sideB;
+}
+
+/* :117-155 [Q6] */
+__device__ __forceinline__ float rayAndTriangle(V3 o, V3 d, V3 p0, V3 p1, V3 p2, float& u, float& v)
+{
+    const float EPSILON = 0.000001f;
+    const V3 E1 = p0 - p2, E2 = p1 - p2;
+    const V3 cross1 = cross(d, E2);
+    const float determinant = dot(E1, cross1);
+    if (determinant < EPSILON && determinant > -EPSILON) return -1.f;
+    const float inverseDet = 1.f / determinant;
+    const V3 rayMoved = o - p2;
+    u = dot(rayMoved, cross1) * inverseDet;
+    if (u < -EPSILON) return -1.f;
+    const V3 cross2 = cross(rayMoved, E1);
+    v = dot(d, cross2) * inverseDet;
+    if (v < -EPSILON || u + v > 1.0f) return -1.f;
+    const float t1 = dot(E2, cross2) * inverseDet;
+    if (t1 < -EPSILON) return -1.f;
+    return t1;
+}
+
+/* :183-197 with 1/direction hoisted (same value the shader recomputes per box) */
+__device__ __forceinline__ float rayAndAABBDist(V3 o, V3 idir, V3 bmin, V3 bmax)
+{
+    const V3 tMin = (bmin - o) * idir;
+    const V3 tMax = (bmax - o) * idir;
+    const float distFar = fminf(fminf(fmaxf(tMin.x, tMax.x), fmaxf(tMin.y, tMax.y)), fmaxf(tMin.z, tMax.z));
+    const float distNear = fmaxf(fmaxf(fminf(tMin.x, tMax.x), fminf(tMin.y, tMax.y)), fminf(tMin.z, tMax.z));
+    const bool didHit = distFar >= distNear && distFar > 0.f;
+    return didHit ? distNear : OKRT_FLT_MAX;
+}
+__device__ __forceinline__ V3 rcp3(V3 d) { return v3(1.f / d.x, 1.f / d.y, 1.f / d.z); }
+
+/* --------------------------------------------------------------- textures */
+__device__ __forceinline__ V3 texelRgb(uchar4 t) { return v3((float)t.x / 255.0f, (float)t.y / 255.0f, (float)t.z / 255.0f); }
+__device__ __forceinline__ bool finitef_(float x) { return x - x == 0.0f; }
+__device__ __forceinline__ V3 bilerp(V3 c00, V3 c10, V3 c01, V3 c11, float fx, float fy)
+{
+    const float wx0 = 1.0f - fx, wy0 = 1.0f - fy;
+    const V3 top = c00 * wx0 + c10 * fx;
+    const V3 bot = c01 * wx0 + c11 * fx;
+    return top * wy0 + bot * fy;
+}
+
+/* RaytracerCS.hlsl:133-136 [Q12]: bilinear, WRAP, lod 0.  Four point fetches through the texture
+ * unit (uchar4, no hardware filtering) and a float32 lerp: D3D's 8-bit fixed-point filter weights
+ * are not reproducible on a CPU, the float lerp is. */
+__device__ __forceinline__ V3 sampleTexture(const DeviceScene& s, uint32_t textureIdx, V2 uv)
+{
+    if (s.texLayers == 0u) return v3(0.f, 0.f, 0.f);
+    const int layer = (int)(textureIdx < s.texLayers ? textureIdx : s.texLayers - 1u);
+    const int N = (int)s.texSize;
+    const float u = finitef_(uv.x) ? uv.x : 0.0f, v = finitef_(uv.y) ? uv.y : 0.0f;
+    float x = u * (float)N - 0.5f, y = v * (float)N - 0.5f;
+    if (!(fabsf(x) < 1.0e9f)) x = 0.0f;
+    if (!(fabsf(y) < 1.0e9f)) y = 0.0f;
+    const float xf = floorf(x), yf = floorf(y);
+    const float fx = x - xf, fy = y - yf;
+    int x0 = (int)xf % N; if (x0 < 0) x0 += N;
+    int y0 = (int)yf % N; if (y0 < 0) y0 += N;
+    const int x1 = x0 + 1 == N ? 0 : x0 + 1;
+    const int y1 = y0 + 1 == N ? 0 : y0 + 1;
+    const uchar4 t00 = tex2DLayered<uchar4>(s.textures, (float)x0 + 0.5f, (float)y0 + 0.5f, layer);
+    const uchar4 t10 = tex2DLayered<uchar4>(s.textures, (float)x1 + 0.5f, (float)y0 + 0.5f, layer);
+    const uchar4 t01 = tex2DLayered<uchar4>(s.textures, (float)x0 + 0.5f, (float)y1 + 0.5f, layer);
+    const uchar4 t11 = tex2DLayered<uchar4>(s.textures, (float)x1 + 0.5f, (float)y1 + 0.5f, layer);
+    return bilerp(texelRgb(t00), texelRgb(t10), texelRgb(t01), texelRgb(t11), fx, fy);
+}
+
+/* RaytracerCS.hlsl:86-88 [Q13] */
+__device__ __forceinline__ V3 environmentLight(const DeviceScene& s, V3 d)
+{
+    if (s.envW == 0u || s.envH == 0u) return v3(0.f, 0.f, 0.f);
+    const float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
+    int face; float sc, tc, ma;
+    if (ax >= ay && ax >= az) { ma = ax; if (d.x >= 0) { face = 0; sc = -d.z; tc = -d.y; } else { face = 1; sc = d.z; tc = -d.y; } }
+    else if (ay >= az)        { ma = ay; if (d.y >= 0) { face = 2; sc = d.x; tc = d.z; } else { face = 3; sc = d.x; tc = -d.z; } }
+    else                      { ma = az; if (d.z >= 0) { face = 4; sc = d.x; tc = -d.y; } else { face = 5; sc = -d.x; tc = -d.y; } }
+    if (!(ma > 0.0f) || !finitef_(ma) || !finitef_(sc) || !finitef_(tc)) return v3(0.f, 0.f, 0.f);
+    const float u = (sc / ma + 1.0f) * 0.5f, v = (tc / ma + 1.0f) * 0.5f;
+    const int W = (int)s.envW, H = (int)s.envH;
+    const float x = u * (float)W - 0.5f, y = v * (float)H - 0.5f;
+    const float xf = floorf(x), yf = floorf(y);
+    const float fx = x - xf, fy = y - yf;
+    int x0 = (int)xf, y0 = (int)yf, x1 = x0 + 1, y1 = y0 + 1;
+    x0 = min(max(x0, 0), W - 1); x1 = min(max(x1, 0), W - 1);
+    y0 = min(max(y0, 0), H - 1); y1 = min(max(y1, 0), H - 1);
+    const uchar4 t00 = tex2DLayered<uchar4>(s.environment, (float)x0 + 0.5f, (float)y0 + 0.5f, face);
+    const uchar4 t10 = tex2DLayered<uchar4>(s.environment, (float)x1 + 0.5f, (float)y0 + 0.5f, face);
+    const uchar4 t01 = tex2DLayered<uchar4>(s.environment, (float)x0 + 0.5f, (float)y1 + 0.5f, face);
+    const uchar4 t11 = tex2DLayered<uchar4>(s.environment, (float)x1 + 0.5f, (float)y1 + 0.5f, face);
+    return bilerp(texelRgb(t00), texelRgb(t10), texelRgb(t01), texelRgb(t11), fx, fy);
+}
+
+/* ------------------------------------------------------------ hit record */
+struct Hit {
+    float distance;        /* payload.distance */
+    uint32_t kind;         /* 0 miss, 1 sphere, 2 mesh */
+    uint32_t idx;          /* sphere or instance index (reference order) */
+    uint32_t tri;
+    float u, v;
+};
+
+struct Surface {           /* what shading needs from Payload (RaytracerCS.hlsl:10-17) */
+    okrt_material material;
+    V3 worldPosition;
+    V3 worldNormal;
+};
+
+/* ------------------------------------------- reference-order traversal
+ * RaytracerCS.hlsl:228-334 [Q4,Q5], visit order and counters exactly as the shader. */
+__device__ __noinline__ void traverseExact(const DeviceScene& s, uint32_t numSpheres, V3 o, V3 d, Hit& hit,
+                                           uint32_t& bbCheckCount, uint32_t& triCheckCount)
+{
+    hit.distance = OKRT_FLT_MAX; hit.kind = 0u; hit.idx = 0xFFFFFFFFu; hit.tri = 0xFFFFFFFFu; hit.u = 0.f; hit.v = 0.f;
+
+    for (uint32_t i = 0; i < numSpheres; i++) {
+        const okrt_sphere& sp = s.spheres[i];
+        const float t = rayAndSphere(o, d, v3(sp.position), sp.radius);
+        if (t > 0.f && t < hit.distance) { hit.distance = t; hit.idx = i; hit.kind = 1u; }
+    }
+
+    uint32_t octStack[kExactOctStackCapacity];
+    uint32_t bvhStack[kExactBvhStackCapacity];
+    uint32_t octStackSize = s.numOctNodes ? 1u : 0u;
+    octStack[0] = 0u;
+    const V3 idirWorld = rcp3(d);
+
+    while (octStackSize > 0u) {
+        const uint32_t octIdx = octStack[--octStackSize];
+        const okrt_octree_node& on = s.octNodes[octIdx];
+        bbCheckCount += 1u;
+        if (rayAndAABBDist(o, idirWorld, v3(on.boundingBox.min), v3(on.boundingBox.max)) >= hit.distance)
+            continue;
+
+        const uint32_t mStart = on.meshesStartIdx, mEnd = on.meshesEndIdx;
+        for (uint32_t i = mStart; i < mEnd; i++) {
+            bbCheckCount += 1u;
+            const okrt_mesh_instance& inst = s.instances[i];
+            uint32_t bvhStackSize = 1u;
+            bvhStack[0] = inst.bvhNodeStartIdx;
+            const V3 lo = mulPoint(o, inst.inverseTransformMatrix);
+            const V3 ld = normalize(mulDir(d, inst.inverseTransformMatrix));
+            const V3 lidir = rcp3(ld);
+
+            while (bvhStackSize > 0u) {
+                const uint32_t nodeIdx = bvhStack[--bvhStackSize];
+                const okrt_bvh_node& bn = s.bvhNodes[nodeIdx];
+                bbCheckCount += 1u;
+                if (rayAndAABBDist(lo, lidir, v3(bn.boundingBox.min), v3(bn.boundingBox.max)) >= hit.distance)
+                    continue;
+                const uint32_t first = bn.firstChildIdx;
+                if (first != 0xFFFFFFFFu) {
+                    bvhStack[bvhStackSize++] = first;
+                    bvhStack[bvhStackSize++] = first + 1u;
+                    continue;
+                }
+                const uint32_t tEnd = bn.triEnd;
+                for (uint32_t j = bn.triStart; j < tEnd; j++) {
+                    const float* tp = s.triPos + (size_t)j * 9;
+                    float bu = 0.f, bv = 0.f;
+                    triCheckCount += 1u;
+                    float t = rayAndTriangle(lo, ld, v3(tp), v3(tp + 3), v3(tp + 6), bu, bv);
+                    if (t <= 0.f) continue;
+                    t = length(mulDir(ld * t, inst.transformMatrix));     /* RaytracerCS.hlsl:312-314 */
+                    if (t < hit.distance) { hit.distance = t; hit.idx = i; hit.kind = 2u; hit.tri = j; hit.u = bu; hit.v = bv; }
+                }
+            }
+        }
+        for (uint32_t c = 0; c < on.numChildren; c++)
+            octStack[octStackSize++] = on.firstChildIdx + c;
+    }
+}
+
+/* ------------------------------------------------ near-first traversal
+ * Same boxes, same triangles, same arithmetic — different visiting order and a different culling
+ * hierarchy at the top.  Correctness argument (DESIGN.md "Order independence"): with relaxed culling
+ * (a box is skipped only if distNear >= best*(1+delta)) every triangle whose distance is within
+ * delta of the final minimum is tested; if exactly one candidate lies in that window the reference's
+ * order-dependent culls cannot change the winner, so the result equals the reference's bit for bit.
+ * Otherwise (ties, coplanar duplicates, hits on a shared edge) `ambiguous` is set and the caller
+ * re-traces the ray with traverseExact. */
+#define OKRT_DELTA 1.0e-4f
+/* a missed box reports FLT_MAX and must never pass, also while nothing has been hit yet */
+__device__ __forceinline__ float relaxedLimit(float best) { return fminf(best * (1.0f + OKRT_DELTA), OKRT_FLT_MAX); }
+
+struct FastCtx {
+    float best, second;     /* closest and second-closest candidate distance */
+};
+
+__device__ __forceinline__ void fastCandidate(FastCtx& c, Hit& hit, float t, uint32_t kind, uint32_t idx, uint32_t tri, float u, float v)
+{
+    if (t < c.best) {
+        c.second = c.best; c.best = t;
+        hit.distance = t; hit.kind = kind; hit.idx = idx; hit.tri = tri; hit.u = u; hit.v = v;
+    } else if (t < c.second) c.second = t;
+}
+
+__device__ __forceinline__ bool traverseFast(const DeviceScene& s, uint32_t numSpheres, V3 o, V3 d, Hit& hit)
+{
+    hit.distance = OKRT_FLT_MAX; hit.kind = 0u; hit.idx = 0xFFFFFFFFu; hit.tri = 0xFFFFFFFFu; hit.u = 0.f; hit.v = 0.f;
+    FastCtx c; c.best = OKRT_FLT_MAX; c.second = OKRT_FLT_MAX;
+
+    for (uint32_t i = 0; i < numSpheres; i++) {
+        const okrt_sphere& sp = s.spheres[i];
+        const float t = rayAndSphere(o, d, v3(sp.position), sp.radius);
+        if (t > 0.f) fastCandidate(c, hit, t, 1u, i, 0xFFFFFFFFu, 0.f, 0.f);
+    }
+
+    if (s.topRef != kRefNone) {
+        const uint32_t EXIT_INSTANCE = 0xFFFFFFFEu;
+        uint32_t stack[kFastStackCapacity];
+        int sp = 0;
+        const V3 idirWorld = rcp3(d);
+        /* normalize(d * I) is what every identity-transform instance sees as its local direction */
+        const V3 dn = normalize(mulDirRows(d, make_float4(1, 0, 0, 0), make_float4(0, 1, 0, 0), make_float4(0, 0, 1, 0)));
+        const V3 idirN = rcp3(dn);
+        const V3 oI = mulPointRows(o, make_float4(1, 0, 0, 0), make_float4(0, 1, 0, 0), make_float4(0, 0, 1, 0));
+
+        V3 ro = o, rd = d, ridir = idirWorld;    /* current ray: world at the top level, local inside an instance */
+        float4 t0 = make_float4(1, 0, 0, 0), t1 = make_float4(0, 1, 0, 0), t2 = make_float4(0, 0, 1, 0);
+        uint32_t instIdx = 0xFFFFFFFFu;
+        uint32_t cur = s.topRef;                 /* always an interior reference here */
+
+        for (;;) {
+            const uint32_t tag = cur & kRefTagMask;
+            if (tag == kRefInterior) {
+                const float4* q = s.fastNodes + (size_t)cur * 4;
+                const float4 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3);
+                const float limit = relaxedLimit(c.best);
+                const float n0 = rayAndAABBDist(ro, ridir, v3(q0.x, q0.y, q0.z), v3(q1.x, q1.y, q1.z));
+                const float n1 = rayAndAABBDist(ro, ridir, v3(q2.x, q2.y, q2.z), v3(q3.x, q3.y, q3.z));
+                const uint32_t r0 = __float_as_uint(q0.w), r1 = __float_as_uint(q1.w);
+                const bool h0 = n0 < limit && r0 != kRefNone;
+                const bool h1 = n1 < limit && r1 != kRefNone;
+                if (h0 && h1) {
+                    const bool firstIs1 = n1 < n0;
+                    stack[sp++] = firstIs1 ? r0 : r1;
+                    cur = firstIs1 ? r1 : r0;
+                    continue;
+                }
+                if (h0) { cur = r0; continue; }
+                if (h1) { cur = r1; continue; }
+            } else if (tag == kRefTriLeaf) {
+                const uint32_t first = cur & (kMaxTriIndex - 1u);
+                const uint32_t count = ((cur >> 27) & 7u) + 1u;
+                for (uint32_t j = first; j < first + count; j++) {
+                    const float4* tp = s.fastTris + (size_t)j * 3;
+                    const float4 a = __ldg(tp), b = __ldg(tp + 1), cc = __ldg(tp + 2);
+                    float bu = 0.f, bv = 0.f;
+                    float t = rayAndTriangle(ro, rd, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(cc.x, cc.y, cc.z), bu, bv);
+                    if (t <= 0.f) continue;
+                    t = length(mulDirRows(rd * t, t0, t1, t2));
+                    fastCandidate(c, hit, t, 2u, instIdx, j, bu, bv);
+                }
+            } else if (cur == EXIT_INSTANCE) {
+                ro = o; rd = d; ridir = idirWorld; instIdx = 0xFFFFFFFFu;
+            } else {                                         /* instance leaf */
+                const float4* rec = s.fastInstances + (size_t)(cur & ~kRefTagMask) * 8;
+                const float4 r6 = __ldg(rec + 6), r7 = __ldg(rec + 7);
+                const float limit = relaxedLimit(c.best);
+                /* every oct-tree box the reference tests on its way to this instance (RaytracerCS.hlsl:262) */
+                bool enter = true;
+                for (uint32_t on = __float_as_uint(r7.y); on != 0xFFFFFFFFu; on = __ldg(s.octParent + on)) {
+                    const okrt_octree_node& node = s.octNodes[on];
+                    if (!(rayAndAABBDist(o, idirWorld, v3(node.boundingBox.min), v3(node.boundingBox.max)) < limit)) { enter = false; break; }
+                }
+                if (enter) {
+                    const float4 i0 = __ldg(rec), i1 = __ldg(rec + 1), i2 = __ldg(rec + 2);
+                    const float4 a0 = __ldg(rec + 3), a1 = __ldg(rec + 4), a2 = __ldg(rec + 5);
+                    V3 lo, ld, lidir;
+                    if (__float_as_uint(r6.w) & 1u) { lo = oI; ld = dn; lidir = idirN; }
+                    else {
+                        lo = mulPointRows(o, i0, i1, i2);
+                        ld = normalize(mulDirRows(d, i0, i1, i2));
+                        lidir = rcp3(ld);
+                    }
+                    /* the mesh's root box (RaytracerCS.hlsl:285 on the first popped node) */
+                    if (rayAndAABBDist(lo, lidir, v3(a0.w, a1.w, a2.w), v3(r6.x, r6.y, r6.z)) < limit) {
+                        stack[sp++] = EXIT_INSTANCE;
+                        ro = lo; rd = ld; ridir = lidir; t0 = a0; t1 = a1; t2 = a2;
+                        instIdx = __float_as_uint(r7.z);
+                        cur = __float_as_uint(r7.x);
+                        continue;
+                    }
+                }
+            }
+            if (sp == 0) break;
+            cur = stack[--sp];
+        }
+    }
+    return c.second < relaxedLimit(c.best);    /* ambiguous? */
+}
+
+/* ------------------------------------------------------------ hit resolve
+ * RaytracerCS.hlsl:336-392 [Q8] */
+__device__ __forceinline__ void findMaterialTextureColours(const DeviceScene& s, okrt_material& m, V2 uv)   /* :138-165 */
+{
+    if (m.albedoTextureIdx != 0xFFFFFFFFu) {
+        const V3 t = sampleTexture(s, m.albedoTextureIdx, uv);
+        m.albedo[0] = t.x; m.albedo[1] = t.y; m.albedo[2] = t.z;
+    }
+    if (m.roughnessTextureIdx != 0xFFFFFFFFu)
+        m.roughness = fminf(fmaxf(sampleTexture(s, m.roughnessTextureIdx, uv).x, m.roughness), 1.f);
+    if (m.metallicTextureIdx != 0xFFFFFFFFu)
+        m.metallic = fminf(fmaxf(sampleTexture(s, m.metallicTextureIdx, uv).x, m.metallic), 1.f);
+    if (m.specularTextureIdx != 0xFFFFFFFFu)
+        m.specular = fminf(fmaxf(sampleTexture(s, m.specularTextureIdx, uv).x, m.specular), 1.f);
+}
+
+__device__ __forceinline__ V3 sampleNormalMap(const DeviceScene& s, uint32_t textureIdx, V2 uv, V3 normal, V3 tangent, V3 bitangent)   /* :167-175 */
+{
+    V3 sn = sampleTexture(s, textureIdx, uv);
+    sn = sn * 2.f - v3(1.f, 1.f, 1.f);
+    const V3 r = v3((sn.x * tangent.x + sn.y * bitangent.x) + sn.z * normal.x,
+                    (sn.x * tangent.y + sn.y * bitangent.y) + sn.z * normal.y,
+                    (sn.x * tangent.z + sn.y * bitangent.z) + sn.z * normal.z);
+    return normalize(r);
+}
+
+__device__ __forceinline__ void loadMaterial(okrt_material& m, const okrt_material* src)
+{
+    const uint32_t* p = reinterpret_cast<const uint32_t*>(src);
+    uint32_t* q = reinterpret_cast<uint32_t*>(&m);
+#pragma unroll
+    for (int k = 0; k < 17; k++) q[k] = __ldg(p + k);
+}
+
+__device__ __forceinline__ void resolveHit(const DeviceScene& s, V3 o, V3 d, const Hit& hit, Surface& sf)
+{
+    sf.worldPosition = o + d * hit.distance;
+    if (hit.kind == 1u) {                                     /* sphere, :342-362 */
+        const okrt_sphere& sp = s.spheres[hit.idx];
+        loadMaterial(sf.material, &sp.material);
+        const V3 hitNormal = normalize(sf.worldPosition - v3(sp.position));
+        V2 uv;                                                /* normalToUV :77-84 */
+        uv.x = okm::atan2_(hitNormal.x, hitNormal.z) / (2 * OKRT_PI) + 0.5f;
+        uv.y = hitNormal.y * 0.5f + 0.5f;
+        if (sf.material.normalMapIdx != 0xFFFFFFFFu) {
+            const V3 tangent = normalize(cross(v3(0.f, 1.f, 0.f), hitNormal));
+            const V3 bitangent = normalize(cross(tangent, hitNormal));
+            sf.worldNormal = sampleNormalMap(s, sf.material.normalMapIdx, uv, hitNormal, tangent, bitangent);
+        } else sf.worldNormal = hitNormal;
+        findMaterialTextureColours(s, sf.material, uv);
+    } else {                                                  /* mesh, :364-391 */
+        const okrt_mesh_instance& inst = s.instances[hit.idx];
+        loadMaterial(sf.material, &inst.material);
+        const float* ti = s.triInfo + (size_t)hit.tri * 33;   /* VertexInfo: normal 0-2, uv 3-4, tangent 5-7, bitangent 8-10 */
+        const float bu = hit.u, bv = hit.v, bw = 1.f - (hit.u + hit.v);
+        V2 uv;
+        uv.x = (__ldg(ti + 3) * bu + __ldg(ti + 14) * bv) + __ldg(ti + 25) * bw;
+        uv.y = (__ldg(ti + 4) * bu + __ldg(ti + 15) * bv) + __ldg(ti + 26) * bw;
+        const V3 n0 = v3(__ldg(ti + 0), __ldg(ti + 1), __ldg(ti + 2)), n1 = v3(__ldg(ti + 11), __ldg(ti + 12), __ldg(ti + 13)), n2 = v3(__ldg(ti + 22), __ldg(ti + 23), __ldg(ti + 24));
+        V3 normal = normalize(mulDir((n0 * bu + n1 * bv) + n2 * bw, inst.transformMatrix));
+        if (sf.material.normalMapIdx != 0xFFFFFFFFu) {
+            const V3 g0 = v3(__ldg(ti + 5), __ldg(ti + 6), __ldg(ti + 7)), g1 = v3(__ldg(ti + 16), __ldg(ti + 17), __ldg(ti + 18)), g2 = v3(__ldg(ti + 27), __ldg(ti + 28), __ldg(ti + 29));
+            const V3 b0 = v3(__ldg(ti + 8), __ldg(ti + 9), __ldg(ti + 10)), b1 = v3(__ldg(ti + 19), __ldg(ti + 20), __ldg(ti + 21)), b2 = v3(__ldg(ti + 30), __ldg(ti + 31), __ldg(ti + 32));
+            const V3 tangent = normalize(mulDir((g0 * bu + g1 * bv) + g2 * bw, inst.transformMatrix));
+            const V3 bitangent = normalize(mulDir((b0 * bu + b1 * bv) + b2 * bw, inst.transformMatrix));
+            sf.worldNormal = sampleNormalMap(s, sf.material.normalMapIdx, uv, normal, tangent, bitangent);
+        } else sf.worldNormal = normal;
+        findMaterialTextureColours(s, sf.material, uv);
+    }
+}
+
+/* ------------------------------------------------------------- shading */
+__device__ __forceinline__ float reflectance(float cosine, float reflectionIdx)     /* :100-105 [Q7] */
+{
+    float r0 = (1.f - reflectionIdx) / (1.f + reflectionIdx);
+    r0 *= r0;
+    return r0 + (1.f + r0) * okm::pow_(1.f - cosine, 5.f);
+}
+
+__device__ __forceinline__ V3 findReflectDirection(V3 direction, V3 normal, float roughness, uint32_t& seed)   /* :107-112 */
+{
+    const V3 diffuse = normalize(normal + getRandomVector(seed));
+    const V3 specular = reflect(direction, normal);
+    return normalize(lerp3(specular, diffuse, roughness));
+}
+
+__device__ __forceinline__ V3 findTransparencyBounce(V3 direction, V3 normal, float refractionIdx, uint32_t& seed)   /* :114-131 [Q7] */
+{
+    const bool hitFrontFace = dot(direction, normal) < 0.f;
+    const float refractionRatio = hitFrontFace ? 1.f / refractionIdx : refractionIdx;
+    if (!hitFrontFace) normal = normal * -1.f;
+    const float cos_theta = dot(-direction, normal);
+    const float sin_theta = sqrtf(1.f - cos_theta * cos_theta);
+    const bool cannot_refract = refractionRatio * sin_theta > 1.f;
+    const float refl = reflectance(cos_theta, refractionRatio);
+    const float rnd = randomFloat(seed);                      /* always consumed: no short-circuit in HLSL */
+    if (cannot_refract || refl > rnd) direction = reflect(direction, normal);
+    return refractCustom(direction, normal, refractionRatio);
+}
+
+/* :397-418 [Q11] */
+__device__ __forceinline__ V3 getLighting(V3 o, V3 d, bool hitAny, float hitDistance, float transparency, V3 worldNormal,
+                                          V3 lightPos, float lightRadius, V3 lightColour, float lightIntensity)
+{
+    const float dist = rayAndSphere(o, d, lightPos, lightRadius);
+    if (dist < 0.f) return v3(0.f, 0.f, 0.f);
+    float modifier = 1.f;
+    if (hitAny && hitDistance > dist) modifier *= clampedDot(d, -worldNormal);
+    else if (hitAny && hitDistance < dist) modifier *= transparency * clampedDot(d, -worldNormal);
+    return (lightColour * lightIntensity) * modifier;
+}
+
+__device__ __forceinline__ uchar4 toUnorm8(float r, float g, float b, float a)
+{
+    return make_uchar4((unsigned char)(saturate(r) * 255.0f + 0.5f), (unsigned char)(saturate(g) * 255.0f + 0.5f),
+                       (unsigned char)(saturate(b) * 255.0f + 0.5f), (unsigned char)(saturate(a) * 255.0f + 0.5f));
+}
+
+/* --------------------------------------------------------------- kernel
+ * RaytracerCS::main (RaytracerCS.hlsl:421-537): one thread per pixel, 16x8 pixel tiles. */
+constexpr int kTileW = 16, kTileH = 8;
+
+__global__ void __launch_bounds__(kTileW * kTileH)
+pathTraceKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ FrameParams fp)
+{
+    const okrt_render_data& rd = fp.rd;
+    const uint32_t px = blockIdx.x * kTileW + (threadIdx.x % kTileW);
+    uint32_t py = blockIdx.y * kTileH + (threadIdx.x / kTileW);
+    if (fp.shardCount > 1u) {
+        /* blockIdx.y enumerates this rank's bands: local band b -> global band b*shardCount + rank */
+        const uint32_t rowInRank = py;
+        const uint32_t band = rowInRank / fp.bandRows;
+        py = (band * fp.shardCount + fp.shardRank) * fp.bandRows + rowInRank % fp.bandRows;
+    }
+    const bool active = px < fp.coveredW && py < fp.coveredH;
+
+    uint32_t segments = 0u, fallbacks = 0u;
+    if (active) {
+        /* [Q3] */
+        uint32_t seed = px + (py + 74813u) * rd.textureDims[0] * (fp.seedFrame + 1u);
+
+        /* createRay :177-206 [Q2] */
+        V3 pos = v3((float)px, (float)(rd.textureDims[1] - py), rd.cameraNearZ);
+        pos.x += randomFloat(seed) - 0.5f;
+        pos.y += randomFloat(seed) - 0.5f;
+        pos.x /= (float)rd.textureDims[0]; pos.y /= (float)rd.textureDims[1];
+        pos.x *= 2.f; pos.y *= 2.f;
+        pos.x -= 1.f; pos.y -= 1.f;
+        const float* ip = rd.cameraInverseProjectionMatrix;
+        const V3 target = mulPoint(pos, ip);
+        V3 o = v3(rd.cameraPosition);
+        V3 d = mulDir(normalize(v3(target.x / target.z, target.y / target.z, target.z / target.z)), rd.cameraInverseViewMatrix);
+
+        /* applyDOF :208-216 */
+        {
+            const V2 j = randomPointInCircle(seed);
+            const float jx = j.x * rd.dofStrength, jy = j.y * rd.dofStrength;
+            const V3 rayOffset = v3(rd.cameraRightDir) * jx + v3(rd.cameraUpDir) * jy;
+            const V3 focusPoint = o + d * (rd.dofDistance + rd.cameraNearZ);
+            o = o + rayOffset;
+            d = normalize(focusPoint - o);
+        }
+
+        V3 light = v3(0.f, 0.f, 0.f);
+        V3 contribution = v3(1.f, 1.f, 1.f);
+        uint32_t bbCheckCount = 0u, triCheckCount = 0u;
+        const bool exactMode = fp.traversal == OKRT_TRAVERSAL_EXACT;
+        Hit first; first.kind = 0u; first.idx = 0xFFFFFFFFu; first.tri = 0xFFFFFFFFu; first.u = first.v = 0.f; first.distance = OKRT_FLT_MAX;
+        uint32_t firstFlags = 0u;
+
+        for (uint32_t i = 0; i <= fp.maxBounces; i++) {
+            Hit hit;
+            bool usedFallback = false;
+            if (exactMode) traverseExact(s, rd.numSpheres < s.numSpheres ? rd.numSpheres : s.numSpheres, o, d, hit, bbCheckCount, triCheckCount);
+            else if (traverseFast(s, rd.numSpheres < s.numSpheres ? rd.numSpheres : s.numSpheres, o, d, hit)) {
+                uint32_t bb = 0u, tc = 0u;
+                traverseExact(s, rd.numSpheres < s.numSpheres ? rd.numSpheres : s.numSpheres, o, d, hit, bb, tc);
+                usedFallback = true; fallbacks++;
+            }
+            segments++;
+            if (i == 0u) { first = hit; firstFlags = usedFallback ? 1u : 0u; }
+
+            const bool hitAny = hit.kind != 0u;
+            Surface sf;
+            if (hitAny) resolveHit(s, o, d, hit, sf);
+            else { sf.worldNormal = v3(0.f, 0.f, 0.f); sf.worldPosition = v3(0.f, 0.f, 0.f); sf.material.transparency = 0.f; }
+
+            /* lights :448-487 [Q11] */
+            const uint32_t nPoint = rd.numPointLights < s.numPointLights ? rd.numPointLights : s.numPointLights;
+            for (uint32_t p = 0u; p < nPoint; p++) {
+                const okrt_point_light& pl = s.pointLights[p];
+                const V3 l = getLighting(o, d, hitAny, hit.distance, sf.material.transparency, sf.worldNormal, v3(pl.position), pl.radius, v3(pl.colour), pl.intensity);
+                light = light + l * contribution;
+            }
+            const uint32_t nSpot = rd.numSpotLights < s.numSpotLights ? rd.numSpotLights : s.numSpotLights;
+            for (uint32_t q = 0u; q < nSpot; q++) {
+                const okrt_spot_light& sl = s.spotLights[q];
+                const V3 rayToLight = normalize((v3(sl.position) + getRandomVector(seed) * 0.01f) - o);
+                const float cosTheta = dot(rayToLight, -v3(sl.direction));
+                if (cosTheta < sl.maxAngle) continue;
+                const V3 l = getLighting(o, d, hitAny, hit.distance, sf.material.transparency, sf.worldNormal, v3(sl.position), sl.radius, v3(sl.colour), sl.intensity);
+                light = light + l * contribution;
+            }
+            const uint32_t nDir = rd.numDirLights < s.numDirLights ? rd.numDirLights : s.numDirLights;
+            for (uint32_t q = 0u; q < nDir; q++) {
+                const okrt_directional_light& dl = s.dirLights[q];
+                if (clampedDot(d, -v3(dl.direction)) < dl.effectiveAngle) continue;
+                float modifier = 1.f;
+                if (hitAny && i) modifier *= sf.material.transparency * clampedDot(d, -sf.worldNormal);
+                else if (!i) modifier = 0.f;
+                light = light + ((v3(dl.colour) * dl.intensity) * contribution) * modifier;
+            }
+
+            if (!hitAny) {                                     /* :489-493 */
+                light = light + environmentLight(s, d) * contribution;
+                break;
+            }
+
+            const okrt_material& m = sf.material;              /* :495-513 [Q10] */
+            const float metallicFactor = (m.metallic * (1.f - m.roughness)) >= randomFloat(seed) ? 1.f : 0.f;
+            const float specularFactor = (m.specular * (1.f - m.roughness)) >= randomFloat(seed) ? 1.f : 0.f;
+            const float transparencyFactor = m.transparency >= randomFloat(seed) ? 1.f : 0.f;
+
+            const V3 reflectDir = findReflectDirection(d, sf.worldNormal, m.roughness * (1.f - specularFactor), seed);
+            const V3 refractDir = findTransparencyBounce(d, sf.worldNormal, m.indexOfRefraction, seed);
+            const V3 bounceDir = normalize(lerp3(reflectDir, refractDir, transparencyFactor));
+            const V3 hitPoint = sf.worldPosition + bounceDir * 0.001f;
+
+            contribution = contribution * lerp3(v3(m.albedo), v3(1.f, 1.f, 1.f), metallicFactor);
+            light = light + ((v3(m.emissionColour) * m.emissionPower) * contribution) * (1.f - transparencyFactor);
+
+            o = hitPoint;
+            d = bounceDir;
+        }
+
+        /* debug heat maps :516-520 */
+        if (rd.debugMode == 1u)
+            light = bbCheckCount > rd.debugMaxCount ? v3(1.f, 0.f, 0.f) : v3(1.f, 1.f, 1.f) * ((float)bbCheckCount / (float)rd.debugMaxCount);
+        else if (rd.debugMode == 2u)
+            light = triCheckCount > rd.debugMaxCount ? v3(1.f, 0.f, 0.f) : v3(1.f, 1.f, 1.f) * ((float)triCheckCount / (float)rd.debugMaxCount);
+
+        /* accumulate + store :525-536 [Q14] */
+        const size_t pi = (size_t)py * rd.textureDims[0] + px;
+        float r, g, b, a;
+        if (rd.accumulationEnabled == 1u) {
+            float4 acc = fp.accumulation[pi];
+            acc.x += light.x; acc.y += light.y; acc.z += light.z; acc.w += 1.f;
+            fp.accumulation[pi] = acc;
+            const float n = (float)rd.numAccumulationFrames;
+            r = acc.x / n; g = acc.y / n; b = acc.z / n; a = acc.w / n;
+        } else { r = light.x; g = light.y; b = light.z; a = 1.f; }
+        fp.result[pi] = toUnorm8(r, g, b, a);
+
+        if (fp.aov) {
+            okrt_aov av;
+            av.hitKind = first.kind; av.hitIdx = first.idx; av.triIdx = first.kind == 2u ? first.tri : 0xFFFFFFFFu;
+            av.baryU = first.kind == 2u ? first.u : 0.f; av.baryV = first.kind == 2u ? first.v : 0.f;
+            av.distance = first.distance;
+            av.bbCheckCount = bbCheckCount; av.triCheckCount = triCheckCount;
+            av.numSegments = segments; av.flags = firstFlags;
+            av.radiance[0] = light.x; av.radiance[1] = light.y; av.radiance[2] = light.z; av.reserved = 0u;
+            fp.aov[pi] = av;
+        }
+    }
+
+    /* ray counters: one atomic per warp */
+    const uint32_t segSum = __reduce_add_sync(0xFFFFFFFFu, segments);
+    const uint32_t fbSum = __reduce_add_sync(0xFFFFFFFFu, fallbacks);
+    const uint32_t pxSum = __reduce_add_sync(0xFFFFFFFFu, active ? 1u : 0u);
+    if ((threadIdx.x & 31u) == 0u && pxSum) {
+        atomicAdd(fp.counters + 0, (unsigned long long)segSum);
+        if (fbSum) atomicAdd(fp.counters + 1, (unsigned long long)fbSum);
+        atomicAdd(fp.counters + 2, (unsigned long long)pxSum);
+    }
+}
+
+/* host clear of the result target, RayTracer.cpp:227-228: (0.2, 0.4, 0.6, 1) as UNORM8 */
+__global__ void clearResultKernel(uchar4* result, size_t n)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) result[i] = make_uchar4(51, 102, 153, 255);
+}
+
+/* result = saturate(accumulation / frames), RaytracerCS.hlsl:529 — used after an external reduction */
+__global__ void resolveKernel(const float4* accumulation, uchar4* result, size_t n, float frames, uint32_t width, uint32_t coveredW, uint32_t coveredH)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t x = (uint32_t)(i % width), y = (uint32_t)(i / width);
+    if (x >= coveredW || y >= coveredH) { result[i] = make_uchar4(51, 102, 153, 255); return; }
+    const float4 a = accumulation[i];
+    result[i] = toUnorm8(a.x / frames, a.y / frames, a.z / frames, a.w / frames);
+}
+
+} // namespace okrt

@@ -1,0 +1,378 @@
+/*
+ * okrt.h — C ABI of the B200-native path-tracing core.
+ *
+ * This is the drop-in boundary for ONE hot path of Olowerr/GPU-Raytracer: the
+ * compute-shader path tracer (resources/shaders/RaytracerCS.hlsl) and the host
+ * code that feeds it (source/Graphics/RayTracer.cpp, BvhBuilder.cpp).  The
+ * reference has no FFI layer; its boundary is the C++ class `RayTracer`
+ * (source/Graphics/RayTracer.h:71-193) on top and the D3D11 binding table
+ * (resources/shaders/ShaderResourceRegisters.h:9-29, bound at
+ * source/Graphics/RayTracer.cpp:230-253) underneath.  Every entry point below
+ * names the reference interface it replaces.
+ *
+ * Plain C: PODs, pointers and sizes only.  All wire structs are 4-byte aligned
+ * with no padding and are byte-identical to the reference's GPU structs
+ * (resources/shaders/GPU-Structs.hlsli) and their CPU mirrors.
+ *
+ * Ownership: the caller owns every host array; `okrt_set_*` copies to the
+ * device before returning (reference: CreateBuffer with initial data /
+ * Map(WRITE_DISCARD)+memcpy, source/DirectX/DX11.cpp:104-156).
+ * Errors: every call returns an int status (0 = OKRT_OK); the library never
+ * aborts (reference: OKAY_ASSERT + bool, source/Utilities.h:12).
+ * Threading: one host thread per renderer handle; one CUDA stream per handle;
+ * `okrt_render*` is asynchronous, `okrt_sync`/`okrt_read_*` synchronise.
+ */
+#ifndef OKRT_H
+#define OKRT_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define OKRT_API __attribute__((visibility("default")))
+#else
+#define OKRT_API
+#endif
+
+#define OKRT_INVALID_UINT 0xFFFFFFFFu /* Okay::INVALID_UINT, source/Utilities.h:23 */
+
+/* ------------------------------------------------------------------ status */
+enum {
+    OKRT_OK = 0,
+    OKRT_ERR_INVALID_ARGUMENT = 1,
+    OKRT_ERR_CUDA = 2,          /* a CUDA runtime call failed; see okrt_last_error() */
+    OKRT_ERR_STATE = 3,         /* call order violated (e.g. render before geometry) */
+    OKRT_ERR_CAPACITY = 4,      /* a fixed traversal stack would overflow for this scene */
+    OKRT_ERR_NO_DEVICE = 5      /* no CUDA device: the product path has no CPU fallback */
+};
+
+/* ------------------------------------------------------------- wire structs
+ * Byte layouts: SURVEY.md §8.2.  Sizes are static_assert'ed in the library. */
+
+typedef struct okrt_triangle {          /* 36 B  GPU-Structs.hlsli:95-98, Utilities.h:103-106 */
+    float position[3][3];
+} okrt_triangle;
+
+typedef struct okrt_vertex_info {       /* 44 B  GPU-Structs.hlsli:100-106, Utilities.h:108-114 */
+    float normal[3];
+    float uv[2];
+    float tangent[3];
+    float bitangent[3];
+} okrt_vertex_info;
+
+typedef struct okrt_triangle_info {     /* 132 B GPU-Structs.hlsli:108-111, Utilities.h:116-119 */
+    okrt_vertex_info vertexInfo[3];
+} okrt_triangle_info;
+
+typedef struct okrt_aabb {              /* 24 B  GPU-Structs.hlsli:73-78, Utilities.h:63-70 */
+    float min[3];
+    float max[3];
+} okrt_aabb;
+
+typedef struct okrt_bvh_node {          /* 36 B  GPU-Structs.hlsli:159-165, RayTracer.h:23-29 */
+    okrt_aabb boundingBox;
+    uint32_t triStart;                  /* leaf: [triStart, triEnd) in the leaf-ordered arrays */
+    uint32_t triEnd;
+    uint32_t firstChildIdx;             /* OKRT_INVALID_UINT <=> leaf; children at idx, idx+1 */
+} okrt_bvh_node;
+
+typedef struct okrt_octree_node {       /* 48 B  GPU-Structs.hlsli:167-179, RayTracer.h:57-69 */
+    okrt_aabb boundingBox;
+    uint32_t meshesStartIdx;
+    uint32_t meshesEndIdx;
+    uint32_t spheresStartIdx;           /* unused by the shader */
+    uint32_t spheresEndIdx;             /* unused by the shader */
+    uint32_t firstChildIdx;
+    uint32_t numChildren;
+} okrt_octree_node;
+
+typedef struct okrt_material {          /* 68 B  GPU-Structs.hlsli:36-71, Components.h:42-56 */
+    float    albedo[3];
+    uint32_t albedoTextureIdx;
+    float    roughness;
+    uint32_t roughnessTextureIdx;
+    float    metallic;
+    uint32_t metallicTextureIdx;
+    float    specular;
+    uint32_t specularTextureIdx;
+    uint32_t normalMapIdx;
+    float    emissionColour[3];
+    float    emissionPower;
+    float    transparency;
+    float    indexOfRefraction;
+} okrt_material;
+
+typedef struct okrt_mesh_instance {     /* 232 B GPU-Structs.hlsli:113-125, Components.h:117-128 */
+    float    transformMatrix[16];       /* 16 floats in memory = row-major T (host uploads glm::transpose(T),
+                                           RayTracer.cpp:747-749); world = T * local */
+    float    inverseTransformMatrix[16];/* row-major inverse(T) */
+    uint32_t triStart;
+    uint32_t triEnd;
+    okrt_aabb boundingBox;              /* mesh-local */
+    okrt_material material;
+    uint32_t bvhNodeStartIdx;
+} okrt_mesh_instance;
+
+typedef struct okrt_sphere {            /* 84 B  GPU-Structs.hlsli:86-93, RayTracer.cpp:88 */
+    float position[3];
+    okrt_material material;
+    float radius;
+} okrt_sphere;
+
+typedef struct okrt_directional_light { /* 32 B  GPU-Structs.hlsli:127-135 */
+    float colour[3];
+    float intensity;
+    float effectiveAngle;               /* cos(angle) — RayTracer.cpp:448 */
+    float direction[3];
+} okrt_directional_light;
+
+typedef struct okrt_point_light {       /* 32 B  GPU-Structs.hlsli:137-145 */
+    float colour[3];
+    float intensity;
+    float radius;
+    float position[3];
+} okrt_point_light;
+
+typedef struct okrt_spot_light {        /* 48 B  GPU-Structs.hlsli:147-157 */
+    float colour[3];
+    float intensity;
+    float radius;
+    float maxAngle;                     /* cos(angle) — RayTracer.cpp:477 */
+    float position[3];
+    float direction[3];
+} okrt_spot_light;
+
+typedef struct okrt_render_data {       /* 240 B RaytracerCS.hlsl:19-47, RayTracer.h:129-157 */
+    uint32_t accumulationEnabled;
+    uint32_t numAccumulationFrames;
+    uint32_t numSpheres;
+    uint32_t numMeshes;
+    uint32_t numDirLights;
+    uint32_t numPointLights;
+    uint32_t numSpotLights;
+    uint32_t debugMode;                 /* 0 none, 1 bbCheckCount, 2 triCheckCount (RayTracer.h:74-79) */
+    uint32_t textureDims[2];
+    float    viewPlaneDims[2];
+    float    cameraInverseProjectionMatrix[16]; /* row-major inverse(P) (transposed upload, RayTracer.cpp:295) */
+    float    cameraInverseViewMatrix[16];       /* row-major inverse(V) (RayTracer.cpp:306) */
+    float    cameraPosition[3];
+    float    cameraNearZ;
+    float    cameraUpDir[3];
+    float    dofStrength;
+    float    cameraRightDir[3];
+    float    dofDistance;
+    uint32_t debugMaxCount;
+    float    pad0[3];
+} okrt_render_data;
+
+/* ------------------------------------------------ host-side scene inputs
+ * These replace the EnTT registry (source/Scene) with plain arrays. */
+
+typedef struct okrt_mesh_desc {         /* RayTracer.h:15-21 */
+    uint32_t startIdx;
+    uint32_t endIdx;
+    uint32_t bvhTreeStartIdx;
+    uint32_t numBvhNodes;
+} okrt_mesh_desc;
+
+typedef struct okrt_mesh_view {         /* one Mesh asset: Mesh.h:44-46 */
+    const okrt_triangle*      trianglesPos;
+    const okrt_triangle_info* trianglesInfo;
+    uint32_t                  numTriangles;
+    okrt_aabb                 boundingBox;   /* Importer.cpp:52-53 */
+} okrt_mesh_view;
+
+typedef struct okrt_transform {         /* Components.h:6-24 (rotation = Euler degrees) */
+    float position[3];
+    float rotation[3];
+    float scale[3];
+} okrt_transform;
+
+typedef struct okrt_mesh_entity {       /* Transform + MeshComponent, Components.h:108-112 */
+    okrt_transform transform;
+    okrt_material  material;
+    uint32_t       meshID;
+} okrt_mesh_entity;
+
+typedef struct okrt_sphere_entity {     /* Transform + Sphere, Components.h:102-106 */
+    okrt_transform transform;
+    okrt_material  material;
+    float          radius;
+} okrt_sphere_entity;
+
+typedef struct okrt_camera {            /* Transform + Camera, Components.h:130-139 */
+    float position[3];
+    float rotation[3];                  /* Euler degrees */
+    float fov;                          /* degrees */
+    float nearZ;
+    float farZ;
+} okrt_camera;
+
+/* ------------------------------------------------------------- new fields
+ * Parameters the reference fixes at compile time or does not have. */
+
+enum { OKRT_TRAVERSAL_FAST = 0,   /* near-first traversal of the re-packed child-pair BVH with
+                                     exact-arithmetic commit; falls back to reference order on ties */
+       OKRT_TRAVERSAL_EXACT = 1 };/* reference visit order, RaytracerCS.hlsl:244-334 (debug counters exact) */
+
+enum { OKRT_SHARD_NONE = 0,
+       OKRT_SHARD_TILE = 1 };     /* this renderer traces only its interleaved row bands */
+
+typedef struct okrt_options {
+    uint32_t maxBounces;          /* NUM_BOUNCES, RaytracerCS.hlsl:6 (loop is i <= maxBounces) */
+    uint32_t traversal;           /* OKRT_TRAVERSAL_* */
+    uint32_t coverAllPixels;      /* 0: reference coverage Dispatch(W/16,H/9) (RayTracer.cpp:256), uncovered
+                                     pixels keep the clear colour; 1: trace every pixel */
+    uint32_t writeAov;            /* 1: record okrt_aov per pixel after the first findClosestHit */
+    uint32_t shardMode;           /* OKRT_SHARD_* */
+    uint32_t shardRank;
+    uint32_t shardCount;
+    uint32_t shardBandRows;       /* rows per interleaved band (tile mode); 0 = default */
+    uint32_t frameOffset;         /* sample sharding: seed frame of local frame k (1-based) is */
+    uint32_t frameStride;         /*   frameOffset + (k-1)*frameStride + 1; defaults 0 / 1 */
+    uint32_t reserved[6];
+} okrt_options;
+
+typedef struct okrt_aov {         /* parity tap, one per pixel (new) */
+    uint32_t hitKind;             /* 0 miss, 1 sphere, 2 mesh triangle */
+    uint32_t hitIdx;              /* sphere index or mesh-instance index */
+    uint32_t triIdx;              /* index into the leaf-ordered triangle arrays */
+    float    baryU;
+    float    baryV;
+    float    distance;            /* payload.distance (world space) */
+    uint32_t bbCheckCount;        /* totals over the whole path, exact in OKRT_TRAVERSAL_EXACT */
+    uint32_t triCheckCount;
+    uint32_t numSegments;         /* findClosestHit calls on this path */
+    uint32_t flags;               /* bit0: first segment resolved by the reference-order fallback */
+    float    radiance[3];         /* this frame's `light` before accumulation */
+    uint32_t reserved;
+} okrt_aov;
+
+typedef struct okrt_stats {
+    uint64_t raySegments;         /* findClosestHit calls since the last reset_stats */
+    uint64_t fallbackSegments;    /* of those, resolved by the reference-order fallback */
+    uint64_t pixelsTraced;
+    uint64_t kernelLaunches;      /* CUDA kernels launched by this handle since reset_stats */
+    float    lastRenderMs;        /* device time of the last okrt_render/_frames call (CUDA events) */
+    float    reserved[3];
+} okrt_stats;
+
+typedef struct okrt_renderer okrt_renderer;   /* RayTracer instance */
+typedef struct okrt_geometry okrt_geometry;   /* result of loadMeshAndBvhData */
+typedef struct okrt_octree   okrt_octree;     /* result of createOctTree/loadOctTree */
+
+/* -------------------------------------------------------------- utilities */
+OKRT_API const char* okrt_version(void);
+OKRT_API const char* okrt_last_error(void);      /* thread-local message of the last failing call */
+OKRT_API int  okrt_device_count(void);           /* 0 when no CUDA device is visible */
+OKRT_API void okrt_material_default(okrt_material* m);   /* Components.h:42-56 defaults */
+OKRT_API void okrt_options_default(okrt_options* o);     /* maxBounces 1 (HEAD), FAST, reference coverage */
+OKRT_API void okrt_render_data_default(okrt_render_data* rd); /* RayTracer.h:131-156 defaults */
+
+/* ------------------------------------------------ host builders (CPU, C++)
+ * a10: RayTracer::loadMeshAndBvhData (RayTracer.cpp:120-217) + BvhBuilder
+ * (BvhBuilder.cpp:12-230).  Produces the identical node array, node order and
+ * leaf-ordered triangle arrays as the reference builder (bit-exact), using an
+ * exact binned evaluation of the same 3 x 99 SAH candidates. */
+OKRT_API int okrt_geometry_build(const okrt_mesh_view* meshes, uint32_t numMeshes,
+                                 uint32_t maxDepth, uint32_t maxLeafTriangles,
+                                 okrt_geometry** out);
+OKRT_API void okrt_geometry_free(okrt_geometry* g);
+OKRT_API uint32_t okrt_geometry_num_triangles(const okrt_geometry* g);
+OKRT_API uint32_t okrt_geometry_num_nodes(const okrt_geometry* g);
+OKRT_API uint32_t okrt_geometry_num_meshes(const okrt_geometry* g);
+OKRT_API const okrt_triangle*      okrt_geometry_triangles_pos(const okrt_geometry* g);   /* t0 */
+OKRT_API const okrt_triangle_info* okrt_geometry_triangles_info(const okrt_geometry* g);  /* t1 */
+OKRT_API const okrt_bvh_node*      okrt_geometry_bvh_nodes(const okrt_geometry* g);       /* t2 */
+OKRT_API const okrt_mesh_desc*     okrt_geometry_mesh_descs(const okrt_geometry* g);
+OKRT_API const okrt_aabb*          okrt_geometry_mesh_bounds(const okrt_geometry* g);
+/* Single-mesh form of BvhBuilder::buildTree (BvhBuilder.cpp:12-36): nodes use
+ * mesh-local indices, triOrder[k] = source triangle stored at leaf slot k.
+ * outNodes needs capacity 2*numTriangles+1, outTriOrder numTriangles. */
+OKRT_API int okrt_build_bvh(const okrt_triangle* tris, uint32_t numTriangles, const okrt_aabb* rootBounds,
+                            uint32_t maxDepth, uint32_t maxLeafTriangles,
+                            okrt_bvh_node* outNodes, uint32_t nodeCapacity, uint32_t* outNumNodes,
+                            uint32_t* outTriOrder);
+
+/* a11: RayTracer::createOctTree + loadOctTree (RayTracer.cpp:523-788).
+ * `meshEntities` / `sphereEntities` are given in the order the reference's
+ * registry views would enumerate them. */
+OKRT_API int okrt_octree_build(const okrt_geometry* g,
+                               const okrt_mesh_entity* meshEntities, uint32_t numMeshEntities,
+                               const okrt_sphere_entity* sphereEntities, uint32_t numSphereEntities,
+                               uint32_t maxDepth, uint32_t maxLeafObjects,
+                               okrt_octree** out);
+OKRT_API void okrt_octree_free(okrt_octree* t);
+OKRT_API uint32_t okrt_octree_num_nodes(const okrt_octree* t);
+OKRT_API uint32_t okrt_octree_num_instances(const okrt_octree* t);
+OKRT_API const okrt_octree_node*   okrt_octree_nodes(const okrt_octree* t);       /* t5 */
+OKRT_API const okrt_mesh_instance* okrt_octree_instances(const okrt_octree* t);   /* t7 */
+
+/* a12: Transform::calculateMatrix (Components.h:13-18) and
+ * RayTracer::calculateProjectionData (RayTracer.cpp:268-308). */
+OKRT_API void okrt_transform_matrix(const okrt_transform* t, float outRowMajor[16]);
+OKRT_API int  okrt_calculate_projection_data(const okrt_camera* cam, uint32_t width, uint32_t height,
+                                             okrt_render_data* inout);
+
+/* a13: RayTracer::loadTextureData (RayTracer.cpp:310-342) + Okay::scaleTexture
+ * (DX11.cpp:232-270) and RayTracer::loadEnvironmentMap (RayTracer.cpp:344-432). */
+OKRT_API uint32_t okrt_texture_array_size(const uint32_t* widths, const uint32_t* heights, uint32_t count);
+OKRT_API int okrt_scale_texture(const uint8_t* srcRgba8, uint32_t srcW, uint32_t srcH,
+                                uint8_t* dstRgba8, uint32_t dstW, uint32_t dstH);
+OKRT_API int okrt_environment_cross_to_faces(const uint8_t* crossRgba8, uint32_t imgW, uint32_t imgH,
+                                             uint8_t* outFaces6 /* 6*(imgW/4)*(imgH/3)*4 */);
+
+/* ------------------------------------------------------- renderer (device) */
+OKRT_API int  okrt_create(int device, uint32_t width, uint32_t height, okrt_renderer** out); /* RayTracer::initiate :60 */
+OKRT_API void okrt_destroy(okrt_renderer* r);                                                 /* RayTracer::shutdown :34 */
+OKRT_API int  okrt_resize(okrt_renderer* r, uint32_t width, uint32_t height);                 /* RayTracer::onResize :494 */
+
+/* binding table (ShaderResourceRegisters.h:9-29) */
+OKRT_API int okrt_set_triangles(okrt_renderer* r, const okrt_triangle* pos, const okrt_triangle_info* info, uint32_t n); /* t0,t1 RayTracer.cpp:209-210 */
+OKRT_API int okrt_set_bvh_nodes(okrt_renderer* r, const okrt_bvh_node* nodes, uint32_t n);          /* t2 :211 */
+OKRT_API int okrt_set_textures(okrt_renderer* r, const uint8_t* rgba8, uint32_t size, uint32_t layers); /* t3 :335 */
+OKRT_API int okrt_set_environment_map(okrt_renderer* r, const uint8_t* faces6, uint32_t faceW, uint32_t faceH); /* t4 :420-429 */
+OKRT_API int okrt_set_octree(okrt_renderer* r, const okrt_octree_node* nodes, uint32_t n);           /* t5 :778 */
+OKRT_API int okrt_set_spheres(okrt_renderer* r, const okrt_sphere* spheres, uint32_t n);             /* t6 :88 */
+OKRT_API int okrt_set_mesh_instances(okrt_renderer* r, const okrt_mesh_instance* inst, uint32_t n);  /* t7 :777 */
+OKRT_API int okrt_set_directional_lights(okrt_renderer* r, const okrt_directional_light* l, uint32_t n); /* t8 :438-451 */
+OKRT_API int okrt_set_point_lights(okrt_renderer* r, const okrt_point_light* l, uint32_t n);         /* t9 :453-465 */
+OKRT_API int okrt_set_spot_lights(okrt_renderer* r, const okrt_spot_light* l, uint32_t n);           /* t10 :467-481 */
+OKRT_API int okrt_set_render_data(okrt_renderer* r, const okrt_render_data* rd);                     /* b0 :491 */
+OKRT_API int okrt_get_render_data(const okrt_renderer* r, okrt_render_data* out);
+OKRT_API int okrt_set_options(okrt_renderer* r, const okrt_options* o);
+
+/* RayTracer::render (RayTracer.cpp:219-260): numAccumulationFrames += accumulationEnabled (:489), clear the
+ * result to (0.2,0.4,0.6,1) (:227-228), dispatch.  okrt_render_frames repeats it `frames` times. */
+OKRT_API int okrt_render(okrt_renderer* r);
+OKRT_API int okrt_render_frames(okrt_renderer* r, uint32_t frames);
+OKRT_API int okrt_sync(okrt_renderer* r);
+
+OKRT_API int okrt_toggle_accumulation(okrt_renderer* r, int enable);   /* RayTracer.h:197-201 */
+OKRT_API int okrt_reset_accumulation(okrt_renderer* r);                /* RayTracer.h:203-209 */
+OKRT_API uint32_t okrt_get_num_accumulation_frames(const okrt_renderer* r); /* RayTracer.h:211 */
+
+/* u0 / u1 read-back (reference: staging copy, DX11.cpp:196-230) */
+OKRT_API int okrt_read_result(okrt_renderer* r, uint8_t* outRgba8);            /* W*H*4 bytes */
+OKRT_API int okrt_read_accumulation(okrt_renderer* r, float* outRgba32f);      /* W*H*4 floats */
+OKRT_API int okrt_read_aov(okrt_renderer* r, okrt_aov* out);                   /* W*H entries; needs writeAov */
+/* progressive-state restore / merge (new): replaces the accumulation buffer and frame counter */
+OKRT_API int okrt_write_accumulation(okrt_renderer* r, const float* rgba32f, uint32_t numAccumulationFrames);
+/* recompute u0 = saturate(u1 / frames) (RaytracerCS.hlsl:529) after an external reduction of u1 */
+OKRT_API int okrt_resolve(okrt_renderer* r, uint32_t totalFrames);
+
+/* device pointers for peer/NCCL exchange (sample-sharded mode reduces u1 in place) */
+OKRT_API void* okrt_accumulation_device_ptr(okrt_renderer* r);
+OKRT_API void* okrt_result_device_ptr(okrt_renderer* r);
+OKRT_API void* okrt_cuda_stream(okrt_renderer* r);
+
+OKRT_API int okrt_get_stats(okrt_renderer* r, okrt_stats* out);   /* synchronises */
+OKRT_API int okrt_reset_stats(okrt_renderer* r);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OKRT_H */
