@@ -171,6 +171,9 @@ struct Ctx {
     const RenderData* rd;
     int mathMode;
     uint32_t stackOverflow;               /* times the reference's fixed stacks would have overflowed */
+    /* visit totals for the algorithmic-bytes roofline: oct-tree nodes, instances, BVH nodes,
+     * triangle tests, segments that hit something, texture taps */
+    uint64_t nOct = 0, nInst = 0, nBvh = 0, nTri = 0, nHit = 0, nTap = 0;
 };
 
 inline float m_log(const Ctx& c, float x) { return c.mathMode == ORACLE_MATH_LIBM ? std::log(x) : omath::c_log(x); }
@@ -343,6 +346,7 @@ inline float3 bilerp(float3 c00, float3 c10, float3 c01, float3 c11, float fx, f
 inline float3 sampleTexture(const Ctx& c, uint32_t textureIdx, float2 uv)
 {
     const OracleScene& s = *c.s;
+    const_cast<Ctx&>(c).nTap++;
     if (!s.textures || s.texLayers == 0 || s.texSize == 0) return f3(0, 0, 0);   /* null SRV reads 0 */
     uint32_t layer = textureIdx < s.texLayers ? textureIdx : s.texLayers - 1;     /* slice index clamps */
     const int N = (int)s.texSize;
@@ -557,11 +561,13 @@ Payload findClosestHit(Ctx& c, const Ray& ray, uint32_t& bbCheckCount, uint32_t&
         const OctTreeNode& octNode = s.octNodes[octCurrentNodeIdx];
 
         bbCheckCount += 1;
+        c.nOct++;
         if (RayAndAABBDist(ray, octNode.boundingBox) >= payload.distance)
             continue;
 
         for (uint32_t i = octNode.meshesStartIdx; i < octNode.meshesEndIdx; i++) {
             bbCheckCount += 1;
+            c.nInst++;
             const Mesh& mesh = s.meshes[i];
             bvhStack[0] = mesh.bvhNodeStartIdx;
             bvhStackSize = 1;
@@ -575,6 +581,7 @@ Payload findClosestHit(Ctx& c, const Ray& ray, uint32_t& bbCheckCount, uint32_t&
                 const BvhNode& bvhNode = s.bvhNodes[currentNodeIdx];
 
                 bbCheckCount += 1;
+                c.nBvh++;
                 if (RayAndAABBDist(localRay, bvhNode.boundingBox) >= payload.distance)
                     continue;
 
@@ -590,6 +597,7 @@ Payload findClosestHit(Ctx& c, const Ray& ray, uint32_t& bbCheckCount, uint32_t&
                     const Triangle& tri = s.triPos[j];
                     float2 baryUVCoords = float2{0.f, 0.f};
                     triCheckCount += 1;
+                    c.nTri++;
                     float distanceToHit = RayAndTriangle(localRay, f3(tri.position[0]), f3(tri.position[1]), f3(tri.position[2]), baryUVCoords);
                     if (distanceToHit <= 0.f)
                         continue;
@@ -630,6 +638,7 @@ Payload findClosestHit(Ctx& c, const Ray& ray, uint32_t& bbCheckCount, uint32_t&
     /* [Q8] on a miss the shader runs the sphere branch on zeros and discards the result. */
     if (!payload.hit)
         return payload;
+    c.nHit++;
 
     if (hitType == 0) {                   /* RaytracerCS.hlsl:342-362 */
         const Sphere& sp = s.spheres[hitIdx];
@@ -791,6 +800,11 @@ ORACLE_API const char* oracle_description(void)
     return "okrt CPU oracle: scalar restatement of RaytracerCS.hlsl / GPU-Utilities.hlsli (test infrastructure)";
 }
 
+/* visit totals of the last oracle_render call: segments, oct-tree nodes, instances, BVH nodes, triangle tests,
+ * hit segments, texture taps */
+static uint64_t g_lastVisits[7];
+ORACLE_API void oracle_last_visit_totals(uint64_t* out7) { for (int k = 0; k < 7; k++) out7[k] = g_lastVisits[k]; }
+
 /* Full frame (or row band [y0,y1)) of RaytracerCS::main, RaytracerCS.hlsl:421-537, preceded by the host's
  * clear of the result target (RayTracer.cpp:227-228) for those rows.
  *   seedFrame   value of renderData.numAccumulationFrames used in the seed [Q3]
@@ -813,6 +827,8 @@ ORACLE_API uint32_t oracle_render(const OracleScene* scene, const RenderData* rd
     std::atomic<uint32_t> nextRow(y0);
     std::atomic<uint64_t> segTotal(0);
     std::atomic<uint32_t> ovfTotal(0);
+    std::atomic<uint64_t> visit[6];
+    for (auto& v : visit) v = 0;
     auto worker = [&]() {
         Ctx c{scene, rd, mathMode, 0};
         uint64_t localSegments = 0;
@@ -848,6 +864,7 @@ ORACLE_API uint32_t oracle_render(const OracleScene* scene, const RenderData* rd
         }
         segTotal += localSegments;
         ovfTotal += c.stackOverflow;
+        visit[0] += c.nOct; visit[1] += c.nInst; visit[2] += c.nBvh; visit[3] += c.nTri; visit[4] += c.nHit; visit[5] += c.nTap;
     };
     if (nthreads <= 1) worker();
     else {
@@ -857,6 +874,8 @@ ORACLE_API uint32_t oracle_render(const OracleScene* scene, const RenderData* rd
     }
     segments = segTotal.load();
     overflow = ovfTotal.load();
+    g_lastVisits[0] = segments;
+    for (int k = 0; k < 6; k++) g_lastVisits[k + 1] = visit[k].load();
     if (outSegments) *outSegments = segments;
     return overflow;
 }

@@ -47,6 +47,8 @@ class Oracle:
         self.lib = lib
         lib.oracle_render.restype = _U
         lib.oracle_render.argtypes = [ctypes.POINTER(OracleScene), _P, _U, _U, _U, _P, _P, _P, _U, _U, _I, _I, ctypes.POINTER(ctypes.c_uint64)]
+        lib.oracle_last_visit_totals.restype = None
+        lib.oracle_last_visit_totals.argtypes = [_P]
         lib.oracle_pcg_hash.restype = _U
         lib.oracle_pcg_hash.argtypes = [ctypes.POINTER(_U)]
         lib.oracle_random_float.restype = _F
@@ -122,7 +124,10 @@ class Oracle:
         ovf = self.lib.oracle_render(ctypes.byref(scene), rd.ctypes.data_as(_P), maxBounces, seedFrame, coverAll,
                                      accum.ctypes.data_as(_P), result.ctypes.data_as(_P),
                                      None if aov is None else aov.ctypes.data_as(_P), y0, y1, threads, math, ctypes.byref(seg))
-        return dict(accum=accum, result=result, aov=aov, segments=seg.value, overflow=ovf)
+        v = np.zeros(7, np.uint64)
+        self.lib.oracle_last_visit_totals(v.ctypes.data_as(_P))
+        visits = dict(zip(("segments", "octNodes", "instances", "bvhNodes", "triangles", "hits", "textureTaps"), (int(x) for x in v)))
+        return dict(accum=accum, result=result, aov=aov, segments=seg.value, overflow=ovf, visits=visits)
 
 
 _oracle = None
