@@ -131,6 +131,7 @@ struct okrt_renderer {
     okrt_options opt;
     uint64_t launches = 0;
     float lastRenderMs = 0.f;
+    int numSms = 0, blocksPerSmLean = 1, blocksPerSmInstrumented = 1;   /* persistent grid = SMs x resident blocks */
 };
 
 namespace {
@@ -257,8 +258,17 @@ int launchFrame(okrt_renderer* r)
      * overwrites every covered pixel; uncovered pixels [Q9] are cleared once, when the images are created
      * or the coverage option changes, and never written afterwards */
     if (rows == 0) return OKRT_OK;
-    const dim3 grid((r->width + kTileW - 1) / kTileW, (rows + kTileH - 1) / kTileH, 1);
-    pathTraceKernel<<<grid, kTileW * kTileH, 0, r->stream>>>(sceneView(r), fp);
+    fp.tilesX = (r->width + kTileW - 1) / kTileW;
+    fp.numTiles = fp.tilesX * ((rows + kTileH - 1) / kTileH);
+    fp.workCounter = reinterpret_cast<uint32_t*>(r->counters + 3);
+    OKRT_CUDA(cudaMemsetAsync(fp.workCounter, 0, sizeof(unsigned long long), r->stream));
+    /* AOV taps and the debug heat maps live in the instrumented build of the kernel */
+    const bool instrumented = fp.aov != nullptr || r->rd.debugMode != 0u;
+    const int blocksPerSm = instrumented ? r->blocksPerSmInstrumented : r->blocksPerSmLean;
+    const unsigned wantBlocks = (unsigned)((fp.numTiles * (uint32_t)kTilePixels + kBlockThreads - 1) / kBlockThreads);
+    const unsigned grid = std::min<unsigned>((unsigned)(r->numSms * blocksPerSm), std::max(1u, wantBlocks));
+    if (instrumented) pathTraceKernel<true><<<grid, kBlockThreads, 0, r->stream>>>(sceneView(r), fp);
+    else pathTraceKernel<false><<<grid, kBlockThreads, 0, r->stream>>>(sceneView(r), fp);
     r->launches++;
     OKRT_CUDA(cudaGetLastError());
     return OKRT_OK;
@@ -305,6 +315,17 @@ int okrt_create(int device, uint32_t width, uint32_t height, okrt_renderer** out
         okrt_destroy(r);
         return OKRT_ERR_CUDA;
     }
+    cudaDeviceProp prop;
+    if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess ||
+        (e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&r->blocksPerSmLean, pathTraceKernel<false>, kBlockThreads, 0)) != cudaSuccess ||
+        (e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&r->blocksPerSmInstrumented, pathTraceKernel<true>, kBlockThreads, 0)) != cudaSuccess) {
+        setError(std::string("okrt_create: ") + cudaGetErrorString(e));
+        okrt_destroy(r);
+        return OKRT_ERR_CUDA;
+    }
+    r->numSms = prop.multiProcessorCount;
+    r->blocksPerSmLean = std::max(1, r->blocksPerSmLean);
+    r->blocksPerSmInstrumented = std::max(1, r->blocksPerSmInstrumented);
     const int rc = allocateImages(r);
     if (rc) { okrt_destroy(r); return rc; }
     *out = r;

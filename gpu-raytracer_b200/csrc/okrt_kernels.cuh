@@ -100,6 +100,8 @@ struct FrameParams {
     uint32_t traversal;
     uint32_t coveredW, coveredH;              /* [Q9] */
     uint32_t bandRows, shardRank, shardCount; /* tile sharding: row band b belongs to rank b % shardCount */
+    uint32_t tilesX, numTiles;                /* 16x8 tiles this launch owns */
+    uint32_t* workCounter;                    /* next tile to hand out (zeroed before the launch) */
     float4* accumulation;                     /* u1 */
     uchar4* result;                           /* u0 */
     okrt_aov* aov;                            /* optional */
@@ -371,88 +373,101 @@ __device__ __forceinline__ bool traverseFast(const DeviceScene& s, uint32_t numS
         const float t = rayAndSphere(o, d, v3(sp.position), sp.radius);
         if (t > 0.f) fastCandidate(c, hit, t, 1u, i, 0xFFFFFFFFu, 0.f, 0.f);
     }
+    if (s.topRef == kRefNone) return false;
 
-    if (s.topRef != kRefNone) {
-        const uint32_t EXIT_INSTANCE = 0xFFFFFFFEu;
-        uint32_t stack[kFastStackCapacity];
-        int sp = 0;
-        const V3 idirWorld = rcp3(d);
-        /* normalize(d * I) is what every identity-transform instance sees as its local direction */
-        const V3 dn = normalize(mulDirRows(d, make_float4(1, 0, 0, 0), make_float4(0, 1, 0, 0), make_float4(0, 0, 1, 0)));
-        const V3 idirN = rcp3(dn);
-        const V3 oI = mulPointRows(o, make_float4(1, 0, 0, 0), make_float4(0, 1, 0, 0), make_float4(0, 0, 1, 0));
+    const uint32_t EXIT_INSTANCE = 0xFFFFFFFEu;
+    const uint32_t DONE = 0xFFFFFFFDu;
+    uint32_t stack[kFastStackCapacity];
+    int sp = 0;
+    const V3 idirWorld = rcp3(d);
+    /* what every identity-transform instance sees as its local ray: mul by I, then normalize [Q1] */
+    const V3 dn = normalize(mulDirRows(d, make_float4(1, 0, 0, 0), make_float4(0, 1, 0, 0), make_float4(0, 0, 1, 0)));
+    const V3 idirN = rcp3(dn);
+    const V3 oI = mulPointRows(o, make_float4(1, 0, 0, 0), make_float4(0, 1, 0, 0), make_float4(0, 0, 1, 0));
 
-        V3 ro = o, rd = d, ridir = idirWorld;    /* current ray: world at the top level, local inside an instance */
-        float4 t0 = make_float4(1, 0, 0, 0), t1 = make_float4(0, 1, 0, 0), t2 = make_float4(0, 0, 1, 0);
-        uint32_t instIdx = 0xFFFFFFFFu;
-        uint32_t cur = s.topRef;                 /* always an interior reference here */
+    /* per-ray cache of the reference's oct-tree box tests (hit / miss only: ray dependent, not `best` dependent) */
+    unsigned long long octTested = 0ull, octHit = 0ull;
 
-        for (;;) {
-            const uint32_t tag = cur & kRefTagMask;
-            if (tag == kRefInterior) {
-                const float4* q = s.fastNodes + (size_t)cur * 4;
-                const float4 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3);
-                const float limit = relaxedLimit(c.best);
-                const float n0 = rayAndAABBDist(ro, ridir, v3(q0.x, q0.y, q0.z), v3(q1.x, q1.y, q1.z));
-                const float n1 = rayAndAABBDist(ro, ridir, v3(q2.x, q2.y, q2.z), v3(q3.x, q3.y, q3.z));
-                const uint32_t r0 = __float_as_uint(q0.w), r1 = __float_as_uint(q1.w);
-                const bool h0 = n0 < limit && r0 != kRefNone;
-                const bool h1 = n1 < limit && r1 != kRefNone;
-                if (h0 && h1) {
-                    const bool firstIs1 = n1 < n0;
-                    stack[sp++] = firstIs1 ? r0 : r1;
-                    cur = firstIs1 ? r1 : r0;
+    V3 ro = o, rd = d, ridir = idirWorld;        /* current ray: world at the top level, local inside an instance */
+    float4 t0 = make_float4(1, 0, 0, 0), t1 = make_float4(0, 1, 0, 0), t2 = make_float4(0, 0, 1, 0);
+    uint32_t instIdx = 0xFFFFFFFFu;
+    uint32_t cur = s.topRef;                     /* interior */
+
+    for (;;) {
+        /* phase 1: walk interior pair nodes until something that is not one comes up */
+        while ((cur & kRefTagMask) == kRefInterior) {
+            const float4* q = s.fastNodes + (size_t)cur * 4;
+            const float4 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3);
+            const float limit = relaxedLimit(c.best);
+            const float n0 = rayAndAABBDist(ro, ridir, v3(q0.x, q0.y, q0.z), v3(q1.x, q1.y, q1.z));
+            const float n1 = rayAndAABBDist(ro, ridir, v3(q2.x, q2.y, q2.z), v3(q3.x, q3.y, q3.z));
+            const uint32_t r0 = __float_as_uint(q0.w), r1 = __float_as_uint(q1.w);
+            const bool h0 = n0 < limit && r0 != kRefNone;
+            const bool h1 = n1 < limit && r1 != kRefNone;
+            if (h0 && h1) {
+                const bool firstIs1 = n1 < n0;
+                stack[sp++] = firstIs1 ? r0 : r1;
+                cur = firstIs1 ? r1 : r0;
+            } else if (h0) cur = r0;
+            else if (h1) cur = r1;
+            else cur = sp ? stack[--sp] : DONE;
+        }
+        if (cur == DONE) break;
+
+        /* phase 2: a triangle leaf, an instance leaf or the end of an instance */
+        if ((cur & kRefTagMask) == kRefTriLeaf) {
+            const uint32_t first = cur & (kMaxTriIndex - 1u);
+            const uint32_t count = ((cur >> 27) & 7u) + 1u;
+            for (uint32_t j = first; j < first + count; j++) {
+                const float4* tp = s.fastTris + (size_t)j * 3;
+                const float4 a = __ldg(tp), b = __ldg(tp + 1), cc = __ldg(tp + 2);
+                float bu = 0.f, bv = 0.f;
+                float t = rayAndTriangle(ro, rd, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(cc.x, cc.y, cc.z), bu, bv);
+                if (t <= 0.f) continue;
+                t = length(mulDirRows(rd * t, t0, t1, t2));              /* RaytracerCS.hlsl:312-314 */
+                fastCandidate(c, hit, t, 2u, instIdx, j, bu, bv);
+            }
+        } else if (cur == EXIT_INSTANCE) {
+            ro = o; rd = d; ridir = idirWorld; instIdx = 0xFFFFFFFFu;
+        } else {                                                         /* instance leaf */
+            const float4* rec = s.fastInstances + (size_t)(cur & ~kRefTagMask) * 8;
+            const float4 r6 = __ldg(rec + 6), r7 = __ldg(rec + 7);
+            /* every oct-tree box the reference tests on its way to this instance (RaytracerCS.hlsl:262) must be HIT;
+             * its `>= payload.distance` part is an order-dependent cull that the window argument covers */
+            bool enter = true;
+            for (uint32_t on = __float_as_uint(r7.y); on != 0xFFFFFFFFu; on = __ldg(s.octParent + on)) {
+                bool boxHit;
+                const unsigned long long bit = 1ull << (on & 63u);
+                if (on < 64u && (octTested & bit)) boxHit = (octHit & bit) != 0ull;
+                else {
+                    const okrt_octree_node& node = s.octNodes[on];
+                    boxHit = rayAndAABBDist(o, idirWorld, v3(node.boundingBox.min), v3(node.boundingBox.max)) < OKRT_FLT_MAX;
+                    if (on < 64u) { octTested |= bit; if (boxHit) octHit |= bit; }
+                }
+                if (!boxHit) { enter = false; break; }
+            }
+            if (enter) {
+                const float4 a0 = __ldg(rec + 3), a1 = __ldg(rec + 4), a2 = __ldg(rec + 5);
+                V3 lo, ld, lidir;
+                if (__float_as_uint(r6.w) & 1u) { lo = oI; ld = dn; lidir = idirN; }
+                else {
+                    const float4 i0 = __ldg(rec), i1 = __ldg(rec + 1), i2 = __ldg(rec + 2);
+                    lo = mulPointRows(o, i0, i1, i2);
+                    ld = normalize(mulDirRows(d, i0, i1, i2));
+                    lidir = rcp3(ld);
+                }
+                /* the mesh's root box (RaytracerCS.hlsl:285 on the first popped node) */
+                if (rayAndAABBDist(lo, lidir, v3(a0.w, a1.w, a2.w), v3(r6.x, r6.y, r6.z)) < relaxedLimit(c.best)) {
+                    stack[sp++] = EXIT_INSTANCE;
+                    ro = lo; rd = ld; ridir = lidir; t0 = a0; t1 = a1; t2 = a2;
+                    instIdx = __float_as_uint(r7.z);
+                    cur = __float_as_uint(r7.x);
                     continue;
                 }
-                if (h0) { cur = r0; continue; }
-                if (h1) { cur = r1; continue; }
-            } else if (tag == kRefTriLeaf) {
-                const uint32_t first = cur & (kMaxTriIndex - 1u);
-                const uint32_t count = ((cur >> 27) & 7u) + 1u;
-                for (uint32_t j = first; j < first + count; j++) {
-                    const float4* tp = s.fastTris + (size_t)j * 3;
-                    const float4 a = __ldg(tp), b = __ldg(tp + 1), cc = __ldg(tp + 2);
-                    float bu = 0.f, bv = 0.f;
-                    float t = rayAndTriangle(ro, rd, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(cc.x, cc.y, cc.z), bu, bv);
-                    if (t <= 0.f) continue;
-                    t = length(mulDirRows(rd * t, t0, t1, t2));
-                    fastCandidate(c, hit, t, 2u, instIdx, j, bu, bv);
-                }
-            } else if (cur == EXIT_INSTANCE) {
-                ro = o; rd = d; ridir = idirWorld; instIdx = 0xFFFFFFFFu;
-            } else {                                         /* instance leaf */
-                const float4* rec = s.fastInstances + (size_t)(cur & ~kRefTagMask) * 8;
-                const float4 r6 = __ldg(rec + 6), r7 = __ldg(rec + 7);
-                const float limit = relaxedLimit(c.best);
-                /* every oct-tree box the reference tests on its way to this instance (RaytracerCS.hlsl:262) */
-                bool enter = true;
-                for (uint32_t on = __float_as_uint(r7.y); on != 0xFFFFFFFFu; on = __ldg(s.octParent + on)) {
-                    const okrt_octree_node& node = s.octNodes[on];
-                    if (!(rayAndAABBDist(o, idirWorld, v3(node.boundingBox.min), v3(node.boundingBox.max)) < limit)) { enter = false; break; }
-                }
-                if (enter) {
-                    const float4 i0 = __ldg(rec), i1 = __ldg(rec + 1), i2 = __ldg(rec + 2);
-                    const float4 a0 = __ldg(rec + 3), a1 = __ldg(rec + 4), a2 = __ldg(rec + 5);
-                    V3 lo, ld, lidir;
-                    if (__float_as_uint(r6.w) & 1u) { lo = oI; ld = dn; lidir = idirN; }
-                    else {
-                        lo = mulPointRows(o, i0, i1, i2);
-                        ld = normalize(mulDirRows(d, i0, i1, i2));
-                        lidir = rcp3(ld);
-                    }
-                    /* the mesh's root box (RaytracerCS.hlsl:285 on the first popped node) */
-                    if (rayAndAABBDist(lo, lidir, v3(a0.w, a1.w, a2.w), v3(r6.x, r6.y, r6.z)) < limit) {
-                        stack[sp++] = EXIT_INSTANCE;
-                        ro = lo; rd = ld; ridir = lidir; t0 = a0; t1 = a1; t2 = a2;
-                        instIdx = __float_as_uint(r7.z);
-                        cur = __float_as_uint(r7.x);
-                        continue;
-                    }
-                }
             }
-            if (sp == 0) break;
-            cur = stack[--sp];
         }
+        if (sp == 0) break;
+        cur = stack[--sp];
     }
     return c.second < relaxedLimit(c.best);    /* ambiguous? */
 }
@@ -576,74 +591,115 @@ __device__ __forceinline__ uchar4 toUnorm8(float r, float g, float b, float a)
 }
 
 /* --------------------------------------------------------------- kernel
- * RaytracerCS::main (RaytracerCS.hlsl:421-537): one thread per pixel, 16x8 pixel tiles. */
+ * RaytracerCS::main (RaytracerCS.hlsl:421-537) as a persistent kernel.  The shader maps one thread to one
+ * pixel and lets it loop over its bounces; paths end after 1..maxBounces+1 segments, so most lanes of a
+ * warp idle while the longest path finishes.  Here a lane owns a PATH for as long as it lives and picks
+ * the next pixel as soon as it ends ("path regeneration"): warps stay full until the image runs out.
+ * Pixels are handed out in 16x8 tiles (one atomic per 128 pixels), lanes of a warp are refilled from the
+ * warp's current tile by ballot + prefix popcount.  Per-pixel results do not depend on which lane traced
+ * them: the seed is a function of (x, y, frame) only [Q3]. */
 constexpr int kTileW = 16, kTileH = 8;
+constexpr int kTilePixels = kTileW * kTileH;
+constexpr int kBlockThreads = 128;
 
-__global__ void __launch_bounds__(kTileW * kTileH)
+struct PathState {
+    V3 o, d, light, contribution;
+    uint32_t seed, pixel, bounce;       /* pixel = y * width + x */
+};
+
+template <bool kInstrumented>
+__global__ void __launch_bounds__(kBlockThreads)
 pathTraceKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ FrameParams fp)
 {
     const okrt_render_data& rd = fp.rd;
-    const uint32_t px = blockIdx.x * kTileW + (threadIdx.x % kTileW);
-    uint32_t py = blockIdx.y * kTileH + (threadIdx.x / kTileW);
-    if (fp.shardCount > 1u) {
-        /* blockIdx.y enumerates this rank's bands: local band b -> global band b*shardCount + rank */
-        const uint32_t rowInRank = py;
-        const uint32_t band = rowInRank / fp.bandRows;
-        py = (band * fp.shardCount + fp.shardRank) * fp.bandRows + rowInRank % fp.bandRows;
-    }
-    const bool active = px < fp.coveredW && py < fp.coveredH;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t laneMaskLt = (1u << lane) - 1u;
+    const uint32_t width = rd.textureDims[0];
+    const uint32_t numSpheres = rd.numSpheres < s.numSpheres ? rd.numSpheres : s.numSpheres;
+    const bool exactMode = fp.traversal == OKRT_TRAVERSAL_EXACT;
 
-    uint32_t segments = 0u, fallbacks = 0u;
-    if (active) {
-        /* [Q3] */
-        uint32_t seed = px + (py + 74813u) * rd.textureDims[0] * (fp.seedFrame + 1u);
+    uint32_t slotNext = 0u, slotEnd = 0u;     /* warp-uniform: unassigned pixel slots of the warp's current tile */
+    bool exhausted = false;                   /* warp-uniform: the tile queue is empty */
+    bool alive = false;
+    PathState ps;
+    ps.o = ps.d = ps.light = ps.contribution = v3(0.f, 0.f, 0.f); ps.seed = 0u; ps.pixel = 0u; ps.bounce = 0u;
+    uint32_t segments = 0u, fallbacks = 0u, pixels = 0u;
+    /* instrumentation (AOV tap, debug heat maps): only in the kInstrumented build of the kernel */
+    uint32_t bbCheckCount = 0u, triCheckCount = 0u, pathSegments = 0u, firstFlags = 0u;
+    Hit first; first.kind = 0u; first.idx = 0xFFFFFFFFu; first.tri = 0xFFFFFFFFu; first.u = first.v = 0.f; first.distance = OKRT_FLT_MAX;
 
-        /* createRay :177-206 [Q2] */
-        V3 pos = v3((float)px, (float)(rd.textureDims[1] - py), rd.cameraNearZ);
-        pos.x += randomFloat(seed) - 0.5f;
-        pos.y += randomFloat(seed) - 0.5f;
-        pos.x /= (float)rd.textureDims[0]; pos.y /= (float)rd.textureDims[1];
-        pos.x *= 2.f; pos.y *= 2.f;
-        pos.x -= 1.f; pos.y -= 1.f;
-        const float* ip = rd.cameraInverseProjectionMatrix;
-        const V3 target = mulPoint(pos, ip);
-        V3 o = v3(rd.cameraPosition);
-        V3 d = mulDir(normalize(v3(target.x / target.z, target.y / target.z, target.z / target.z)), rd.cameraInverseViewMatrix);
-
-        /* applyDOF :208-216 */
-        {
-            const V2 j = randomPointInCircle(seed);
-            const float jx = j.x * rd.dofStrength, jy = j.y * rd.dofStrength;
-            const V3 rayOffset = v3(rd.cameraRightDir) * jx + v3(rd.cameraUpDir) * jy;
-            const V3 focusPoint = o + d * (rd.dofDistance + rd.cameraNearZ);
-            o = o + rayOffset;
-            d = normalize(focusPoint - o);
+    for (;;) {
+        /* ---- refill dead lanes */
+        uint32_t dead = __ballot_sync(0xFFFFFFFFu, !alive);
+        while (dead != 0u && !exhausted) {
+            if (slotNext == slotEnd) {
+                uint32_t tile = 0u;
+                if (lane == 0u) tile = atomicAdd(fp.workCounter, 1u);
+                tile = __shfl_sync(0xFFFFFFFFu, tile, 0);
+                if (tile >= fp.numTiles) { exhausted = true; break; }
+                slotNext = tile * kTilePixels; slotEnd = slotNext + kTilePixels;
+            }
+            const uint32_t want = __popc(dead), avail = slotEnd - slotNext;
+            const uint32_t take = want < avail ? want : avail;
+            const uint32_t rank = __popc(dead & laneMaskLt);
+            if (!alive && rank < take) {
+                const uint32_t slot = slotNext + rank;
+                const uint32_t tile = slot / kTilePixels, j = slot % kTilePixels;
+                const uint32_t tileX = tile % fp.tilesX, tileRowLocal = tile / fp.tilesX;
+                /* tile sharding: this rank's k-th band is global band k*shardCount + shardRank */
+                const uint32_t tilesPerBand = fp.bandRows / kTileH;
+                const uint32_t tileRow = ((tileRowLocal / tilesPerBand) * fp.shardCount + fp.shardRank) * tilesPerBand + tileRowLocal % tilesPerBand;
+                const uint32_t px = tileX * kTileW + j % kTileW, py = tileRow * kTileH + j / kTileW;
+                if (px < fp.coveredW && py < fp.coveredH) {
+                    /* [Q3] seed, createRay :177-206 [Q2], applyDOF :208-216 */
+                    uint32_t seed = px + (py + 74813u) * width * (fp.seedFrame + 1u);
+                    V3 pos = v3((float)px, (float)(rd.textureDims[1] - py), rd.cameraNearZ);
+                    pos.x += randomFloat(seed) - 0.5f;
+                    pos.y += randomFloat(seed) - 0.5f;
+                    pos.x /= (float)rd.textureDims[0]; pos.y /= (float)rd.textureDims[1];
+                    pos.x *= 2.f; pos.y *= 2.f;
+                    pos.x -= 1.f; pos.y -= 1.f;
+                    const V3 target = mulPoint(pos, rd.cameraInverseProjectionMatrix);
+                    V3 o = v3(rd.cameraPosition);
+                    V3 d = mulDir(normalize(v3(target.x / target.z, target.y / target.z, target.z / target.z)), rd.cameraInverseViewMatrix);
+                    const V2 jit = randomPointInCircle(seed);
+                    const float jx = jit.x * rd.dofStrength, jy = jit.y * rd.dofStrength;
+                    const V3 rayOffset = v3(rd.cameraRightDir) * jx + v3(rd.cameraUpDir) * jy;
+                    const V3 focusPoint = o + d * (rd.dofDistance + rd.cameraNearZ);
+                    o = o + rayOffset;
+                    d = normalize(focusPoint - o);
+                    ps.o = o; ps.d = d; ps.seed = seed; ps.pixel = py * width + px; ps.bounce = 0u;
+                    ps.light = v3(0.f, 0.f, 0.f); ps.contribution = v3(1.f, 1.f, 1.f);
+                    alive = true; pixels++;
+                    if (kInstrumented) { bbCheckCount = 0u; triCheckCount = 0u; pathSegments = 0u; firstFlags = 0u; }
+                }
+            }
+            slotNext += take;
+            dead = __ballot_sync(0xFFFFFFFFu, !alive);
         }
+        if (__ballot_sync(0xFFFFFFFFu, alive) == 0u) break;
 
-        V3 light = v3(0.f, 0.f, 0.f);
-        V3 contribution = v3(1.f, 1.f, 1.f);
-        uint32_t bbCheckCount = 0u, triCheckCount = 0u;
-        const bool exactMode = fp.traversal == OKRT_TRAVERSAL_EXACT;
-        Hit first; first.kind = 0u; first.idx = 0xFFFFFFFFu; first.tri = 0xFFFFFFFFu; first.u = first.v = 0.f; first.distance = OKRT_FLT_MAX;
-        uint32_t firstFlags = 0u;
-
-        for (uint32_t i = 0; i <= fp.maxBounces; i++) {
+        if (alive) {
+            /* ---- one path segment: findClosestHit + lights + bounce, RaytracerCS.hlsl:444-514 */
+            const V3 o = ps.o, d = ps.d;
+            const uint32_t i = ps.bounce;
             Hit hit;
             bool usedFallback = false;
-            if (exactMode) traverseExact(s, rd.numSpheres < s.numSpheres ? rd.numSpheres : s.numSpheres, o, d, hit, bbCheckCount, triCheckCount);
-            else if (traverseFast(s, rd.numSpheres < s.numSpheres ? rd.numSpheres : s.numSpheres, o, d, hit)) {
+            if (exactMode) traverseExact(s, numSpheres, o, d, hit, bbCheckCount, triCheckCount);
+            else if (traverseFast(s, numSpheres, o, d, hit)) {
                 uint32_t bb = 0u, tc = 0u;
-                traverseExact(s, rd.numSpheres < s.numSpheres ? rd.numSpheres : s.numSpheres, o, d, hit, bb, tc);
+                traverseExact(s, numSpheres, o, d, hit, bb, tc);
                 usedFallback = true; fallbacks++;
             }
             segments++;
-            if (i == 0u) { first = hit; firstFlags = usedFallback ? 1u : 0u; }
+            if (kInstrumented) { pathSegments++; if (i == 0u) { first = hit; firstFlags = usedFallback ? 1u : 0u; } }
 
             const bool hitAny = hit.kind != 0u;
             Surface sf;
             if (hitAny) resolveHit(s, o, d, hit, sf);
             else { sf.worldNormal = v3(0.f, 0.f, 0.f); sf.worldPosition = v3(0.f, 0.f, 0.f); sf.material.transparency = 0.f; }
 
+            V3 light = ps.light, contribution = ps.contribution;
             /* lights :448-487 [Q11] */
             const uint32_t nPoint = rd.numPointLights < s.numPointLights ? rd.numPointLights : s.numPointLights;
             for (uint32_t p = 0u; p < nPoint; p++) {
@@ -654,7 +710,7 @@ pathTraceKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ F
             const uint32_t nSpot = rd.numSpotLights < s.numSpotLights ? rd.numSpotLights : s.numSpotLights;
             for (uint32_t q = 0u; q < nSpot; q++) {
                 const okrt_spot_light& sl = s.spotLights[q];
-                const V3 rayToLight = normalize((v3(sl.position) + getRandomVector(seed) * 0.01f) - o);
+                const V3 rayToLight = normalize((v3(sl.position) + getRandomVector(ps.seed) * 0.01f) - o);
                 const float cosTheta = dot(rayToLight, -v3(sl.direction));
                 if (cosTheta < sl.maxAngle) continue;
                 const V3 l = getLighting(o, d, hitAny, hit.distance, sf.material.transparency, sf.worldNormal, v3(sl.position), sl.radius, v3(sl.colour), sl.intensity);
@@ -670,63 +726,65 @@ pathTraceKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ F
                 light = light + ((v3(dl.colour) * dl.intensity) * contribution) * modifier;
             }
 
+            bool finished;
             if (!hitAny) {                                     /* :489-493 */
                 light = light + environmentLight(s, d) * contribution;
-                break;
+                finished = true;
+            } else {
+                const okrt_material& m = sf.material;          /* :495-513 [Q10] */
+                const float metallicFactor = (m.metallic * (1.f - m.roughness)) >= randomFloat(ps.seed) ? 1.f : 0.f;
+                const float specularFactor = (m.specular * (1.f - m.roughness)) >= randomFloat(ps.seed) ? 1.f : 0.f;
+                const float transparencyFactor = m.transparency >= randomFloat(ps.seed) ? 1.f : 0.f;
+                const V3 reflectDir = findReflectDirection(d, sf.worldNormal, m.roughness * (1.f - specularFactor), ps.seed);
+                const V3 refractDir = findTransparencyBounce(d, sf.worldNormal, m.indexOfRefraction, ps.seed);
+                const V3 bounceDir = normalize(lerp3(reflectDir, refractDir, transparencyFactor));
+                const V3 hitPoint = sf.worldPosition + bounceDir * 0.001f;
+                contribution = contribution * lerp3(v3(m.albedo), v3(1.f, 1.f, 1.f), metallicFactor);
+                light = light + ((v3(m.emissionColour) * m.emissionPower) * contribution) * (1.f - transparencyFactor);
+                ps.o = hitPoint; ps.d = bounceDir;
+                ps.bounce = i + 1u;
+                finished = ps.bounce > fp.maxBounces;
             }
+            ps.light = light; ps.contribution = contribution;
 
-            const okrt_material& m = sf.material;              /* :495-513 [Q10] */
-            const float metallicFactor = (m.metallic * (1.f - m.roughness)) >= randomFloat(seed) ? 1.f : 0.f;
-            const float specularFactor = (m.specular * (1.f - m.roughness)) >= randomFloat(seed) ? 1.f : 0.f;
-            const float transparencyFactor = m.transparency >= randomFloat(seed) ? 1.f : 0.f;
-
-            const V3 reflectDir = findReflectDirection(d, sf.worldNormal, m.roughness * (1.f - specularFactor), seed);
-            const V3 refractDir = findTransparencyBounce(d, sf.worldNormal, m.indexOfRefraction, seed);
-            const V3 bounceDir = normalize(lerp3(reflectDir, refractDir, transparencyFactor));
-            const V3 hitPoint = sf.worldPosition + bounceDir * 0.001f;
-
-            contribution = contribution * lerp3(v3(m.albedo), v3(1.f, 1.f, 1.f), metallicFactor);
-            light = light + ((v3(m.emissionColour) * m.emissionPower) * contribution) * (1.f - transparencyFactor);
-
-            o = hitPoint;
-            d = bounceDir;
-        }
-
-        /* debug heat maps :516-520 */
-        if (rd.debugMode == 1u)
-            light = bbCheckCount > rd.debugMaxCount ? v3(1.f, 0.f, 0.f) : v3(1.f, 1.f, 1.f) * ((float)bbCheckCount / (float)rd.debugMaxCount);
-        else if (rd.debugMode == 2u)
-            light = triCheckCount > rd.debugMaxCount ? v3(1.f, 0.f, 0.f) : v3(1.f, 1.f, 1.f) * ((float)triCheckCount / (float)rd.debugMaxCount);
-
-        /* accumulate + store :525-536 [Q14] */
-        const size_t pi = (size_t)py * rd.textureDims[0] + px;
-        float r, g, b, a;
-        if (rd.accumulationEnabled == 1u) {
-            float4 acc = fp.accumulation[pi];
-            acc.x += light.x; acc.y += light.y; acc.z += light.z; acc.w += 1.f;
-            fp.accumulation[pi] = acc;
-            const float n = (float)rd.numAccumulationFrames;
-            r = acc.x / n; g = acc.y / n; b = acc.z / n; a = acc.w / n;
-        } else { r = light.x; g = light.y; b = light.z; a = 1.f; }
-        fp.result[pi] = toUnorm8(r, g, b, a);
-
-        if (fp.aov) {
-            okrt_aov av;
-            av.hitKind = first.kind; av.hitIdx = first.idx; av.triIdx = first.kind == 2u ? first.tri : 0xFFFFFFFFu;
-            av.baryU = first.kind == 2u ? first.u : 0.f; av.baryV = first.kind == 2u ? first.v : 0.f;
-            av.distance = first.distance;
-            av.bbCheckCount = bbCheckCount; av.triCheckCount = triCheckCount;
-            av.numSegments = segments; av.flags = firstFlags;
-            av.radiance[0] = light.x; av.radiance[1] = light.y; av.radiance[2] = light.z; av.reserved = 0u;
-            fp.aov[pi] = av;
+            if (finished) {
+                if (kInstrumented) {                           /* debug heat maps :516-520 */
+                    if (rd.debugMode == 1u)
+                        light = bbCheckCount > rd.debugMaxCount ? v3(1.f, 0.f, 0.f) : v3(1.f, 1.f, 1.f) * ((float)bbCheckCount / (float)rd.debugMaxCount);
+                    else if (rd.debugMode == 2u)
+                        light = triCheckCount > rd.debugMaxCount ? v3(1.f, 0.f, 0.f) : v3(1.f, 1.f, 1.f) * ((float)triCheckCount / (float)rd.debugMaxCount);
+                }
+                /* accumulate + store :525-536 [Q14] */
+                const size_t pi = ps.pixel;
+                float r, g, b, a;
+                if (rd.accumulationEnabled == 1u) {
+                    float4 acc = fp.accumulation[pi];
+                    acc.x += light.x; acc.y += light.y; acc.z += light.z; acc.w += 1.f;
+                    fp.accumulation[pi] = acc;
+                    const float n = (float)rd.numAccumulationFrames;
+                    r = acc.x / n; g = acc.y / n; b = acc.z / n; a = acc.w / n;
+                } else { r = light.x; g = light.y; b = light.z; a = 1.f; }
+                fp.result[pi] = toUnorm8(r, g, b, a);
+                if (kInstrumented && fp.aov) {
+                    okrt_aov av;
+                    av.hitKind = first.kind; av.hitIdx = first.idx; av.triIdx = first.kind == 2u ? first.tri : 0xFFFFFFFFu;
+                    av.baryU = first.kind == 2u ? first.u : 0.f; av.baryV = first.kind == 2u ? first.v : 0.f;
+                    av.distance = first.distance;
+                    av.bbCheckCount = bbCheckCount; av.triCheckCount = triCheckCount;
+                    av.numSegments = pathSegments; av.flags = firstFlags;
+                    av.radiance[0] = light.x; av.radiance[1] = light.y; av.radiance[2] = light.z; av.reserved = 0u;
+                    fp.aov[pi] = av;
+                }
+                alive = false;
+            }
         }
     }
 
     /* ray counters: one atomic per warp */
     const uint32_t segSum = __reduce_add_sync(0xFFFFFFFFu, segments);
     const uint32_t fbSum = __reduce_add_sync(0xFFFFFFFFu, fallbacks);
-    const uint32_t pxSum = __reduce_add_sync(0xFFFFFFFFu, active ? 1u : 0u);
-    if ((threadIdx.x & 31u) == 0u && pxSum) {
+    const uint32_t pxSum = __reduce_add_sync(0xFFFFFFFFu, pixels);
+    if (lane == 0u && pxSum) {
         atomicAdd(fp.counters + 0, (unsigned long long)segSum);
         if (fbSum) atomicAdd(fp.counters + 1, (unsigned long long)fbSum);
         atomicAdd(fp.counters + 2, (unsigned long long)pxSum);
