@@ -19,6 +19,7 @@
 #include "okrt_accel.h"
 #include "okrt_internal.h"
 #include "okrt_kernels.cuh"
+#include "okrt_wavefront.cuh"
 
 using namespace okrt;
 
@@ -132,6 +133,9 @@ struct okrt_renderer {
     uint64_t launches = 0;
     float lastRenderMs = 0.f;
     int numSms = 0, blocksPerSmLean = 1, blocksPerSmInstrumented = 1;   /* persistent grid = SMs x resident blocks */
+    int blocksPerSmTrace = 1;
+    WavefrontBuffers wb{};                      /* path state of the wavefront pipeline (sized for width x height) */
+    size_t wbPaths = 0;
 };
 
 namespace {
@@ -223,6 +227,56 @@ void coveredExtent(const okrt_renderer* r, uint32_t& cw, uint32_t& ch)
     ch = r->opt.coverAllPixels ? r->height : 9u * (r->height / 9u);
 }
 
+void freeWavefront(okrt_renderer* r)
+{
+    void* ptrs[] = {r->wb.rayO, r->wb.rayD, r->wb.radiance, r->wb.throughput, r->wb.hitA, r->wb.hitB, r->wb.queue[0], r->wb.queue[1], r->wb.counts};
+    for (void* p : ptrs) if (p) cudaFree(p);
+    std::memset(&r->wb, 0, sizeof(r->wb));
+    r->wbPaths = 0;
+}
+
+int ensureWavefront(okrt_renderer* r, size_t paths)
+{
+    if (r->wbPaths >= paths && r->wb.counts) return OKRT_OK;
+    freeWavefront(r);
+    OKRT_CUDA(cudaMalloc(&r->wb.rayO, paths * sizeof(float4)));
+    OKRT_CUDA(cudaMalloc(&r->wb.rayD, paths * sizeof(float4)));
+    OKRT_CUDA(cudaMalloc(&r->wb.radiance, paths * sizeof(float4)));
+    OKRT_CUDA(cudaMalloc(&r->wb.throughput, paths * sizeof(float4)));
+    OKRT_CUDA(cudaMalloc(&r->wb.hitA, paths * sizeof(float4)));
+    OKRT_CUDA(cudaMalloc(&r->wb.hitB, paths * sizeof(uint32_t)));
+    OKRT_CUDA(cudaMalloc(&r->wb.queue[0], paths * sizeof(uint32_t)));
+    OKRT_CUDA(cudaMalloc(&r->wb.queue[1], paths * sizeof(uint32_t)));
+    OKRT_CUDA(cudaMalloc(&r->wb.counts, kMaxQueueCounts * sizeof(uint32_t)));
+    r->wbPaths = paths;
+    return OKRT_OK;
+}
+
+/* generate -> (trace, shade) x (maxBounces + 1); queue sizes stay on the device, nothing syncs with the host */
+int launchWavefront(okrt_renderer* r, const FrameParams& fp, bool instrumented)
+{
+    const size_t paths = (size_t)fp.numTiles * kTilePixels;
+    int rc = ensureWavefront(r, paths);
+    if (rc) return rc;
+    const DeviceScene scene = sceneView(r);
+    OKRT_CUDA(cudaMemsetAsync(r->wb.counts, 0, kMaxQueueCounts * sizeof(uint32_t), r->stream));
+    const unsigned flatGrid = (unsigned)((paths + 127) / 128);
+    generateKernel<<<flatGrid, 128, 0, r->stream>>>(fp, r->wb);
+    r->launches++;
+    const unsigned traceGrid = std::min<unsigned>((unsigned)(r->numSms * r->blocksPerSmTrace), std::max(1u, flatGrid));
+    for (uint32_t b = 0; b <= fp.maxBounces; b++) {
+        const uint32_t* qin = b == 0u ? nullptr : r->wb.queue[(b - 1u) & 1u];
+        uint32_t* qout = r->wb.queue[b & 1u];
+        if (fp.traversal == OKRT_TRAVERSAL_EXACT) traceExactKernel<<<flatGrid, 128, 0, r->stream>>>(scene, fp, r->wb, qin, b);
+        else traceFastKernel<<<traceGrid, kTraceBlockThreads, 0, r->stream>>>(scene, fp, r->wb, qin, b);
+        if (instrumented) shadeKernel<true><<<flatGrid, 128, 0, r->stream>>>(scene, fp, r->wb, qin, qout, b);
+        else shadeKernel<false><<<flatGrid, 128, 0, r->stream>>>(scene, fp, r->wb, qin, qout, b);
+        r->launches += 2;
+    }
+    OKRT_CUDA(cudaGetLastError());
+    return OKRT_OK;
+}
+
 int launchFrame(okrt_renderer* r)
 {
     /* updateBuffers: the counter advances before the constants are uploaded (RayTracer.cpp:489) */
@@ -242,7 +296,10 @@ int launchFrame(okrt_renderer* r)
     coveredExtent(r, fp.coveredW, fp.coveredH);
     fp.accumulation = r->accumulation;
     fp.result = r->result;
-    fp.aov = r->opt.writeAov ? r->aov : nullptr;
+    /* AOV taps and the debug heat maps (which display the reference's visit counters) are instrumented builds */
+    const bool instrumented = r->opt.writeAov != 0u || r->rd.debugMode != 0u;
+    if (instrumented) { const int rcA = ensureAov(r); if (rcA) return rcA; }
+    fp.aov = instrumented ? r->aov : nullptr;
     fp.counters = r->counters;
 
     uint32_t rows = r->height;
@@ -262,8 +319,7 @@ int launchFrame(okrt_renderer* r)
     fp.numTiles = fp.tilesX * ((rows + kTileH - 1) / kTileH);
     fp.workCounter = reinterpret_cast<uint32_t*>(r->counters + 3);
     OKRT_CUDA(cudaMemsetAsync(fp.workCounter, 0, sizeof(unsigned long long), r->stream));
-    /* AOV taps and the debug heat maps live in the instrumented build of the kernel */
-    const bool instrumented = fp.aov != nullptr || r->rd.debugMode != 0u;
+    if (r->opt.pipeline == OKRT_PIPELINE_WAVEFRONT && fp.maxBounces <= kMaxWavefrontBounces) return launchWavefront(r, fp, instrumented);
     const int blocksPerSm = instrumented ? r->blocksPerSmInstrumented : r->blocksPerSmLean;
     const unsigned wantBlocks = (unsigned)((fp.numTiles * (uint32_t)kTilePixels + kBlockThreads - 1) / kBlockThreads);
     const unsigned grid = std::min<unsigned>((unsigned)(r->numSms * blocksPerSm), std::max(1u, wantBlocks));
@@ -318,7 +374,8 @@ int okrt_create(int device, uint32_t width, uint32_t height, okrt_renderer** out
     cudaDeviceProp prop;
     if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess ||
         (e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&r->blocksPerSmLean, pathTraceKernel<false>, kBlockThreads, 0)) != cudaSuccess ||
-        (e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&r->blocksPerSmInstrumented, pathTraceKernel<true>, kBlockThreads, 0)) != cudaSuccess) {
+        (e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&r->blocksPerSmInstrumented, pathTraceKernel<true>, kBlockThreads, 0)) != cudaSuccess ||
+        (e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&r->blocksPerSmTrace, traceFastKernel, kTraceBlockThreads, 0)) != cudaSuccess) {
         setError(std::string("okrt_create: ") + cudaGetErrorString(e));
         okrt_destroy(r);
         return OKRT_ERR_CUDA;
@@ -326,6 +383,7 @@ int okrt_create(int device, uint32_t width, uint32_t height, okrt_renderer** out
     r->numSms = prop.multiProcessorCount;
     r->blocksPerSmLean = std::max(1, r->blocksPerSmLean);
     r->blocksPerSmInstrumented = std::max(1, r->blocksPerSmInstrumented);
+    r->blocksPerSmTrace = std::max(1, r->blocksPerSmTrace);
     const int rc = allocateImages(r);
     if (rc) { okrt_destroy(r); return rc; }
     *out = r;
@@ -345,6 +403,7 @@ void okrt_destroy(okrt_renderer* r)
     if (r->result) cudaFree(r->result);
     if (r->aov) cudaFree(r->aov);
     if (r->counters) cudaFree(r->counters);
+    freeWavefront(r);
     if (r->evStart) cudaEventDestroy(r->evStart);
     if (r->evStop) cudaEventDestroy(r->evStop);
     if (r->stream) cudaStreamDestroy(r->stream);
@@ -463,7 +522,7 @@ int okrt_get_render_data(const okrt_renderer* r, okrt_render_data* out)
 int okrt_set_options(okrt_renderer* r, const okrt_options* o)
 {
     if (!r || !o) { setError("okrt_set_options: null argument"); return OKRT_ERR_INVALID_ARGUMENT; }
-    if (o->traversal > OKRT_TRAVERSAL_EXACT || o->shardMode > OKRT_SHARD_TILE) { setError("okrt_set_options: unknown mode"); return OKRT_ERR_INVALID_ARGUMENT; }
+    if (o->traversal > OKRT_TRAVERSAL_EXACT || o->shardMode > OKRT_SHARD_TILE || o->pipeline > OKRT_PIPELINE_MEGAKERNEL) { setError("okrt_set_options: unknown mode"); return OKRT_ERR_INVALID_ARGUMENT; }
     if (o->shardMode == OKRT_SHARD_TILE && (o->shardCount == 0u || o->shardRank >= o->shardCount)) { setError("okrt_set_options: shardRank/shardCount"); return OKRT_ERR_INVALID_ARGUMENT; }
     if (o->shardBandRows % kTileH) { setError("okrt_set_options: shardBandRows must be a multiple of 8"); return OKRT_ERR_INVALID_ARGUMENT; }
     const bool coverageChanged = (r->opt.coverAllPixels != 0u) != (o->coverAllPixels != 0u);

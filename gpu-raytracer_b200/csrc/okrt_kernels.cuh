@@ -590,6 +590,73 @@ __device__ __forceinline__ uchar4 toUnorm8(float r, float g, float b, float a)
                        (unsigned char)(saturate(b) * 255.0f + 0.5f), (unsigned char)(saturate(a) * 255.0f + 0.5f));
 }
 
+/* ------------------------------------------------------ one path segment
+ * Everything RaytracerCS::main does between two findClosestHit calls (RaytracerCS.hlsl:448-513): lights,
+ * miss -> environment, lobe pick, bounce.  Shared by the wavefront shade kernel and the megakernel. */
+struct PathState {
+    V3 o, d, light, contribution;
+    uint32_t seed, pixel, bounce;       /* pixel = y * width + x */
+};
+
+__device__ __forceinline__ bool shadeSegment(const DeviceScene& s, const okrt_render_data& rd, uint32_t maxBounces, const Hit& hit, PathState& ps)
+{
+    const V3 o = ps.o, d = ps.d;
+    const uint32_t i = ps.bounce;
+    const bool hitAny = hit.kind != 0u;
+    Surface sf;
+    if (hitAny) resolveHit(s, o, d, hit, sf);
+    else { sf.worldNormal = v3(0.f, 0.f, 0.f); sf.worldPosition = v3(0.f, 0.f, 0.f); sf.material.transparency = 0.f; }
+
+    V3 light = ps.light, contribution = ps.contribution;
+    /* lights :448-487 [Q11] */
+    const uint32_t nPoint = rd.numPointLights < s.numPointLights ? rd.numPointLights : s.numPointLights;
+    for (uint32_t p = 0u; p < nPoint; p++) {
+        const okrt_point_light& pl = s.pointLights[p];
+        const V3 l = getLighting(o, d, hitAny, hit.distance, sf.material.transparency, sf.worldNormal, v3(pl.position), pl.radius, v3(pl.colour), pl.intensity);
+        light = light + l * contribution;
+    }
+    const uint32_t nSpot = rd.numSpotLights < s.numSpotLights ? rd.numSpotLights : s.numSpotLights;
+    for (uint32_t q = 0u; q < nSpot; q++) {
+        const okrt_spot_light& sl = s.spotLights[q];
+        const V3 rayToLight = normalize((v3(sl.position) + getRandomVector(ps.seed) * 0.01f) - o);
+        const float cosTheta = dot(rayToLight, -v3(sl.direction));
+        if (cosTheta < sl.maxAngle) continue;
+        const V3 l = getLighting(o, d, hitAny, hit.distance, sf.material.transparency, sf.worldNormal, v3(sl.position), sl.radius, v3(sl.colour), sl.intensity);
+        light = light + l * contribution;
+    }
+    const uint32_t nDir = rd.numDirLights < s.numDirLights ? rd.numDirLights : s.numDirLights;
+    for (uint32_t q = 0u; q < nDir; q++) {
+        const okrt_directional_light& dl = s.dirLights[q];
+        if (clampedDot(d, -v3(dl.direction)) < dl.effectiveAngle) continue;
+        float modifier = 1.f;
+        if (hitAny && i) modifier *= sf.material.transparency * clampedDot(d, -sf.worldNormal);
+        else if (!i) modifier = 0.f;
+        light = light + ((v3(dl.colour) * dl.intensity) * contribution) * modifier;
+    }
+
+    bool finished;
+    if (!hitAny) {                                     /* :489-493 */
+        light = light + environmentLight(s, d) * contribution;
+        finished = true;
+    } else {
+        const okrt_material& m = sf.material;          /* :495-513 [Q10] */
+        const float metallicFactor = (m.metallic * (1.f - m.roughness)) >= randomFloat(ps.seed) ? 1.f : 0.f;
+        const float specularFactor = (m.specular * (1.f - m.roughness)) >= randomFloat(ps.seed) ? 1.f : 0.f;
+        const float transparencyFactor = m.transparency >= randomFloat(ps.seed) ? 1.f : 0.f;
+        const V3 reflectDir = findReflectDirection(d, sf.worldNormal, m.roughness * (1.f - specularFactor), ps.seed);
+        const V3 refractDir = findTransparencyBounce(d, sf.worldNormal, m.indexOfRefraction, ps.seed);
+        const V3 bounceDir = normalize(lerp3(reflectDir, refractDir, transparencyFactor));
+        const V3 hitPoint = sf.worldPosition + bounceDir * 0.001f;
+        contribution = contribution * lerp3(v3(m.albedo), v3(1.f, 1.f, 1.f), metallicFactor);
+        light = light + ((v3(m.emissionColour) * m.emissionPower) * contribution) * (1.f - transparencyFactor);
+        ps.o = hitPoint; ps.d = bounceDir;
+        ps.bounce = i + 1u;
+        finished = ps.bounce > maxBounces;
+    }
+    ps.light = light; ps.contribution = contribution;
+    return finished;
+}
+
 /* --------------------------------------------------------------- kernel
  * RaytracerCS::main (RaytracerCS.hlsl:421-537) as a persistent kernel.  The shader maps one thread to one
  * pixel and lets it loop over its bounces; paths end after 1..maxBounces+1 segments, so most lanes of a
@@ -601,11 +668,6 @@ __device__ __forceinline__ uchar4 toUnorm8(float r, float g, float b, float a)
 constexpr int kTileW = 16, kTileH = 8;
 constexpr int kTilePixels = kTileW * kTileH;
 constexpr int kBlockThreads = 128;
-
-struct PathState {
-    V3 o, d, light, contribution;
-    uint32_t seed, pixel, bounce;       /* pixel = y * width + x */
-};
 
 template <bool kInstrumented>
 __global__ void __launch_bounds__(kBlockThreads)
@@ -694,58 +756,8 @@ pathTraceKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ F
             segments++;
             if (kInstrumented) { pathSegments++; if (i == 0u) { first = hit; firstFlags = usedFallback ? 1u : 0u; } }
 
-            const bool hitAny = hit.kind != 0u;
-            Surface sf;
-            if (hitAny) resolveHit(s, o, d, hit, sf);
-            else { sf.worldNormal = v3(0.f, 0.f, 0.f); sf.worldPosition = v3(0.f, 0.f, 0.f); sf.material.transparency = 0.f; }
-
-            V3 light = ps.light, contribution = ps.contribution;
-            /* lights :448-487 [Q11] */
-            const uint32_t nPoint = rd.numPointLights < s.numPointLights ? rd.numPointLights : s.numPointLights;
-            for (uint32_t p = 0u; p < nPoint; p++) {
-                const okrt_point_light& pl = s.pointLights[p];
-                const V3 l = getLighting(o, d, hitAny, hit.distance, sf.material.transparency, sf.worldNormal, v3(pl.position), pl.radius, v3(pl.colour), pl.intensity);
-                light = light + l * contribution;
-            }
-            const uint32_t nSpot = rd.numSpotLights < s.numSpotLights ? rd.numSpotLights : s.numSpotLights;
-            for (uint32_t q = 0u; q < nSpot; q++) {
-                const okrt_spot_light& sl = s.spotLights[q];
-                const V3 rayToLight = normalize((v3(sl.position) + getRandomVector(ps.seed) * 0.01f) - o);
-                const float cosTheta = dot(rayToLight, -v3(sl.direction));
-                if (cosTheta < sl.maxAngle) continue;
-                const V3 l = getLighting(o, d, hitAny, hit.distance, sf.material.transparency, sf.worldNormal, v3(sl.position), sl.radius, v3(sl.colour), sl.intensity);
-                light = light + l * contribution;
-            }
-            const uint32_t nDir = rd.numDirLights < s.numDirLights ? rd.numDirLights : s.numDirLights;
-            for (uint32_t q = 0u; q < nDir; q++) {
-                const okrt_directional_light& dl = s.dirLights[q];
-                if (clampedDot(d, -v3(dl.direction)) < dl.effectiveAngle) continue;
-                float modifier = 1.f;
-                if (hitAny && i) modifier *= sf.material.transparency * clampedDot(d, -sf.worldNormal);
-                else if (!i) modifier = 0.f;
-                light = light + ((v3(dl.colour) * dl.intensity) * contribution) * modifier;
-            }
-
-            bool finished;
-            if (!hitAny) {                                     /* :489-493 */
-                light = light + environmentLight(s, d) * contribution;
-                finished = true;
-            } else {
-                const okrt_material& m = sf.material;          /* :495-513 [Q10] */
-                const float metallicFactor = (m.metallic * (1.f - m.roughness)) >= randomFloat(ps.seed) ? 1.f : 0.f;
-                const float specularFactor = (m.specular * (1.f - m.roughness)) >= randomFloat(ps.seed) ? 1.f : 0.f;
-                const float transparencyFactor = m.transparency >= randomFloat(ps.seed) ? 1.f : 0.f;
-                const V3 reflectDir = findReflectDirection(d, sf.worldNormal, m.roughness * (1.f - specularFactor), ps.seed);
-                const V3 refractDir = findTransparencyBounce(d, sf.worldNormal, m.indexOfRefraction, ps.seed);
-                const V3 bounceDir = normalize(lerp3(reflectDir, refractDir, transparencyFactor));
-                const V3 hitPoint = sf.worldPosition + bounceDir * 0.001f;
-                contribution = contribution * lerp3(v3(m.albedo), v3(1.f, 1.f, 1.f), metallicFactor);
-                light = light + ((v3(m.emissionColour) * m.emissionPower) * contribution) * (1.f - transparencyFactor);
-                ps.o = hitPoint; ps.d = bounceDir;
-                ps.bounce = i + 1u;
-                finished = ps.bounce > fp.maxBounces;
-            }
-            ps.light = light; ps.contribution = contribution;
+            const bool finished = shadeSegment(s, rd, fp.maxBounces, hit, ps);
+            V3 light = ps.light;
 
             if (finished) {
                 if (kInstrumented) {                           /* debug heat maps :516-520 */

@@ -1,0 +1,392 @@
+/*
+ * okrt_wavefront.cuh — the wavefront form of RaytracerCS::main (RaytracerCS.hlsl:421-537).
+ *
+ * The shader is a megakernel: one thread per pixel loops over bounces, and inside each bounce over BVH
+ * nodes.  On a 32-wide SIMT machine both loops diverge: ncu on the persistent megakernel of this repo
+ * (profiles/r1_b_*) shows ~10 of 32 lanes active in the node loop, because a warp waits for its slowest
+ * ray before any lane can shade and start its next segment.  The wavefront form removes that coupling:
+ *
+ *   generate  : one thread per pixel -> primary ray + path state in HBM (64 B per path)
+ *   per bounce: trace  — persistent warps pull rays from a queue; a lane whose ray is finished writes its
+ *                        hit record (20 B) and immediately pulls the next ray (ballot/popc refill), so the
+ *                        traversal loop always runs with (nearly) full warps;
+ *               shade  — one thread per queued path: hit resolve, lights, environment, lobe pick, bounce;
+ *                        surviving paths are appended to the next queue by warp-aggregated atomics,
+ *                        finished paths accumulate into u1 and store u0.
+ *
+ * Per-path arithmetic is the same code as the megakernel (traverseExact / the fast traversal's box and
+ * triangle tests / shadeSegment), so results are bit-identical between the two pipelines and the oracle.
+ * Path state traffic: (64 B read + 64 B write + 2 x 20 B hit) per segment ~ 1.5 GB per 1080p frame,
+ * i.e. ~0.25 ms of HBM time against several ms of traversal.
+ */
+#pragma once
+#include "okrt_kernels.cuh"
+
+namespace okrt {
+
+struct WavefrontBuffers {
+    float4* rayO;          /* o.xyz, bits(seed) */
+    float4* rayD;          /* d.xyz, bits(pixel index) */
+    float4* radiance;      /* light.xyz, bits(bounce) */
+    float4* throughput;    /* contribution.xyz, unused */
+    float4* hitA;          /* distance, u, v, bits(triangle) */
+    uint32_t* hitB;        /* kind << 30 | instance-or-sphere index */
+    uint32_t* queue[2];    /* ping-pong queues of path slots */
+    uint32_t* counts;      /* [2*bounce] number of queued paths, [2*bounce+1] trace work counter; zeroed per frame */
+};
+constexpr uint32_t kMaxWavefrontBounces = 63;
+constexpr uint32_t kMaxQueueCounts = 2 * (kMaxWavefrontBounces + 2);
+constexpr int kTraceBlockThreads = 128;
+constexpr uint32_t kTraceChunk = 64;         /* rays a warp claims per atomic */
+
+/* ---------------------------------------------------------------- generate
+ * [Q3] seed, createRay :177-206 [Q2], applyDOF :208-216.  Slot order = 16x8 tile order of this rank's tiles. */
+__global__ void __launch_bounds__(128)
+generateKernel(const __grid_constant__ FrameParams fp, const WavefrontBuffers wb)
+{
+    const okrt_render_data& rd = fp.rd;
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t tile = slot / kTilePixels, j = slot % kTilePixels;
+    if (tile >= fp.numTiles) return;
+    const uint32_t tileX = tile % fp.tilesX, tileRowLocal = tile / fp.tilesX;
+    const uint32_t tilesPerBand = fp.bandRows / kTileH;
+    const uint32_t tileRow = ((tileRowLocal / tilesPerBand) * fp.shardCount + fp.shardRank) * tilesPerBand + tileRowLocal % tilesPerBand;
+    const uint32_t px = tileX * kTileW + j % kTileW, py = tileRow * kTileH + j / kTileW;
+    const bool covered = px < fp.coveredW && py < fp.coveredH;
+
+    /* compact covered pixels into queue 0 (keeps tile order inside a warp) */
+    const uint32_t mask = __ballot_sync(0xFFFFFFFFu, covered);
+    uint32_t base = 0u;
+    if ((threadIdx.x & 31u) == 0u && mask) base = atomicAdd(wb.counts + 0, (uint32_t)__popc(mask));
+    base = __shfl_sync(0xFFFFFFFFu, base, 0);
+    if (!covered) return;
+    const uint32_t path = base + __popc(mask & ((1u << (threadIdx.x & 31u)) - 1u));
+
+    const uint32_t width = rd.textureDims[0];
+    uint32_t seed = px + (py + 74813u) * width * (fp.seedFrame + 1u);
+    V3 pos = v3((float)px, (float)(rd.textureDims[1] - py), rd.cameraNearZ);
+    pos.x += randomFloat(seed) - 0.5f;
+    pos.y += randomFloat(seed) - 0.5f;
+    pos.x /= (float)rd.textureDims[0]; pos.y /= (float)rd.textureDims[1];
+    pos.x *= 2.f; pos.y *= 2.f;
+    pos.x -= 1.f; pos.y -= 1.f;
+    const V3 target = mulPoint(pos, rd.cameraInverseProjectionMatrix);
+    V3 o = v3(rd.cameraPosition);
+    V3 d = mulDir(normalize(v3(target.x / target.z, target.y / target.z, target.z / target.z)), rd.cameraInverseViewMatrix);
+    const V2 jit = randomPointInCircle(seed);
+    const float jx = jit.x * rd.dofStrength, jy = jit.y * rd.dofStrength;
+    const V3 rayOffset = v3(rd.cameraRightDir) * jx + v3(rd.cameraUpDir) * jy;
+    const V3 focusPoint = o + d * (rd.dofDistance + rd.cameraNearZ);
+    o = o + rayOffset;
+    d = normalize(focusPoint - o);
+
+    wb.rayO[path] = make_float4(o.x, o.y, o.z, __uint_as_float(seed));
+    wb.rayD[path] = make_float4(d.x, d.y, d.z, __uint_as_float(py * width + px));
+    wb.radiance[path] = make_float4(0.f, 0.f, 0.f, __uint_as_float(0u));
+    wb.throughput[path] = make_float4(1.f, 1.f, 1.f, 0.f);
+    if (fp.aov) {
+        okrt_aov av;
+        av.hitKind = 0u; av.hitIdx = 0xFFFFFFFFu; av.triIdx = 0xFFFFFFFFu; av.baryU = 0.f; av.baryV = 0.f; av.distance = OKRT_FLT_MAX;
+        av.bbCheckCount = 0u; av.triCheckCount = 0u; av.numSegments = 0u; av.flags = 0u;
+        av.radiance[0] = av.radiance[1] = av.radiance[2] = 0.f; av.reserved = 0u;
+        fp.aov[py * width + px] = av;
+    }
+}
+
+/* ------------------------------------------------------------------- trace
+ * Reference-order traversal (debug counters, scaled instances, forced exact mode): one thread per ray. */
+__global__ void __launch_bounds__(128)
+traceExactKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ FrameParams fp, const WavefrontBuffers wb,
+                 const uint32_t* __restrict__ queueIn, uint32_t bounce)
+{
+    const uint32_t count = wb.counts[2u * bounce];
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= count) return;
+    const uint32_t path = queueIn ? queueIn[k] : k;
+    const float4 ro = wb.rayO[path], rdv = wb.rayD[path];
+    const uint32_t numSpheres = fp.rd.numSpheres < s.numSpheres ? fp.rd.numSpheres : s.numSpheres;
+    Hit hit;
+    uint32_t bb = 0u, tc = 0u;
+    traverseExact(s, numSpheres, v3(ro.x, ro.y, ro.z), v3(rdv.x, rdv.y, rdv.z), hit, bb, tc);
+    wb.hitA[path] = make_float4(hit.distance, hit.u, hit.v, __uint_as_float(hit.tri));
+    wb.hitB[path] = (hit.kind << 30) | (hit.idx & 0x3FFFFFFFu);
+    if (fp.aov) {
+        okrt_aov* av = fp.aov + __float_as_uint(rdv.w);
+        av->bbCheckCount += bb; av->triCheckCount += tc;
+    }
+}
+
+/* Near-first traversal with lane refill.  Same tests and arithmetic as traverseFast (okrt_kernels.cuh); the
+ * traversal state lives across refills so that a lane can start its next ray while its neighbours are still
+ * walking theirs. */
+struct TraceLane {
+    V3 o, d;                 /* world ray */
+    V3 ro, rd, ridir;        /* current ray (local inside an instance) */
+    float best, second;
+    uint32_t hitKindIdx, hitTri;
+    float hitU, hitV;
+    uint32_t cur;
+    int sp;
+    uint32_t inst;           /* instance record index, bit 31 = identity transform; 0xFFFFFFFF at the top level */
+    unsigned long long octTested, octHit;
+    uint32_t path;
+};
+
+constexpr uint32_t kTraceDone = 0xFFFFFFFDu;
+constexpr uint32_t kTraceExitInstance = 0xFFFFFFFEu;
+
+__device__ __forceinline__ void laneCandidate(TraceLane& L, float t, uint32_t kindIdx, uint32_t tri, float u, float v)
+{
+    if (t < L.best) { L.second = L.best; L.best = t; L.hitKindIdx = kindIdx; L.hitTri = tri; L.hitU = u; L.hitV = v; }
+    else if (t < L.second) L.second = t;
+}
+
+/* one round of the while-while loop: interior nodes until a leaf comes up, then that leaf */
+__device__ __forceinline__ void traceRound(const DeviceScene& s, TraceLane& L, uint32_t* stack)
+{
+    uint32_t cur = L.cur;
+    int sp = L.sp;
+    while ((cur & kRefTagMask) == kRefInterior) {
+        const float4* q = s.fastNodes + (size_t)cur * 4;
+        const float4 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3);
+        const float limit = relaxedLimit(L.best);
+        const float n0 = rayAndAABBDist(L.ro, L.ridir, v3(q0.x, q0.y, q0.z), v3(q1.x, q1.y, q1.z));
+        const float n1 = rayAndAABBDist(L.ro, L.ridir, v3(q2.x, q2.y, q2.z), v3(q3.x, q3.y, q3.z));
+        const uint32_t r0 = __float_as_uint(q0.w), r1 = __float_as_uint(q1.w);
+        const bool h0 = n0 < limit && r0 != kRefNone;
+        const bool h1 = n1 < limit && r1 != kRefNone;
+        if (h0 && h1) {
+            const bool firstIs1 = n1 < n0;
+            stack[sp++] = firstIs1 ? r0 : r1;
+            cur = firstIs1 ? r1 : r0;
+        } else if (h0) cur = r0;
+        else if (h1) cur = r1;
+        else cur = sp ? stack[--sp] : kTraceDone;
+    }
+    if (cur != kTraceDone) {
+        bool pop = true;
+        if ((cur & kRefTagMask) == kRefTriLeaf) {
+            const uint32_t first = cur & (kMaxTriIndex - 1u);
+            const uint32_t count = ((cur >> 27) & 7u) + 1u;
+            for (uint32_t j = first; j < first + count; j++) {
+                const float4* tp = s.fastTris + (size_t)j * 3;
+                const float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
+                float bu = 0.f, bv = 0.f;
+                float t = rayAndTriangle(L.ro, L.rd, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), bu, bv);
+                if (t <= 0.f) continue;
+                V3 w = L.rd * t;                                        /* RaytracerCS.hlsl:312-314 */
+                if (!(L.inst & 0x80000000u)) {                           /* T == I maps w to itself */
+                    const float4* rec = s.fastInstances + (size_t)L.inst * 8;
+                    w = mulDirRows(w, __ldg(rec + 3), __ldg(rec + 4), __ldg(rec + 5));
+                }
+                t = length(w);
+                const uint32_t instRef = __float_as_uint(__ldg(s.fastInstances + (size_t)(L.inst & 0x7FFFFFFFu) * 8 + 7).z);
+                laneCandidate(L, t, (2u << 30) | instRef, j, bu, bv);
+            }
+        } else if (cur == kTraceExitInstance) {
+            L.ro = L.o; L.rd = L.d; L.ridir = rcp3(L.d); L.inst = 0xFFFFFFFFu;
+        } else {                                                         /* instance leaf */
+            const uint32_t recIdx = cur & ~kRefTagMask;
+            const float4* rec = s.fastInstances + (size_t)recIdx * 8;
+            const float4 r6 = __ldg(rec + 6), r7 = __ldg(rec + 7);
+            const V3 idirWorld = L.ridir;                                /* top level: current ray is the world ray */
+            bool enter = true;
+            for (uint32_t on = __float_as_uint(r7.y); on != 0xFFFFFFFFu; on = __ldg(s.octParent + on)) {
+                bool boxHit;
+                const unsigned long long bit = 1ull << (on & 63u);
+                if (on < 64u && (L.octTested & bit)) boxHit = (L.octHit & bit) != 0ull;
+                else {
+                    const okrt_octree_node& node = s.octNodes[on];
+                    boxHit = rayAndAABBDist(L.o, idirWorld, v3(node.boundingBox.min), v3(node.boundingBox.max)) < OKRT_FLT_MAX;
+                    if (on < 64u) { L.octTested |= bit; if (boxHit) L.octHit |= bit; }
+                }
+                if (!boxHit) { enter = false; break; }
+            }
+            if (enter) {
+                const bool identity = (__float_as_uint(r6.w) & 1u) != 0u;
+                float4 i0 = make_float4(1, 0, 0, 0), i1 = make_float4(0, 1, 0, 0), i2 = make_float4(0, 0, 1, 0);
+                if (!identity) { i0 = __ldg(rec); i1 = __ldg(rec + 1); i2 = __ldg(rec + 2); }
+                const V3 lo = mulPointRows(L.o, i0, i1, i2);
+                const V3 ld = normalize(mulDirRows(L.d, i0, i1, i2));
+                const V3 lidir = rcp3(ld);
+                const float4 a0 = __ldg(rec + 3), a1 = __ldg(rec + 4), a2 = __ldg(rec + 5);
+                if (rayAndAABBDist(lo, lidir, v3(a0.w, a1.w, a2.w), v3(r6.x, r6.y, r6.z)) < relaxedLimit(L.best)) {
+                    stack[sp++] = kTraceExitInstance;
+                    L.ro = lo; L.rd = ld; L.ridir = lidir;
+                    L.inst = recIdx | (identity ? 0x80000000u : 0u);
+                    cur = __float_as_uint(r7.x);
+                    pop = false;
+                }
+            }
+        }
+        if (pop) cur = sp ? stack[--sp] : kTraceDone;
+    }
+    L.cur = cur;
+    L.sp = sp;
+}
+
+__global__ void __launch_bounds__(kTraceBlockThreads)
+traceFastKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ FrameParams fp, const WavefrontBuffers wb,
+                const uint32_t* __restrict__ queueIn, uint32_t bounce)
+{
+    const uint32_t count = wb.counts[2u * bounce];
+    uint32_t* workCounter = wb.counts + 2u * bounce + 1u;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t laneMaskLt = (1u << lane) - 1u;
+    const uint32_t numSpheres = fp.rd.numSpheres < s.numSpheres ? fp.rd.numSpheres : s.numSpheres;
+
+    uint32_t stack[kFastStackCapacity];
+    TraceLane L;
+    L.cur = kTraceDone; L.sp = 0; L.path = 0u; L.inst = 0xFFFFFFFFu;
+    bool have = false;                        /* this lane owns a ray whose result is not written yet */
+    uint32_t next = 0u, end = 0u;             /* warp-uniform: unclaimed part of the warp's current chunk */
+    bool exhausted = false;                   /* warp-uniform */
+    uint32_t fallbacks = 0u;
+
+    for (;;) {
+        /* ---- refill */
+        uint32_t need = __ballot_sync(0xFFFFFFFFu, !have);
+        while (need != 0u && !exhausted) {
+            if (next == end) {
+                uint32_t base = 0u;
+                if (lane == 0u) base = atomicAdd(workCounter, kTraceChunk);
+                base = __shfl_sync(0xFFFFFFFFu, base, 0);
+                if (base >= count) { exhausted = true; break; }
+                next = base; end = min(base + kTraceChunk, count);
+            }
+            const uint32_t want = __popc(need), avail = end - next;
+            const uint32_t take = want < avail ? want : avail;
+            const uint32_t rank = __popc(need & laneMaskLt);
+            if (!have && rank < take) {
+                const uint32_t k = next + rank;
+                L.path = queueIn ? __ldg(queueIn + k) : k;
+                const float4 ro = wb.rayO[L.path], rdv = wb.rayD[L.path];
+                L.o = v3(ro.x, ro.y, ro.z); L.d = v3(rdv.x, rdv.y, rdv.z);
+                L.ro = L.o; L.rd = L.d; L.ridir = rcp3(L.d);
+                L.best = OKRT_FLT_MAX; L.second = OKRT_FLT_MAX;
+                L.hitKindIdx = 0x3FFFFFFFu; L.hitTri = 0xFFFFFFFFu; L.hitU = 0.f; L.hitV = 0.f;
+                L.octTested = 0ull; L.octHit = 0ull; L.inst = 0xFFFFFFFFu; L.sp = 0;
+                for (uint32_t i = 0; i < numSpheres; i++) {                /* RaytracerCS.hlsl:232-242 */
+                    const okrt_sphere& sp = s.spheres[i];
+                    const float t = rayAndSphere(L.o, L.d, v3(sp.position), sp.radius);
+                    if (t > 0.f) laneCandidate(L, t, (1u << 30) | i, 0xFFFFFFFFu, 0.f, 0.f);
+                }
+                L.cur = s.topRef == kRefNone ? kTraceDone : s.topRef;
+                have = true;
+            }
+            next += take;
+            need = __ballot_sync(0xFFFFFFFFu, !have);
+        }
+        if (__ballot_sync(0xFFFFFFFFu, have) == 0u) break;
+
+        /* ---- traverse until enough lanes have finished to make a refill worthwhile */
+        const uint32_t keepRunning = exhausted ? 1u : 24u;
+        for (;;) {
+            if (have && L.cur != kTraceDone) traceRound(s, L, stack);
+            const uint32_t running = __popc(__ballot_sync(0xFFFFFFFFu, have && L.cur != kTraceDone));
+            if (running < keepRunning) break;
+        }
+
+        /* ---- finished lanes write their hit record */
+        if (have && L.cur == kTraceDone) {
+            Hit hit;
+            hit.distance = L.best; hit.kind = L.best < OKRT_FLT_MAX ? (L.hitKindIdx >> 30) : 0u;
+            hit.idx = hit.kind ? (L.hitKindIdx & 0x3FFFFFFFu) : 0xFFFFFFFFu; hit.tri = L.hitTri; hit.u = L.hitU; hit.v = L.hitV;
+            uint32_t flag = 0u;
+            if (L.second < relaxedLimit(L.best)) {                         /* ambiguous: ask the reference order */
+                uint32_t bb = 0u, tc = 0u;
+                traverseExact(s, numSpheres, L.o, L.d, hit, bb, tc);
+                fallbacks++; flag = 1u;
+            }
+            wb.hitA[L.path] = make_float4(hit.distance, hit.u, hit.v, __uint_as_float(hit.tri));
+            wb.hitB[L.path] = (hit.kind << 30) | (hit.idx & 0x3FFFFFFFu);
+            if (fp.aov && bounce == 0u && flag) fp.aov[__float_as_uint(wb.rayD[L.path].w)].flags = 1u;
+            have = false;
+        }
+    }
+    const uint32_t fbSum = __reduce_add_sync(0xFFFFFFFFu, fallbacks);
+    if (lane == 0u && fbSum) atomicAdd(fp.counters + 1, (unsigned long long)fbSum);
+}
+
+/* ------------------------------------------------------------------- shade
+ * RaytracerCS.hlsl:336-392 (hit resolve) + :448-536 for one queued path per thread. */
+template <bool kInstrumented>
+__global__ void __launch_bounds__(128)
+shadeKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ FrameParams fp, const WavefrontBuffers wb,
+            const uint32_t* __restrict__ queueIn, uint32_t* __restrict__ queueOut, uint32_t bounce)
+{
+    const okrt_render_data& rd = fp.rd;
+    const uint32_t count = wb.counts[2u * bounce];
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool active = k < count;
+    bool survives = false;
+    uint32_t path = 0u;
+    if (active) {
+        path = queueIn ? __ldg(queueIn + k) : k;
+        const float4 ro = wb.rayO[path], rdv = wb.rayD[path], li = wb.radiance[path], th = wb.throughput[path];
+        const float4 ha = wb.hitA[path];
+        const uint32_t hb = wb.hitB[path];
+        PathState ps;
+        ps.o = v3(ro.x, ro.y, ro.z); ps.seed = __float_as_uint(ro.w);
+        ps.d = v3(rdv.x, rdv.y, rdv.z); ps.pixel = __float_as_uint(rdv.w);
+        ps.light = v3(li.x, li.y, li.z); ps.bounce = __float_as_uint(li.w);
+        ps.contribution = v3(th.x, th.y, th.z);
+        Hit hit;
+        hit.distance = ha.x; hit.u = ha.y; hit.v = ha.z; hit.tri = __float_as_uint(ha.w);
+        hit.kind = hb >> 30; hit.idx = hit.kind ? (hb & 0x3FFFFFFFu) : 0xFFFFFFFFu;
+
+        const bool finished = shadeSegment(s, rd, fp.maxBounces, hit, ps);
+        V3 light = ps.light;
+        const size_t pi = ps.pixel;
+
+        if (kInstrumented && fp.aov) {
+            okrt_aov* av = fp.aov + pi;
+            av->numSegments = bounce + 1u;
+            if (bounce == 0u) {
+                av->hitKind = hit.kind; av->hitIdx = hit.idx; av->triIdx = hit.kind == 2u ? hit.tri : 0xFFFFFFFFu;
+                av->baryU = hit.kind == 2u ? hit.u : 0.f; av->baryV = hit.kind == 2u ? hit.v : 0.f; av->distance = hit.distance;
+            }
+        }
+        if (finished) {
+            if (kInstrumented && fp.aov) {                      /* debug heat maps :516-520 */
+                const uint32_t bb = fp.aov[pi].bbCheckCount, tc = fp.aov[pi].triCheckCount;
+                if (rd.debugMode == 1u)
+                    light = bb > rd.debugMaxCount ? v3(1.f, 0.f, 0.f) : v3(1.f, 1.f, 1.f) * ((float)bb / (float)rd.debugMaxCount);
+                else if (rd.debugMode == 2u)
+                    light = tc > rd.debugMaxCount ? v3(1.f, 0.f, 0.f) : v3(1.f, 1.f, 1.f) * ((float)tc / (float)rd.debugMaxCount);
+                fp.aov[pi].radiance[0] = light.x; fp.aov[pi].radiance[1] = light.y; fp.aov[pi].radiance[2] = light.z;
+            }
+            /* accumulate + store :525-536 [Q14] */
+            float r, g, b, a;
+            if (rd.accumulationEnabled == 1u) {
+                float4 acc = fp.accumulation[pi];
+                acc.x += light.x; acc.y += light.y; acc.z += light.z; acc.w += 1.f;
+                fp.accumulation[pi] = acc;
+                const float n = (float)rd.numAccumulationFrames;
+                r = acc.x / n; g = acc.y / n; b = acc.z / n; a = acc.w / n;
+            } else { r = light.x; g = light.y; b = light.z; a = 1.f; }
+            fp.result[pi] = toUnorm8(r, g, b, a);
+        } else {
+            wb.rayO[path] = make_float4(ps.o.x, ps.o.y, ps.o.z, __uint_as_float(ps.seed));
+            wb.rayD[path] = make_float4(ps.d.x, ps.d.y, ps.d.z, rdv.w);
+            wb.radiance[path] = make_float4(ps.light.x, ps.light.y, ps.light.z, __uint_as_float(ps.bounce));
+            wb.throughput[path] = make_float4(ps.contribution.x, ps.contribution.y, ps.contribution.z, 0.f);
+            survives = true;
+        }
+    }
+    /* surviving paths -> next queue, one atomic per warp */
+    const uint32_t mask = __ballot_sync(0xFFFFFFFFu, survives);
+    if (mask) {
+        uint32_t base = 0u;
+        const uint32_t lane = threadIdx.x & 31u;
+        if (lane == (uint32_t)(__ffs(mask) - 1)) base = atomicAdd(wb.counts + 2u * (bounce + 1u), (uint32_t)__popc(mask));
+        base = __shfl_sync(0xFFFFFFFFu, base, __ffs(mask) - 1);
+        if (survives) queueOut[base + __popc(mask & ((1u << lane) - 1u))] = path;
+    }
+    if (k == 0u) {
+        atomicAdd(fp.counters + 0, (unsigned long long)count);
+        if (bounce == 0u) atomicAdd(fp.counters + 2, (unsigned long long)count);
+    }
+}
+
+} // namespace okrt

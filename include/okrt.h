@@ -218,6 +218,9 @@ enum { OKRT_TRAVERSAL_FAST = 0,   /* near-first traversal of the re-packed child
                                      exact-arithmetic commit; falls back to reference order on ties */
        OKRT_TRAVERSAL_EXACT = 1 };/* reference visit order, RaytracerCS.hlsl:244-334 (debug counters exact) */
 
+enum { OKRT_PIPELINE_WAVEFRONT = 0,  /* generate / trace / shade kernels with ray queues in HBM (default) */
+       OKRT_PIPELINE_MEGAKERNEL = 1 }; /* one persistent kernel with per-lane path regeneration */
+
 enum { OKRT_SHARD_NONE = 0,
        OKRT_SHARD_TILE = 1 };     /* this renderer traces only its interleaved row bands */
 
@@ -233,7 +236,8 @@ typedef struct okrt_options {
     uint32_t shardBandRows;       /* rows per interleaved band (tile mode); 0 = default */
     uint32_t frameOffset;         /* sample sharding: seed frame of local frame k (1-based) is */
     uint32_t frameStride;         /*   frameOffset + (k-1)*frameStride + 1; defaults 0 / 1 */
-    uint32_t reserved[6];
+    uint32_t pipeline;            /* OKRT_PIPELINE_*: same results, different kernel organisation */
+    uint32_t reserved[5];
 } okrt_options;
 
 typedef struct okrt_aov {         /* parity tap, one per pixel (new) */

@@ -27,6 +27,9 @@ def oracle_scene(oracle, host, envFaces=None, dirLights=None, pointLights=None, 
                              dirLights=dirLights, pointLights=pointLights, spotLights=spotLights)
 
 
+DEFAULT_PIPELINE = 0      # tests parametrize this: 0 wavefront, 1 persistent megakernel
+
+
 class Renderer:
     """Low-level use of the C ABI (binding-table setters), as the parity tests drive it."""
 
@@ -51,6 +54,7 @@ class Renderer:
             f = np.ascontiguousarray(envFaces)
             abi.check(self.L.okrt_set_environment_map(h, abi.ptr(f), f.shape[2], f.shape[1]))
         self.opt = abi.default_options()
+        self.opt[0]["pipeline"] = DEFAULT_PIPELINE
 
     def set_lights(self, dirLights=None, pointLights=None, spotLights=None):
         abi = self.abi

@@ -10,6 +10,15 @@ from tests import helpers
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(autouse=True, params=[0, 1], ids=["wavefront", "megakernel"])
+def pipeline(request):
+    """Every parity test runs through both kernel organisations; they must agree with the oracle bit for bit."""
+    old = helpers.DEFAULT_PIPELINE
+    helpers.DEFAULT_PIPELINE = request.param
+    yield request.param
+    helpers.DEFAULT_PIPELINE = old
+
+
 def _require_gpu(okrt):
     if okrt.abi.lib().okrt_device_count() <= 0:
         pytest.fail("no CUDA device visible: the product path has no CPU fallback")
