@@ -12,6 +12,8 @@
 #include <functional>
 #include <string>
 #include <unordered_map>
+#include <utility>
+#include <vector>
 
 namespace okrt {
 namespace {
@@ -79,7 +81,7 @@ struct Builder {
     }
 };
 
-struct TopLeaf { double lo[3], hi[3]; uint32_t record; };
+struct TopLeaf { double lo[3], hi[3]; uint32_t ref; };
 
 inline float roundDown(double v) { float f = (float)v; return (double)f > v ? std::nextafterf(f, -INFINITY) : f; }
 inline float roundUp(double v) { float f = (float)v; return (double)f < v ? std::nextafterf(f, INFINITY) : f; }
@@ -137,6 +139,10 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
     /* bottom level: one conversion per distinct BVH root */
     Builder b{tris, numTris, nodes, numNodes, out};
     std::unordered_map<uint32_t, uint32_t> rootRefOf;
+    std::unordered_map<uint32_t, uint32_t> rootUsers;            /* reachable instances per BVH root */
+    for (uint32_t i = 0; i < numInstances; i++)
+        if (instOct[i] != 0xFFFFFFFFu) rootUsers[instances[i].bvhNodeStartIdx]++;
+    out.triOwner.assign(numTris, 0xFFFFFFFFu);
     std::vector<TopLeaf> leaves;
     for (uint32_t i = 0; i < numInstances; i++) {
         if (instOct[i] == 0xFFFFFFFFu) continue;                 /* never visited by the reference either */
@@ -182,8 +188,33 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
         r[6] = Float4{rb.max[0], rb.max[1], rb.max[2], bitsToFloat(identity ? 1u : 0u)};
         r[7] = Float4{bitsToFloat(rootRef), bitsToFloat(instOct[i]), bitsToFloat(i), 0.f};
 
+        /* An identity-transform instance that is the only user of its mesh is MERGED into the top level: its
+         * local ray is the same for all such instances (normalize(d*I), o*I), so the top-level tree can link
+         * straight to its BVH root with the root's exact box — no ray switch, no exit marker.  Its triangles
+         * remember their owner so that a hit can name the instance (and check its oct-tree chain). */
+        bool merged = identity && rootUsers[inst.bvhNodeStartIdx] == 1u;
+        std::vector<std::pair<uint32_t, uint32_t>> ranges;
+        if (merged) {
+            std::vector<uint32_t> st{inst.bvhNodeStartIdx};
+            while (!st.empty() && merged) {
+                const okrt_bvh_node& n = nodes[st.back()]; st.pop_back();
+                if (n.firstChildIdx != OKRT_INVALID_UINT) { st.push_back(n.firstChildIdx); st.push_back(n.firstChildIdx + 1); continue; }
+                if (n.triStart == OKRT_INVALID_UINT || n.triEnd <= n.triStart) continue;
+                for (uint32_t j = n.triStart; j < n.triEnd; j++) if (out.triOwner[j] != 0xFFFFFFFFu) { merged = false; break; }
+                ranges.emplace_back(n.triStart, n.triEnd);
+            }
+        }
+        if (merged) {
+            for (auto& rg : ranges) for (uint32_t j = rg.first; j < rg.second; j++) out.triOwner[j] = rec;
+            TopLeaf leaf; leaf.ref = rootRef;
+            for (int k = 0; k < 3; k++) { leaf.lo[k] = rb.min[k]; leaf.hi[k] = rb.max[k]; }   /* exact: this IS the reference's root-box test */
+            leaves.push_back(leaf);
+            out.numMerged++;
+            continue;
+        }
+
         /* world box of the root box, padded: the top level only has to be conservative */
-        TopLeaf leaf; leaf.record = rec;
+        TopLeaf leaf; leaf.ref = kRefInstance | rec;
         for (int k = 0; k < 3; k++) { leaf.lo[k] = DBL_MAX; leaf.hi[k] = -DBL_MAX; }
         for (int corner = 0; corner < 8; corner++) {
             const double v[3] = {(corner & 1) ? rb.max[0] : rb.min[0], (corner & 2) ? rb.max[1] : rb.min[1], (corner & 4) ? rb.max[2] : rb.min[2]};
@@ -212,7 +243,9 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
                 cl[k] = std::min(cl[k], c); ch[k] = std::max(ch[k], c);
             }
         for (int k = 0; k < 3; k++) { box.min[k] = roundDown(bl[k]); box.max[k] = roundUp(bh[k]); }
-        if (hi - lo == 1) return kRefInstance | leaves[lo].record;
+        if (hi - lo == 1) return leaves[lo].ref;
+        /* unions of exact boxes are exact; one ulp outward keeps "child hit => parent hit" safe in every rounding case */
+        for (int k = 0; k < 3; k++) { box.min[k] = std::nextafterf(box.min[k], -INFINITY); box.max[k] = std::nextafterf(box.max[k], INFINITY); }
         int axis = 0;
         if (ch[1] - cl[1] > ch[axis] - cl[axis]) axis = 1;
         if (ch[2] - cl[2] > ch[axis] - cl[axis]) axis = 2;
@@ -231,8 +264,8 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
     if (!leaves.empty()) {
         okrt_aabb rootBox;
         out.topRef = buildTop(0, leaves.size(), 0, rootBox);
-        if ((out.topRef & kRefTagMask) == kRefInstance) {
-            /* single instance: wrap it in a pair node so the kernel always starts at an interior node */
+        if (leaves.size() == 1) {
+            /* single instance: wrap it in a pair node so the kernel always starts at an interior node (and tests its box) */
             const uint32_t p = b.newPair();
             okrt_aabb empty; for (int k = 0; k < 3; k++) { empty.min[k] = FLT_MAX; empty.max[k] = -FLT_MAX; }
             b.setChild(p, 0, rootBox, out.topRef);

@@ -116,115 +116,7 @@ traceExactKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ 
     }
 }
 
-/* Near-first traversal with lane refill.  Same tests and arithmetic as traverseFast (okrt_kernels.cuh); the
- * traversal state lives across refills so that a lane can start its next ray while its neighbours are still
- * walking theirs. */
-struct TraceLane {
-    V3 o, d;                 /* world ray */
-    V3 ro, rd, ridir;        /* current ray (local inside an instance) */
-    float best, second;
-    uint32_t hitKindIdx, hitTri;
-    float hitU, hitV;
-    uint32_t cur;
-    int sp;
-    uint32_t inst;           /* instance record index, bit 31 = identity transform; 0xFFFFFFFF at the top level */
-    unsigned long long octTested, octHit;
-    uint32_t path;
-};
-
-constexpr uint32_t kTraceDone = 0xFFFFFFFDu;
-constexpr uint32_t kTraceExitInstance = 0xFFFFFFFEu;
-
-__device__ __forceinline__ void laneCandidate(TraceLane& L, float t, uint32_t kindIdx, uint32_t tri, float u, float v)
-{
-    if (t < L.best) { L.second = L.best; L.best = t; L.hitKindIdx = kindIdx; L.hitTri = tri; L.hitU = u; L.hitV = v; }
-    else if (t < L.second) L.second = t;
-}
-
-/* one round of the while-while loop: interior nodes until a leaf comes up, then that leaf */
-__device__ __forceinline__ void traceRound(const DeviceScene& s, TraceLane& L, uint32_t* stack)
-{
-    uint32_t cur = L.cur;
-    int sp = L.sp;
-    while ((cur & kRefTagMask) == kRefInterior) {
-        const float4* q = s.fastNodes + (size_t)cur * 4;
-        const float4 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3);
-        const float limit = relaxedLimit(L.best);
-        const float n0 = rayAndAABBDist(L.ro, L.ridir, v3(q0.x, q0.y, q0.z), v3(q1.x, q1.y, q1.z));
-        const float n1 = rayAndAABBDist(L.ro, L.ridir, v3(q2.x, q2.y, q2.z), v3(q3.x, q3.y, q3.z));
-        const uint32_t r0 = __float_as_uint(q0.w), r1 = __float_as_uint(q1.w);
-        const bool h0 = n0 < limit && r0 != kRefNone;
-        const bool h1 = n1 < limit && r1 != kRefNone;
-        if (h0 && h1) {
-            const bool firstIs1 = n1 < n0;
-            stack[sp++] = firstIs1 ? r0 : r1;
-            cur = firstIs1 ? r1 : r0;
-        } else if (h0) cur = r0;
-        else if (h1) cur = r1;
-        else cur = sp ? stack[--sp] : kTraceDone;
-    }
-    if (cur != kTraceDone) {
-        bool pop = true;
-        if ((cur & kRefTagMask) == kRefTriLeaf) {
-            const uint32_t first = cur & (kMaxTriIndex - 1u);
-            const uint32_t count = ((cur >> 27) & 7u) + 1u;
-            for (uint32_t j = first; j < first + count; j++) {
-                const float4* tp = s.fastTris + (size_t)j * 3;
-                const float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
-                float bu = 0.f, bv = 0.f;
-                float t = rayAndTriangle(L.ro, L.rd, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), bu, bv);
-                if (t <= 0.f) continue;
-                V3 w = L.rd * t;                                        /* RaytracerCS.hlsl:312-314 */
-                if (!(L.inst & 0x80000000u)) {                           /* T == I maps w to itself */
-                    const float4* rec = s.fastInstances + (size_t)L.inst * 8;
-                    w = mulDirRows(w, __ldg(rec + 3), __ldg(rec + 4), __ldg(rec + 5));
-                }
-                t = length(w);
-                const uint32_t instRef = __float_as_uint(__ldg(s.fastInstances + (size_t)(L.inst & 0x7FFFFFFFu) * 8 + 7).z);
-                laneCandidate(L, t, (2u << 30) | instRef, j, bu, bv);
-            }
-        } else if (cur == kTraceExitInstance) {
-            L.ro = L.o; L.rd = L.d; L.ridir = rcp3(L.d); L.inst = 0xFFFFFFFFu;
-        } else {                                                         /* instance leaf */
-            const uint32_t recIdx = cur & ~kRefTagMask;
-            const float4* rec = s.fastInstances + (size_t)recIdx * 8;
-            const float4 r6 = __ldg(rec + 6), r7 = __ldg(rec + 7);
-            const V3 idirWorld = L.ridir;                                /* top level: current ray is the world ray */
-            bool enter = true;
-            for (uint32_t on = __float_as_uint(r7.y); on != 0xFFFFFFFFu; on = __ldg(s.octParent + on)) {
-                bool boxHit;
-                const unsigned long long bit = 1ull << (on & 63u);
-                if (on < 64u && (L.octTested & bit)) boxHit = (L.octHit & bit) != 0ull;
-                else {
-                    const okrt_octree_node& node = s.octNodes[on];
-                    boxHit = rayAndAABBDist(L.o, idirWorld, v3(node.boundingBox.min), v3(node.boundingBox.max)) < OKRT_FLT_MAX;
-                    if (on < 64u) { L.octTested |= bit; if (boxHit) L.octHit |= bit; }
-                }
-                if (!boxHit) { enter = false; break; }
-            }
-            if (enter) {
-                const bool identity = (__float_as_uint(r6.w) & 1u) != 0u;
-                float4 i0 = make_float4(1, 0, 0, 0), i1 = make_float4(0, 1, 0, 0), i2 = make_float4(0, 0, 1, 0);
-                if (!identity) { i0 = __ldg(rec); i1 = __ldg(rec + 1); i2 = __ldg(rec + 2); }
-                const V3 lo = mulPointRows(L.o, i0, i1, i2);
-                const V3 ld = normalize(mulDirRows(L.d, i0, i1, i2));
-                const V3 lidir = rcp3(ld);
-                const float4 a0 = __ldg(rec + 3), a1 = __ldg(rec + 4), a2 = __ldg(rec + 5);
-                if (rayAndAABBDist(lo, lidir, v3(a0.w, a1.w, a2.w), v3(r6.x, r6.y, r6.z)) < relaxedLimit(L.best)) {
-                    stack[sp++] = kTraceExitInstance;
-                    L.ro = lo; L.rd = ld; L.ridir = lidir;
-                    L.inst = recIdx | (identity ? 0x80000000u : 0u);
-                    cur = __float_as_uint(r7.x);
-                    pop = false;
-                }
-            }
-        }
-        if (pop) cur = sp ? stack[--sp] : kTraceDone;
-    }
-    L.cur = cur;
-    L.sp = sp;
-}
-
+/* Near-first traversal (TraceLane / traceRound, okrt_kernels.cuh) with lane refill. */
 __global__ void __launch_bounds__(kTraceBlockThreads)
 traceFastKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ FrameParams fp, const WavefrontBuffers wb,
                 const uint32_t* __restrict__ queueIn, uint32_t bounce)
@@ -237,7 +129,7 @@ traceFastKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ F
 
     uint32_t stack[kFastStackCapacity];
     TraceLane L;
-    L.cur = kTraceDone; L.sp = 0; L.path = 0u; L.inst = 0xFFFFFFFFu;
+    L.cur = kTraceDone; L.sp = 0; L.path = 0u; L.inst = kTraceTop;
     bool have = false;                        /* this lane owns a ray whose result is not written yet */
     uint32_t next = 0u, end = 0u;             /* warp-uniform: unclaimed part of the warp's current chunk */
     bool exhausted = false;                   /* warp-uniform */
@@ -261,17 +153,7 @@ traceFastKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ F
                 const uint32_t k = next + rank;
                 L.path = queueIn ? __ldg(queueIn + k) : k;
                 const float4 ro = wb.rayO[L.path], rdv = wb.rayD[L.path];
-                L.o = v3(ro.x, ro.y, ro.z); L.d = v3(rdv.x, rdv.y, rdv.z);
-                L.ro = L.o; L.rd = L.d; L.ridir = rcp3(L.d);
-                L.best = OKRT_FLT_MAX; L.second = OKRT_FLT_MAX;
-                L.hitKindIdx = 0x3FFFFFFFu; L.hitTri = 0xFFFFFFFFu; L.hitU = 0.f; L.hitV = 0.f;
-                L.octTested = 0ull; L.octHit = 0ull; L.inst = 0xFFFFFFFFu; L.sp = 0;
-                for (uint32_t i = 0; i < numSpheres; i++) {                /* RaytracerCS.hlsl:232-242 */
-                    const okrt_sphere& sp = s.spheres[i];
-                    const float t = rayAndSphere(L.o, L.d, v3(sp.position), sp.radius);
-                    if (t > 0.f) laneCandidate(L, t, (1u << 30) | i, 0xFFFFFFFFu, 0.f, 0.f);
-                }
-                L.cur = s.topRef == kRefNone ? kTraceDone : s.topRef;
+                laneInit(s, L, numSpheres, v3(ro.x, ro.y, ro.z), v3(rdv.x, rdv.y, rdv.z));
                 have = true;
             }
             next += take;
@@ -290,10 +172,8 @@ traceFastKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ F
         /* ---- finished lanes write their hit record */
         if (have && L.cur == kTraceDone) {
             Hit hit;
-            hit.distance = L.best; hit.kind = L.best < OKRT_FLT_MAX ? (L.hitKindIdx >> 30) : 0u;
-            hit.idx = hit.kind ? (L.hitKindIdx & 0x3FFFFFFFu) : 0xFFFFFFFFu; hit.tri = L.hitTri; hit.u = L.hitU; hit.v = L.hitV;
             uint32_t flag = 0u;
-            if (L.second < relaxedLimit(L.best)) {                         /* ambiguous: ask the reference order */
+            if (laneResult(L, hit)) {                                      /* ambiguous: ask the reference order */
                 uint32_t bb = 0u, tc = 0u;
                 traverseExact(s, numSpheres, L.o, L.d, hit, bb, tc);
                 fallbacks++; flag = 1u;
