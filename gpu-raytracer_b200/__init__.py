@@ -8,3 +8,4 @@ from . import _abi as abi                      # noqa: F401
 from .raytracer import Mesh, OctTree, Geometry, RayTracer, ResourceManager, Scene  # noqa: F401
 from .raytracer import environmentCrossToFaces, scaleTexturesToArray            # noqa: F401
 from . import scenes                           # noqa: F401
+from . import sharding                         # noqa: F401

@@ -11,7 +11,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libokrt.so")
+LIB_PATH = os.environ.get("OKRT_LIB") or os.path.join(HERE, "libokrt.so")   # OKRT_LIB: alternative build (tuning experiments)
 
 INVALID_UINT = 0xFFFFFFFF
 
@@ -135,6 +135,8 @@ SYMBOLS = [
     ("okrt_accumulation_device_ptr", _P, [_P]),
     ("okrt_result_device_ptr", _P, [_P]),
     ("okrt_cuda_stream", _P, [_P]),
+    ("okrt_shard_owner_of_row", _U, [_U, _U, _U]),
+    ("okrt_shard_seed_frame", _U, [_P, _U, _U]),
     ("okrt_get_stats", _I, [_P, _P]),
     ("okrt_reset_stats", _I, [_P]),
 ]

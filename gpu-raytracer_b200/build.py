@@ -42,7 +42,10 @@ def _stale(target, deps):
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build_library(force=False, verbose=False, extra_nvcc=()):
+def build_library(force=False, verbose=False, extra_nvcc=(), out=None):
+    global OUT
+    if out:
+        OUT = out
     os.makedirs(OBJ, exist_ok=True)
     inc = ["-I" + os.path.join(ROOT, "include"), "-I" + CSRC]
     common_deps = [os.path.join(ROOT, "include", "okrt.h")] + [os.path.join(CSRC, h) for h in HEADERS]

@@ -291,7 +291,7 @@ int launchFrame(okrt_renderer* r)
     fp.maxBounces = r->opt.maxBounces;
     /* sample sharding: local frame k (1-based) draws the seed of global frame offset + (k-1)*stride + 1 */
     const uint32_t localFrame = r->rd.numAccumulationFrames;
-    fp.seedFrame = r->rd.accumulationEnabled ? r->opt.frameOffset + (localFrame - 1u) * r->opt.frameStride + 1u : r->opt.frameOffset;
+    fp.seedFrame = okrt_shard_seed_frame(&r->opt, localFrame, r->rd.accumulationEnabled);
     /* scaled instances make the reference's local-vs-world culling order dependent; debug heat maps
      * display the reference's own visit counters: both need the reference visiting order */
     fp.traversal = (r->opt.traversal == OKRT_TRAVERSAL_EXACT || !r->allRigid || r->rd.debugMode != 0u) ? OKRT_TRAVERSAL_EXACT : OKRT_TRAVERSAL_FAST;

@@ -737,6 +737,21 @@ int okrt_calculate_projection_data(const okrt_camera* cam, uint32_t width, uint3
     return OKRT_OK;
 }
 
+/* ------------------------------------------------------------ sharding */
+uint32_t okrt_shard_owner_of_row(uint32_t y, uint32_t bandRows, uint32_t shardCount)
+{
+    if (bandRows == 0u) bandRows = 8u;
+    if (shardCount == 0u) shardCount = 1u;
+    return (y / bandRows) % shardCount;
+}
+
+uint32_t okrt_shard_seed_frame(const okrt_options* o, uint32_t localFrame, uint32_t accumulationEnabled)
+{
+    const uint32_t stride = o && o->frameStride ? o->frameStride : 1u;
+    const uint32_t offset = o ? o->frameOffset : 0u;
+    return accumulationEnabled ? offset + (localFrame - 1u) * stride + 1u : offset;
+}
+
 /* ------------------------------------------------------------ textures */
 uint32_t okrt_texture_array_size(const uint32_t* widths, const uint32_t* heights, uint32_t count)
 {

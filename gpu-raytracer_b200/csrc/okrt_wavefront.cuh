@@ -37,6 +37,12 @@ struct WavefrontBuffers {
 constexpr uint32_t kMaxWavefrontBounces = 63;
 constexpr uint32_t kMaxQueueCounts = 2 * (kMaxWavefrontBounces + 2);
 constexpr int kTraceBlockThreads = 128;
+#ifndef OKRT_TRACE_MIN_BLOCKS
+#define OKRT_TRACE_MIN_BLOCKS 6
+#endif
+#ifndef OKRT_KEEP_RUNNING
+#define OKRT_KEEP_RUNNING 16
+#endif
 constexpr uint32_t kTraceChunk = 64;         /* rays a warp claims per atomic */
 
 /* ---------------------------------------------------------------- generate
@@ -117,7 +123,7 @@ traceExactKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ 
 }
 
 /* Near-first traversal (TraceLane / traceRound, okrt_kernels.cuh) with lane refill. */
-__global__ void __launch_bounds__(kTraceBlockThreads)
+__global__ void __launch_bounds__(kTraceBlockThreads, OKRT_TRACE_MIN_BLOCKS)
 traceFastKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ FrameParams fp, const WavefrontBuffers wb,
                 const uint32_t* __restrict__ queueIn, uint32_t bounce)
 {
@@ -162,7 +168,7 @@ traceFastKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ F
         if (__ballot_sync(0xFFFFFFFFu, have) == 0u) break;
 
         /* ---- traverse until enough lanes have finished to make a refill worthwhile */
-        const uint32_t keepRunning = exhausted ? 1u : 24u;
+        const uint32_t keepRunning = exhausted ? 1u : (uint32_t)OKRT_KEEP_RUNNING;
         for (;;) {
             if (have && L.cur != kTraceDone) traceRound(s, L, stack);
             const uint32_t running = __popc(__ballot_sync(0xFFFFFFFFu, have && L.cur != kTraceDone));

@@ -131,8 +131,9 @@ def procedural_texture(kind, size, seed):
     rng = np.random.default_rng(seed)
     y, x = np.mgrid[0:size, 0:size].astype(np.float32) / size
     base = rng.uniform(0.25, 0.9, 3).astype(np.float32)
-    lowres = rng.uniform(0.0, 1.0, (32, 32)).astype(np.float32)
-    noise = np.kron(lowres, np.ones((size // 32, size // 32), np.float32))
+    cells = 32 if size % 32 == 0 and size >= 32 else 1
+    lowres = rng.uniform(0.0, 1.0, (32, 32)).astype(np.float32)[:cells, :cells]
+    noise = np.kron(lowres, np.ones((size // cells, size // cells), np.float32))
     if kind == "bricks":
         row = np.floor(y * 16)
         bx = (x * 8 + 0.5 * (row % 2)) % 1.0

@@ -373,6 +373,11 @@ OKRT_API void* okrt_accumulation_device_ptr(okrt_renderer* r);
 OKRT_API void* okrt_result_device_ptr(okrt_renderer* r);
 OKRT_API void* okrt_cuda_stream(okrt_renderer* r);
 
+/* sharding arithmetic (host-only, no device needed): which rank traces image row y in tile mode, and which
+ * global frame's seed the k-th (1-based) local frame of a sample-sharded renderer draws */
+OKRT_API uint32_t okrt_shard_owner_of_row(uint32_t y, uint32_t bandRows, uint32_t shardCount);
+OKRT_API uint32_t okrt_shard_seed_frame(const okrt_options* o, uint32_t localFrame, uint32_t accumulationEnabled);
+
 OKRT_API int okrt_get_stats(okrt_renderer* r, okrt_stats* out);   /* synchronises */
 OKRT_API int okrt_reset_stats(okrt_renderer* r);
 

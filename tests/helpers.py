@@ -20,6 +20,19 @@ def build_host_side(okrt, rm, sc, info, width, height, spheres=False):
     return dict(geometry=geo, octree=oct_, rd=rd, spheres=sph, textures=tex)
 
 
+def scene_digest(host, env=None):
+    """sha256 over every array of the binding table: numpy's transcendental kernels differ in the last bit between
+    CPU generations, so a golden render is only comparable where the generated scene is bit-identical."""
+    import hashlib
+    h = hashlib.sha256()
+    g, t = host["geometry"], host["octree"]
+    for a in (g.trianglesPos, g.trianglesInfo, g.bvhNodes, t.nodes, t.instances, host["spheres"], host["textures"], host["rd"]):
+        h.update(np.ascontiguousarray(a).tobytes())
+    if env is not None:
+        h.update(np.ascontiguousarray(env).tobytes())
+    return h.hexdigest()
+
+
 def oracle_scene(oracle, host, envFaces=None, dirLights=None, pointLights=None, spotLights=None):
     g, t = host["geometry"], host["octree"]
     return oracle.make_scene(g.trianglesPos, g.trianglesInfo, g.bvhNodes, t.nodes, t.instances, spheres=host["spheres"],
