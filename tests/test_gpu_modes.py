@@ -1,0 +1,175 @@
+"""GPU tests of the modes around the hot path: sharding, progressive state, the RayTracer mirror, full-size runs."""
+import numpy as np
+import pytest
+
+from tests import helpers
+
+pytestmark = pytest.mark.gpu
+
+
+def _scene(okrt, W, H, tris=20000):
+    rm, sc, info = okrt.scenes.sponza_standin(tris, texture_size=64)
+    host = helpers.build_host_side(okrt, rm, sc, info, W, H)
+    env = okrt.scenes.procedural_sky_faces(32)
+    return host, env
+
+
+@pytest.mark.parametrize("pipeline", [0, 1])
+def test_tile_sharding_union_equals_single(okrt, pipeline):
+    """Tile mode: ranks render disjoint interleaved bands; the union is the single-GPU image, bit for bit."""
+    W, H = 320, 184
+    host, env = _scene(okrt, W, H)
+    single = helpers.Renderer(okrt, host, W, H, envFaces=env)
+    single.options(maxBounces=4, coverAllPixels=1, pipeline=pipeline)
+    single.render(host["rd"].copy(), frames=2)
+    ref_acc = single.accumulation()
+    total = int(single.stats()["raySegments"])
+    for world, band in ((2, 8), (3, 16), (8, 8)):
+        acc = np.zeros_like(ref_acc)
+        segs = 0
+        for rank in range(world):
+            r = helpers.Renderer(okrt, host, W, H, envFaces=env)
+            r.options(maxBounces=4, coverAllPixels=1, pipeline=pipeline, **okrt.sharding.tile_options(rank, world, band))
+            r.render(host["rd"].copy(), frames=2)
+            a = r.accumulation()
+            rows = okrt.sharding.rows_of_rank(rank, world, H, band)
+            other = np.setdiff1d(np.arange(H), rows)
+            assert not a[other].any(), "a rank wrote outside its bands"
+            acc[rows] = a[rows]
+            segs += int(r.stats()["raySegments"])
+            r.close()
+        assert np.array_equal(acc.view(np.uint32), ref_acc.view(np.uint32))
+        assert segs == total
+    single.close()
+
+
+def test_sample_sharding_matches_sequential(okrt):
+    """Sample mode: rank r renders frames r+1, r+1+G, ...; summed u1 == sequential u1 up to float summation order."""
+    W, H, total, world = 256, 144, 8, 4
+    host, env = _scene(okrt, W, H)
+    seq = helpers.Renderer(okrt, host, W, H, envFaces=env)
+    seq.options(maxBounces=4)
+    seq.render(host["rd"].copy(), frames=total)
+    want = seq.accumulation()
+    summed = np.zeros_like(want, dtype=np.float64)
+    for rank in range(world):
+        r = helpers.Renderer(okrt, host, W, H, envFaces=env)
+        r.options(maxBounces=4, **okrt.sharding.sample_options(rank, world))
+        r.render(host["rd"].copy(), frames=total // world)
+        summed += r.accumulation()
+        r.close()
+    rmse = float(np.sqrt(np.mean((summed / total - want.astype(np.float64) / total) ** 2)))
+    assert rmse <= 1e-4, rmse
+    assert np.array_equal(summed[..., 3], want[..., 3])
+    # merge through the ABI: write the reduced buffer back and resolve (what the all-reduce path does)
+    seq.abi.check(seq.L.okrt_write_accumulation(seq.h, seq.abi.ptr(summed.astype(np.float32)), total))
+    seq.abi.check(seq.L.okrt_resolve(seq.h, total))
+    img = seq.result()
+    exp = np.clip(summed[..., :3] / total, 0, 1) * 255.0 + 0.5
+    covered = img[:9 * (H // 9), :16 * (W // 16), :3].astype(np.int32)
+    assert np.abs(covered - exp[:9 * (H // 9), :16 * (W // 16)].astype(np.int32)).max() <= 1
+    seq.close()
+
+
+def test_progressive_state_reset_resize(okrt, oracle):
+    """toggle/resetAccumulation (RayTracer.h:197-209), onResize (RayTracer.cpp:494-501), determinism of re-rendering."""
+    W, H = 160, 90
+    host, env = _scene(okrt, W, H, tris=8000)
+    r = helpers.Renderer(okrt, host, W, H, envFaces=env)
+    r.options(maxBounces=3)
+    rd = host["rd"].copy()
+    r.render(rd, frames=3)
+    a3 = r.accumulation()
+    assert r.L.okrt_get_num_accumulation_frames(r.h) == 3
+    r.abi.check(r.L.okrt_reset_accumulation(r.h))
+    assert r.L.okrt_get_num_accumulation_frames(r.h) == 0 and not r.accumulation().any()
+    r.abi.check(r.L.okrt_render_frames(r.h, 3)); r.abi.check(r.L.okrt_sync(r.h))
+    assert np.array_equal(r.accumulation().view(np.uint32), a3.view(np.uint32))          # same seeds -> same bits
+    # accumulation off: the counter stays 0 and every frame is the same image [Q3]
+    r.abi.check(r.L.okrt_toggle_accumulation(r.h, 0))
+    r.abi.check(r.L.okrt_render_frames(r.h, 1)); r.abi.check(r.L.okrt_sync(r.h)); i1 = r.result()
+    r.abi.check(r.L.okrt_render_frames(r.h, 1)); r.abi.check(r.L.okrt_sync(r.h)); i2 = r.result()
+    assert np.array_equal(i1, i2) and r.L.okrt_get_num_accumulation_frames(r.h) == 0
+    # resize: new images, counter reset, clear colour in the uncovered border [Q9]
+    r.abi.check(r.L.okrt_toggle_accumulation(r.h, 1))
+    r.abi.check(r.L.okrt_resize(r.h, 100, 50))
+    r.W, r.H = 100, 50
+    host2 = helpers.build_host_side(okrt, *okrt.scenes.sponza_standin(8000, texture_size=64), 100, 50)
+    r.render(host2["rd"].copy())
+    img = r.result()
+    assert np.all(img[45:, :] == np.array([51, 102, 153, 255], np.uint8)) and np.all(img[:, 96:] == np.array([51, 102, 153, 255], np.uint8))
+    o = oracle.render(helpers.oracle_scene(oracle, host2, envFaces=env), _frame1(host2["rd"]), 3)
+    assert np.array_equal(img, o["result"])
+    r.close()
+
+
+def _frame1(rd):
+    rd = rd.copy(); rd[0]["numAccumulationFrames"] = 1
+    return rd
+
+
+def test_raytracer_mirror_class(okrt, oracle):
+    """The reference-facing class (raytracer.py mirrors RayTracer.h:82-116) end to end."""
+    rm, sc, info = okrt.scenes.test_scene(with_textures=True)
+    W, H = 192, 108
+    rt = okrt.RayTracer(0)
+    rt.initiate(W, H, rm, environmentMapFaces=okrt.scenes.procedural_sky_faces(32), maxBounces=3)
+    rt.setScene(sc)
+    rt.bindSpheres(True)
+    rt.createOctTree(sc, 2, 50)
+    rt.render(frames=2)
+    rt.sync()
+    assert rt.getNumAccumulationFrames() == 2
+    host = helpers.build_host_side(okrt, rm, sc, info, W, H, spheres=True)
+    os_ = helpers.oracle_scene(oracle, host, envFaces=okrt.scenes.procedural_sky_faces(32))
+    acc = np.zeros((H, W, 4), np.float32); res = np.zeros((H, W, 4), np.uint8)
+    rd = host["rd"].copy()
+    for f in (1, 2):
+        rd[0]["numAccumulationFrames"] = f
+        oracle.render(os_, rd, 3, accum=acc, result=res)
+    assert np.array_equal(rt.readAccumulation().view(np.uint32), acc.view(np.uint32))
+    assert np.array_equal(rt.readResult(), res)
+    rt.resetAccumulation()
+    assert rt.getNumAccumulationFrames() == 0
+    rt.shutdown()
+
+
+def test_full_size_primary_hits_1080p(okrt, oracle):
+    """BASELINE size: the 262k-triangle stand-in at 1920x1080, primary rays — every triangle id equals the oracle's."""
+    import bench
+    host, env, info = bench.build_scene(okrt)
+    r = helpers.Renderer(okrt, host, bench.WIDTH, bench.HEIGHT, envFaces=env)
+    r.options(maxBounces=0, writeAov=1)
+    r.render(host["rd"].copy())
+    g = r.aov()
+    o = oracle.render(helpers.oracle_scene(oracle, host, envFaces=env), _frame1(host["rd"]), 0, aov_dtype=okrt.abi.AOV)
+    assert np.array_equal(g["triIdx"], o["aov"]["triIdx"]) and np.array_equal(g["hitIdx"], o["aov"]["hitIdx"])
+    for f in ("baryU", "baryV", "distance"):
+        assert np.array_equal(g[f].view(np.uint32), o["aov"][f].view(np.uint32))
+    assert np.array_equal(r.accumulation().view(np.uint32), o["accum"].view(np.uint32))
+    r.close()
+
+
+def test_full_size_8_bounces_properties(okrt):
+    """BASELINE size, 8 bounces: size-independent properties — the two pipelines and the two traversal orders agree
+    bit for bit, segment counts agree, alpha counts samples, fallback stays rare."""
+    import bench
+    host, env, info = bench.build_scene(okrt)
+    outs = []
+    for pipeline, traversal in ((0, 0), (1, 0), (0, 1)):
+        r = helpers.Renderer(okrt, host, bench.WIDTH, bench.HEIGHT, envFaces=env)
+        r.options(maxBounces=8, pipeline=pipeline, traversal=traversal)
+        r.render(host["rd"].copy(), frames=2)
+        st = r.stats()
+        outs.append((r.accumulation(), int(st["raySegments"]), int(st["fallbackSegments"])))
+        r.close()
+    for acc, seg, fb in outs[1:]:
+        assert np.array_equal(acc.view(np.uint32), outs[0][0].view(np.uint32)) and seg == outs[0][1]
+    assert np.all(outs[0][0][..., 3] == 2.0)
+    assert outs[0][2] < 0.001 * outs[0][1]
+    assert 2 * bench.WIDTH * bench.HEIGHT <= outs[0][1] <= 2 * 9 * bench.WIDTH * bench.HEIGHT
+
+
+def test_cpp_mirror_on_gpu(okrt, tmp_path):
+    from tests.test_cpu_host_mirror import test_cpp_mirror_builds_and_runs
+    test_cpp_mirror_builds_and_runs(okrt, tmp_path)
