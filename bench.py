@@ -134,15 +134,12 @@ def run_reference_arm(args):
     host, env, info = build_scene(okrt)
     scene = helpers.oracle_scene(oracle, host, envFaces=env)
     rd = host["rd"].copy()
-    bands = [(y, min(y + 8, HEIGHT)) for y in range(0, HEIGHT, 8)][::8]          # every 8th 8-row band: 1/8 of the frame
+    rows = np.array([y for y in range(HEIGHT) if (y // 8) % 8 == 0], np.uint32)     # every 8th 8-row band: 1/8 of the frame
     cores = os.cpu_count() or 1
 
     def step(frame):
         rd[0]["numAccumulationFrames"] = frame
-        seg = 0
-        for y0, y1 in bands:
-            seg += oracle.render(scene, rd, MAX_BOUNCES, rows=(y0, y1))["segments"]
-        return seg
+        return oracle.render(scene, rd, MAX_BOUNCES, row_list=rows)["segments"]
     for w in range(args.warmup):
         step(w + 1)
     t0 = time.perf_counter()

@@ -254,10 +254,12 @@ int ensureWavefront(okrt_renderer* r, size_t paths)
     return OKRT_OK;
 }
 
-/* generate -> (trace, shade) x (maxBounces + 1); queue sizes stay on the device, nothing syncs with the host */
+/* generate -> (trace, shade) x (maxBounces + 1) -> accumulate, for `fp.batchFrames` frames at once; queue sizes
+ * stay on the device, nothing syncs with the host */
 int launchWavefront(okrt_renderer* r, const FrameParams& fp, bool instrumented)
 {
-    const size_t paths = (size_t)fp.numTiles * kTilePixels;
+    const size_t slots = (size_t)fp.numTiles * kTilePixels;
+    const size_t paths = slots * fp.batchFrames;
     int rc = ensureWavefront(r, paths);
     if (rc) return rc;
     const DeviceScene scene = sceneView(r);
@@ -267,22 +269,38 @@ int launchWavefront(okrt_renderer* r, const FrameParams& fp, bool instrumented)
     r->launches++;
     const unsigned traceGrid = std::min<unsigned>((unsigned)(r->numSms * r->blocksPerSmTrace), std::max(1u, flatGrid));
     for (uint32_t b = 0; b <= fp.maxBounces; b++) {
-        const uint32_t* qin = b == 0u ? nullptr : r->wb.queue[(b - 1u) & 1u];
-        uint32_t* qout = r->wb.queue[b & 1u];
+        const uint32_t* qin = r->wb.queue[b & 1u];
+        uint32_t* qout = r->wb.queue[(b + 1u) & 1u];
         if (fp.traversal == OKRT_TRAVERSAL_EXACT) traceExactKernel<<<flatGrid, 128, 0, r->stream>>>(scene, fp, r->wb, qin, b);
         else traceFastKernel<<<traceGrid, kTraceBlockThreads, 0, r->stream>>>(scene, fp, r->wb, qin, b);
         if (instrumented) shadeKernel<true><<<flatGrid, 128, 0, r->stream>>>(scene, fp, r->wb, qin, qout, b);
         else shadeKernel<false><<<flatGrid, 128, 0, r->stream>>>(scene, fp, r->wb, qin, qout, b);
         r->launches += 2;
     }
+    accumulateKernel<<<(unsigned)((slots + 127) / 128), 128, 0, r->stream>>>(fp, r->wb);
+    r->launches++;
     OKRT_CUDA(cudaGetLastError());
     return OKRT_OK;
 }
 
-int launchFrame(okrt_renderer* r)
+/* Renders up to `want` frames in one go and reports how many (`done`).  The wavefront pipeline traces several
+ * progressive frames together (more rays per launch, fewer launches, better strong scaling); u1 still receives
+ * them in frame order.  Instrumented runs, the megakernel and accumulation-off render one frame per call. */
+constexpr uint32_t kMaxBatchFrames = 8;
+constexpr size_t kMaxBatchPaths = (size_t)1 << 26;
+
+int launchFrames(okrt_renderer* r, uint32_t want, uint32_t& done)
 {
+    done = 1u;
+    const bool instrumentedRun = r->opt.writeAov != 0u || r->rd.debugMode != 0u;
+    const bool wavefront = r->opt.pipeline == OKRT_PIPELINE_WAVEFRONT && r->opt.maxBounces <= kMaxWavefrontBounces;
+    if (wavefront && !instrumentedRun && r->rd.accumulationEnabled == 1u) {
+        const size_t slots = (size_t)((r->width + kTileW - 1) / kTileW) * ((r->height + kTileH - 1) / kTileH) * kTilePixels;
+        done = (uint32_t)std::max<size_t>(1, std::min<size_t>(std::min<uint32_t>(want, kMaxBatchFrames), kMaxBatchPaths / std::max<size_t>(slots, 1)));
+    }
     /* updateBuffers: the counter advances before the constants are uploaded (RayTracer.cpp:489) */
-    r->rd.numAccumulationFrames += r->rd.accumulationEnabled;
+    const uint32_t firstLocalFrame = r->rd.numAccumulationFrames + r->rd.accumulationEnabled;
+    r->rd.numAccumulationFrames += r->rd.accumulationEnabled * done;
     r->rd.textureDims[0] = r->width; r->rd.textureDims[1] = r->height;
 
     FrameParams fp;
@@ -290,8 +308,9 @@ int launchFrame(okrt_renderer* r)
     fp.rd = r->rd;
     fp.maxBounces = r->opt.maxBounces;
     /* sample sharding: local frame k (1-based) draws the seed of global frame offset + (k-1)*stride + 1 */
-    const uint32_t localFrame = r->rd.numAccumulationFrames;
-    fp.seedFrame = okrt_shard_seed_frame(&r->opt, localFrame, r->rd.accumulationEnabled);
+    fp.seedFrame = okrt_shard_seed_frame(&r->opt, firstLocalFrame, r->rd.accumulationEnabled);
+    fp.seedStride = r->rd.accumulationEnabled ? r->opt.frameStride : 0u;
+    fp.batchFrames = done;
     /* scaled instances make the reference's local-vs-world culling order dependent; debug heat maps
      * display the reference's own visit counters: both need the reference visiting order */
     fp.traversal = (r->opt.traversal == OKRT_TRAVERSAL_EXACT || !r->allRigid || r->rd.debugMode != 0u) ? OKRT_TRAVERSAL_EXACT : OKRT_TRAVERSAL_FAST;
@@ -547,8 +566,11 @@ int okrt_render_frames(okrt_renderer* r, uint32_t frames)
     if (r->layoutDirty && (rc = rebuildLayout(r))) return rc;
     if (r->opt.writeAov && (rc = ensureAov(r))) return rc;
     OKRT_CUDA(cudaEventRecord(r->evStart, r->stream));
-    for (uint32_t f = 0; f < frames; f++)
-        if ((rc = launchFrame(r))) return rc;
+    for (uint32_t f = 0; f < frames;) {
+        uint32_t done = 1u;
+        if ((rc = launchFrames(r, frames - f, done))) return rc;
+        f += done;
+    }
     OKRT_CUDA(cudaEventRecord(r->evStop, r->stream));
     return OKRT_OK;
 }

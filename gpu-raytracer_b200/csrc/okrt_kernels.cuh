@@ -97,7 +97,8 @@ struct DeviceScene {
 struct FrameParams {
     okrt_render_data rd;                      /* b0 */
     uint32_t maxBounces;
-    uint32_t seedFrame;                       /* numAccumulationFrames as used by the seed [Q3] */
+    uint32_t seedFrame;                       /* numAccumulationFrames as used by the seed [Q3] (first frame of a batch) */
+    uint32_t seedStride, batchFrames;         /* wavefront: frames traced together; frame f uses seedFrame + f*seedStride */
     uint32_t traversal;
     uint32_t coveredW, coveredH;              /* [Q9] */
     uint32_t bandRows, shardRank, shardCount; /* tile sharding: row band b belongs to rank b % shardCount */

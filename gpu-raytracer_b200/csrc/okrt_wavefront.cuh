@@ -51,25 +51,29 @@ __global__ void __launch_bounds__(128)
 generateKernel(const __grid_constant__ FrameParams fp, const WavefrontBuffers wb)
 {
     const okrt_render_data& rd = fp.rd;
-    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t gslot = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t numSlots = fp.numTiles * kTilePixels;            /* a multiple of 128: warps never straddle frames */
+    const uint32_t frame = gslot / numSlots, slot = gslot % numSlots;
+    if (frame >= fp.batchFrames) return;
     const uint32_t tile = slot / kTilePixels, j = slot % kTilePixels;
-    if (tile >= fp.numTiles) return;
     const uint32_t tileX = tile % fp.tilesX, tileRowLocal = tile / fp.tilesX;
     const uint32_t tilesPerBand = fp.bandRows / kTileH;
     const uint32_t tileRow = ((tileRowLocal / tilesPerBand) * fp.shardCount + fp.shardRank) * tilesPerBand + tileRowLocal % tilesPerBand;
     const uint32_t px = tileX * kTileW + j % kTileW, py = tileRow * kTileH + j / kTileW;
     const bool covered = px < fp.coveredW && py < fp.coveredH;
 
-    /* compact covered pixels into queue 0 (keeps tile order inside a warp) */
+    /* path slot = frame * numSlots + pixel slot (so that the final gather can add frames in order); covered
+     * pixels are compacted into queue 0 (keeps tile order inside a warp) */
     const uint32_t mask = __ballot_sync(0xFFFFFFFFu, covered);
     uint32_t base = 0u;
     if ((threadIdx.x & 31u) == 0u && mask) base = atomicAdd(wb.counts + 0, (uint32_t)__popc(mask));
     base = __shfl_sync(0xFFFFFFFFu, base, 0);
     if (!covered) return;
-    const uint32_t path = base + __popc(mask & ((1u << (threadIdx.x & 31u)) - 1u));
+    const uint32_t path = gslot;
+    wb.queue[0][base + __popc(mask & ((1u << (threadIdx.x & 31u)) - 1u))] = path;
 
     const uint32_t width = rd.textureDims[0];
-    uint32_t seed = px + (py + 74813u) * width * (fp.seedFrame + 1u);
+    uint32_t seed = px + (py + 74813u) * width * ((fp.seedFrame + frame * fp.seedStride) + 1u);
     V3 pos = v3((float)px, (float)(rd.textureDims[1] - py), rd.cameraNearZ);
     pos.x += randomFloat(seed) - 0.5f;
     pos.y += randomFloat(seed) - 0.5f;
@@ -242,16 +246,8 @@ shadeKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ Frame
                     light = tc > rd.debugMaxCount ? v3(1.f, 0.f, 0.f) : v3(1.f, 1.f, 1.f) * ((float)tc / (float)rd.debugMaxCount);
                 fp.aov[pi].radiance[0] = light.x; fp.aov[pi].radiance[1] = light.y; fp.aov[pi].radiance[2] = light.z;
             }
-            /* accumulate + store :525-536 [Q14] */
-            float r, g, b, a;
-            if (rd.accumulationEnabled == 1u) {
-                float4 acc = fp.accumulation[pi];
-                acc.x += light.x; acc.y += light.y; acc.z += light.z; acc.w += 1.f;
-                fp.accumulation[pi] = acc;
-                const float n = (float)rd.numAccumulationFrames;
-                r = acc.x / n; g = acc.y / n; b = acc.z / n; a = acc.w / n;
-            } else { r = light.x; g = light.y; b = light.z; a = 1.f; }
-            fp.result[pi] = toUnorm8(r, g, b, a);
+            /* the path's radiance waits in its slot; accumulateKernel adds the batch's frames in frame order */
+            wb.radiance[path] = make_float4(light.x, light.y, light.z, __uint_as_float(ps.bounce));
         } else {
             wb.rayO[path] = make_float4(ps.o.x, ps.o.y, ps.o.z, __uint_as_float(ps.seed));
             wb.rayD[path] = make_float4(ps.d.x, ps.d.y, ps.d.z, rdv.w);
@@ -273,6 +269,40 @@ shadeKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ Frame
         atomicAdd(fp.counters + 0, (unsigned long long)count);
         if (bounce == 0u) atomicAdd(fp.counters + 2, (unsigned long long)count);
     }
+}
+
+/* ------------------------------------------------------------ accumulate
+ * RaytracerCS.hlsl:525-536 [Q14] for a batch: u1 += light of frame 0, 1, ... in that order (the order the
+ * reference's frame loop adds them, so u1 stays bit-identical), then u0 = saturate(u1 / numAccumulationFrames). */
+__global__ void __launch_bounds__(128)
+accumulateKernel(const __grid_constant__ FrameParams fp, const WavefrontBuffers wb)
+{
+    const okrt_render_data& rd = fp.rd;
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t numSlots = fp.numTiles * kTilePixels;
+    if (slot >= numSlots) return;
+    const uint32_t tile = slot / kTilePixels, j = slot % kTilePixels;
+    const uint32_t tileX = tile % fp.tilesX, tileRowLocal = tile / fp.tilesX;
+    const uint32_t tilesPerBand = fp.bandRows / kTileH;
+    const uint32_t tileRow = ((tileRowLocal / tilesPerBand) * fp.shardCount + fp.shardRank) * tilesPerBand + tileRowLocal % tilesPerBand;
+    const uint32_t px = tileX * kTileW + j % kTileW, py = tileRow * kTileH + j / kTileW;
+    if (px >= fp.coveredW || py >= fp.coveredH) return;
+    const size_t pi = (size_t)py * rd.textureDims[0] + px;
+    float r, g, b, a;
+    if (rd.accumulationEnabled == 1u) {
+        float4 acc = fp.accumulation[pi];
+        for (uint32_t f = 0; f < fp.batchFrames; f++) {
+            const float4 l = wb.radiance[(size_t)f * numSlots + slot];
+            acc.x += l.x; acc.y += l.y; acc.z += l.z; acc.w += 1.f;
+        }
+        fp.accumulation[pi] = acc;
+        const float n = (float)rd.numAccumulationFrames;
+        r = acc.x / n; g = acc.y / n; b = acc.z / n; a = acc.w / n;
+    } else {
+        const float4 l = wb.radiance[(size_t)(fp.batchFrames - 1u) * numSlots + slot];
+        r = l.x; g = l.y; b = l.z; a = 1.f;
+    }
+    fp.result[pi] = toUnorm8(r, g, b, a);
 }
 
 } // namespace okrt

@@ -812,9 +812,9 @@ ORACLE_API void oracle_last_visit_totals(uint64_t* out7) { for (int k = 0; k < 7
  *   accum       RGBA32F accumulation image, read-modify-write (u1)
  *   result      RGBA8 result image (u0)
  * Returns the number of stack overflows the reference's fixed stacks would have had. */
-ORACLE_API uint32_t oracle_render(const OracleScene* scene, const RenderData* rd, uint32_t maxBounces, uint32_t seedFrame,
-                                  uint32_t coverAll, float* accum, uint8_t* result, Aov* aov,
-                                  uint32_t y0, uint32_t y1, int threads, int mathMode, uint64_t* outSegments)
+static uint32_t renderRows(const OracleScene* scene, const RenderData* rd, uint32_t maxBounces, uint32_t seedFrame,
+                           uint32_t coverAll, float* accum, uint8_t* result, Aov* aov,
+                           const uint32_t* rowList, uint32_t y0, uint32_t y1, int threads, int mathMode, uint64_t* outSegments)
 {
     const uint32_t W = rd->textureDims[0], H = rd->textureDims[1];
     if (y1 > H) y1 = H;
@@ -833,8 +833,10 @@ ORACLE_API uint32_t oracle_render(const OracleScene* scene, const RenderData* rd
         Ctx c{scene, rd, mathMode, 0};
         uint64_t localSegments = 0;
         for (;;) {
-            const uint32_t y = nextRow.fetch_add(1);
-            if (y >= y1) break;
+            const uint32_t slotIdx = nextRow.fetch_add(1);
+            if (slotIdx >= y1) break;
+            const uint32_t y = rowList ? rowList[slotIdx] : slotIdx;
+            if (y >= H) continue;
             for (uint32_t x = 0; x < W; x++) {
                 const size_t pi = (size_t)y * W + x;
                 if (result) { result[pi * 4 + 0] = 51; result[pi * 4 + 1] = 102; result[pi * 4 + 2] = 153; result[pi * 4 + 3] = 255; }
@@ -878,6 +880,21 @@ ORACLE_API uint32_t oracle_render(const OracleScene* scene, const RenderData* rd
     for (int k = 0; k < 6; k++) g_lastVisits[k + 1] = visit[k].load();
     if (outSegments) *outSegments = segments;
     return overflow;
+}
+
+ORACLE_API uint32_t oracle_render(const OracleScene* scene, const RenderData* rd, uint32_t maxBounces, uint32_t seedFrame,
+                                  uint32_t coverAll, float* accum, uint8_t* result, Aov* aov,
+                                  uint32_t y0, uint32_t y1, int threads, int mathMode, uint64_t* outSegments)
+{
+    return renderRows(scene, rd, maxBounces, seedFrame, coverAll, accum, result, aov, nullptr, y0, y1, threads, mathMode, outSegments);
+}
+
+/* same, for an explicit list of image rows (bounded samples of a frame, tile-sharded ranks) */
+ORACLE_API uint32_t oracle_render_rows(const OracleScene* scene, const RenderData* rd, uint32_t maxBounces, uint32_t seedFrame,
+                                       uint32_t coverAll, float* accum, uint8_t* result, Aov* aov,
+                                       const uint32_t* rows, uint32_t numRows, int threads, int mathMode, uint64_t* outSegments)
+{
+    return renderRows(scene, rd, maxBounces, seedFrame, coverAll, accum, result, aov, rows, 0u, numRows, threads, mathMode, outSegments);
 }
 
 /* ---------------------------------------------------------------- KATs */

@@ -47,6 +47,8 @@ class Oracle:
         self.lib = lib
         lib.oracle_render.restype = _U
         lib.oracle_render.argtypes = [ctypes.POINTER(OracleScene), _P, _U, _U, _U, _P, _P, _P, _U, _U, _I, _I, ctypes.POINTER(ctypes.c_uint64)]
+        lib.oracle_render_rows.restype = _U
+        lib.oracle_render_rows.argtypes = [ctypes.POINTER(OracleScene), _P, _U, _U, _U, _P, _P, _P, _P, _U, _I, _I, ctypes.POINTER(ctypes.c_uint64)]
         lib.oracle_last_visit_totals.restype = None
         lib.oracle_last_visit_totals.argtypes = [_P]
         lib.oracle_pcg_hash.restype = _U
@@ -109,7 +111,7 @@ class Oracle:
         return s
 
     def render(self, scene, rd, maxBounces, seedFrame=None, coverAll=0, accum=None, result=None, aov_dtype=None,
-               rows=None, threads=0, math=MATH_CANONICAL):
+               rows=None, threads=0, math=MATH_CANONICAL, row_list=None):
         """One frame.  rd: 1-element RENDER_DATA array.  Returns dict(accum, result, aov, segments, overflow)."""
         W, H = int(rd[0]["textureDims"][0]), int(rd[0]["textureDims"][1])
         if accum is None:
@@ -117,13 +119,19 @@ class Oracle:
         if result is None:
             result = np.zeros((H, W, 4), np.uint8)
         aov = np.zeros((H, W), aov_dtype) if aov_dtype is not None else None
-        y0, y1 = (0, H) if rows is None else rows
         seg = ctypes.c_uint64(0)
         if seedFrame is None:
             seedFrame = int(rd[0]["numAccumulationFrames"])
-        ovf = self.lib.oracle_render(ctypes.byref(scene), rd.ctypes.data_as(_P), maxBounces, seedFrame, coverAll,
-                                     accum.ctypes.data_as(_P), result.ctypes.data_as(_P),
-                                     None if aov is None else aov.ctypes.data_as(_P), y0, y1, threads, math, ctypes.byref(seg))
+        if row_list is not None:
+            rl = np.ascontiguousarray(row_list, np.uint32)
+            ovf = self.lib.oracle_render_rows(ctypes.byref(scene), rd.ctypes.data_as(_P), maxBounces, seedFrame, coverAll,
+                                              accum.ctypes.data_as(_P), result.ctypes.data_as(_P),
+                                              None if aov is None else aov.ctypes.data_as(_P), rl.ctypes.data_as(_P), len(rl), threads, math, ctypes.byref(seg))
+        else:
+            y0, y1 = (0, H) if rows is None else rows
+            ovf = self.lib.oracle_render(ctypes.byref(scene), rd.ctypes.data_as(_P), maxBounces, seedFrame, coverAll,
+                                         accum.ctypes.data_as(_P), result.ctypes.data_as(_P),
+                                         None if aov is None else aov.ctypes.data_as(_P), y0, y1, threads, math, ctypes.byref(seg))
         v = np.zeros(7, np.uint64)
         self.lib.oracle_last_visit_totals(v.ctypes.data_as(_P))
         visits = dict(zip(("segments", "octNodes", "instances", "bvhNodes", "triangles", "hits", "textureTaps"), (int(x) for x in v)))
