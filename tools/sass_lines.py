@@ -24,7 +24,11 @@ out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_ou
 rows = list(csv.reader(out.splitlines()))
 hi = [i for i, r in enumerate(rows) if r and r[0] == "Address"][0]
 hdr = rows[hi]
-body = rows[hi + 1:]
+body = []
+for r in rows[hi + 1:]:
+    if not r or r[0] in ("Kernel Name", "Address") or len(r) < len(hdr) // 2:
+        break
+    body.append(r)
 ci = {n: hdr.index(n) for n in ("# Samples", "Instructions Executed", "Thread Instructions Executed", "Source")}
 print("sass instructions: nvdisasm %d, ncu %d" % (len(lines), len(body)))
 agg = collections.defaultdict(lambda: [0, 0, 0, 0])
