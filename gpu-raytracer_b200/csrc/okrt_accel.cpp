@@ -81,7 +81,31 @@ struct Builder {
     }
 };
 
-struct TopLeaf { double lo[3], hi[3]; uint32_t ref; };
+struct TopLeaf { double lo[3], hi[3]; uint32_t ref; uint32_t weight; };   /* weight: triangles below (SAH cost) */
+
+/* true if every interior node's box contains both child boxes (component-wise, exactly) and nothing is NaN */
+bool flattenable(const okrt_bvh_node* nodes, uint32_t numNodes, uint32_t root)
+{
+    std::vector<uint32_t> st{root};
+    size_t visited = 0;
+    while (!st.empty()) {
+        const uint32_t idx = st.back(); st.pop_back();
+        if (idx >= numNodes || ++visited > numNodes) return false;
+        const okrt_bvh_node& n = nodes[idx];
+        for (int k = 0; k < 3; k++) if (!(n.boundingBox.min[k] <= n.boundingBox.max[k])) { if (n.firstChildIdx != OKRT_INVALID_UINT || (n.triStart != OKRT_INVALID_UINT && n.triEnd > n.triStart)) return false; }
+        if (n.firstChildIdx == OKRT_INVALID_UINT) continue;
+        if ((uint64_t)n.firstChildIdx + 1 >= numNodes) return false;
+        for (int c = 0; c < 2; c++) {
+            const okrt_bvh_node& ch = nodes[n.firstChildIdx + c];
+            const bool empty = ch.firstChildIdx == OKRT_INVALID_UINT && (ch.triStart == OKRT_INVALID_UINT || ch.triEnd <= ch.triStart);
+            if (empty) continue;
+            for (int k = 0; k < 3; k++)
+                if (!(n.boundingBox.min[k] <= ch.boundingBox.min[k] && ch.boundingBox.max[k] <= n.boundingBox.max[k])) return false;
+            st.push_back(n.firstChildIdx + c);
+        }
+    }
+    return true;
+}
 
 inline float roundDown(double v) { float f = (float)v; return (double)f > v ? std::nextafterf(f, -INFINITY) : f; }
 inline float roundUp(double v) { float f = (float)v; return (double)f < v ? std::nextafterf(f, INFINITY) : f; }
@@ -144,6 +168,7 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
         if (instOct[i] != 0xFFFFFFFFu) rootUsers[instances[i].bvhNodeStartIdx]++;
     out.triOwner.assign(numTris, 0xFFFFFFFFu);
     std::vector<TopLeaf> leaves;
+    uint32_t chainDepth = 0;                                     /* pair levels of oversized-leaf chains below a flattened leaf */
     for (uint32_t i = 0; i < numInstances; i++) {
         if (instOct[i] == 0xFFFFFFFFu) continue;                 /* never visited by the reference either */
         const okrt_mesh_instance& inst = instances[i];
@@ -206,15 +231,39 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
         }
         if (merged) {
             for (auto& rg : ranges) for (uint32_t j = rg.first; j < rg.second; j++) out.triOwner[j] = rec;
-            TopLeaf leaf; leaf.ref = rootRef;
-            for (int k = 0; k < 3; k++) { leaf.lo[k] = rb.min[k]; leaf.hi[k] = rb.max[k]; }   /* exact: this IS the reference's root-box test */
-            leaves.push_back(leaf);
             out.numMerged++;
+            if (flattenable(nodes, numNodes, inst.bvhNodeStartIdx)) {
+                /* every REFERENCE LEAF becomes a primitive of one scene-wide SAH tree.  Its box is the reference's own
+                 * (bit copy) and is tested with the reference's arithmetic; a reference parent box contains its
+                 * children's boxes exactly (BvhBuilder.cpp:209-222 takes min/max over the same points), and the slab
+                 * test is monotone under rounding, so "leaf box hit" implies that every ancestor the reference
+                 * tests on its way down is hit too — the per-mesh interior nodes need not be visited. */
+                std::vector<uint32_t> st{inst.bvhNodeStartIdx};
+                while (!st.empty()) {
+                    const okrt_bvh_node& n = nodes[st.back()]; st.pop_back();
+                    if (n.firstChildIdx != OKRT_INVALID_UINT) { st.push_back(n.firstChildIdx); st.push_back(n.firstChildIdx + 1); continue; }
+                    if (n.triStart == OKRT_INVALID_UINT || n.triEnd <= n.triStart) continue;
+                    const uint32_t before = b.deepestPair;
+                    b.deepestPair = 0;
+                    TopLeaf leaf; leaf.ref = b.leafRef(n.triStart, n.triEnd - n.triStart, n.boundingBox, 0, 0);
+                    chainDepth = std::max(chainDepth, b.deepestPair);
+                    b.deepestPair = before;
+                    if (b.failed) return false;
+                    leaf.weight = n.triEnd - n.triStart;
+                    for (int k = 0; k < 3; k++) { leaf.lo[k] = n.boundingBox.min[k]; leaf.hi[k] = n.boundingBox.max[k]; }
+                    leaves.push_back(leaf);
+                    out.numFlattenedLeaves++;
+                }
+            } else {
+                TopLeaf leaf; leaf.ref = rootRef; leaf.weight = std::max<uint32_t>(1u, inst.triEnd > inst.triStart ? inst.triEnd - inst.triStart : 1u);
+                for (int k = 0; k < 3; k++) { leaf.lo[k] = rb.min[k]; leaf.hi[k] = rb.max[k]; }   /* exact: this IS the reference's root-box test */
+                leaves.push_back(leaf);
+            }
             continue;
         }
 
         /* world box of the root box, padded: the top level only has to be conservative */
-        TopLeaf leaf; leaf.ref = kRefInstance | rec;
+        TopLeaf leaf; leaf.ref = kRefInstance | rec; leaf.weight = std::max<uint32_t>(1u, inst.triEnd > inst.triStart ? inst.triEnd - inst.triStart : 1u);
         for (int k = 0; k < 3; k++) { leaf.lo[k] = DBL_MAX; leaf.hi[k] = -DBL_MAX; }
         for (int corner = 0; corner < 8; corner++) {
             const double v[3] = {(corner & 1) ? rb.max[0] : rb.min[0], (corner & 2) ? rb.max[1] : rb.min[1], (corner & 4) ? rb.max[2] : rb.min[2]};
@@ -231,8 +280,11 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
     }
     out.exactBvhDepth = b.deepestLeafLevel + 1;
 
-    /* top level: median split on the widest centroid axis, one instance per leaf */
+    /* top level: binned SAH (32 bins per axis, cost = area x triangles below) over reference leaves and instances;
+     * median split when the SAH finds nothing or the tree gets too deep for the traversal stack */
     uint32_t topDepth = 0;
+    constexpr int kBins = 32;
+    constexpr uint32_t kSahDepthLimit = 44;
     std::function<uint32_t(size_t, size_t, uint32_t, okrt_aabb&)> buildTop = [&](size_t lo, size_t hi, uint32_t level, okrt_aabb& box) -> uint32_t {
         double bl[3] = {DBL_MAX, DBL_MAX, DBL_MAX}, bh[3] = {-DBL_MAX, -DBL_MAX, -DBL_MAX};
         double cl[3] = {DBL_MAX, DBL_MAX, DBL_MAX}, ch[3] = {-DBL_MAX, -DBL_MAX, -DBL_MAX};
@@ -246,12 +298,57 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
         if (hi - lo == 1) return leaves[lo].ref;
         /* unions of exact boxes are exact; one ulp outward keeps "child hit => parent hit" safe in every rounding case */
         for (int k = 0; k < 3; k++) { box.min[k] = std::nextafterf(box.min[k], -INFINITY); box.max[k] = std::nextafterf(box.max[k], INFINITY); }
-        int axis = 0;
-        if (ch[1] - cl[1] > ch[axis] - cl[axis]) axis = 1;
-        if (ch[2] - cl[2] > ch[axis] - cl[axis]) axis = 2;
-        const size_t mid = lo + (hi - lo) / 2;
-        std::nth_element(leaves.begin() + (ptrdiff_t)lo, leaves.begin() + (ptrdiff_t)mid, leaves.begin() + (ptrdiff_t)hi,
-                         [axis](const TopLeaf& a, const TopLeaf& c) { return a.lo[axis] + a.hi[axis] < c.lo[axis] + c.hi[axis]; });
+
+        size_t mid = lo;
+        if (hi - lo > 2 && level < kSahDepthLimit) {
+            double bestCost = DBL_MAX; int bestAxis = -1, bestBin = -1;
+            for (int axis = 0; axis < 3; axis++) {
+                const double ext = ch[axis] - cl[axis];
+                if (!(ext > 0)) continue;
+                struct Bin { double lo[3], hi[3]; uint64_t w; } bins[kBins];
+                for (auto& bn : bins) { for (int k = 0; k < 3; k++) { bn.lo[k] = DBL_MAX; bn.hi[k] = -DBL_MAX; } bn.w = 0; }
+                const double scale = kBins / ext;
+                for (size_t i = lo; i < hi; i++) {
+                    const double c = 0.5 * (leaves[i].lo[axis] + leaves[i].hi[axis]);
+                    const int bi = std::min(kBins - 1, std::max(0, (int)((c - cl[axis]) * scale)));
+                    Bin& bn = bins[bi];
+                    for (int k = 0; k < 3; k++) { bn.lo[k] = std::min(bn.lo[k], leaves[i].lo[k]); bn.hi[k] = std::max(bn.hi[k], leaves[i].hi[k]); }
+                    bn.w += leaves[i].weight;
+                }
+                double rightArea[kBins]; uint64_t rightW[kBins];
+                double rl[3] = {DBL_MAX, DBL_MAX, DBL_MAX}, rh[3] = {-DBL_MAX, -DBL_MAX, -DBL_MAX}; uint64_t rw = 0;
+                auto area = [](const double* l, const double* h) { const double dx = h[0] - l[0], dy = h[1] - l[1], dz = h[2] - l[2]; return (dx < 0 || dy < 0 || dz < 0) ? 0.0 : 2.0 * (dx * dy + dy * dz + dz * dx); };
+                for (int bi = kBins - 1; bi > 0; bi--) {
+                    for (int k = 0; k < 3; k++) { rl[k] = std::min(rl[k], bins[bi].lo[k]); rh[k] = std::max(rh[k], bins[bi].hi[k]); }
+                    rw += bins[bi].w; rightArea[bi] = area(rl, rh); rightW[bi] = rw;
+                }
+                double ll[3] = {DBL_MAX, DBL_MAX, DBL_MAX}, lh[3] = {-DBL_MAX, -DBL_MAX, -DBL_MAX}; uint64_t lw = 0;
+                for (int bi = 0; bi < kBins - 1; bi++) {
+                    for (int k = 0; k < 3; k++) { ll[k] = std::min(ll[k], bins[bi].lo[k]); lh[k] = std::max(lh[k], bins[bi].hi[k]); }
+                    lw += bins[bi].w;
+                    if (lw == 0 || rightW[bi + 1] == 0) continue;
+                    const double cost = area(ll, lh) * (double)lw + rightArea[bi + 1] * (double)rightW[bi + 1];
+                    if (cost < bestCost) { bestCost = cost; bestAxis = axis; bestBin = bi; }
+                }
+            }
+            if (bestAxis >= 0) {
+                const double scale = kBins / (ch[bestAxis] - cl[bestAxis]), c0 = cl[bestAxis];
+                const int axis = bestAxis, split = bestBin;
+                auto it = std::partition(leaves.begin() + (ptrdiff_t)lo, leaves.begin() + (ptrdiff_t)hi, [=](const TopLeaf& a) {
+                    const double c = 0.5 * (a.lo[axis] + a.hi[axis]);
+                    return std::min(kBins - 1, std::max(0, (int)((c - c0) * scale))) <= split;
+                });
+                mid = (size_t)(it - leaves.begin());
+            }
+        }
+        if (mid == lo || mid == hi) {
+            int axis = 0;
+            if (ch[1] - cl[1] > ch[axis] - cl[axis]) axis = 1;
+            if (ch[2] - cl[2] > ch[axis] - cl[axis]) axis = 2;
+            mid = lo + (hi - lo) / 2;
+            std::nth_element(leaves.begin() + (ptrdiff_t)lo, leaves.begin() + (ptrdiff_t)mid, leaves.begin() + (ptrdiff_t)hi,
+                             [axis](const TopLeaf& a, const TopLeaf& c) { return a.lo[axis] + a.hi[axis] < c.lo[axis] + c.hi[axis]; });
+        }
         const uint32_t p = b.newPair();
         topDepth = std::max(topDepth, level + 1);
         okrt_aabb b0, b1;
@@ -277,7 +374,7 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
     if ((out.nodes.size() / 4) >= (1u << 30) || (out.instances.size() / 8) >= (1u << 30)) { out.error = "scene too large for 30-bit references"; return false; }
 
     /* fast stack: one deferred sibling per level in each tree, plus the instance-exit marker */
-    out.maxStackDepth = topDepth + b.deepestPair + 2;
+    out.maxStackDepth = topDepth + std::max(b.deepestPair, chainDepth) + 2;
     if (b.failed) return false;
     return true;
 }

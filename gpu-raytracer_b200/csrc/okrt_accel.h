@@ -56,6 +56,7 @@ struct FastLayout {
     std::vector<uint32_t> octParent;    /* parent index per oct-tree node (root: 0xFFFFFFFF) */
     std::vector<uint32_t> triOwner;     /* per triangle: instance record of the merged instance that owns it, else ~0u */
     uint32_t numMerged = 0;             /* instances linked straight into the top level */
+    uint32_t numFlattenedLeaves = 0;    /* reference leaves that became primitives of the scene-wide SAH tree */
     uint32_t topRef = kRefNone;         /* reference to the top-level root (interior or instance leaf) */
     uint32_t maxStackDepth = 0;         /* worst-case fast-stack occupancy */
     uint32_t exactBvhDepth = 0;         /* worst-case reference BVH stack occupancy */

@@ -219,6 +219,7 @@ DeviceScene sceneView(const okrt_renderer* r)
     s.octParent = (const uint32_t*)r->octParent.ptr;
     s.triOwner = (const uint32_t*)r->triOwner.ptr;
     s.topRef = r->topRef;
+    s.numFastNodes = r->fastNodes.count / 4u; s.numFastInstances = r->fastInstances.count / 8u;
     return s;
 }
 
@@ -231,11 +232,13 @@ void coveredExtent(const okrt_renderer* r, uint32_t& cw, uint32_t& ch)
 
 void freeWavefront(okrt_renderer* r)
 {
-    void* ptrs[] = {r->wb.rayO, r->wb.rayD, r->wb.radiance, r->wb.throughput, r->wb.hitA, r->wb.hitB, r->wb.queue[0], r->wb.queue[1], r->wb.counts};
+    void* ptrs[] = {r->wb.rayO, r->wb.rayD, r->wb.radiance, r->wb.throughput, r->wb.hitA, r->wb.hitB, r->wb.queue[0], r->wb.queue[1], r->wb.counts, r->wb.fallbackQueue};
     for (void* p : ptrs) if (p) cudaFree(p);
     std::memset(&r->wb, 0, sizeof(r->wb));
     r->wbPaths = 0;
 }
+
+constexpr uint32_t kCountWords = kMaxQueueCounts + kMaxWavefrontBounces + 2;
 
 int ensureWavefront(okrt_renderer* r, size_t paths)
 {
@@ -249,7 +252,9 @@ int ensureWavefront(okrt_renderer* r, size_t paths)
     OKRT_CUDA(cudaMalloc(&r->wb.hitB, paths * sizeof(uint32_t)));
     OKRT_CUDA(cudaMalloc(&r->wb.queue[0], paths * sizeof(uint32_t)));
     OKRT_CUDA(cudaMalloc(&r->wb.queue[1], paths * sizeof(uint32_t)));
-    OKRT_CUDA(cudaMalloc(&r->wb.counts, kMaxQueueCounts * sizeof(uint32_t)));
+    OKRT_CUDA(cudaMalloc(&r->wb.fallbackQueue, paths * sizeof(uint32_t)));
+    OKRT_CUDA(cudaMalloc(&r->wb.counts, kCountWords * sizeof(uint32_t)));
+    r->wb.fallbackCounts = r->wb.counts + kMaxQueueCounts;
     r->wbPaths = paths;
     return OKRT_OK;
 }
@@ -263,16 +268,21 @@ int launchWavefront(okrt_renderer* r, const FrameParams& fp, bool instrumented)
     int rc = ensureWavefront(r, paths);
     if (rc) return rc;
     const DeviceScene scene = sceneView(r);
-    OKRT_CUDA(cudaMemsetAsync(r->wb.counts, 0, kMaxQueueCounts * sizeof(uint32_t), r->stream));
+    OKRT_CUDA(cudaMemsetAsync(r->wb.counts, 0, kCountWords * sizeof(uint32_t), r->stream));
     const unsigned flatGrid = (unsigned)((paths + 127) / 128);
     generateKernel<<<flatGrid, 128, 0, r->stream>>>(fp, r->wb);
     r->launches++;
     const unsigned traceGrid = std::min<unsigned>((unsigned)(r->numSms * r->blocksPerSmTrace), std::max(1u, flatGrid));
+    const unsigned fallbackGrid = std::min<unsigned>((unsigned)(r->numSms * 8), std::max(1u, flatGrid));   /* 4 rays (warps) per block */
     for (uint32_t b = 0; b <= fp.maxBounces; b++) {
         const uint32_t* qin = r->wb.queue[b & 1u];
         uint32_t* qout = r->wb.queue[(b + 1u) & 1u];
         if (fp.traversal == OKRT_TRAVERSAL_EXACT) traceExactKernel<<<flatGrid, 128, 0, r->stream>>>(scene, fp, r->wb, qin, b);
-        else traceFastKernel<<<traceGrid, kTraceBlockThreads, 0, r->stream>>>(scene, fp, r->wb, qin, b);
+        else {
+            traceFastKernel<<<traceGrid, kTraceBlockThreads, 0, r->stream>>>(scene, fp, r->wb, qin, b);
+            traceFallbackKernel<<<fallbackGrid, 128, 0, r->stream>>>(scene, fp, r->wb, b);
+            r->launches++;
+        }
         if (instrumented) shadeKernel<true><<<flatGrid, 128, 0, r->stream>>>(scene, fp, r->wb, qin, qout, b);
         else shadeKernel<false><<<flatGrid, 128, 0, r->stream>>>(scene, fp, r->wb, qin, qout, b);
         r->launches += 2;

@@ -11,6 +11,12 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <cstdint>
+#ifdef OKRT_DEBUG_CHECKS
+#include <cassert>
+#define OKRT_CHECK(c) assert(c)
+#else
+#define OKRT_CHECK(c) ((void)0)
+#endif
 
 #include "okrt.h"
 #include "okrt_accel.h"
@@ -91,6 +97,7 @@ struct DeviceScene {
     const uint32_t* octParent;
     const uint32_t* triOwner;
     uint32_t topRef;
+    uint32_t numFastNodes, numFastInstances;
     uint32_t pad0;
 };
 
@@ -278,8 +285,12 @@ struct Surface {           /* what shading needs from Payload (RaytracerCS.hlsl:
 
 /* ------------------------------------------- reference-order traversal
  * RaytracerCS.hlsl:228-334 [Q4,Q5], visit order and counters exactly as the shader. */
+/* `limit` = FLT_MAX gives the reference's traversal verbatim.  The fallback of the near-first traversal passes
+ * best*(1+delta) of the distance it found: boxes that start at or beyond it hold no candidate inside the window
+ * and cannot influence which window candidate the reference returns (order independence), so they
+ * are skipped — the traversal then costs a few dozen boxes instead of a few hundred. */
 __device__ __noinline__ void traverseExact(const DeviceScene& s, uint32_t numSpheres, V3 o, V3 d, Hit& hit,
-                                           uint32_t& bbCheckCount, uint32_t& triCheckCount)
+                                           uint32_t& bbCheckCount, uint32_t& triCheckCount, float limit = OKRT_FLT_MAX)
 {
     hit.distance = OKRT_FLT_MAX; hit.kind = 0u; hit.idx = 0xFFFFFFFFu; hit.tri = 0xFFFFFFFFu; hit.u = 0.f; hit.v = 0.f;
 
@@ -299,7 +310,8 @@ __device__ __noinline__ void traverseExact(const DeviceScene& s, uint32_t numSph
         const uint32_t octIdx = octStack[--octStackSize];
         const okrt_octree_node& on = s.octNodes[octIdx];
         bbCheckCount += 1u;
-        if (rayAndAABBDist(o, idirWorld, v3(on.boundingBox.min), v3(on.boundingBox.max)) >= hit.distance)
+        const float octNear = rayAndAABBDist(o, idirWorld, v3(on.boundingBox.min), v3(on.boundingBox.max));
+        if (octNear >= hit.distance || octNear >= limit)
             continue;
 
         const uint32_t mStart = on.meshesStartIdx, mEnd = on.meshesEndIdx;
@@ -316,7 +328,8 @@ __device__ __noinline__ void traverseExact(const DeviceScene& s, uint32_t numSph
                 const uint32_t nodeIdx = bvhStack[--bvhStackSize];
                 const okrt_bvh_node& bn = s.bvhNodes[nodeIdx];
                 bbCheckCount += 1u;
-                if (rayAndAABBDist(lo, lidir, v3(bn.boundingBox.min), v3(bn.boundingBox.max)) >= hit.distance)
+                const float boxNear = rayAndAABBDist(lo, lidir, v3(bn.boundingBox.min), v3(bn.boundingBox.max));
+                if (boxNear >= hit.distance || boxNear >= limit)
                     continue;
                 const uint32_t first = bn.firstChildIdx;
                 if (first != 0xFFFFFFFFu) {
@@ -517,6 +530,178 @@ __device__ __forceinline__ bool traverseFast(const DeviceScene& s, uint32_t numS
     laneInit(s, L, numSpheres, o, d);
     while (L.cur != kTraceDone) traceRound(s, L, stack);
     return laneResult(L, hit);
+}
+
+/* ------------------------------------------- near-first traversal, step form
+ * The same traversal as traceRound(), cut into STEPS of similar cost so that a warp can vote which kind of step
+ * to run next (traceFastKernel, okrt_wavefront.cuh).  ncu on the while-while form (profiles/r1_d_*): 9.2 of 32
+ * lanes active per instruction — a round lasts as long as its slowest lane's run of interior nodes, and the
+ * per-candidate oct-tree chain test ran with 2.3 lanes.  Here
+ *   - a lane that pops a triangle leaf only records the range (triNext, triEnd) and already holds its next node;
+ *   - one node step = one child-pair node, one triangle step = one triangle;
+ *   - the oct-tree chain of a merged instance is tested once, for the winning triangle, when the ray finishes
+ *     (a failed chain or two candidates inside the window send the ray to the reference-order kernel).
+ * Arithmetic per box and per triangle is unchanged, so are the results. */
+struct StepLane {
+    V3 ro, rd, ridir;        /* current ray: identity-local at the top level, instance-local inside an instance */
+    float best, second;
+    uint32_t hitRec;         /* 1<<30 | sphere, or 2<<30 | (instance record, or 0x3FFFFFFF = "merged: look up triOwner") */
+    uint32_t hitTri;
+    float hitU, hitV;
+    uint32_t cur;            /* next node reference (interior / instance / exit marker / leaf not yet opened / done) */
+    uint32_t triNext, triEnd;/* triangles of the opened leaf still to test */
+    int sp;
+    uint32_t inst;           /* instance record inside a generic instance; kTraceTop at the top level */
+    uint32_t path;
+};
+constexpr uint32_t kMergedRec = 0x3FFFFFFFu;
+
+__device__ __forceinline__ void stepCandidate(StepLane& L, float t, uint32_t rec, uint32_t tri, float u, float v)
+{
+    if (t < L.best) { L.second = L.best; L.best = t; L.hitRec = rec; L.hitTri = tri; L.hitU = u; L.hitV = v; }
+    else if (t < L.second) L.second = t;
+}
+
+__device__ __forceinline__ void stepTopRay(StepLane& L, V3 o, V3 d)
+{
+    const float4 i0 = make_float4(1, 0, 0, 0), i1 = make_float4(0, 1, 0, 0), i2 = make_float4(0, 0, 1, 0);
+    L.ro = mulPointRows(o, i0, i1, i2);
+    L.rd = normalize(mulDirRows(d, i0, i1, i2));
+    L.ridir = rcp3(L.rd);
+    L.inst = kTraceTop;
+}
+
+/* `needPop`: the current reference is used up, take the next one off the stack.  Then, if the lane stands on a
+ * triangle leaf, open it: the range goes to triNext/triEnd and the node after it comes off the stack as well
+ * (which may again be a leaf; it is opened when the range is exhausted). */
+__device__ __forceinline__ void stepAdvance(StepLane& L, const uint32_t* stack, bool needPop)
+{
+    OKRT_CHECK(L.sp >= 0 && L.sp <= (int)kFastStackCapacity);
+    if (needPop) { if (L.sp) L.cur = stack[--L.sp]; else L.cur = kTraceDone; }
+    if ((L.cur & kRefTagMask) == kRefTriLeaf) {                  /* done / exit / instance references carry tag 11 */
+        L.triNext = L.cur & (kMaxTriIndex - 1u);
+        L.triEnd = L.triNext + ((L.cur >> 27) & 7u) + 1u;
+        if (L.sp) L.cur = stack[--L.sp]; else L.cur = kTraceDone;
+    }
+}
+
+__device__ __forceinline__ void stepInit(const DeviceScene& s, StepLane& L, const uint32_t* stack, uint32_t numSpheres, V3 o, V3 d)
+{
+    L.best = OKRT_FLT_MAX; L.second = OKRT_FLT_MAX;
+    L.hitRec = 0x3FFFFFFFu; L.hitTri = 0xFFFFFFFFu; L.hitU = 0.f; L.hitV = 0.f;
+    L.sp = 0; L.triNext = 0u; L.triEnd = 0u;
+    stepTopRay(L, o, d);
+    for (uint32_t i = 0; i < numSpheres; i++) {                /* RaytracerCS.hlsl:232-242 */
+        const okrt_sphere& sp = s.spheres[i];
+        const float t = rayAndSphere(o, d, v3(sp.position), sp.radius);
+        if (t > 0.f) stepCandidate(L, t, (1u << 30) | i, 0xFFFFFFFFu, 0.f, 0.f);
+    }
+    L.cur = s.topRef == kRefNone ? kTraceDone : s.topRef;
+    stepAdvance(L, stack, false);
+}
+
+/* one child-pair node */
+__device__ __forceinline__ void stepNode(const DeviceScene& s, StepLane& L, uint32_t* stack)
+{
+    OKRT_CHECK(L.cur < s.numFastNodes);
+    const float4* q = s.fastNodes + (size_t)L.cur * 4;
+    const float4 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3);
+    const float limit = relaxedLimit(L.best);
+    const float n0 = rayAndAABBDist(L.ro, L.ridir, v3(q0.x, q0.y, q0.z), v3(q1.x, q1.y, q1.z));
+    const float n1 = rayAndAABBDist(L.ro, L.ridir, v3(q2.x, q2.y, q2.z), v3(q3.x, q3.y, q3.z));
+    const uint32_t r0 = __float_as_uint(q0.w), r1 = __float_as_uint(q1.w);
+    const bool h0 = n0 < limit && r0 != kRefNone;
+    const bool h1 = n1 < limit && r1 != kRefNone;
+    const bool firstIs1 = h1 && (!h0 || n1 < n0);
+    OKRT_CHECK(L.sp >= 0 && L.sp < (int)kFastStackCapacity);
+    if (h0 && h1) stack[L.sp++] = firstIs1 ? r0 : r1;
+    L.cur = firstIs1 ? r1 : r0;
+    stepAdvance(L, stack, !(h0 || h1));
+}
+
+/* one triangle of the opened leaf */
+__device__ __forceinline__ void stepTriangle(const DeviceScene& s, StepLane& L, const uint32_t* stack)
+{
+    const uint32_t j = L.triNext++;
+    OKRT_CHECK(j < s.numTris);
+    const float4* tp = s.fastTris + (size_t)j * 3;
+    const float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
+    float bu = 0.f, bv = 0.f;
+    float t = rayAndTriangle(L.ro, L.rd, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), bu, bv);
+    if (t > 0.f) {
+        V3 w = L.rd * t;                                        /* RaytracerCS.hlsl:312-314; T == I for merged instances */
+        uint32_t rec = kMergedRec;
+        if (L.inst != kTraceTop) {
+            const float4* r = s.fastInstances + (size_t)L.inst * 8;
+            w = mulDirRows(w, __ldg(r + 3), __ldg(r + 4), __ldg(r + 5));
+            rec = L.inst;
+        }
+        t = length(w);
+        stepCandidate(L, t, (2u << 30) | rec, j, bu, bv);
+    }
+    if (L.triNext == L.triEnd) stepAdvance(L, stack, false);
+}
+
+/* oct-tree boxes on the way to an instance, world ray (RaytracerCS.hlsl:262): all must be HIT */
+__device__ __forceinline__ bool octChainHitWorld(const DeviceScene& s, V3 o, V3 d, uint32_t octNode)
+{
+    const V3 idirWorld = rcp3(d);
+    for (uint32_t on = octNode; on != 0xFFFFFFFFu; on = __ldg(s.octParent + on)) {
+        const okrt_octree_node& node = s.octNodes[on];
+        if (!(rayAndAABBDist(o, idirWorld, v3(node.boundingBox.min), v3(node.boundingBox.max)) < OKRT_FLT_MAX)) return false;
+    }
+    return true;
+}
+
+/* the rare references: entering a generic (non-merged) instance, leaving one */
+__device__ __forceinline__ void stepMisc(const DeviceScene& s, StepLane& L, uint32_t* stack, V3 o, V3 d)
+{
+    bool pop = true;
+    if (L.cur == kTraceExitInstance) {
+        stepTopRay(L, o, d);
+    } else {                                                     /* generic instance leaf */
+        const uint32_t recIdx = L.cur & ~kRefTagMask;
+        OKRT_CHECK(recIdx < s.numFastInstances);
+        const float4* rec = s.fastInstances + (size_t)recIdx * 8;
+        const float4 r6 = __ldg(rec + 6), r7 = __ldg(rec + 7);
+        if (octChainHitWorld(s, o, d, __float_as_uint(r7.y))) {
+            const float4 i0 = __ldg(rec), i1 = __ldg(rec + 1), i2 = __ldg(rec + 2);
+            const V3 lo = mulPointRows(o, i0, i1, i2);
+            const V3 ld = normalize(mulDirRows(d, i0, i1, i2));
+            const V3 lidir = rcp3(ld);
+            const float4 a0 = __ldg(rec + 3), a1 = __ldg(rec + 4), a2 = __ldg(rec + 5);
+            /* the mesh's root box (RaytracerCS.hlsl:285 on the first popped node) */
+            if (rayAndAABBDist(lo, lidir, v3(a0.w, a1.w, a2.w), v3(r6.x, r6.y, r6.z)) < relaxedLimit(L.best)) {
+                stack[L.sp++] = kTraceExitInstance;
+                L.ro = lo; L.rd = ld; L.ridir = lidir;
+                L.inst = recIdx;
+                L.cur = __float_as_uint(r7.x);
+                pop = false;
+            }
+        }
+    }
+    stepAdvance(L, stack, pop);
+}
+
+/* the finished lane's hit; returns true when the reference order has to decide */
+__device__ __forceinline__ bool stepResult(const DeviceScene& s, const StepLane& L, V3 o, V3 d, Hit& hit, float& seed)
+{
+    seed = L.best;                                               /* the reference's answer lies inside the window above it */
+    hit.distance = L.best;
+    hit.kind = L.best < OKRT_FLT_MAX ? (L.hitRec >> 30) : 0u;
+    hit.idx = hit.kind ? (L.hitRec & 0x3FFFFFFFu) : 0xFFFFFFFFu;
+    hit.tri = L.hitTri; hit.u = L.hitU; hit.v = L.hitV;
+    bool ambiguous = L.second < relaxedLimit(L.best);
+    if (hit.kind == 2u) {
+        const bool merged = hit.idx == kMergedRec;
+        OKRT_CHECK(hit.tri < s.numTris);
+        const uint32_t rec = merged ? __ldg(s.triOwner + hit.tri) : hit.idx;
+        OKRT_CHECK(rec < s.numFastInstances);
+        const float4 r7 = __ldg(s.fastInstances + (size_t)rec * 8 + 7);
+        hit.idx = __float_as_uint(r7.z);
+        if (merged && !octChainHitWorld(s, o, d, __float_as_uint(r7.y))) { ambiguous = true; seed = OKRT_FLT_MAX; }   /* the reference never reaches this instance: no bound known */
+    }
+    return ambiguous;
 }
 
 /* ------------------------------------------------------------ hit resolve

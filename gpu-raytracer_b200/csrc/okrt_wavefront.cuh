@@ -33,6 +33,8 @@ struct WavefrontBuffers {
     uint32_t* hitB;        /* kind << 30 | instance-or-sphere index */
     uint32_t* queue[2];    /* ping-pong queues of path slots */
     uint32_t* counts;      /* [2*bounce] number of queued paths, [2*bounce+1] trace work counter; zeroed per frame */
+    uint32_t* fallbackQueue;   /* paths whose hit the reference-order kernel has to decide (this bounce) */
+    uint32_t* fallbackCounts;  /* [bounce]; zeroed per frame (lives behind counts) */
 };
 constexpr uint32_t kMaxWavefrontBounces = 63;
 constexpr uint32_t kMaxQueueCounts = 2 * (kMaxWavefrontBounces + 2);
@@ -126,7 +128,37 @@ traceExactKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ 
     }
 }
 
-/* Near-first traversal (TraceLane / traceRound, okrt_kernels.cuh) with lane refill. */
+/* The rays traceFastKernel could not decide (two candidates inside the window, or an oct-tree chain that the
+ * winner's instance fails): reference order, full warps, one launch per bounce. */
+__global__ void __launch_bounds__(128)
+traceFallbackKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ FrameParams fp, const WavefrontBuffers wb, uint32_t bounce)
+{
+    const uint32_t count = wb.fallbackCounts[bounce];
+    const uint32_t numSpheres = fp.rd.numSpheres < s.numSpheres ? fp.rd.numSpheres : s.numSpheres;
+    /* one ray per WARP, traced by lane 0: 32 unrelated reference-order traversals in one warp diverge completely and
+     * serialise (measured: ~1 ms per launch for ~2000 rays); with a warp each the launch lasts one traversal */
+    const uint32_t warpsPerGrid = gridDim.x * (blockDim.x >> 5);
+    if ((threadIdx.x & 31u) == 0u)
+    for (uint32_t k = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); k < count; k += warpsPerGrid) {
+        const uint32_t path = wb.fallbackQueue[k];
+        const float4 ro = wb.rayO[path], rdv = wb.rayD[path];
+        const float limit = relaxedLimit(wb.hitA[path].x);          /* the near-first traversal's closest distance */
+        Hit hit;
+        uint32_t bb = 0u, tc = 0u;
+        traverseExact(s, numSpheres, v3(ro.x, ro.y, ro.z), v3(rdv.x, rdv.y, rdv.z), hit, bb, tc, limit);
+        wb.hitA[path] = make_float4(hit.distance, hit.u, hit.v, __uint_as_float(hit.tri));
+        wb.hitB[path] = (hit.kind << 30) | (hit.idx & 0x3FFFFFFFu);
+        if (fp.aov && bounce == 0u) fp.aov[__float_as_uint(rdv.w)].flags = 1u;
+    }
+    if (blockIdx.x == 0u && threadIdx.x == 0u && count) atomicAdd(fp.counters + 1, (unsigned long long)count);
+}
+
+/* Near-first traversal in step form (StepLane, okrt_kernels.cuh): persistent warps, lane refill, and a warp
+ * vote per iteration between "every lane that stands on an interior node tests one child pair" and "every
+ * lane with an opened leaf tests one triangle". */
+#ifndef OKRT_REFILL_IDLE
+#define OKRT_REFILL_IDLE 8          /* refill as soon as this many lanes have no ray */
+#endif
 __global__ void __launch_bounds__(kTraceBlockThreads, OKRT_TRACE_MIN_BLOCKS)
 traceFastKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ FrameParams fp, const WavefrontBuffers wb,
                 const uint32_t* __restrict__ queueIn, uint32_t bounce)
@@ -138,64 +170,75 @@ traceFastKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ F
     const uint32_t numSpheres = fp.rd.numSpheres < s.numSpheres ? fp.rd.numSpheres : s.numSpheres;
 
     uint32_t stack[kFastStackCapacity];
-    TraceLane L;
-    L.cur = kTraceDone; L.sp = 0; L.path = 0u; L.inst = kTraceTop;
+    StepLane L;
+    L.cur = kTraceDone; L.sp = 0; L.path = 0u; L.inst = kTraceTop; L.triNext = 0u; L.triEnd = 0u;
     bool have = false;                        /* this lane owns a ray whose result is not written yet */
     uint32_t next = 0u, end = 0u;             /* warp-uniform: unclaimed part of the warp's current chunk */
     bool exhausted = false;                   /* warp-uniform */
-    uint32_t fallbacks = 0u;
 
     for (;;) {
-        /* ---- refill */
-        uint32_t need = __ballot_sync(0xFFFFFFFFu, !have);
-        while (need != 0u && !exhausted) {
-            if (next == end) {
-                uint32_t base = 0u;
-                if (lane == 0u) base = atomicAdd(workCounter, kTraceChunk);
-                base = __shfl_sync(0xFFFFFFFFu, base, 0);
-                if (base >= count) { exhausted = true; break; }
-                next = base; end = min(base + kTraceChunk, count);
-            }
-            const uint32_t want = __popc(need), avail = end - next;
-            const uint32_t take = want < avail ? want : avail;
-            const uint32_t rank = __popc(need & laneMaskLt);
-            if (!have && rank < take) {
-                const uint32_t k = next + rank;
-                L.path = queueIn ? __ldg(queueIn + k) : k;
+        const bool wantTri = have && L.triNext < L.triEnd;
+        const bool wantNode = have && !wantTri && (L.cur & kRefTagMask) == kRefInterior;
+        const bool wantMisc = have && !wantTri && !wantNode && L.cur != kTraceDone;
+        const uint32_t mTri = __ballot_sync(0xFFFFFFFFu, wantTri);
+        const uint32_t mNode = __ballot_sync(0xFFFFFFFFu, wantNode);
+        const uint32_t mMisc = __ballot_sync(0xFFFFFFFFu, wantMisc);
+        const uint32_t busy = mTri | mNode | mMisc;
+
+        if (mMisc) {                                                    /* instance entry / exit: rare, handled at once */
+            if (wantMisc) {
                 const float4 ro = wb.rayO[L.path], rdv = wb.rayD[L.path];
-                laneInit(s, L, numSpheres, v3(ro.x, ro.y, ro.z), v3(rdv.x, rdv.y, rdv.z));
-                have = true;
+                stepMisc(s, L, stack, v3(ro.x, ro.y, ro.z), v3(rdv.x, rdv.y, rdv.z));
             }
-            next += take;
-            need = __ballot_sync(0xFFFFFFFFu, !have);
-        }
-        if (__ballot_sync(0xFFFFFFFFu, have) == 0u) break;
-
-        /* ---- traverse until enough lanes have finished to make a refill worthwhile */
-        const uint32_t keepRunning = exhausted ? 1u : (uint32_t)OKRT_KEEP_RUNNING;
-        for (;;) {
-            if (have && L.cur != kTraceDone) traceRound(s, L, stack);
-            const uint32_t running = __popc(__ballot_sync(0xFFFFFFFFu, have && L.cur != kTraceDone));
-            if (running < keepRunning) break;
+            continue;
         }
 
-        /* ---- finished lanes write their hit record */
-        if (have && L.cur == kTraceDone) {
-            Hit hit;
-            uint32_t flag = 0u;
-            if (laneResult(L, hit)) {                                      /* ambiguous: ask the reference order */
-                uint32_t bb = 0u, tc = 0u;
-                traverseExact(s, numSpheres, L.o, L.d, hit, bb, tc);
-                fallbacks++; flag = 1u;
+        const uint32_t idle = 32u - (uint32_t)__popc(busy);
+        if (busy == 0u || (!exhausted && idle >= (uint32_t)OKRT_REFILL_IDLE)) {
+            /* ---- finished lanes write their hit record (or queue the ray for the reference order) */
+            if (have && !(busy & (1u << lane))) {
+                const float4 ro = wb.rayO[L.path], rdv = wb.rayD[L.path];
+                Hit hit;
+                float seed;
+                if (stepResult(s, L, v3(ro.x, ro.y, ro.z), v3(rdv.x, rdv.y, rdv.z), hit, seed)) {
+                    wb.fallbackQueue[atomicAdd(wb.fallbackCounts + bounce, 1u)] = L.path;
+                    wb.hitA[L.path].x = seed;                            /* bounds the reference-order traversal's search */
+                } else {
+                    wb.hitA[L.path] = make_float4(hit.distance, hit.u, hit.v, __uint_as_float(hit.tri));
+                    wb.hitB[L.path] = (hit.kind << 30) | (hit.idx & 0x3FFFFFFFu);
+                }
+                have = false;
             }
-            wb.hitA[L.path] = make_float4(hit.distance, hit.u, hit.v, __uint_as_float(hit.tri));
-            wb.hitB[L.path] = (hit.kind << 30) | (hit.idx & 0x3FFFFFFFu);
-            if (fp.aov && bounce == 0u && flag) fp.aov[__float_as_uint(wb.rayD[L.path].w)].flags = 1u;
-            have = false;
+            /* ---- refill */
+            uint32_t need = __ballot_sync(0xFFFFFFFFu, !have);
+            while (need != 0u && !exhausted) {
+                if (next == end) {
+                    uint32_t base = 0u;
+                    if (lane == 0u) base = atomicAdd(workCounter, kTraceChunk);
+                    base = __shfl_sync(0xFFFFFFFFu, base, 0);
+                    if (base >= count) { exhausted = true; break; }
+                    next = base; end = min(base + kTraceChunk, count);
+                }
+                const uint32_t want = __popc(need), avail = end - next;
+                const uint32_t take = want < avail ? want : avail;
+                const uint32_t rank = __popc(need & laneMaskLt);
+                if (!have && rank < take) {
+                    const uint32_t k = next + rank;
+                    L.path = queueIn ? __ldg(queueIn + k) : k;
+                    const float4 ro = wb.rayO[L.path], rdv = wb.rayD[L.path];
+                    stepInit(s, L, stack, numSpheres, v3(ro.x, ro.y, ro.z), v3(rdv.x, rdv.y, rdv.z));
+                    have = true;
+                }
+                next += take;
+                need = __ballot_sync(0xFFFFFFFFu, !have);
+            }
+            if (__ballot_sync(0xFFFFFFFFu, have) == 0u) break;
+            continue;
         }
+
+        if (__popc(mNode) >= __popc(mTri)) { if (wantNode) stepNode(s, L, stack); }
+        else { if (wantTri) stepTriangle(s, L, stack); }
     }
-    const uint32_t fbSum = __reduce_add_sync(0xFFFFFFFFu, fallbacks);
-    if (lane == 0u && fbSum) atomicAdd(fp.counters + 1, (unsigned long long)fbSum);
 }
 
 /* ------------------------------------------------------------------- shade

@@ -47,7 +47,7 @@ def text(key):
         except Exception: src[f] = []
     L = src[f]
     return L[key[1] - 1].strip()[:90] if 0 < key[1] <= len(L) else ""
-print("%7s %7s %6s %5s  %s" % ("samp%", "inst%", "thr/i", "sass", "line"))
+print("%7s %7s %6s %5s %9s  %s" % ("samp%", "inst%", "thr/i", "sass", "Mexec", "line"))
 for key, a in sorted(agg.items(), key=lambda kv: -kv[1][0])[:top]:
-    print("%6.2f%% %6.2f%% %6.1f %5d  %s:%s %s | %s" % (100.0 * a[0] / max(1, tot_s), 100.0 * a[1] / max(1, tot_i), a[2] / max(1, a[1]), a[3],
+    print("%6.2f%% %6.2f%% %6.1f %5d %9.2f  %s:%s %s | %s" % (100.0 * a[0] / max(1, tot_s), 100.0 * a[1] / max(1, tot_i), a[2] / max(1, a[1]), a[3], a[1] / max(1, a[3]) / 1e6,
           key[0] if key else "?", key[1] if key else "?", (key[2][:30] if key else ""), text(key)))
