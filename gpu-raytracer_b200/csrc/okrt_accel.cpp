@@ -37,6 +37,13 @@ struct Builder {
     void setChild(uint32_t pair, int which, const okrt_aabb& box, uint32_t ref)
     {
         Float4* q = &out.nodes[(size_t)pair * 4];
+        if (ref == kRefNone) {                 /* empty child: a NaN box fails every comparison of the slab test */
+            const float nan = std::nanf("");
+            q[which * 2 + 0].x = q[which * 2 + 0].y = q[which * 2 + 0].z = nan;
+            q[which * 2 + 1].x = q[which * 2 + 1].y = q[which * 2 + 1].z = nan;
+            if (which == 0) q[0].w = bitsToFloat(ref); else q[1].w = bitsToFloat(ref);
+            return;
+        }
         q[which * 2 + 0].x = box.min[0]; q[which * 2 + 0].y = box.min[1]; q[which * 2 + 0].z = box.min[2];
         q[which * 2 + 1].x = box.max[0]; q[which * 2 + 1].y = box.max[1]; q[which * 2 + 1].z = box.max[2];
         if (which == 0) q[0].w = bitsToFloat(ref); else q[1].w = bitsToFloat(ref);
@@ -119,10 +126,16 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
     out = FastLayout();
 
     /* triangles: 3 x float4 */
+    /* triangles: p2 | E1 = p0 - p2 | E2 = p1 - p2 (GPU-Utilities.hlsli:124: the same float32 subtractions, done once) */
     out.tris.resize((size_t)numTris * 3);
-    for (uint32_t t = 0; t < numTris; t++)
-        for (int v = 0; v < 3; v++)
-            out.tris[(size_t)t * 3 + v] = Float4{tris[t].position[v][0], tris[t].position[v][1], tris[t].position[v][2], 0.f};
+    for (uint32_t t = 0; t < numTris; t++) {
+        const float (*p)[3] = tris[t].position;
+        volatile float e[6];
+        for (int k = 0; k < 3; k++) { e[k] = p[0][k] - p[2][k]; e[3 + k] = p[1][k] - p[2][k]; }
+        out.tris[(size_t)t * 3 + 0] = Float4{p[2][0], p[2][1], p[2][2], e[0]};
+        out.tris[(size_t)t * 3 + 1] = Float4{e[1], e[2], e[3], e[4]};
+        out.tris[(size_t)t * 3 + 2] = Float4{e[5], 0.f, 0.f, 0.f};
+    }
 
     /* oct-tree: parents, reachability, reference stack bound */
     out.octParent.assign(numOctNodes, 0xFFFFFFFFu);

@@ -354,6 +354,8 @@ __device__ __noinline__ void traverseExact(const DeviceScene& s, uint32_t numSph
     }
 }
 
+__device__ __forceinline__ float rayAndTriangleEdges(V3 o, V3 d, V3 p2, V3 E1, V3 E2, float& u, float& v);
+
 /* ------------------------------------------------ near-first traversal
  * Same boxes, same triangles, same arithmetic — different visiting order and a different culling
  * hierarchy at the top.  Correctness argument (DESIGN.md "Order independence"): with relaxed culling
@@ -466,7 +468,7 @@ __device__ __forceinline__ void traceRound(const DeviceScene& s, TraceLane& L, u
                 const float4* tp = s.fastTris + (size_t)j * 3;
                 const float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
                 float bu = 0.f, bv = 0.f;
-                float t = rayAndTriangle(L.ro, L.rd, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), bu, bv);
+                float t = rayAndTriangleEdges(L.ro, L.rd, v3(a.x, a.y, a.z), v3(a.w, b.x, b.y), v3(b.z, b.w, c.x), bu, bv);   /* p2 | E1 | E2 */
                 if (t <= 0.f) continue;
                 V3 w = L.rd * t;                                        /* RaytracerCS.hlsl:312-314 */
                 uint32_t rec = L.inst;
@@ -533,12 +535,12 @@ __device__ __forceinline__ bool traverseFast(const DeviceScene& s, uint32_t numS
 }
 
 /* ------------------------------------------- near-first traversal, step form
- * The same traversal as traceRound(), cut into STEPS of similar cost so that a warp can vote which kind of step
+ * The same traversal as traceRound(), cut into STEPS of similar cost so that a warp can choose which kind of step
  * to run next (traceFastKernel, okrt_wavefront.cuh).  ncu on the while-while form (profiles/r1_d_*): 9.2 of 32
  * lanes active per instruction — a round lasts as long as its slowest lane's run of interior nodes, and the
  * per-candidate oct-tree chain test ran with 2.3 lanes.  Here
- *   - a lane that pops a triangle leaf only records the range (triNext, triEnd) and already holds its next node;
- *   - one node step = one child-pair node, one triangle step = one triangle;
+ *   - one node step = one child-pair node, one triangle step = one triangle of the leaf the lane stands on;
+ *   - the stack holds a sentinel at the bottom, so a pop is one unconditional load;
  *   - the oct-tree chain of a merged instance is tested once, for the winning triangle, when the ray finishes
  *     (a failed chain or two candidates inside the window send the ray to the reference-order kernel).
  * Arithmetic per box and per triangle is unchanged, so are the results. */
@@ -548,9 +550,9 @@ struct StepLane {
     uint32_t hitRec;         /* 1<<30 | sphere, or 2<<30 | (instance record, or 0x3FFFFFFF = "merged: look up triOwner") */
     uint32_t hitTri;
     float hitU, hitV;
-    uint32_t cur;            /* next node reference (interior / instance / exit marker / leaf not yet opened / done) */
-    uint32_t triNext, triEnd;/* triangles of the opened leaf still to test */
-    int sp;
+    uint32_t cur;            /* reference the lane stands on: interior / triangle leaf / instance / exit marker / done */
+    uint32_t triNext;        /* next triangle of the leaf in `cur` */
+    int sp;                  /* next free stack slot; slot 0 holds kTraceDone */
     uint32_t inst;           /* instance record inside a generic instance; kTraceTop at the top level */
     uint32_t path;
 };
@@ -571,63 +573,89 @@ __device__ __forceinline__ void stepTopRay(StepLane& L, V3 o, V3 d)
     L.inst = kTraceTop;
 }
 
-/* `needPop`: the current reference is used up, take the next one off the stack.  Then, if the lane stands on a
- * triangle leaf, open it: the range goes to triNext/triEnd and the node after it comes off the stack as well
- * (which may again be a leaf; it is opened when the range is exhausted). */
-__device__ __forceinline__ void stepAdvance(StepLane& L, const uint32_t* stack, bool needPop)
+/* the lane moves to `ref`; a triangle leaf starts at its first triangle */
+__device__ __forceinline__ void stepEnter(StepLane& L, uint32_t ref)
 {
-    OKRT_CHECK(L.sp >= 0 && L.sp <= (int)kFastStackCapacity);
-    if (needPop) { if (L.sp) L.cur = stack[--L.sp]; else L.cur = kTraceDone; }
-    if ((L.cur & kRefTagMask) == kRefTriLeaf) {                  /* done / exit / instance references carry tag 11 */
-        L.triNext = L.cur & (kMaxTriIndex - 1u);
-        L.triEnd = L.triNext + ((L.cur >> 27) & 7u) + 1u;
-        if (L.sp) L.cur = stack[--L.sp]; else L.cur = kTraceDone;
-    }
+    L.cur = ref;
+    if ((ref & kRefTagMask) == kRefTriLeaf) L.triNext = ref & (kMaxTriIndex - 1u);
+}
+__device__ __forceinline__ void stepPop(StepLane& L, const uint32_t* stack)
+{
+    OKRT_CHECK(L.sp >= 1 && L.sp <= (int)kFastStackCapacity);
+    stepEnter(L, stack[--L.sp]);
 }
 
-__device__ __forceinline__ void stepInit(const DeviceScene& s, StepLane& L, const uint32_t* stack, uint32_t numSpheres, V3 o, V3 d)
+__device__ __forceinline__ void stepInit(const DeviceScene& s, StepLane& L, uint32_t* stack, uint32_t numSpheres, V3 o, V3 d)
 {
     L.best = OKRT_FLT_MAX; L.second = OKRT_FLT_MAX;
     L.hitRec = 0x3FFFFFFFu; L.hitTri = 0xFFFFFFFFu; L.hitU = 0.f; L.hitV = 0.f;
-    L.sp = 0; L.triNext = 0u; L.triEnd = 0u;
+    stack[0] = kTraceDone; L.sp = 1;
     stepTopRay(L, o, d);
     for (uint32_t i = 0; i < numSpheres; i++) {                /* RaytracerCS.hlsl:232-242 */
         const okrt_sphere& sp = s.spheres[i];
         const float t = rayAndSphere(o, d, v3(sp.position), sp.radius);
         if (t > 0.f) stepCandidate(L, t, (1u << 30) | i, 0xFFFFFFFFu, 0.f, 0.f);
     }
-    L.cur = s.topRef == kRefNone ? kTraceDone : s.topRef;
-    stepAdvance(L, stack, false);
+    stepEnter(L, s.topRef == kRefNone ? kTraceDone : s.topRef);
 }
 
-/* one child-pair node */
+/* GPU-Utilities.hlsli:183-197 for one box, as the three conditions the traversal needs: hit, in front, before `limit` */
+__device__ __forceinline__ bool boxPasses(V3 o, V3 idir, float4 lo, float4 hi, float limit, float& distNear)
+{
+    const V3 tMin = (v3(lo.x, lo.y, lo.z) - o) * idir;
+    const V3 tMax = (v3(hi.x, hi.y, hi.z) - o) * idir;
+    const float distFar = fminf(fminf(fmaxf(tMin.x, tMax.x), fmaxf(tMin.y, tMax.y)), fmaxf(tMin.z, tMax.z));
+    distNear = fmaxf(fmaxf(fminf(tMin.x, tMax.x), fminf(tMin.y, tMax.y)), fminf(tMin.z, tMax.z));
+    return distFar >= distNear && distFar > 0.f && distNear < limit;
+}
+
+/* one child-pair node.  Empty children carry NaN boxes (okrt_accel.cpp), which never pass. */
 __device__ __forceinline__ void stepNode(const DeviceScene& s, StepLane& L, uint32_t* stack)
 {
     OKRT_CHECK(L.cur < s.numFastNodes);
     const float4* q = s.fastNodes + (size_t)L.cur * 4;
     const float4 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3);
     const float limit = relaxedLimit(L.best);
-    const float n0 = rayAndAABBDist(L.ro, L.ridir, v3(q0.x, q0.y, q0.z), v3(q1.x, q1.y, q1.z));
-    const float n1 = rayAndAABBDist(L.ro, L.ridir, v3(q2.x, q2.y, q2.z), v3(q3.x, q3.y, q3.z));
+    float n0, n1;
+    const bool h0 = boxPasses(L.ro, L.ridir, q0, q1, limit, n0);
+    const bool h1 = boxPasses(L.ro, L.ridir, q2, q3, limit, n1);
     const uint32_t r0 = __float_as_uint(q0.w), r1 = __float_as_uint(q1.w);
-    const bool h0 = n0 < limit && r0 != kRefNone;
-    const bool h1 = n1 < limit && r1 != kRefNone;
     const bool firstIs1 = h1 && (!h0 || n1 < n0);
-    OKRT_CHECK(L.sp >= 0 && L.sp < (int)kFastStackCapacity);
+    OKRT_CHECK(L.sp >= 1 && L.sp < (int)kFastStackCapacity);
     if (h0 && h1) stack[L.sp++] = firstIs1 ? r0 : r1;
-    L.cur = firstIs1 ? r1 : r0;
-    stepAdvance(L, stack, !(h0 || h1));
+    uint32_t nxt = firstIs1 ? r1 : r0;
+    if (!(h0 || h1)) nxt = stack[--L.sp];
+    stepEnter(L, nxt);
 }
 
-/* one triangle of the opened leaf */
+/* GPU-Utilities.hlsli:117-155 [Q6] with E1 = p0 - p2 and E2 = p1 - p2 formed at upload (the same float32 subtraction) */
+__device__ __forceinline__ float rayAndTriangleEdges(V3 o, V3 d, V3 p2, V3 E1, V3 E2, float& u, float& v)
+{
+    const float EPSILON = 0.000001f;
+    const V3 cross1 = cross(d, E2);
+    const float determinant = dot(E1, cross1);
+    if (determinant < EPSILON && determinant > -EPSILON) return -1.f;
+    const float inverseDet = 1.f / determinant;
+    const V3 rayMoved = o - p2;
+    u = dot(rayMoved, cross1) * inverseDet;
+    if (u < -EPSILON) return -1.f;
+    const V3 cross2 = cross(rayMoved, E1);
+    v = dot(d, cross2) * inverseDet;
+    if (v < -EPSILON || u + v > 1.0f) return -1.f;
+    const float t1 = dot(E2, cross2) * inverseDet;
+    if (t1 < -EPSILON) return -1.f;
+    return t1;
+}
+
+/* one triangle of the leaf the lane stands on */
 __device__ __forceinline__ void stepTriangle(const DeviceScene& s, StepLane& L, const uint32_t* stack)
 {
     const uint32_t j = L.triNext++;
     OKRT_CHECK(j < s.numTris);
     const float4* tp = s.fastTris + (size_t)j * 3;
-    const float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
+    const float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);       /* p2 | E1 | E2 */
     float bu = 0.f, bv = 0.f;
-    float t = rayAndTriangle(L.ro, L.rd, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), bu, bv);
+    float t = rayAndTriangleEdges(L.ro, L.rd, v3(a.x, a.y, a.z), v3(a.w, b.x, b.y), v3(b.z, b.w, c.x), bu, bv);
     if (t > 0.f) {
         V3 w = L.rd * t;                                        /* RaytracerCS.hlsl:312-314; T == I for merged instances */
         uint32_t rec = kMergedRec;
@@ -639,7 +667,8 @@ __device__ __forceinline__ void stepTriangle(const DeviceScene& s, StepLane& L, 
         t = length(w);
         stepCandidate(L, t, (2u << 30) | rec, j, bu, bv);
     }
-    if (L.triNext == L.triEnd) stepAdvance(L, stack, false);
+    const uint32_t end = (L.cur & (kMaxTriIndex - 1u)) + ((L.cur >> 27) & 7u) + 1u;
+    if (L.triNext == end) stepPop(L, stack);
 }
 
 /* oct-tree boxes on the way to an instance, world ray (RaytracerCS.hlsl:262): all must be HIT */
@@ -656,7 +685,6 @@ __device__ __forceinline__ bool octChainHitWorld(const DeviceScene& s, V3 o, V3 
 /* the rare references: entering a generic (non-merged) instance, leaving one */
 __device__ __forceinline__ void stepMisc(const DeviceScene& s, StepLane& L, uint32_t* stack, V3 o, V3 d)
 {
-    bool pop = true;
     if (L.cur == kTraceExitInstance) {
         stepTopRay(L, o, d);
     } else {                                                     /* generic instance leaf */
@@ -672,15 +700,16 @@ __device__ __forceinline__ void stepMisc(const DeviceScene& s, StepLane& L, uint
             const float4 a0 = __ldg(rec + 3), a1 = __ldg(rec + 4), a2 = __ldg(rec + 5);
             /* the mesh's root box (RaytracerCS.hlsl:285 on the first popped node) */
             if (rayAndAABBDist(lo, lidir, v3(a0.w, a1.w, a2.w), v3(r6.x, r6.y, r6.z)) < relaxedLimit(L.best)) {
+                OKRT_CHECK(L.sp >= 1 && L.sp < (int)kFastStackCapacity);
                 stack[L.sp++] = kTraceExitInstance;
                 L.ro = lo; L.rd = ld; L.ridir = lidir;
                 L.inst = recIdx;
-                L.cur = __float_as_uint(r7.x);
-                pop = false;
+                stepEnter(L, __float_as_uint(r7.x));
+                return;
             }
         }
     }
-    stepAdvance(L, stack, pop);
+    stepPop(L, stack);
 }
 
 /* the finished lane's hit; returns true when the reference order has to decide */

@@ -40,7 +40,7 @@ constexpr uint32_t kMaxWavefrontBounces = 63;
 constexpr uint32_t kMaxQueueCounts = 2 * (kMaxWavefrontBounces + 2);
 constexpr int kTraceBlockThreads = 128;
 #ifndef OKRT_TRACE_MIN_BLOCKS
-#define OKRT_TRACE_MIN_BLOCKS 6
+#define OKRT_TRACE_MIN_BLOCKS 8
 #endif
 #ifndef OKRT_KEEP_RUNNING
 #define OKRT_KEEP_RUNNING 16
@@ -153,11 +153,19 @@ traceFallbackKernel(const __grid_constant__ DeviceScene s, const __grid_constant
     if (blockIdx.x == 0u && threadIdx.x == 0u && count) atomicAdd(fp.counters + 1, (unsigned long long)count);
 }
 
-/* Near-first traversal in step form (StepLane, okrt_kernels.cuh): persistent warps, lane refill, and a warp
- * vote per iteration between "every lane that stands on an interior node tests one child pair" and "every
- * lane with an opened leaf tests one triangle". */
+/* Near-first traversal in step form (StepLane, okrt_kernels.cuh): persistent warps with lane refill.  A warp
+ * alternates between a NODE phase (every lane that stands on an interior node tests one child pair per
+ * iteration) and a TRIANGLE phase (every lane that stands on a leaf tests one triangle per iteration); a phase
+ * ends when fewer than a threshold of its lanes are left, so that no phase drags on for a few stragglers while
+ * the other lanes wait (the while-while form waits for the LAST lane: 9.2 of 32 lanes active, profiles/r1_d_*). */
 #ifndef OKRT_REFILL_IDLE
-#define OKRT_REFILL_IDLE 8          /* refill as soon as this many lanes have no ray */
+#define OKRT_REFILL_IDLE 16         /* refill as soon as this many lanes have no ray */
+#endif
+#ifndef OKRT_NODE_KEEP
+#define OKRT_NODE_KEEP 8            /* stay in the node phase while at least this many lanes want a node step */
+#endif
+#ifndef OKRT_TRI_KEEP
+#define OKRT_TRI_KEEP 8             /* stay in the triangle phase while at least this many lanes want a triangle step */
 #endif
 __global__ void __launch_bounds__(kTraceBlockThreads, OKRT_TRACE_MIN_BLOCKS)
 traceFastKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ FrameParams fp, const WavefrontBuffers wb,
@@ -171,32 +179,32 @@ traceFastKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ F
 
     uint32_t stack[kFastStackCapacity];
     StepLane L;
-    L.cur = kTraceDone; L.sp = 0; L.path = 0u; L.inst = kTraceTop; L.triNext = 0u; L.triEnd = 0u;
+    L.cur = kTraceDone; L.sp = 1; L.path = 0u; L.inst = kTraceTop; L.triNext = 0u;
+    stack[0] = kTraceDone;
     bool have = false;                        /* this lane owns a ray whose result is not written yet */
     uint32_t next = 0u, end = 0u;             /* warp-uniform: unclaimed part of the warp's current chunk */
     bool exhausted = false;                   /* warp-uniform */
 
+    /* lanes without a ray stand on kTraceDone, which belongs to no phase */
     for (;;) {
-        const bool wantTri = have && L.triNext < L.triEnd;
-        const bool wantNode = have && !wantTri && (L.cur & kRefTagMask) == kRefInterior;
-        const bool wantMisc = have && !wantTri && !wantNode && L.cur != kTraceDone;
-        const uint32_t mTri = __ballot_sync(0xFFFFFFFFu, wantTri);
-        const uint32_t mNode = __ballot_sync(0xFFFFFFFFu, wantNode);
-        const uint32_t mMisc = __ballot_sync(0xFFFFFFFFu, wantMisc);
-        const uint32_t busy = mTri | mNode | mMisc;
+        const uint32_t tag = L.cur & kRefTagMask;
+        const uint32_t mNode = __ballot_sync(0xFFFFFFFFu, tag == kRefInterior);
+        const uint32_t mTri = __ballot_sync(0xFFFFFFFFu, tag == kRefTriLeaf);
+        const uint32_t mMisc = __ballot_sync(0xFFFFFFFFu, tag == kRefInstance && L.cur != kTraceDone);
+        const uint32_t nNode = (uint32_t)__popc(mNode), nTri = (uint32_t)__popc(mTri);
 
         if (mMisc) {                                                    /* instance entry / exit: rare, handled at once */
-            if (wantMisc) {
+            if (tag == kRefInstance && L.cur != kTraceDone) {
                 const float4 ro = wb.rayO[L.path], rdv = wb.rayD[L.path];
                 stepMisc(s, L, stack, v3(ro.x, ro.y, ro.z), v3(rdv.x, rdv.y, rdv.z));
             }
             continue;
         }
 
-        const uint32_t idle = 32u - (uint32_t)__popc(busy);
-        if (busy == 0u || (!exhausted && idle >= (uint32_t)OKRT_REFILL_IDLE)) {
+        const uint32_t active = nNode + nTri;
+        if (active == 0u || (!exhausted && active <= 32u - (uint32_t)OKRT_REFILL_IDLE)) {
             /* ---- finished lanes write their hit record (or queue the ray for the reference order) */
-            if (have && !(busy & (1u << lane))) {
+            if (have && L.cur == kTraceDone) {
                 const float4 ro = wb.rayO[L.path], rdv = wb.rayD[L.path];
                 Hit hit;
                 float seed;
@@ -236,8 +244,19 @@ traceFastKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ F
             continue;
         }
 
-        if (__popc(mNode) >= __popc(mTri)) { if (wantNode) stepNode(s, L, stack); }
-        else { if (wantTri) stepTriangle(s, L, stack); }
+        if (nNode >= nTri) {
+            /* ---- node phase */
+            const uint32_t keep = min((uint32_t)OKRT_NODE_KEEP, nNode);
+            do {
+                if ((L.cur & kRefTagMask) == kRefInterior) stepNode(s, L, stack);
+            } while ((uint32_t)__popc(__ballot_sync(0xFFFFFFFFu, (L.cur & kRefTagMask) == kRefInterior)) >= keep);
+        } else {
+            /* ---- triangle phase */
+            const uint32_t keep = min((uint32_t)OKRT_TRI_KEEP, nTri);
+            do {
+                if ((L.cur & kRefTagMask) == kRefTriLeaf) stepTriangle(s, L, stack);
+            } while ((uint32_t)__popc(__ballot_sync(0xFFFFFFFFu, (L.cur & kRefTagMask) == kRefTriLeaf)) >= keep);
+        }
     }
 }
 
