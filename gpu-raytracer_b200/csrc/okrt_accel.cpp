@@ -160,6 +160,17 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
         out.exactOctDepth = (uint32_t)maxOcc;
     }
 
+    /* octNested[n]: every box on the way from n up to the root contains the box below it (component-wise, exactly) */
+    std::vector<uint8_t> octNested(numOctNodes, 0);
+    for (uint32_t n = 0; n < numOctNodes; n++) {
+        if (!reachable[n]) continue;
+        bool nested = true;
+        for (uint32_t c = n, p = out.octParent[n]; p != 0xFFFFFFFFu && nested; c = p, p = out.octParent[p])
+            for (int k = 0; k < 3; k++)
+                nested = nested && octNodes[p].boundingBox.min[k] <= octNodes[c].boundingBox.min[k] && octNodes[c].boundingBox.max[k] <= octNodes[p].boundingBox.max[k];
+        octNested[n] = nested ? 1 : 0;
+    }
+
     /* which (reachable) oct-tree node lists each instance */
     std::vector<uint32_t> instOct(numInstances, 0xFFFFFFFFu);
     for (uint32_t n = 0; n < numOctNodes; n++) {
@@ -218,13 +229,16 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
         bool identity = true;
         for (int k = 0; k < 16; k++) identity = identity && T[k] == I16[k] && Ti[k] == I16[k];
 
-        const uint32_t rec = (uint32_t)(out.instances.size() / 8);
-        out.instances.resize(out.instances.size() + 8);
-        Float4* r = &out.instances[(size_t)rec * 8];
+        const uint32_t rec = (uint32_t)(out.instances.size() / kInstQuads);
+        out.instances.resize(out.instances.size() + kInstQuads);
+        Float4* r = &out.instances[(size_t)rec * kInstQuads];
         for (int row = 0; row < 3; row++) r[row] = Float4{Ti[row * 4 + 0], Ti[row * 4 + 1], Ti[row * 4 + 2], Ti[row * 4 + 3]};
         for (int row = 0; row < 3; row++) r[3 + row] = Float4{T[row * 4 + 0], T[row * 4 + 1], T[row * 4 + 2], rb.min[row]};
         r[6] = Float4{rb.max[0], rb.max[1], rb.max[2], bitsToFloat(identity ? 1u : 0u)};
-        r[7] = Float4{bitsToFloat(rootRef), bitsToFloat(instOct[i]), bitsToFloat(i), 0.f};
+        r[7] = Float4{bitsToFloat(rootRef), bitsToFloat(instOct[i]), bitsToFloat(i), bitsToFloat(octNested[instOct[i]] ? 1u : 0u)};
+        const okrt_aabb& ob = octNodes[instOct[i]].boundingBox;
+        r[8] = Float4{ob.min[0], ob.min[1], ob.min[2], 0.f};
+        r[9] = Float4{ob.max[0], ob.max[1], ob.max[2], 0.f};
 
         /* An identity-transform instance that is the only user of its mesh is MERGED into the top level: its
          * local ray is the same for all such instances (normalize(d*I), o*I), so the top-level tree can link
@@ -384,11 +398,12 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
             topDepth = 1;
         }
     }
-    if ((out.nodes.size() / 4) >= (1u << 30) || (out.instances.size() / 8) >= (1u << 30)) { out.error = "scene too large for 30-bit references"; return false; }
+    if ((out.nodes.size() / 4) >= (1u << 30) || (out.instances.size() / kInstQuads) >= (1u << 30)) { out.error = "scene too large for 30-bit references"; return false; }
 
     /* fast stack: one deferred sibling per level in each tree, plus the instance-exit marker */
     out.maxStackDepth = topDepth + std::max(b.deepestPair, chainDepth) + 2;
     if (b.failed) return false;
+    for (uint32_t t = 0; t < numTris; t++) out.tris[(size_t)t * 3 + 2].y = bitsToFloat(out.triOwner[t]);
     return true;
 }
 

@@ -16,14 +16,17 @@
  * Leaves with more than 8 triangles (possible when the SAH refuses to split or maxDepth is hit) are
  * chained through extra pair nodes that repeat the leaf's box.
  *
- * Triangle: 48 B = three float4 {p.xyz, 0}; positions are bit copies (E1/E2 are formed in the kernel
- * exactly as GPU-Utilities.hlsli:124 does).
+ * Triangle: 48 B = three float4 { p2.xyz, E1.x | E1.yz, E2.xy | E2.z, bits(owner), 0, 0 } with E1 = p0 - p2 and
+ * E2 = p1 - p2 (GPU-Utilities.hlsli:124; the same float32 subtraction, done once at upload); owner = instance record
+ * of the merged instance the triangle belongs to (what triOwner holds), so a hit names its instance without a lookup.
  *
- * Instance record: 128 B = eight float4
+ * Instance record: 160 B = ten float4
  *     r0..r2  rows 0..2 of inverseTransformMatrix           (world -> local)
  *     r3..r5  rows 0..2 of transformMatrix, .w = root box min (local -> world for directions)
  *     r6      root box max.xyz, .w = bits(flags)  (bit0: transform is exactly identity)
- *     r7      bits{ rootRef, octNodeIdx, instanceIdx (reference order), 0 }
+ *     r7      bits{ rootRef, octNodeIdx, instanceIdx (reference order), flags } (flags bit0: the oct-tree boxes above the
+ *             instance are nested, i.e. a point inside r8/r9 is inside every ancestor box)
+ *     r8,r9   min.xyz / max.xyz of the oct-tree node that lists the instance
  * The top-level tree over instance world boxes replaces the reference's oct-tree walk for CULLING
  * only; every oct-tree box the reference would test on the way to an instance is still tested (with
  * its arithmetic) before the instance is entered, so hit/miss decisions are unchanged.
@@ -42,6 +45,7 @@ constexpr uint32_t kRefTriLeaf = 0x80000000u;
 constexpr uint32_t kRefInstance = 0xC0000000u;
 constexpr uint32_t kRefNone = 0xFFFFFFFFu;        /* empty scene / empty child */
 constexpr uint32_t kMaxLeafTris = 8;
+constexpr uint32_t kInstQuads = 10;               /* float4 per instance record */
 constexpr uint32_t kMaxTriIndex = (1u << 27);
 constexpr uint32_t kFastStackCapacity = 64;       /* entries; validated against tree depth at upload */
 constexpr uint32_t kExactBvhStackCapacity = 64;   /* reference: 50, RaytracerCS.hlsl:249 */

@@ -11,6 +11,7 @@
 
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -219,7 +220,7 @@ DeviceScene sceneView(const okrt_renderer* r)
     s.octParent = (const uint32_t*)r->octParent.ptr;
     s.triOwner = (const uint32_t*)r->triOwner.ptr;
     s.topRef = r->topRef;
-    s.numFastNodes = r->fastNodes.count / 4u; s.numFastInstances = r->fastInstances.count / 8u;
+    s.numFastNodes = r->fastNodes.count / 4u; s.numFastInstances = r->fastInstances.count / kInstQuads;
     return s;
 }
 
@@ -232,7 +233,7 @@ void coveredExtent(const okrt_renderer* r, uint32_t& cw, uint32_t& ch)
 
 void freeWavefront(okrt_renderer* r)
 {
-    void* ptrs[] = {r->wb.rayO, r->wb.rayD, r->wb.radiance, r->wb.throughput, r->wb.hitA, r->wb.hitB, r->wb.queue[0], r->wb.queue[1], r->wb.counts, r->wb.fallbackQueue};
+    void* ptrs[] = {r->wb.rayO, r->wb.rayD, r->wb.radiance, r->wb.throughput, r->wb.hitA, r->wb.hitB, r->wb.queue[0], r->wb.queue[1], r->wb.counts, r->wb.fallbackQueue, r->wb.traceStats};
     for (void* p : ptrs) if (p) cudaFree(p);
     std::memset(&r->wb, 0, sizeof(r->wb));
     r->wbPaths = 0;
@@ -253,6 +254,7 @@ int ensureWavefront(okrt_renderer* r, size_t paths)
     OKRT_CUDA(cudaMalloc(&r->wb.queue[0], paths * sizeof(uint32_t)));
     OKRT_CUDA(cudaMalloc(&r->wb.queue[1], paths * sizeof(uint32_t)));
     OKRT_CUDA(cudaMalloc(&r->wb.fallbackQueue, paths * sizeof(uint32_t)));
+    OKRT_CUDA(cudaMalloc(&r->wb.traceStats, 8 * (kMaxWavefrontBounces + 2) * sizeof(unsigned long long)));
     OKRT_CUDA(cudaMalloc(&r->wb.counts, kCountWords * sizeof(uint32_t)));
     r->wb.fallbackCounts = r->wb.counts + kMaxQueueCounts;
     r->wbPaths = paths;
@@ -269,6 +271,9 @@ int launchWavefront(okrt_renderer* r, const FrameParams& fp, bool instrumented)
     if (rc) return rc;
     const DeviceScene scene = sceneView(r);
     OKRT_CUDA(cudaMemsetAsync(r->wb.counts, 0, kCountWords * sizeof(uint32_t), r->stream));
+#ifdef OKRT_TRACE_STATS
+    OKRT_CUDA(cudaMemsetAsync(r->wb.traceStats, 0, 8 * (kMaxWavefrontBounces + 2) * sizeof(unsigned long long), r->stream));
+#endif
     const unsigned flatGrid = (unsigned)((paths + 127) / 128);
     generateKernel<<<flatGrid, 128, 0, r->stream>>>(fp, r->wb);
     r->launches++;
@@ -290,6 +295,24 @@ int launchWavefront(okrt_renderer* r, const FrameParams& fp, bool instrumented)
     accumulateKernel<<<(unsigned)((slots + 127) / 128), 128, 0, r->stream>>>(fp, r->wb);
     r->launches++;
     OKRT_CUDA(cudaGetLastError());
+    if (std::getenv("OKRT_DEBUG_COUNTS")) {          /* diagnostic: rays per bounce of this batch */
+        std::vector<uint32_t> h(kCountWords);
+        cudaMemcpyAsync(h.data(), r->wb.counts, kCountWords * sizeof(uint32_t), cudaMemcpyDeviceToHost, r->stream);
+        cudaStreamSynchronize(r->stream);
+        std::fprintf(stderr, "okrt: batch of %u frames, rays per bounce:", fp.batchFrames);
+        for (uint32_t b = 0; b <= fp.maxBounces; b++) std::fprintf(stderr, " %u(fb %u)", h[2 * b], h[kMaxQueueCounts + b]);
+        std::fprintf(stderr, "\n");
+#ifdef OKRT_TRACE_STATS
+        std::vector<unsigned long long> st(8 * (fp.maxBounces + 1));
+        cudaMemcpy(st.data(), r->wb.traceStats, st.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+        for (uint32_t b = 0; b <= fp.maxBounces; b++) {
+            const unsigned long long* t = &st[8 * b];
+            std::fprintf(stderr, "  bounce %u: rays %llu  node steps/ray %.1f (lanes/iter %.1f)  tri steps/ray %.1f (lanes/iter %.1f)  refills/warp %.1f  warp clocks avg %.0f max %llu\n",
+                         b, t[0], (double)t[1] / std::max(1ull, t[0]), (double)t[1] / std::max(1ull, t[3]), (double)t[2] / std::max(1ull, t[0]), (double)t[2] / std::max(1ull, t[4]),
+                         (double)t[5] / (traceGrid * 4.0), (double)t[6] / (traceGrid * 4.0), t[7]);
+        }
+#endif
+    }
     return OKRT_OK;
 }
 

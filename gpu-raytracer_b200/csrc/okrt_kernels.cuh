@@ -475,21 +475,21 @@ __device__ __forceinline__ void traceRound(const DeviceScene& s, TraceLane& L, u
                 if (rec == kTraceTop) {
                     /* a triangle of a merged (identity, single-user) instance: T == I maps w to itself */
                     rec = __ldg(s.triOwner + j);
-                    const uint32_t octNode = __float_as_uint(__ldg(s.fastInstances + (size_t)rec * 8 + 7).y);
+                    const uint32_t octNode = __float_as_uint(__ldg(s.fastInstances + (size_t)rec * kInstQuads + 7).y);
                     if (!octChainHit(s, L, octNode)) continue;           /* the reference never reaches this instance */
                 } else {
-                    const float4* r = s.fastInstances + (size_t)rec * 8;
+                    const float4* r = s.fastInstances + (size_t)rec * kInstQuads;
                     w = mulDirRows(w, __ldg(r + 3), __ldg(r + 4), __ldg(r + 5));
                 }
                 t = length(w);
-                const uint32_t instRef = __float_as_uint(__ldg(s.fastInstances + (size_t)rec * 8 + 7).z);
+                const uint32_t instRef = __float_as_uint(__ldg(s.fastInstances + (size_t)rec * kInstQuads + 7).z);
                 laneCandidate(L, t, (2u << 30) | instRef, j, bu, bv);
             }
         } else if (cur == kTraceExitInstance) {
             laneTopRay(L);
         } else {                                                         /* generic instance leaf */
             const uint32_t recIdx = cur & ~kRefTagMask;
-            const float4* rec = s.fastInstances + (size_t)recIdx * 8;
+            const float4* rec = s.fastInstances + (size_t)recIdx * kInstQuads;
             const float4 r6 = __ldg(rec + 6), r7 = __ldg(rec + 7);
             if (octChainHit(s, L, __float_as_uint(r7.y))) {
                 const float4 i0 = __ldg(rec), i1 = __ldg(rec + 1), i2 = __ldg(rec + 2);
@@ -547,7 +547,7 @@ __device__ __forceinline__ bool traverseFast(const DeviceScene& s, uint32_t numS
 struct StepLane {
     V3 ro, rd, ridir;        /* current ray: identity-local at the top level, instance-local inside an instance */
     float best, second;
-    uint32_t hitRec;         /* 1<<30 | sphere, or 2<<30 | (instance record, or 0x3FFFFFFF = "merged: look up triOwner") */
+    uint32_t hitRec;         /* 1<<30 | sphere, or 2<<30 | instance record */
     uint32_t hitTri;
     float hitU, hitV;
     uint32_t cur;            /* reference the lane stands on: interior / triangle leaf / instance / exit marker / done */
@@ -556,7 +556,6 @@ struct StepLane {
     uint32_t inst;           /* instance record inside a generic instance; kTraceTop at the top level */
     uint32_t path;
 };
-constexpr uint32_t kMergedRec = 0x3FFFFFFFu;
 
 __device__ __forceinline__ void stepCandidate(StepLane& L, float t, uint32_t rec, uint32_t tri, float u, float v)
 {
@@ -658,9 +657,9 @@ __device__ __forceinline__ void stepTriangle(const DeviceScene& s, StepLane& L, 
     float t = rayAndTriangleEdges(L.ro, L.rd, v3(a.x, a.y, a.z), v3(a.w, b.x, b.y), v3(b.z, b.w, c.x), bu, bv);
     if (t > 0.f) {
         V3 w = L.rd * t;                                        /* RaytracerCS.hlsl:312-314; T == I for merged instances */
-        uint32_t rec = kMergedRec;
+        uint32_t rec = __float_as_uint(c.y);                    /* owner of a merged instance's triangle */
         if (L.inst != kTraceTop) {
-            const float4* r = s.fastInstances + (size_t)L.inst * 8;
+            const float4* r = s.fastInstances + (size_t)L.inst * kInstQuads;
             w = mulDirRows(w, __ldg(r + 3), __ldg(r + 4), __ldg(r + 5));
             rec = L.inst;
         }
@@ -690,7 +689,7 @@ __device__ __forceinline__ void stepMisc(const DeviceScene& s, StepLane& L, uint
     } else {                                                     /* generic instance leaf */
         const uint32_t recIdx = L.cur & ~kRefTagMask;
         OKRT_CHECK(recIdx < s.numFastInstances);
-        const float4* rec = s.fastInstances + (size_t)recIdx * 8;
+        const float4* rec = s.fastInstances + (size_t)recIdx * kInstQuads;
         const float4 r6 = __ldg(rec + 6), r7 = __ldg(rec + 7);
         if (octChainHitWorld(s, o, d, __float_as_uint(r7.y))) {
             const float4 i0 = __ldg(rec), i1 = __ldg(rec + 1), i2 = __ldg(rec + 2);
@@ -712,8 +711,9 @@ __device__ __forceinline__ void stepMisc(const DeviceScene& s, StepLane& L, uint
     stepPop(L, stack);
 }
 
-/* the finished lane's hit; returns true when the reference order has to decide */
-__device__ __forceinline__ bool stepResult(const DeviceScene& s, const StepLane& L, V3 o, V3 d, Hit& hit, float& seed)
+/* the finished lane's hit; returns true when the reference order has to decide.  `L` stands at the top level
+ * again (the exit marker of an instance restores the top ray), so L.ro is the world origin. */
+__device__ __forceinline__ bool stepResult(const DeviceScene& s, const StepLane& L, const float4* rayD, Hit& hit, float& seed)
 {
     seed = L.best;                                               /* the reference's answer lies inside the window above it */
     hit.distance = L.best;
@@ -722,13 +722,23 @@ __device__ __forceinline__ bool stepResult(const DeviceScene& s, const StepLane&
     hit.tri = L.hitTri; hit.u = L.hitU; hit.v = L.hitV;
     bool ambiguous = L.second < relaxedLimit(L.best);
     if (hit.kind == 2u) {
-        const bool merged = hit.idx == kMergedRec;
-        OKRT_CHECK(hit.tri < s.numTris);
-        const uint32_t rec = merged ? __ldg(s.triOwner + hit.tri) : hit.idx;
+        const uint32_t rec = hit.idx;
         OKRT_CHECK(rec < s.numFastInstances);
-        const float4 r7 = __ldg(s.fastInstances + (size_t)rec * 8 + 7);
+        const float4* r = s.fastInstances + (size_t)rec * kInstQuads;
+        const float4 r6 = __ldg(r + 6), r7 = __ldg(r + 7), lo = __ldg(r + 8), hi = __ldg(r + 9);
         hit.idx = __float_as_uint(r7.z);
-        if (merged && !octChainHitWorld(s, o, d, __float_as_uint(r7.y))) { ambiguous = true; seed = OKRT_FLT_MAX; }   /* the reference never reaches this instance: no bound known */
+        if ((__float_as_uint(r6.w) & 1u) != 0u) {
+            /* identity instance: the reference reaches it only through the oct-tree boxes above it (RaytracerCS.hlsl:262).
+             * An origin strictly inside a box hits it — both slabs of every axis have opposite signs, |1/d| >= 1/2 for
+             * the unit directions the shader produces, so distFar > 0 >= distNear — and the boxes above are nested. */
+            const float m = 1.0e-20f;
+            const bool inside = (__float_as_uint(r7.w) & 1u) != 0u &&
+                                L.ro.x - lo.x > m && hi.x - L.ro.x > m && L.ro.y - lo.y > m && hi.y - L.ro.y > m && L.ro.z - lo.z > m && hi.z - L.ro.z > m;
+            if (!inside) {
+                const float4 d = *rayD;
+                if (!octChainHitWorld(s, L.ro, v3(d.x, d.y, d.z), __float_as_uint(r7.y))) { ambiguous = true; seed = OKRT_FLT_MAX; }   /* no bound known */
+            }
+        }
     }
     return ambiguous;
 }

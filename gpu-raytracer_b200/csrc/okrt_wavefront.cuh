@@ -33,6 +33,7 @@ struct WavefrontBuffers {
     uint32_t* hitB;        /* kind << 30 | instance-or-sphere index */
     uint32_t* queue[2];    /* ping-pong queues of path slots */
     uint32_t* counts;      /* [2*bounce] number of queued paths, [2*bounce+1] trace work counter; zeroed per frame */
+    unsigned long long* traceStats;   /* OKRT_TRACE_STATS builds: 8 counters per bounce (diagnostic) */
     uint32_t* fallbackQueue;   /* paths whose hit the reference-order kernel has to decide (this bounce) */
     uint32_t* fallbackCounts;  /* [bounce]; zeroed per frame (lives behind counts) */
 };
@@ -46,6 +47,7 @@ constexpr int kTraceBlockThreads = 128;
 #define OKRT_KEEP_RUNNING 16
 #endif
 constexpr uint32_t kTraceChunk = 64;         /* rays a warp claims per atomic */
+
 
 /* ---------------------------------------------------------------- generate
  * [Q3] seed, createRay :177-206 [Q2], applyDOF :208-216.  Slot order = 16x8 tile order of this rank's tiles. */
@@ -184,6 +186,10 @@ traceFastKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ F
     bool have = false;                        /* this lane owns a ray whose result is not written yet */
     uint32_t next = 0u, end = 0u;             /* warp-uniform: unclaimed part of the warp's current chunk */
     bool exhausted = false;                   /* warp-uniform */
+#ifdef OKRT_TRACE_STATS
+    uint32_t stNodeIters = 0u, stNodeSteps = 0u, stTriIters = 0u, stTriSteps = 0u, stRefills = 0u, stRays = 0u;
+    const long long stStart = clock64();
+#endif
 
     /* lanes without a ray stand on kTraceDone, which belongs to no phase */
     for (;;) {
@@ -205,10 +211,9 @@ traceFastKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ F
         if (active == 0u || (!exhausted && active <= 32u - (uint32_t)OKRT_REFILL_IDLE)) {
             /* ---- finished lanes write their hit record (or queue the ray for the reference order) */
             if (have && L.cur == kTraceDone) {
-                const float4 ro = wb.rayO[L.path], rdv = wb.rayD[L.path];
                 Hit hit;
                 float seed;
-                if (stepResult(s, L, v3(ro.x, ro.y, ro.z), v3(rdv.x, rdv.y, rdv.z), hit, seed)) {
+                if (stepResult(s, L, wb.rayD + L.path, hit, seed)) {
                     wb.fallbackQueue[atomicAdd(wb.fallbackCounts + bounce, 1u)] = L.path;
                     wb.hitA[L.path].x = seed;                            /* bounds the reference-order traversal's search */
                 } else {
@@ -218,6 +223,9 @@ traceFastKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ F
                 have = false;
             }
             /* ---- refill */
+#ifdef OKRT_TRACE_STATS
+            stRefills++;
+#endif
             uint32_t need = __ballot_sync(0xFFFFFFFFu, !have);
             while (need != 0u && !exhausted) {
                 if (next == end) {
@@ -236,6 +244,9 @@ traceFastKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ F
                     const float4 ro = wb.rayO[L.path], rdv = wb.rayD[L.path];
                     stepInit(s, L, stack, numSpheres, v3(ro.x, ro.y, ro.z), v3(rdv.x, rdv.y, rdv.z));
                     have = true;
+#ifdef OKRT_TRACE_STATS
+                    stRays++;
+#endif
                 }
                 next += take;
                 need = __ballot_sync(0xFFFFFFFFu, !have);
@@ -248,16 +259,33 @@ traceFastKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ F
             /* ---- node phase */
             const uint32_t keep = min((uint32_t)OKRT_NODE_KEEP, nNode);
             do {
+#ifdef OKRT_TRACE_STATS
+                stNodeIters++; if ((L.cur & kRefTagMask) == kRefInterior) stNodeSteps++;
+#endif
                 if ((L.cur & kRefTagMask) == kRefInterior) stepNode(s, L, stack);
             } while ((uint32_t)__popc(__ballot_sync(0xFFFFFFFFu, (L.cur & kRefTagMask) == kRefInterior)) >= keep);
         } else {
             /* ---- triangle phase */
             const uint32_t keep = min((uint32_t)OKRT_TRI_KEEP, nTri);
             do {
+#ifdef OKRT_TRACE_STATS
+                stTriIters++; if ((L.cur & kRefTagMask) == kRefTriLeaf) stTriSteps++;
+#endif
                 if ((L.cur & kRefTagMask) == kRefTriLeaf) stepTriangle(s, L, stack);
             } while ((uint32_t)__popc(__ballot_sync(0xFFFFFFFFu, (L.cur & kRefTagMask) == kRefTriLeaf)) >= keep);
         }
     }
+#ifdef OKRT_TRACE_STATS
+    {
+        unsigned long long* st = wb.traceStats + 8u * bounce;
+        const uint32_t a0 = __reduce_add_sync(0xFFFFFFFFu, stRays), a1 = __reduce_add_sync(0xFFFFFFFFu, stNodeSteps), a2 = __reduce_add_sync(0xFFFFFFFFu, stTriSteps);
+        if (lane == 0u) {
+            atomicAdd(st + 0, (unsigned long long)a0); atomicAdd(st + 1, (unsigned long long)a1); atomicAdd(st + 2, (unsigned long long)a2);
+            atomicAdd(st + 3, (unsigned long long)stNodeIters); atomicAdd(st + 4, (unsigned long long)stTriIters); atomicAdd(st + 5, (unsigned long long)stRefills);
+            atomicAdd(st + 6, (unsigned long long)(clock64() - stStart)); atomicMax(st + 7, (unsigned long long)(clock64() - stStart));
+        }
+    }
+#endif
 }
 
 /* ------------------------------------------------------------------- shade
