@@ -7,5 +7,6 @@ Everything computational lives in libokrt.so (csrc/, built by build.py) behind i
 from . import _abi as abi                      # noqa: F401
 from .raytracer import Mesh, OctTree, Geometry, RayTracer, ResourceManager, Scene  # noqa: F401
 from .raytracer import environmentCrossToFaces, scaleTexturesToArray            # noqa: F401
+from .raytracer import loadObjects, ObjectDescription                           # noqa: F401
 from . import scenes                           # noqa: F401
 from . import sharding                         # noqa: F401

@@ -105,6 +105,12 @@ SYMBOLS = [
     ("okrt_texture_array_size", _U, [_P, _P, _U]),
     ("okrt_scale_texture", _I, [_P, _U, _U, _P, _U, _U]),
     ("okrt_environment_cross_to_faces", _I, [_P, _U, _U, _P]),
+    ("okrt_obj_load", _I, [ctypes.c_char_p, ctypes.c_float, ctypes.POINTER(_P)]),
+    ("okrt_obj_load_memory", _I, [ctypes.c_char_p, ctypes.c_size_t, ctypes.c_char_p, ctypes.c_size_t, ctypes.c_float, ctypes.POINTER(_P)]),
+    ("okrt_obj_free", None, [_P]),
+    ("okrt_obj_num_meshes", _U, [_P]),
+    ("okrt_obj_mesh", _I, [_P, _U, _P, ctypes.POINTER(ctypes.c_char_p)]),
+    ("okrt_obj_texture_path", ctypes.c_char_p, [_P, _U, _U]),
     ("okrt_create", _I, [_I, _U, _U, ctypes.POINTER(_P)]),
     ("okrt_destroy", None, [_P]),
     ("okrt_resize", _I, [_P, _U, _U]),

@@ -112,7 +112,7 @@ struct okrt_renderer {
 
     DeviceBuffer triPos, triInfo, bvhNodes, octNodes, spheres, instances, dirLights, pointLights, spotLights;
     TextureArray textures, environment;
-    DeviceBuffer fastNodes, fastTris, fastInstances, octParent, triOwner;
+    DeviceBuffer fastNodes, fastTris, fastInstances, octParent;
 
     /* host copies needed to (re)build the fast layout */
     std::vector<okrt_triangle> hTris;
@@ -186,7 +186,6 @@ int rebuildLayout(okrt_renderer* r)
     if ((rc = r->fastTris.upload(fl.tris.data(), (uint32_t)fl.tris.size(), sizeof(Float4), r->stream))) return rc;
     if ((rc = r->fastInstances.upload(fl.instances.data(), (uint32_t)fl.instances.size(), sizeof(Float4), r->stream))) return rc;
     if ((rc = r->octParent.upload(fl.octParent.data(), (uint32_t)fl.octParent.size(), sizeof(uint32_t), r->stream))) return rc;
-    if ((rc = r->triOwner.upload(fl.triOwner.data(), (uint32_t)fl.triOwner.size(), sizeof(uint32_t), r->stream))) return rc;
     r->topRef = fl.topRef;
     r->allRigid = fl.allRigid;
     r->fastStackNeed = fl.maxStackDepth; r->exactBvhNeed = fl.exactBvhDepth; r->exactOctNeed = fl.exactOctDepth;
@@ -218,7 +217,6 @@ DeviceScene sceneView(const okrt_renderer* r)
     s.fastTris = (const float4*)r->fastTris.ptr;
     s.fastInstances = (const float4*)r->fastInstances.ptr;
     s.octParent = (const uint32_t*)r->octParent.ptr;
-    s.triOwner = (const uint32_t*)r->triOwner.ptr;
     s.topRef = r->topRef;
     s.numFastNodes = r->fastNodes.count / 4u; s.numFastInstances = r->fastInstances.count / kInstQuads;
     return s;
@@ -451,7 +449,7 @@ void okrt_destroy(okrt_renderer* r)
     if (r->stream) cudaStreamSynchronize(r->stream);
     r->triPos.release(); r->triInfo.release(); r->bvhNodes.release(); r->octNodes.release(); r->spheres.release();
     r->instances.release(); r->dirLights.release(); r->pointLights.release(); r->spotLights.release();
-    r->fastNodes.release(); r->fastTris.release(); r->fastInstances.release(); r->octParent.release(); r->triOwner.release();
+    r->fastNodes.release(); r->fastTris.release(); r->fastInstances.release(); r->octParent.release();
     r->textures.release(); r->environment.release();
     if (r->accumulation) cudaFree(r->accumulation);
     if (r->result) cudaFree(r->result);

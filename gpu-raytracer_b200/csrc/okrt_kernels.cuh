@@ -95,7 +95,6 @@ struct DeviceScene {
     const float4* fastTris;
     const float4* fastInstances;
     const uint32_t* octParent;
-    const uint32_t* triOwner;
     uint32_t topRef;
     uint32_t numFastNodes, numFastInstances;
     uint32_t pad0;
@@ -354,8 +353,6 @@ __device__ __noinline__ void traverseExact(const DeviceScene& s, uint32_t numSph
     }
 }
 
-__device__ __forceinline__ float rayAndTriangleEdges(V3 o, V3 d, V3 p2, V3 E1, V3 E2, float& u, float& v);
-
 /* ------------------------------------------------ near-first traversal
  * Same boxes, same triangles, same arithmetic — different visiting order and a different culling
  * hierarchy at the top.  Correctness argument (DESIGN.md "Order independence"): with relaxed culling
@@ -368,171 +365,9 @@ __device__ __forceinline__ float rayAndTriangleEdges(V3 o, V3 d, V3 p2, V3 E1, V
 /* a missed box reports FLT_MAX and must never pass, also while nothing has been hit yet */
 __device__ __forceinline__ float relaxedLimit(float best) { return fminf(best * (1.0f + OKRT_DELTA), OKRT_FLT_MAX); }
 
-/* Traversal state of one ray.  It survives between calls of traceRound() so that the wavefront trace kernel
- * can refill finished lanes while their neighbours keep walking. */
-struct TraceLane {
-    V3 o, d;                 /* world ray */
-    V3 ro, rd, ridir;        /* current ray: identity-local at the top level, instance-local inside an instance */
-    float best, second;      /* closest and second-closest candidate distance */
-    uint32_t hitKindIdx, hitTri;
-    float hitU, hitV;
-    uint32_t cur;
-    int sp;
-    uint32_t inst;           /* instance record inside a generic instance; kTraceTop at the top level */
-    unsigned long long octTested, octHit;   /* per-ray cache of the reference's oct-tree box tests (hit/miss only) */
-    uint32_t path;
-};
-
 constexpr uint32_t kTraceDone = 0xFFFFFFFDu;
 constexpr uint32_t kTraceExitInstance = 0xFFFFFFFEu;
 constexpr uint32_t kTraceTop = 0xFFFFFFFFu;
-
-__device__ __forceinline__ void laneCandidate(TraceLane& L, float t, uint32_t kindIdx, uint32_t tri, float u, float v)
-{
-    if (t < L.best) { L.second = L.best; L.best = t; L.hitKindIdx = kindIdx; L.hitTri = tri; L.hitU = u; L.hitV = v; }
-    else if (t < L.second) L.second = t;
-}
-
-/* the ray every identity-transform instance sees: mul by I, then normalize (RaytracerCS.hlsl:275-276) */
-__device__ __forceinline__ void laneTopRay(TraceLane& L)
-{
-    const float4 i0 = make_float4(1, 0, 0, 0), i1 = make_float4(0, 1, 0, 0), i2 = make_float4(0, 0, 1, 0);
-    L.ro = mulPointRows(L.o, i0, i1, i2);
-    L.rd = normalize(mulDirRows(L.d, i0, i1, i2));
-    L.ridir = rcp3(L.rd);
-    L.inst = kTraceTop;
-}
-
-/* Every oct-tree box the reference tests on its way to an instance (RaytracerCS.hlsl:262) must be HIT by the
- * world ray; the `>= payload.distance` half of that test is an order-dependent cull that the window argument covers. */
-__device__ __forceinline__ bool octChainHit(const DeviceScene& s, TraceLane& L, uint32_t octNode)
-{
-    const V3 idirWorld = rcp3(L.d);
-    for (uint32_t on = octNode; on != 0xFFFFFFFFu; on = __ldg(s.octParent + on)) {
-        bool boxHit;
-        const unsigned long long bit = 1ull << (on & 63u);
-        if (on < 64u && (L.octTested & bit)) boxHit = (L.octHit & bit) != 0ull;
-        else {
-            const okrt_octree_node& node = s.octNodes[on];
-            boxHit = rayAndAABBDist(L.o, idirWorld, v3(node.boundingBox.min), v3(node.boundingBox.max)) < OKRT_FLT_MAX;
-            if (on < 64u) { L.octTested |= bit; if (boxHit) L.octHit |= bit; }
-        }
-        if (!boxHit) return false;
-    }
-    return true;
-}
-
-__device__ __forceinline__ void laneInit(const DeviceScene& s, TraceLane& L, uint32_t numSpheres, V3 o, V3 d)
-{
-    L.o = o; L.d = d;
-    L.best = OKRT_FLT_MAX; L.second = OKRT_FLT_MAX;
-    L.hitKindIdx = 0x3FFFFFFFu; L.hitTri = 0xFFFFFFFFu; L.hitU = 0.f; L.hitV = 0.f;
-    L.octTested = 0ull; L.octHit = 0ull; L.sp = 0;
-    laneTopRay(L);
-    for (uint32_t i = 0; i < numSpheres; i++) {                /* RaytracerCS.hlsl:232-242 */
-        const okrt_sphere& sp = s.spheres[i];
-        const float t = rayAndSphere(o, d, v3(sp.position), sp.radius);
-        if (t > 0.f) laneCandidate(L, t, (1u << 30) | i, 0xFFFFFFFFu, 0.f, 0.f);
-    }
-    L.cur = s.topRef == kRefNone ? kTraceDone : s.topRef;
-}
-
-/* one round of the while-while loop: interior pair nodes until a leaf comes up, then that leaf */
-__device__ __forceinline__ void traceRound(const DeviceScene& s, TraceLane& L, uint32_t* stack)
-{
-    uint32_t cur = L.cur;
-    int sp = L.sp;
-    while ((cur & kRefTagMask) == kRefInterior) {
-        const float4* q = s.fastNodes + (size_t)cur * 4;
-        const float4 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3);
-        const float limit = relaxedLimit(L.best);
-        const float n0 = rayAndAABBDist(L.ro, L.ridir, v3(q0.x, q0.y, q0.z), v3(q1.x, q1.y, q1.z));
-        const float n1 = rayAndAABBDist(L.ro, L.ridir, v3(q2.x, q2.y, q2.z), v3(q3.x, q3.y, q3.z));
-        const uint32_t r0 = __float_as_uint(q0.w), r1 = __float_as_uint(q1.w);
-        const bool h0 = n0 < limit && r0 != kRefNone;
-        const bool h1 = n1 < limit && r1 != kRefNone;
-        if (h0 && h1) {
-            const bool firstIs1 = n1 < n0;
-            stack[sp++] = firstIs1 ? r0 : r1;
-            cur = firstIs1 ? r1 : r0;
-        } else if (h0) cur = r0;
-        else if (h1) cur = r1;
-        else cur = sp ? stack[--sp] : kTraceDone;
-    }
-    if (cur != kTraceDone) {
-        bool pop = true;
-        if ((cur & kRefTagMask) == kRefTriLeaf) {
-            const uint32_t first = cur & (kMaxTriIndex - 1u);
-            const uint32_t count = ((cur >> 27) & 7u) + 1u;
-            for (uint32_t j = first; j < first + count; j++) {
-                const float4* tp = s.fastTris + (size_t)j * 3;
-                const float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
-                float bu = 0.f, bv = 0.f;
-                float t = rayAndTriangleEdges(L.ro, L.rd, v3(a.x, a.y, a.z), v3(a.w, b.x, b.y), v3(b.z, b.w, c.x), bu, bv);   /* p2 | E1 | E2 */
-                if (t <= 0.f) continue;
-                V3 w = L.rd * t;                                        /* RaytracerCS.hlsl:312-314 */
-                uint32_t rec = L.inst;
-                if (rec == kTraceTop) {
-                    /* a triangle of a merged (identity, single-user) instance: T == I maps w to itself */
-                    rec = __ldg(s.triOwner + j);
-                    const uint32_t octNode = __float_as_uint(__ldg(s.fastInstances + (size_t)rec * kInstQuads + 7).y);
-                    if (!octChainHit(s, L, octNode)) continue;           /* the reference never reaches this instance */
-                } else {
-                    const float4* r = s.fastInstances + (size_t)rec * kInstQuads;
-                    w = mulDirRows(w, __ldg(r + 3), __ldg(r + 4), __ldg(r + 5));
-                }
-                t = length(w);
-                const uint32_t instRef = __float_as_uint(__ldg(s.fastInstances + (size_t)rec * kInstQuads + 7).z);
-                laneCandidate(L, t, (2u << 30) | instRef, j, bu, bv);
-            }
-        } else if (cur == kTraceExitInstance) {
-            laneTopRay(L);
-        } else {                                                         /* generic instance leaf */
-            const uint32_t recIdx = cur & ~kRefTagMask;
-            const float4* rec = s.fastInstances + (size_t)recIdx * kInstQuads;
-            const float4 r6 = __ldg(rec + 6), r7 = __ldg(rec + 7);
-            if (octChainHit(s, L, __float_as_uint(r7.y))) {
-                const float4 i0 = __ldg(rec), i1 = __ldg(rec + 1), i2 = __ldg(rec + 2);
-                const V3 lo = mulPointRows(L.o, i0, i1, i2);
-                const V3 ld = normalize(mulDirRows(L.d, i0, i1, i2));
-                const V3 lidir = rcp3(ld);
-                const float4 a0 = __ldg(rec + 3), a1 = __ldg(rec + 4), a2 = __ldg(rec + 5);
-                /* the mesh's root box (RaytracerCS.hlsl:285 on the first popped node) */
-                if (rayAndAABBDist(lo, lidir, v3(a0.w, a1.w, a2.w), v3(r6.x, r6.y, r6.z)) < relaxedLimit(L.best)) {
-                    stack[sp++] = kTraceExitInstance;
-                    L.ro = lo; L.rd = ld; L.ridir = lidir;
-                    L.inst = recIdx;
-                    cur = __float_as_uint(r7.x);
-                    pop = false;
-                }
-            }
-        }
-        if (pop) cur = sp ? stack[--sp] : kTraceDone;
-    }
-    L.cur = cur;
-    L.sp = sp;
-}
-
-/* the lane's result; returns true when the reference order has to decide (two candidates inside the window) */
-__device__ __forceinline__ bool laneResult(const TraceLane& L, Hit& hit)
-{
-    hit.distance = L.best;
-    hit.kind = L.best < OKRT_FLT_MAX ? (L.hitKindIdx >> 30) : 0u;
-    hit.idx = hit.kind ? (L.hitKindIdx & 0x3FFFFFFFu) : 0xFFFFFFFFu;
-    hit.tri = L.hitTri; hit.u = L.hitU; hit.v = L.hitV;
-    return L.second < relaxedLimit(L.best);
-}
-
-/* whole-ray form, used by the megakernel */
-__device__ __forceinline__ bool traverseFast(const DeviceScene& s, uint32_t numSpheres, V3 o, V3 d, Hit& hit)
-{
-    uint32_t stack[kFastStackCapacity];
-    TraceLane L;
-    L.path = 0u;
-    laneInit(s, L, numSpheres, o, d);
-    while (L.cur != kTraceDone) traceRound(s, L, stack);
-    return laneResult(L, hit);
-}
 
 /* ------------------------------------------- near-first traversal, step form
  * The same traversal as traceRound(), cut into STEPS of similar cost so that a warp can choose which kind of step
@@ -741,6 +576,23 @@ __device__ __forceinline__ bool stepResult(const DeviceScene& s, const StepLane&
         }
     }
     return ambiguous;
+}
+
+/* whole-ray form, used by the megakernel: the same steps, one ray per thread */
+__device__ __forceinline__ bool traverseFast(const DeviceScene& s, uint32_t numSpheres, V3 o, V3 d, Hit& hit, float& seed)
+{
+    uint32_t stack[kFastStackCapacity];
+    StepLane L;
+    L.path = 0u;
+    stepInit(s, L, stack, numSpheres, o, d);
+    while (L.cur != kTraceDone) {
+        const uint32_t tag = L.cur & kRefTagMask;
+        if (tag == kRefInterior) stepNode(s, L, stack);
+        else if (tag == kRefTriLeaf) stepTriangle(s, L, stack);
+        else stepMisc(s, L, stack, o, d);
+    }
+    const float4 dd = make_float4(d.x, d.y, d.z, 0.f);
+    return stepResult(s, L, &dd, hit, seed);
 }
 
 /* ------------------------------------------------------------ hit resolve
@@ -1018,10 +870,11 @@ pathTraceKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ F
             const uint32_t i = ps.bounce;
             Hit hit;
             bool usedFallback = false;
+            float fallbackSeed = OKRT_FLT_MAX;
             if (exactMode) traverseExact(s, numSpheres, o, d, hit, bbCheckCount, triCheckCount);
-            else if (traverseFast(s, numSpheres, o, d, hit)) {
+            else if (traverseFast(s, numSpheres, o, d, hit, fallbackSeed)) {
                 uint32_t bb = 0u, tc = 0u;
-                traverseExact(s, numSpheres, o, d, hit, bb, tc);
+                traverseExact(s, numSpheres, o, d, hit, bb, tc, relaxedLimit(fallbackSeed));
                 usedFallback = true; fallbacks++;
             }
             segments++;

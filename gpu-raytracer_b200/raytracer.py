@@ -121,6 +121,45 @@ class Scene:
         return c
 
 
+class ObjectDescription:
+    """Importer::ObjectDecriptionStr (Importer.h): one aiMesh of an imported file + the texture paths of its material."""
+
+    def __init__(self, mesh, name, texturePaths):
+        self.mesh, self.name = mesh, name
+        (self.albedoTexturePath, self.rougnessTexturePath, self.metallicTexturePath,
+         self.specularTexturePath, self.normalTexturePath) = texturePaths
+
+
+def loadObjects(path=None, scale=1.0, objText=None, mtlText=None):
+    """Importer::loadObjects (Importer.cpp:77-120) for Wavefront OBJ, through okrt_obj_load (csrc/okrt_obj.cpp).
+    Either `path` (the .mtl files it names are read from its directory) or `objText` (+ optional `mtlText`)."""
+    import ctypes
+    L = abi.lib()
+    h = ctypes.c_void_p()
+    if objText is not None:
+        ob = objText.encode() if isinstance(objText, str) else objText
+        mb = (mtlText.encode() if isinstance(mtlText, str) else mtlText) if mtlText else b""
+        abi.check(L.okrt_obj_load_memory(ob, len(ob), mb if mb else None, len(mb), scale, ctypes.byref(h)))
+    else:
+        abi.check(L.okrt_obj_load(str(path).encode(), scale, ctypes.byref(h)))
+    try:
+        out = []
+        for i in range(L.okrt_obj_num_meshes(h)):
+            view = abi.MeshView()
+            name = ctypes.c_char_p()
+            abi.check(L.okrt_obj_mesh(h, i, ctypes.cast(ctypes.pointer(view), ctypes.c_void_p), ctypes.byref(name)))
+            n = int(view.numTriangles)
+            pos = abi.as_array(view.trianglesPos, abi.TRIANGLE, n)
+            info = abi.as_array(view.trianglesInfo, abi.TRIANGLE_INFO, n)
+            box = (np.array([view.boundingBox[k] for k in range(3)], np.float32), np.array([view.boundingBox[3 + k] for k in range(3)], np.float32))
+            nm = (name.value or b"").decode("utf-8", "replace")
+            tex = tuple(L.okrt_obj_texture_path(h, i, s).decode("utf-8", "replace") for s in range(5))
+            out.append(ObjectDescription(Mesh(pos, info, box, nm), nm, tex))
+        return out
+    finally:
+        L.okrt_obj_free(h)
+
+
 class Geometry:
     """Result of loadMeshAndBvhData: the three GPU arrays + mesh descriptors (RayTracer.cpp:120-217)."""
 

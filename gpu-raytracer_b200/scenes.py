@@ -310,6 +310,41 @@ def glass_scene(segments=64, rings=40):
     return rm, sc, info
 
 
+def glass_scene_from_meshes(meshes, note):
+    """BASELINE configs[2] as Application.cpp:42 would set it up: the cups of ikea_glass.obj (scale 10) as glass
+    (transparency 1, IOR 1.5, roughness 0) on a ground quad, sky cube."""
+    rm, sc = ResourceManager(), Scene()
+    for m in meshes:
+        sc.addMeshEntity(rm.addMesh(m), material(albedo=(1, 1, 1), transparency=1.0, indexOfRefraction=1.5, roughness=0.0))
+    ground = rm.addMesh(make_mesh(*quad((-20, 0, -20), (20, 0, -20), (20, 0, 20), (-20, 0, 20), uv_scale=10.0), name="ground"))
+    sc.addMeshEntity(ground, material(albedo=(0.55, 0.5, 0.45)))
+    sc.setCamera((0.65, 1.45, -2.1), (22.0, 0.0, 0.0), 90.0, 0.1)
+    info = dict(name="glass", stand_in=False, octree=(2, 50), bvh=(30, 5), note=note)
+    return rm, sc, info
+
+
+def glass_scene_from_fixture(path):
+    """The real asset from tests/golden/ikea_glass_mesh.npz (written by tests/golden/make_golden.py from the reference's
+    resources/meshes/ikea_glass.obj through okrt.loadObjects)."""
+    z = np.load(path)
+    meshes, start = [], 0
+    for count, name in zip(z["counts"], z["names"]):
+        end = start + int(count)
+        info = np.zeros(end - start, dtype=abi.TRIANGLE_INFO)
+        info["vertexInfo"]["normal"] = z["normals"][start:end]
+        info["vertexInfo"]["uv"] = z["uvs"][start:end]
+        tp = np.zeros(end - start, dtype=abi.TRIANGLE)
+        tp["position"] = z["positions"][start:end]
+        meshes.append(Mesh(tp, info, name=str(name)))
+        start = end
+    return glass_scene_from_meshes(meshes, "ikea_glass.obj via okrt_obj_load (fixture tests/golden/ikea_glass_mesh.npz)")
+
+
+def glass_scene_from_obj(path, scale=10.0):
+    from .raytracer import loadObjects
+    return glass_scene_from_meshes([o.mesh for o in loadObjects(path, scale)], "ikea_glass.obj via okrt_obj_load")
+
+
 # ------------------------------------------------------------------ C4/C5: Sponza stand-in
 _SPONZA_MATERIALS = ["bricks", "stone", "stone", "fabric", "fabric", "fabric", "checker", "stone", "bricks", "stone", "noise",
                      "fabric", "stone", "noise", "stone", "bricks", "noise", "stone", "fabric", "fabric", "fabric", "stone",

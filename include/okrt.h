@@ -25,6 +25,7 @@
 #ifndef OKRT_H
 #define OKRT_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -328,6 +329,23 @@ OKRT_API int okrt_scale_texture(const uint8_t* srcRgba8, uint32_t srcW, uint32_t
                                 uint8_t* dstRgba8, uint32_t dstW, uint32_t dstH);
 OKRT_API int okrt_environment_cross_to_faces(const uint8_t* crossRgba8, uint32_t imgW, uint32_t imgH,
                                              uint8_t* outFaces6 /* 6*(imgW/4)*(imgH/3)*4 */);
+
+/* f1: Importer::loadObjects (Importer.cpp:77-120) + aiMeshToMeshData (:15-56) for Wavefront OBJ / MTL: one mesh
+ * per (object or group, material) as assimp's OBJ importer forms them, run through the reference's post-process
+ * flags Triangulate | ConvertToLeftHanded | CalcTangentSpace, de-indexed, position * scale.  assimp is not
+ * available to this build (prebuilt Windows library in the reference): its behaviour is restated, parity at the
+ * import boundary is unpinned (csrc/okrt_obj.cpp). */
+typedef struct okrt_obj okrt_obj;
+enum { OKRT_OBJ_TEX_ALBEDO = 0, OKRT_OBJ_TEX_ROUGHNESS = 1, OKRT_OBJ_TEX_METALLIC = 2, OKRT_OBJ_TEX_SPECULAR = 3,
+       OKRT_OBJ_TEX_NORMAL = 4 };                /* ObjectDecriptionStr texture paths, Importer.h */
+OKRT_API int okrt_obj_load(const char* path, float scale, okrt_obj** out);       /* reads <path> and the .mtl files it names */
+OKRT_API int okrt_obj_load_memory(const char* objText, size_t objLen, const char* mtlText, size_t mtlLen,
+                                  float scale, okrt_obj** out);
+OKRT_API void okrt_obj_free(okrt_obj* a);
+OKRT_API uint32_t okrt_obj_num_meshes(const okrt_obj* a);
+/* view->trianglesPos / trianglesInfo stay owned by the asset; *name (optional) is the aiMesh name */
+OKRT_API int okrt_obj_mesh(const okrt_obj* a, uint32_t i, okrt_mesh_view* view, const char** name);
+OKRT_API const char* okrt_obj_texture_path(const okrt_obj* a, uint32_t mesh, uint32_t slot);   /* "" when the material binds none */
 
 /* ------------------------------------------------------- renderer (device) */
 OKRT_API int  okrt_create(int device, uint32_t width, uint32_t height, okrt_renderer** out); /* RayTracer::initiate :60 */

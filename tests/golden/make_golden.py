@@ -100,6 +100,27 @@ def main():
                             segments=o["segments"], W=W, H=H, bounces=bounces)
         print("render", name, o["segments"], "segments")
 
+    glass_fixture(okrt)
+
+
+def glass_fixture(okrt):
+    """resources/meshes/ikea_glass.obj as the product's OBJ reader delivers it (scale 10, Application.cpp:42):
+    positions, normals and uvs of the three cups, so that BASELINE configs[2] runs on the real asset where
+    /root/reference does not exist.  Tangents are not stored (no normal map is bound; the loader fills them)."""
+    path = "/root/reference/resources/meshes/ikea_glass.obj"
+    objs = okrt.loadObjects(path, 10.0)
+    np.savez_compressed(os.path.join(HERE, "ikea_glass_mesh.npz"),
+                        positions=np.concatenate([o.mesh.trianglesPos["position"] for o in objs]),
+                        normals=np.concatenate([o.mesh.trianglesInfo["vertexInfo"]["normal"] for o in objs]),
+                        uvs=np.concatenate([o.mesh.trianglesInfo["vertexInfo"]["uv"] for o in objs]),
+                        counts=np.array([len(o.mesh.trianglesPos) for o in objs], np.uint32),
+                        names=np.array([o.name for o in objs]))
+    print("ikea_glass", [len(o.mesh.trianglesPos) for o in objs], "triangles")
+
 
 if __name__ == "__main__":
-    main()
+    import sys
+    if "glass" in sys.argv[1:]:
+        glass_fixture(importlib.import_module("gpu-raytracer_b200"))
+    else:
+        main()
