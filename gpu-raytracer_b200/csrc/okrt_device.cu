@@ -136,7 +136,7 @@ struct okrt_renderer {
     int numSms = 0, blocksPerSmLean = 1, blocksPerSmInstrumented = 1;   /* persistent grid = SMs x resident blocks */
     int blocksPerSmTrace = 1;
     WavefrontBuffers wb{};                      /* path state of the wavefront pipeline (sized for width x height) */
-    size_t wbPaths = 0;
+    size_t wbPaths = 0, wbReserve = 0;
 };
 
 namespace {
@@ -265,7 +265,7 @@ int launchWavefront(okrt_renderer* r, const FrameParams& fp, bool instrumented)
 {
     const size_t slots = (size_t)fp.numTiles * kTilePixels;
     const size_t paths = slots * fp.batchFrames;
-    int rc = ensureWavefront(r, paths);
+    int rc = ensureWavefront(r, std::max(paths, r->wbReserve));
     if (rc) return rc;
     const DeviceScene scene = sceneView(r);
     OKRT_CUDA(cudaMemsetAsync(r->wb.counts, 0, kCountWords * sizeof(uint32_t), r->stream));
@@ -317,17 +317,27 @@ int launchWavefront(okrt_renderer* r, const FrameParams& fp, bool instrumented)
 /* Renders up to `want` frames in one go and reports how many (`done`).  The wavefront pipeline traces several
  * progressive frames together (more rays per launch, fewer launches, better strong scaling); u1 still receives
  * them in frame order.  Instrumented runs, the megakernel and accumulation-off render one frame per call. */
-constexpr uint32_t kMaxBatchFrames = 8;
-constexpr size_t kMaxBatchPaths = (size_t)1 << 26;
+constexpr uint32_t kMaxBatchFrames = 32;
+constexpr size_t kMaxBatchPaths = (size_t)1 << 25;
 
 int launchFrames(okrt_renderer* r, uint32_t want, uint32_t& done)
 {
     done = 1u;
     const bool instrumentedRun = r->opt.writeAov != 0u || r->rd.debugMode != 0u;
     const bool wavefront = r->opt.pipeline == OKRT_PIPELINE_WAVEFRONT && r->opt.maxBounces <= kMaxWavefrontBounces;
+    /* pixel slots this handle traces per frame (its share of the 8-row bands under tile sharding) */
+    uint32_t ownedRows = r->height;
+    if (r->opt.shardMode == OKRT_SHARD_TILE && r->opt.shardCount > 1u) {
+        const uint32_t band = r->opt.shardBandRows ? r->opt.shardBandRows : 8u;
+        const uint32_t bands = (r->height + band - 1u) / band;
+        ownedRows = (bands / r->opt.shardCount + ((bands % r->opt.shardCount) > r->opt.shardRank ? 1u : 0u)) * band;
+    }
+    const size_t slotsPerFrame = (size_t)((r->width + kTileW - 1) / kTileW) * ((ownedRows + kTileH - 1) / kTileH) * kTilePixels;
+    r->wbReserve = slotsPerFrame;
     if (wavefront && !instrumentedRun && r->rd.accumulationEnabled == 1u) {
-        const size_t slots = (size_t)((r->width + kTileW - 1) / kTileW) * ((r->height + kTileH - 1) / kTileH) * kTilePixels;
-        done = (uint32_t)std::max<size_t>(1, std::min<size_t>(std::min<uint32_t>(want, kMaxBatchFrames), kMaxBatchPaths / std::max<size_t>(slots, 1)));
+        const size_t most = std::max<size_t>(1, std::min<size_t>(kMaxBatchFrames, kMaxBatchPaths / std::max<size_t>(slotsPerFrame, 1)));
+        done = (uint32_t)std::min<size_t>(want, most);
+        r->wbReserve = slotsPerFrame * most;          /* allocate for the largest batch at once: no re-allocation between batches */
     }
     /* updateBuffers: the counter advances before the constants are uploaded (RayTracer.cpp:489) */
     const uint32_t firstLocalFrame = r->rd.numAccumulationFrames + r->rd.accumulationEnabled;
