@@ -100,11 +100,12 @@ def measured_peak_gbs():
 
 def algorithmic_bytes_per_segment(visits, pixels_frames):
     """B_seg = 36 N_box + 36 N_tri + 232 N_inst + 48 N_oct + [hit](132 + 68) + 16 per texture tap,
-    with the ORACLE's visit counts in reference order, plus 36 B per pixel per frame (accumulate + store)."""
+    with the ORACLE's visit counts in reference order, plus 36 B per pixel per frame (accumulate + store).
+    Returns (whole path, traversal only): the traversal part (rows a4) is what the dominant kernel is charged with."""
     seg = max(1, visits["segments"])
-    b = (36 * visits["bvhNodes"] + 36 * visits["triangles"] + 232 * visits["instances"] + 48 * visits["octNodes"]
-         + 200 * visits["hits"] + 16 * visits["textureTaps"] + 36 * pixels_frames)
-    return b / seg
+    trav = 36 * visits["bvhNodes"] + 36 * visits["triangles"] + 232 * visits["instances"] + 48 * visits["octNodes"]
+    rest = 200 * visits["hits"] + 16 * visits["textureTaps"] + 36 * pixels_frames
+    return (trav + rest) / seg, trav / seg
 
 
 def cpu_baseline_sample(okrt, host, env, threads=0):
@@ -215,6 +216,7 @@ def main():
     clocks = sampler.finish()
     st = r.stats()
     dev_ms = float(st["lastRenderMs"])
+    trace_ms, trace_launches = float(st["traceKernelMs"]), int(st["traceKernelLaunches"])
     segments = int(st["raySegments"])
     launches = int(st["kernelLaunches"])
     fallback = int(st["fallbackSegments"])
@@ -254,20 +256,25 @@ def main():
         if world == 1 and not args.no_cpu_baseline:
             cpu, visits = cpu_baseline_sample(okrt, host, env, args.cpu_threads)
             line["cpu_baseline"] = cpu
-            bseg = algorithmic_bytes_per_segment(visits, WIDTH * HEIGHT)
+            bseg_path, bseg = algorithmic_bytes_per_segment(visits, WIDTH * HEIGHT)
             peak, which = measured_peak_gbs()
-            achieved = bseg * segments / (dev_ms * 1e-3) / 1e9
+            achieved = bseg * segments / (max(trace_ms, 1e-6) * 1e-3) / 1e9
             traffic = None
             tpath = os.path.join(ROOT, "profiles", "traffic_bytes_per_launch.json")
             if os.path.exists(tpath):
                 try:
                     with open(tpath) as f:
-                        traffic = json.load(f).get("pathTraceKernel")
+                        tj = json.load(f)
+                        # DRAM bytes of the captured launch, scaled to this run's average launch by duration
+                        traffic = tj["traceFastKernel"] * (trace_ms / max(1, trace_launches)) / tj["traceFastKernel_ms"]
                 except Exception:
                     traffic = None
             line["roofline"] = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                                "traffic": traffic, "peak_source": which,
-                                "algorithmic_bytes_per_segment": bseg,
+                                "traffic": traffic, "peak_source": which, "kernel": "traceFastKernel",
+                                "kernel_launches": trace_launches, "kernel_ms_per_launch": trace_ms / max(1, trace_launches),
+                                "kernel_share_of_step": trace_ms / dev_ms,
+                                "algorithmic_bytes_per_launch": bseg * segments / max(1, trace_launches),
+                                "algorithmic_bytes_per_segment": bseg, "algorithmic_bytes_per_segment_whole_path": bseg_path,
                                 "note": "algorithmic bytes = what the reference's traversal order reads per segment (SURVEY.md 8d); the "
                                         "kernel visits far fewer nodes, and the scene is L2-resident, so DRAM traffic is much lower"}
         print(json.dumps(line))

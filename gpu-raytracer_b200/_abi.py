@@ -52,7 +52,7 @@ AOV = np.dtype([("hitKind", "<u4"), ("hitIdx", "<u4"), ("triIdx", "<u4"), ("bary
                 ("distance", "<f4"), ("bbCheckCount", "<u4"), ("triCheckCount", "<u4"), ("numSegments", "<u4"),
                 ("flags", "<u4"), ("radiance", "<f4", 3), ("reserved", "<u4")])
 STATS = np.dtype([("raySegments", "<u8"), ("fallbackSegments", "<u8"), ("pixelsTraced", "<u8"), ("kernelLaunches", "<u8"),
-                  ("lastRenderMs", "<f4"), ("reserved", "<f4", 3)])
+                  ("lastRenderMs", "<f4"), ("traceKernelMs", "<f4"), ("traceKernelLaunches", "<f4"), ("reserved", "<f4", 1)])
 
 WIRE_SIZES = {"TRIANGLE": 36, "VERTEX_INFO": 44, "TRIANGLE_INFO": 132, "AABB": 24, "BVH_NODE": 36, "OCTREE_NODE": 48,
               "MATERIAL": 68, "MESH_INSTANCE": 232, "SPHERE": 84, "DIRECTIONAL_LIGHT": 32, "POINT_LIGHT": 32,

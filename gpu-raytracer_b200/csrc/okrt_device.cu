@@ -108,6 +108,8 @@ struct okrt_renderer {
     int device = 0;
     cudaStream_t stream = nullptr;
     cudaEvent_t evStart = nullptr, evStop = nullptr;
+    std::vector<cudaEvent_t> traceEvents;      /* pairs around every traversal-kernel launch of the last render call */
+    size_t traceEventsUsed = 0;
     uint32_t width = 0, height = 0;
 
     DeviceBuffer triPos, triInfo, bvhNodes, octNodes, spheres, instances, dirLights, pointLights, spotLights;
@@ -282,7 +284,17 @@ int launchWavefront(okrt_renderer* r, const FrameParams& fp, bool instrumented)
         uint32_t* qout = r->wb.queue[(b + 1u) & 1u];
         if (fp.traversal == OKRT_TRAVERSAL_EXACT) traceExactKernel<<<flatGrid, 128, 0, r->stream>>>(scene, fp, r->wb, qin, b);
         else {
+            cudaEvent_t e0 = nullptr, e1 = nullptr;
+            if (r->traceEventsUsed + 2 > r->traceEvents.size()) {
+                r->traceEvents.resize(r->traceEventsUsed + 2, nullptr);
+                OKRT_CUDA(cudaEventCreate(&r->traceEvents[r->traceEventsUsed]));
+                OKRT_CUDA(cudaEventCreate(&r->traceEvents[r->traceEventsUsed + 1]));
+            }
+            e0 = r->traceEvents[r->traceEventsUsed]; e1 = r->traceEvents[r->traceEventsUsed + 1];
+            r->traceEventsUsed += 2;
+            OKRT_CUDA(cudaEventRecord(e0, r->stream));
             traceFastKernel<<<traceGrid, kTraceBlockThreads, 0, r->stream>>>(scene, fp, r->wb, qin, b);
+            OKRT_CUDA(cudaEventRecord(e1, r->stream));
             traceFallbackKernel<<<fallbackGrid, 128, 0, r->stream>>>(scene, fp, r->wb, b);
             r->launches++;
         }
@@ -466,6 +478,7 @@ void okrt_destroy(okrt_renderer* r)
     if (r->aov) cudaFree(r->aov);
     if (r->counters) cudaFree(r->counters);
     freeWavefront(r);
+    for (cudaEvent_t e : r->traceEvents) if (e) cudaEventDestroy(e);
     if (r->evStart) cudaEventDestroy(r->evStart);
     if (r->evStop) cudaEventDestroy(r->evStop);
     if (r->stream) cudaStreamDestroy(r->stream);
@@ -606,6 +619,7 @@ int okrt_render_frames(okrt_renderer* r, uint32_t frames)
     int rc = checkHandle(r, "okrt_render"); if (rc) return rc;
     if (r->layoutDirty && (rc = rebuildLayout(r))) return rc;
     if (r->opt.writeAov && (rc = ensureAov(r))) return rc;
+    r->traceEventsUsed = 0;
     OKRT_CUDA(cudaEventRecord(r->evStart, r->stream));
     for (uint32_t f = 0; f < frames;) {
         uint32_t done = 1u;
@@ -709,6 +723,13 @@ int okrt_get_stats(okrt_renderer* r, okrt_stats* out)
     float ms = 0.f;
     if (cudaEventElapsedTime(&ms, r->evStart, r->evStop) == cudaSuccess) r->lastRenderMs = ms; else cudaGetLastError();
     out->lastRenderMs = r->lastRenderMs;
+    float traceMs = 0.f;
+    for (size_t i = 0; i + 1 < r->traceEventsUsed; i += 2) {
+        float t = 0.f;
+        if (cudaEventElapsedTime(&t, r->traceEvents[i], r->traceEvents[i + 1]) == cudaSuccess) traceMs += t; else cudaGetLastError();
+    }
+    out->traceKernelMs = traceMs;
+    out->traceKernelLaunches = (float)(r->traceEventsUsed / 2);
     return OKRT_OK;
 }
 

@@ -262,7 +262,9 @@ typedef struct okrt_stats {
     uint64_t pixelsTraced;
     uint64_t kernelLaunches;      /* CUDA kernels launched by this handle since reset_stats */
     float    lastRenderMs;        /* device time of the last okrt_render/_frames call (CUDA events) */
-    float    reserved[3];
+    float    traceKernelMs;       /* of that call: summed device time of the traversal kernel launches (CUDA events around each) */
+    float    traceKernelLaunches; /* how many launches traceKernelMs covers */
+    float    reserved[1];
 } okrt_stats;
 
 typedef struct okrt_renderer okrt_renderer;   /* RayTracer instance */
