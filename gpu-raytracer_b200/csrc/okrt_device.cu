@@ -214,6 +214,7 @@ DeviceScene sceneView(const okrt_renderer* r)
     s.numSpheres = r->spheres.count; s.numInstances = r->instances.count;
     s.numDirLights = r->dirLights.count; s.numPointLights = r->pointLights.count; s.numSpotLights = r->spotLights.count;
     s.texSize = r->textures.width; s.texLayers = r->textures.layers;
+    s.texInvSize = r->textures.width ? 1.0f / (float)r->textures.width : 0.f;
     s.envW = r->environment.width; s.envH = r->environment.height;
     s.fastNodes = (const float4*)r->fastNodes.ptr;
     s.fastTris = (const float4*)r->fastTris.ptr;

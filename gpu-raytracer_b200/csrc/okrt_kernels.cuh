@@ -90,6 +90,7 @@ struct DeviceScene {
     const okrt_spot_light* spotLights;        /* t10 */
     uint32_t numTris, numBvhNodes, numOctNodes, numSpheres, numInstances, numDirLights, numPointLights, numSpotLights;
     uint32_t texSize, texLayers, envW, envH;
+    float texInvSize;                          /* 1 / texSize */
     /* fast layout */
     const float4* fastNodes;
     const float4* fastTris;
@@ -207,7 +208,30 @@ __device__ __forceinline__ float rayAndAABBDist(V3 o, V3 idir, V3 bmin, V3 bmax)
 __device__ __forceinline__ V3 rcp3(V3 d) { return v3(1.f / d.x, 1.f / d.y, 1.f / d.z); }
 
 /* --------------------------------------------------------------- textures */
-__device__ __forceinline__ V3 texelRgb(uchar4 t) { return v3((float)t.x / 255.0f, (float)t.y / 255.0f, (float)t.z / 255.0f); }
+/* (float)k / 255.0f for k = 0..255, correctly rounded, without the IEEE division sequence: one Newton step on
+ * q0 = k * RN(1/255) with fused multiply-adds.  Equal to the division for all 256 inputs (checked exhaustively in
+ * exact rational arithmetic, tests/test_cpu_oracle.py::test_unorm8_division_by_refinement). */
+__device__ __forceinline__ float unorm8ToFloat(unsigned char k)
+{
+    const float x = (float)k, r = __uint_as_float(0x3B808081u);
+    const float q0 = __fmul_rn(x, r);
+    return __fmaf_rn(__fmaf_rn(-255.0f, q0, x), r, q0);
+}
+__device__ __forceinline__ V3 texelRgb(uchar4 t) { return v3(unorm8ToFloat(t.x), unorm8ToFloat(t.y), unorm8ToFloat(t.z)); }
+/* floor-mod of an integer-valued float by the texture size (WRAP addressing): the exact remainder, through a
+ * float quotient estimate that is off by at most one below 2^22 */
+__device__ __forceinline__ int wrapIndex(float xf, int N, float invN)
+{
+    const int xi = (int)xf;
+    if (fabsf(xf) < 4194304.0f) {
+        int r = xi - __float2int_rd(xf * invN) * N;
+        if (r < 0) r += N;
+        if (r >= N) r -= N;
+        return r;
+    }
+    int r = xi % N;
+    return r < 0 ? r + N : r;
+}
 __device__ __forceinline__ bool finitef_(float x) { return x - x == 0.0f; }
 __device__ __forceinline__ V3 bilerp(V3 c00, V3 c10, V3 c01, V3 c11, float fx, float fy)
 {
@@ -231,8 +255,7 @@ __device__ __forceinline__ V3 sampleTexture(const DeviceScene& s, uint32_t textu
     if (!(fabsf(y) < 1.0e9f)) y = 0.0f;
     const float xf = floorf(x), yf = floorf(y);
     const float fx = x - xf, fy = y - yf;
-    int x0 = (int)xf % N; if (x0 < 0) x0 += N;
-    int y0 = (int)yf % N; if (y0 < 0) y0 += N;
+    const int x0 = wrapIndex(xf, N, s.texInvSize), y0 = wrapIndex(yf, N, s.texInvSize);
     const int x1 = x0 + 1 == N ? 0 : x0 + 1;
     const int y1 = y0 + 1 == N ? 0 : y0 + 1;
     const uchar4 t00 = tex2DLayered<uchar4>(s.textures, (float)x0 + 0.5f, (float)y0 + 0.5f, layer);

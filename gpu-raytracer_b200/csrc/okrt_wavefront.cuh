@@ -290,8 +290,11 @@ traceFastKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ F
 
 /* ------------------------------------------------------------------- shade
  * RaytracerCS.hlsl:336-392 (hit resolve) + :448-536 for one queued path per thread. */
+#ifndef OKRT_SHADE_MIN_BLOCKS
+#define OKRT_SHADE_MIN_BLOCKS 8
+#endif
 template <bool kInstrumented>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, OKRT_SHADE_MIN_BLOCKS)
 shadeKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ FrameParams fp, const WavefrontBuffers wb,
             const uint32_t* __restrict__ queueIn, uint32_t* __restrict__ queueOut, uint32_t bounce)
 {

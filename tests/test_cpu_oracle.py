@@ -160,3 +160,36 @@ def test_oracle_libm_mode_is_statistically_equal(okrt, oracle):
     assert np.array_equal(a["aov"]["triIdx"], b["aov"]["triIdx"])
     ma, mb = acc[0][..., :3].mean() / 32, acc[1][..., :3].mean() / 32
     assert abs(ma - mb) / max(ma, 1e-6) < 0.03
+
+
+def test_unorm8_division_by_refinement():
+    """csrc/okrt_kernels.cuh unorm8ToFloat: q = fma(fma(-255, q0, k), r, q0) with q0 = RN(k * r), r = RN(1/255), equals the
+    correctly rounded k / 255 (what the oracle's and the shader's division gives) for all 256 texel values —
+    exact rational arithmetic, one rounding per fused operation."""
+    from fractions import Fraction
+
+    def rn(x):
+        if x == 0:
+            return Fraction(0)
+        sign = -1 if x < 0 else 1
+        x = abs(x)
+        e = 0
+        while Fraction(2) ** e > x:
+            e -= 1
+        while Fraction(2) ** (e + 1) <= x:
+            e += 1
+        ulp = Fraction(2) ** (e - 23)
+        q = x / ulp
+        fl = q.numerator // q.denominator
+        rem = q - fl
+        if rem > Fraction(1, 2) or (rem == Fraction(1, 2) and fl % 2 == 1):
+            fl += 1
+        return sign * fl * ulp
+
+    r = rn(Fraction(1, 255))
+    assert r == Fraction(int(np.float32(np.uint32(0x3B808081).view(np.float32)) * 2 ** 40), 2 ** 40) or float(r) == float(np.uint32(0x3B808081).view(np.float32))
+    for k in range(256):
+        q0 = rn(Fraction(k) * r)
+        q = rn(q0 + rn(Fraction(k) - 255 * q0) * r)
+        assert q == rn(Fraction(k, 255)), k
+        assert float(q) == float(np.float32(k) / np.float32(255.0))
