@@ -376,6 +376,78 @@ __device__ __noinline__ void traverseExact(const DeviceScene& s, uint32_t numSph
     }
 }
 
+/* The bounded reference-order traversal for ONE ray, run by a whole warp (traceFallbackKernel).  All lanes hold the
+ * same ray and the same state; control flow is uniform except for the instance lists, where lane l prepares instance
+ * base + l (local ray, distance to the root box of its BVH — the value the reference's first pop of that instance
+ * compares with payload.distance, RaytracerCS.hlsl:285).  The warp then walks the instances whose root box starts
+ * inside the window in the reference's order (ascending index), applying the reference's own cull against the
+ * current payload.distance in that order.  An oct-tree node lists ~70 instances on the bench scene and a few of
+ * them survive: the 70 dependent (instance record -> root node) fetches of the scalar form become 3 parallel rounds. */
+__device__ __noinline__ void traverseExactWarp(const DeviceScene& s, uint32_t numSpheres, V3 o, V3 d, Hit& hit, float limit)
+{
+    const uint32_t lane = threadIdx.x & 31u;
+    hit.distance = OKRT_FLT_MAX; hit.kind = 0u; hit.idx = 0xFFFFFFFFu; hit.tri = 0xFFFFFFFFu; hit.u = 0.f; hit.v = 0.f;
+    for (uint32_t i = 0; i < numSpheres; i++) {
+        const okrt_sphere& sp = s.spheres[i];
+        const float t = rayAndSphere(o, d, v3(sp.position), sp.radius);
+        if (t > 0.f && t < hit.distance) { hit.distance = t; hit.idx = i; hit.kind = 1u; }
+    }
+    uint32_t octStack[kExactOctStackCapacity];
+    uint32_t bvhStack[kExactBvhStackCapacity];
+    uint32_t octStackSize = s.numOctNodes ? 1u : 0u;
+    octStack[0] = 0u;
+    const V3 idirWorld = rcp3(d);
+    while (octStackSize > 0u) {
+        const uint32_t octIdx = octStack[--octStackSize];
+        const okrt_octree_node& on = s.octNodes[octIdx];
+        const float octNear = rayAndAABBDist(o, idirWorld, v3(on.boundingBox.min), v3(on.boundingBox.max));
+        if (octNear >= hit.distance || octNear >= limit) continue;
+        const uint32_t mStart = on.meshesStartIdx, mEnd = on.meshesEndIdx;
+        for (uint32_t base = mStart; base < mEnd; base += 32u) {
+            const uint32_t mine = base + lane;
+            float rootNear = OKRT_FLT_MAX;
+            if (mine < mEnd) {
+                const okrt_mesh_instance& inst = s.instances[mine];
+                const V3 lo = mulPoint(o, inst.inverseTransformMatrix);
+                const V3 lidir = rcp3(normalize(mulDir(d, inst.inverseTransformMatrix)));
+                const okrt_bvh_node& root = s.bvhNodes[inst.bvhNodeStartIdx];
+                rootNear = rayAndAABBDist(lo, lidir, v3(root.boundingBox.min), v3(root.boundingBox.max));
+            }
+            uint32_t pending = __ballot_sync(0xFFFFFFFFu, rootNear < limit);
+            while (pending) {
+                const uint32_t l = (uint32_t)__ffs(pending) - 1u;
+                pending &= pending - 1u;
+                if (__shfl_sync(0xFFFFFFFFu, rootNear, l) >= hit.distance) continue;      /* the reference's cull at the root pop */
+                const uint32_t i = base + l;
+                const okrt_mesh_instance& inst = s.instances[i];
+                const V3 lo = mulPoint(o, inst.inverseTransformMatrix);
+                const V3 ld = normalize(mulDir(d, inst.inverseTransformMatrix));
+                const V3 lidir = rcp3(ld);
+                uint32_t bvhStackSize = 1u;
+                bvhStack[0] = inst.bvhNodeStartIdx;
+                while (bvhStackSize > 0u) {
+                    const uint32_t nodeIdx = bvhStack[--bvhStackSize];
+                    const okrt_bvh_node& bn = s.bvhNodes[nodeIdx];
+                    const float boxNear = rayAndAABBDist(lo, lidir, v3(bn.boundingBox.min), v3(bn.boundingBox.max));
+                    if (boxNear >= hit.distance || boxNear >= limit) continue;
+                    const uint32_t first = bn.firstChildIdx;
+                    if (first != 0xFFFFFFFFu) { bvhStack[bvhStackSize++] = first; bvhStack[bvhStackSize++] = first + 1u; continue; }
+                    const uint32_t tEnd = bn.triEnd;
+                    for (uint32_t j = bn.triStart; j < tEnd; j++) {
+                        const float* tp = s.triPos + (size_t)j * 9;
+                        float bu = 0.f, bv = 0.f;
+                        float t = rayAndTriangle(lo, ld, v3(tp), v3(tp + 3), v3(tp + 6), bu, bv);
+                        if (t <= 0.f) continue;
+                        t = length(mulDir(ld * t, inst.transformMatrix));     /* RaytracerCS.hlsl:312-314 */
+                        if (t < hit.distance) { hit.distance = t; hit.idx = i; hit.kind = 2u; hit.tri = j; hit.u = bu; hit.v = bv; }
+                    }
+                }
+            }
+        }
+        for (uint32_t c = 0; c < on.numChildren; c++) octStack[octStackSize++] = on.firstChildIdx + c;
+    }
+}
+
 /* ------------------------------------------------ near-first traversal
  * Same boxes, same triangles, same arithmetic — different visiting order and a different culling
  * hierarchy at the top.  Correctness argument (DESIGN.md "Order independence"): with relaxed culling

@@ -137,20 +137,22 @@ traceFallbackKernel(const __grid_constant__ DeviceScene s, const __grid_constant
 {
     const uint32_t count = wb.fallbackCounts[bounce];
     const uint32_t numSpheres = fp.rd.numSpheres < s.numSpheres ? fp.rd.numSpheres : s.numSpheres;
-    /* one ray per WARP, traced by lane 0: 32 unrelated reference-order traversals in one warp diverge completely and
-     * serialise (measured: ~1 ms per launch for ~2000 rays); with a warp each the launch lasts one traversal */
+    /* one ray per WARP: 32 unrelated reference-order traversals in one warp diverge completely and serialise
+     * (measured: ~1 ms per launch for ~2000 rays); a warp per ray lasts one traversal, and the warp shares the
+     * instance tests of that traversal among its lanes (traverseExactWarp) */
     const uint32_t warpsPerGrid = gridDim.x * (blockDim.x >> 5);
-    if ((threadIdx.x & 31u) == 0u)
     for (uint32_t k = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); k < count; k += warpsPerGrid) {
         const uint32_t path = wb.fallbackQueue[k];
         const float4 ro = wb.rayO[path], rdv = wb.rayD[path];
         const float limit = relaxedLimit(wb.hitA[path].x);          /* the near-first traversal's closest distance */
         Hit hit;
-        uint32_t bb = 0u, tc = 0u;
-        traverseExact(s, numSpheres, v3(ro.x, ro.y, ro.z), v3(rdv.x, rdv.y, rdv.z), hit, bb, tc, limit);
-        wb.hitA[path] = make_float4(hit.distance, hit.u, hit.v, __uint_as_float(hit.tri));
-        wb.hitB[path] = (hit.kind << 30) | (hit.idx & 0x3FFFFFFFu);
-        if (fp.aov && bounce == 0u) fp.aov[__float_as_uint(rdv.w)].flags = 1u;
+        traverseExactWarp(s, numSpheres, v3(ro.x, ro.y, ro.z), v3(rdv.x, rdv.y, rdv.z), hit, limit);
+        __syncwarp();
+        if ((threadIdx.x & 31u) == 0u) {
+            wb.hitA[path] = make_float4(hit.distance, hit.u, hit.v, __uint_as_float(hit.tri));
+            wb.hitB[path] = (hit.kind << 30) | (hit.idx & 0x3FFFFFFFu);
+            if (fp.aov && bounce == 0u) fp.aov[__float_as_uint(rdv.w)].flags = 1u;
+        }
     }
     if (blockIdx.x == 0u && threadIdx.x == 0u && count) atomicAdd(fp.counters + 1, (unsigned long long)count);
 }
