@@ -223,6 +223,7 @@ def main():
 
     # ---- end-to-end arm: host constants in, result image out, every step, wall clock around the public call
     pinned_out = np.zeros((HEIGHT, WIDTH, 4), np.uint8)
+    abi.check(r.L.okrt_host_register(abi.ptr(pinned_out), pinned_out.nbytes))     # page-locked: the D2H copy is a plain DMA
     abi.check(r.L.okrt_reset_stats(r.h))
     barrier()
     t0 = time.perf_counter()
@@ -234,6 +235,7 @@ def main():
     barrier()
     e2e_s = time.perf_counter() - t0
     e2e_segments = int(r.stats()["raySegments"])
+    abi.check(r.L.okrt_host_unregister(abi.ptr(pinned_out)))
 
     if dist is not None:
         import torch

@@ -138,6 +138,8 @@ SYMBOLS = [
     ("okrt_read_aov", _I, [_P, _P]),
     ("okrt_write_accumulation", _I, [_P, _P, _U]),
     ("okrt_resolve", _I, [_P, _U]),
+    ("okrt_host_register", _I, [_P, ctypes.c_size_t]),
+    ("okrt_host_unregister", _I, [_P]),
     ("okrt_accumulation_device_ptr", _P, [_P]),
     ("okrt_result_device_ptr", _P, [_P]),
     ("okrt_cuda_stream", _P, [_P]),

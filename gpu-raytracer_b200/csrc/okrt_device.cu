@@ -330,7 +330,7 @@ int launchWavefront(okrt_renderer* r, const FrameParams& fp, bool instrumented)
 /* Renders up to `want` frames in one go and reports how many (`done`).  The wavefront pipeline traces several
  * progressive frames together (more rays per launch, fewer launches, better strong scaling); u1 still receives
  * them in frame order.  Instrumented runs, the megakernel and accumulation-off render one frame per call. */
-constexpr uint32_t kMaxBatchFrames = 32;
+constexpr uint32_t kMaxBatchFrames = 128;
 constexpr size_t kMaxBatchPaths = (size_t)1 << 25;
 
 int launchFrames(okrt_renderer* r, uint32_t want, uint32_t& done)
@@ -349,7 +349,9 @@ int launchFrames(okrt_renderer* r, uint32_t want, uint32_t& done)
     r->wbReserve = slotsPerFrame;
     if (wavefront && !instrumentedRun && r->rd.accumulationEnabled == 1u) {
         const size_t most = std::max<size_t>(1, std::min<size_t>(kMaxBatchFrames, kMaxBatchPaths / std::max<size_t>(slotsPerFrame, 1)));
-        done = (uint32_t)std::min<size_t>(want, most);
+        /* split `want` into equal batches rather than full ones and a small remainder */
+        const size_t batches = (want + most - 1) / most;
+        done = (uint32_t)((want + batches - 1) / batches);
         r->wbReserve = slotsPerFrame * most;          /* allocate for the largest batch at once: no re-allocation between batches */
     }
     /* updateBuffers: the counter advances before the constants are uploaded (RayTracer.cpp:489) */
@@ -704,6 +706,20 @@ int okrt_resolve(okrt_renderer* r, uint32_t totalFrames)
     resolveKernel<<<(unsigned)((n + 255) / 256), 256, 0, r->stream>>>(r->accumulation, r->result, n, (float)totalFrames, r->width, cw, ch);
     r->launches++;
     OKRT_CUDA(cudaGetLastError());
+    return OKRT_OK;
+}
+
+int okrt_host_register(void* ptr, size_t bytes)
+{
+    if (!ptr || !bytes) { setError("okrt_host_register: null argument"); return OKRT_ERR_INVALID_ARGUMENT; }
+    OKRT_CUDA(cudaHostRegister(ptr, bytes, cudaHostRegisterDefault));
+    return OKRT_OK;
+}
+
+int okrt_host_unregister(void* ptr)
+{
+    if (!ptr) { setError("okrt_host_unregister: null argument"); return OKRT_ERR_INVALID_ARGUMENT; }
+    OKRT_CUDA(cudaHostUnregister(ptr));
     return OKRT_OK;
 }
 

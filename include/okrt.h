@@ -389,6 +389,10 @@ OKRT_API int okrt_write_accumulation(okrt_renderer* r, const float* rgba32f, uin
 OKRT_API int okrt_resolve(okrt_renderer* r, uint32_t totalFrames);
 
 /* device pointers for peer/NCCL exchange (sample-sharded mode reduces u1 in place) */
+/* Page-locks a caller-owned host buffer so that okrt_read_* / okrt_write_accumulation copy at full PCIe rate and
+ * without a staging copy (the reference maps a staging texture, DX11.cpp:196-230). */
+OKRT_API int okrt_host_register(void* ptr, size_t bytes);
+OKRT_API int okrt_host_unregister(void* ptr);
 OKRT_API void* okrt_accumulation_device_ptr(okrt_renderer* r);
 OKRT_API void* okrt_result_device_ptr(okrt_renderer* r);
 OKRT_API void* okrt_cuda_stream(okrt_renderer* r);
