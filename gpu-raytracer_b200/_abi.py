@@ -84,6 +84,7 @@ SYMBOLS = [
     ("okrt_options_default", None, [_P]),
     ("okrt_render_data_default", None, [_P]),
     ("okrt_geometry_build", _I, [_P, _U, _U, _U, ctypes.POINTER(_P)]),
+    ("okrt_geometry_build_device", _I, [_P, _U, _U, _I, ctypes.POINTER(_P), ctypes.POINTER(ctypes.c_float)]),
     ("okrt_geometry_free", None, [_P]),
     ("okrt_geometry_num_triangles", _U, [_P]),
     ("okrt_geometry_num_nodes", _U, [_P]),

@@ -398,13 +398,7 @@ static void normalize3(float* v)
 using namespace okrt;
 
 /* =============================================================== C ABI */
-struct okrt_geometry {
-    std::vector<okrt_triangle> triPos;
-    std::vector<okrt_triangle_info> triInfo;
-    std::vector<okrt_bvh_node> nodes;
-    std::vector<okrt_mesh_desc> descs;
-    std::vector<okrt_aabb> bounds;
-};
+/* struct okrt_geometry: okrt_internal.h (shared with the device builder) */
 
 struct okrt_octree {
     std::vector<okrt_octree_node> nodes;

@@ -21,6 +21,15 @@ static_assert(sizeof(okrt_spot_light) == 48, "SpotLight");
 static_assert(sizeof(okrt_render_data) == 240, "RenderData");
 static_assert(sizeof(okrt_aov) == 56, "okrt_aov");
 
+/* result of loadMeshAndBvhData: the three arrays the reference uploads + per-mesh descriptors (RayTracer.h:15-21) */
+struct okrt_geometry {
+    std::vector<okrt_triangle> triPos;
+    std::vector<okrt_triangle_info> triInfo;
+    std::vector<okrt_bvh_node> nodes;
+    std::vector<okrt_mesh_desc> descs;
+    std::vector<okrt_aabb> bounds;
+};
+
 namespace okrt {
 void setError(const std::string& msg);
 int buildBvh(const okrt_triangle* tris, uint32_t numTriangles, const okrt_aabb& rootBounds, uint32_t maxDepth,

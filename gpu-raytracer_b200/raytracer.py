@@ -163,7 +163,9 @@ def loadObjects(path=None, scale=1.0, objText=None, mtlText=None):
 class Geometry:
     """Result of loadMeshAndBvhData: the three GPU arrays + mesh descriptors (RayTracer.cpp:120-217)."""
 
-    def __init__(self, meshes, maxDepth, maxLeafTriangles):
+    def __init__(self, meshes, maxDepth, maxLeafTriangles, device=None):
+        """device=None: the reference's SAH tree, bit for bit (CPU).  device=k: LBVH built on cuda:k (row f2) — the
+        reference's node format with a different tree; self.buildMs is the device-timed duration."""
         L = abi.lib()
         views = (abi.MeshView * max(len(meshes), 1))()
         self._keep = meshes
@@ -175,8 +177,15 @@ class Geometry:
                 views[i].boundingBox[k] = float(m.boundingBox[0][k])
                 views[i].boundingBox[3 + k] = float(m.boundingBox[1][k])
         handle = ctypes.c_void_p()
-        abi.check(L.okrt_geometry_build(ctypes.cast(views, ctypes.c_void_p), len(meshes), maxDepth, maxLeafTriangles,
-                                        ctypes.byref(handle)))
+        self.buildMs = None
+        if device is None:
+            abi.check(L.okrt_geometry_build(ctypes.cast(views, ctypes.c_void_p), len(meshes), maxDepth, maxLeafTriangles,
+                                            ctypes.byref(handle)))
+        else:
+            ms = ctypes.c_float(0.0)
+            abi.check(L.okrt_geometry_build_device(ctypes.cast(views, ctypes.c_void_p), len(meshes), maxLeafTriangles, int(device),
+                                                   ctypes.byref(handle), ctypes.byref(ms)))
+            self.buildMs = float(ms.value)
         self.handle = handle
         nt, nn, nm = L.okrt_geometry_num_triangles(handle), L.okrt_geometry_num_nodes(handle), L.okrt_geometry_num_meshes(handle)
         self.trianglesPos = abi.as_array(L.okrt_geometry_triangles_pos(handle), abi.TRIANGLE, nt)

@@ -296,6 +296,15 @@ OKRT_API const okrt_triangle_info* okrt_geometry_triangles_info(const okrt_geome
 OKRT_API const okrt_bvh_node*      okrt_geometry_bvh_nodes(const okrt_geometry* g);       /* t2 */
 OKRT_API const okrt_mesh_desc*     okrt_geometry_mesh_descs(const okrt_geometry* g);
 OKRT_API const okrt_aabb*          okrt_geometry_mesh_bounds(const okrt_geometry* g);
+/* f2: the same outputs from a builder that runs on the GPU (LBVH: Morton sort, parallel radix tree, bottom-up box
+ * fit, subtrees of <= maxLeafTriangles collapsed to leaves).  Replaces BvhBuilder::buildTree (BvhBuilder.cpp:38-207)
+ * behind RayTracer::loadMeshAndBvhData (RayTracer.cpp:143-201) where a different-but-valid tree is acceptable, e.g.
+ * the UI's rebuild button (Application.cpp:405-411).  Node format, child adjacency and leaf-ordered triangle arrays
+ * are the reference's; the tree is NOT the reference's SAH tree, so images agree with the reference's only up to its
+ * traversal-order tie cases.  No depth limit: okrt_render reports OKRT_ERR_CAPACITY if a tree outgrows the stacks.
+ * outBuildMs (may be NULL): device-timed duration including the host<->device copies.  No CPU fallback. */
+OKRT_API int okrt_geometry_build_device(const okrt_mesh_view* meshes, uint32_t numMeshes, uint32_t maxLeafTriangles,
+                                        int device, okrt_geometry** out, float* outBuildMs);
 /* Single-mesh form of BvhBuilder::buildTree (BvhBuilder.cpp:12-36): nodes use
  * mesh-local indices, triOrder[k] = source triangle stored at leaf slot k.
  * outNodes needs capacity 2*numTriangles+1, outTriOrder numTriangles. */

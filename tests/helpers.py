@@ -4,11 +4,11 @@ import ctypes
 import numpy as np
 
 
-def build_host_side(okrt, rm, sc, info, width, height, spheres=False):
+def build_host_side(okrt, rm, sc, info, width, height, spheres=False, bvhDevice=None):
     """Runs the product's host builders (no GPU needed) and returns every array of the binding table."""
     abi = okrt.abi
     L = abi.lib()
-    geo = okrt.Geometry(rm.meshes, *info.get("bvh", (30, 5)))
+    geo = okrt.Geometry(rm.meshes, *info.get("bvh", (30, 5)), device=bvhDevice)
     oct_ = okrt.OctTree(geo, sc, *info.get("octree", (2, 50)))
     rd = abi.default_render_data()
     rd[0]["textureDims"] = (width, height)

@@ -1,6 +1,8 @@
 """CPU tests of the C-ABI library: it loads without a GPU, exports every symbol include/okrt.h declares, validates
 arguments, and refuses to render without a device (no CPU fallback)."""
 import ctypes
+
+import pytest
 import os
 import re
 import subprocess
@@ -51,6 +53,17 @@ def test_no_device_means_no_renderer(okrt):
     rc = L.okrt_create(0, 64, 64, ctypes.byref(h))
     assert rc == 5 and not h.value                    # OKRT_ERR_NO_DEVICE: there is no CPU path
     assert b"no CUDA device" in L.okrt_last_error()
+
+
+def test_no_device_means_no_device_builder(okrt):
+    """okrt_geometry_build_device (row f2) has no CPU fallback either: without a GPU it fails loudly."""
+    L = okrt.abi.lib()
+    if L.okrt_device_count() > 0:
+        return
+    rm, _, _ = okrt.scenes.glass_scene(16, 8)
+    with pytest.raises(okrt.abi.OkrtError) as err:
+        okrt.Geometry(rm.meshes, 30, 5, device=0)
+    assert err.value.code == 5 and "no CPU fallback" in str(err.value)
 
 
 def test_argument_validation(okrt):
