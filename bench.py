@@ -12,6 +12,7 @@ tile-sharded in interleaved 8-row bands (no data-path collective); value = ray s
 ranks / max-over-ranks device time.  A ray segment is one findClosestHit call (RaytracerCS.hlsl:446).
 """
 import argparse
+import ctypes
 import importlib
 import json
 import os
@@ -225,26 +226,35 @@ def main():
     pinned_out = np.zeros((HEIGHT, WIDTH, 4), np.uint8)
     abi.check(r.L.okrt_host_register(abi.ptr(pinned_out), pinned_out.nbytes))     # page-locked: the D2H copy is a plain DMA
     abi.check(r.L.okrt_reset_stats(r.h))
+    moved = ctypes.c_uint64(0)
     barrier()
     t0 = time.perf_counter()
     for k in range(args.steps):
         rd[0]["numAccumulationFrames"] = r.L.okrt_get_num_accumulation_frames(r.h)
         abi.check(r.L.okrt_set_render_data(r.h, abi.ptr(rd)))                  # H2D: 240 B of constants travel with the launch
         abi.check(r.L.okrt_render_frames(r.h, FRAMES_PER_STEP))
-        abi.check(r.L.okrt_read_result(r.h, abi.ptr(pinned_out)))              # D2H: the RGBA8 result image
+        # D2H: the RGBA8 result image; a tile-sharded rank moves only the row bands it owns into the shared image layout
+        abi.check(r.L.okrt_read_result_owned(r.h, abi.ptr(pinned_out), ctypes.byref(moved)))
     barrier()
     e2e_s = time.perf_counter() - t0
     e2e_segments = int(r.stats()["raySegments"])
     abi.check(r.L.okrt_host_unregister(abi.ptr(pinned_out)))
+    d2h_bytes = int(moved.value)                   # per step, this rank; summed over ranks below = one whole image
 
     if dist is not None:
         import torch
         t = torch.tensor([dev_ms, e2e_s], device="cuda", dtype=torch.float64)
+        per_rank = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(per_rank, t)
+        rank_ms = [round(float(x[0]), 3) for x in per_rank]
+        rank_segments = [torch.zeros(1, device="cuda", dtype=torch.int64) for _ in range(world)]
+        dist.all_gather(rank_segments, torch.tensor([segments], device="cuda", dtype=torch.int64))
+        rank_segments = [int(x) for x in rank_segments]
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        c = torch.tensor([segments, e2e_segments, launches, fallback], device="cuda", dtype=torch.int64)
+        c = torch.tensor([segments, e2e_segments, launches, fallback, d2h_bytes], device="cuda", dtype=torch.int64)
         dist.all_reduce(c, op=dist.ReduceOp.SUM)
         dev_ms, e2e_s = float(t[0]), float(t[1])
-        segments, e2e_segments, launches, fallback = (int(x) for x in c)
+        segments, e2e_segments, launches, fallback, d2h_bytes = (int(x) for x in c)
 
     if rank == 0:
         value = segments / (dev_ms * 1e-3) / 1e6
@@ -252,9 +262,12 @@ def main():
                 "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                 "dtype": "f32", "data": "synthetic", "config": workload_config(world), "clocks": clocks,
                 "e2e": {"value": e2e_segments / e2e_s / 1e6, "unit": UNIT, "h2d_bytes_per_step": 240 + 64,
-                        "d2h_bytes_per_step": WIDTH * HEIGHT * 4},
+                        "d2h_bytes_per_step": d2h_bytes},
                 "gpu_launches": launches,
                 "ray_segments": segments, "fallback_segments": fallback, "traversal": args.traversal}
+        if world > 1:
+            line["rank_ms"] = rank_ms                 # device time of each rank's K steps: shows the load balance of the tile split
+            line["rank_segments"] = rank_segments
         if world == 1 and not args.no_cpu_baseline:
             cpu, visits = cpu_baseline_sample(okrt, host, env, args.cpu_threads)
             line["cpu_baseline"] = cpu

@@ -135,6 +135,7 @@ SYMBOLS = [
     ("okrt_reset_accumulation", _I, [_P]),
     ("okrt_get_num_accumulation_frames", _U, [_P]),
     ("okrt_read_result", _I, [_P, _P]),
+    ("okrt_read_result_owned", _I, [_P, _P, ctypes.POINTER(ctypes.c_uint64)]),
     ("okrt_read_accumulation", _I, [_P, _P]),
     ("okrt_read_aov", _I, [_P, _P]),
     ("okrt_write_accumulation", _I, [_P, _P, _U]),

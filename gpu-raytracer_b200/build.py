@@ -56,7 +56,7 @@ def build_library(force=False, verbose=False, extra_nvcc=(), out=None):
         objs.append(o)
         if force or _stale(o, [s] + common_deps):
             cmd = [_host_cxx(), "-std=c++17", "-O2", "-ffp-contract=off", "-fno-fast-math", "-fPIC", "-pthread",
-                   "-fvisibility=hidden", "-Wall", "-c", s, "-o", o] + inc
+                   "-fvisibility=hidden", "-Wall", "-c", s, "-o", o] + inc + [f for f in extra_nvcc if f.startswith("-D")]
             if verbose:
                 print(" ".join(cmd))
             subprocess.run(cmd, check=True)

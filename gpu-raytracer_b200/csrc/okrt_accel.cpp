@@ -127,14 +127,14 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
 
     /* triangles: 3 x float4 */
     /* triangles: p2 | E1 = p0 - p2 | E2 = p1 - p2 (GPU-Utilities.hlsli:124: the same float32 subtractions, done once) */
-    out.tris.resize((size_t)numTris * 3);
+    out.tris.assign((size_t)numTris * kTriQuads, Float4{0.f, 0.f, 0.f, 0.f});
     for (uint32_t t = 0; t < numTris; t++) {
         const float (*p)[3] = tris[t].position;
         volatile float e[6];
         for (int k = 0; k < 3; k++) { e[k] = p[0][k] - p[2][k]; e[3 + k] = p[1][k] - p[2][k]; }
-        out.tris[(size_t)t * 3 + 0] = Float4{p[2][0], p[2][1], p[2][2], e[0]};
-        out.tris[(size_t)t * 3 + 1] = Float4{e[1], e[2], e[3], e[4]};
-        out.tris[(size_t)t * 3 + 2] = Float4{e[5], 0.f, 0.f, 0.f};
+        out.tris[(size_t)t * kTriQuads + 0] = Float4{p[2][0], p[2][1], p[2][2], e[0]};
+        out.tris[(size_t)t * kTriQuads + 1] = Float4{e[1], e[2], e[3], e[4]};
+        out.tris[(size_t)t * kTriQuads + 2] = Float4{e[5], 0.f, 0.f, 0.f};
     }
 
     /* oct-tree: parents, reachability, reference stack bound */
@@ -403,7 +403,7 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
     /* fast stack: one deferred sibling per level in each tree, plus the instance-exit marker */
     out.maxStackDepth = topDepth + std::max(b.deepestPair, chainDepth) + 2;
     if (b.failed) return false;
-    for (uint32_t t = 0; t < numTris; t++) out.tris[(size_t)t * 3 + 2].y = bitsToFloat(out.triOwner[t]);
+    for (uint32_t t = 0; t < numTris; t++) out.tris[(size_t)t * kTriQuads + 2].y = bitsToFloat(out.triOwner[t]);
     return true;
 }
 

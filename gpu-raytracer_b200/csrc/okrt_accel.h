@@ -47,6 +47,10 @@ constexpr uint32_t kRefNone = 0xFFFFFFFFu;        /* empty scene / empty child *
 constexpr uint32_t kMaxLeafTris = 8;
 constexpr uint32_t kInstQuads = 10;               /* float4 per instance record */
 constexpr uint32_t kMaxTriIndex = (1u << 27);
+#ifndef OKRT_TRI_QUADS
+#define OKRT_TRI_QUADS 3
+#endif
+constexpr uint32_t kTriQuads = OKRT_TRI_QUADS;      /* float4 per triangle record: 3 = 48 B packed, 4 = 64 B (two 256-bit loads) */
 constexpr uint32_t kFastStackCapacity = 64;       /* entries; validated against tree depth at upload */
 constexpr uint32_t kExactBvhStackCapacity = 64;   /* reference: 50, RaytracerCS.hlsl:249 */
 constexpr uint32_t kExactOctStackCapacity = 32;   /* reference: 20, RaytracerCS.hlsl:244 */
@@ -55,7 +59,7 @@ struct Float4 { float x, y, z, w; };
 
 struct FastLayout {
     std::vector<Float4> nodes;          /* 4 per pair node */
-    std::vector<Float4> tris;           /* 3 per triangle */
+    std::vector<Float4> tris;           /* kTriQuads per triangle */
     std::vector<Float4> instances;      /* 8 per instance record, top-level order */
     std::vector<uint32_t> octParent;    /* parent index per oct-tree node (root: 0xFFFFFFFF) */
     std::vector<uint32_t> triOwner;     /* per triangle: instance record of the merged instance that owns it, else ~0u */

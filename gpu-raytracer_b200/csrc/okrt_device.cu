@@ -668,6 +668,42 @@ int okrt_read_result(okrt_renderer* r, uint8_t* outRgba8)
     return OKRT_OK;
 }
 
+/* Tile-sharded ranks own interleaved row bands; only those rows of the result carry this rank's pixels.  One strided
+ * DMA moves them into place in a full-size host image (the caller's compositor sees every rank's rows side by side). */
+int okrt_read_result_owned(okrt_renderer* r, uint8_t* outRgba8, uint64_t* outBytes)
+{
+    int rc = checkHandle(r, "okrt_read_result_owned"); if (rc) return rc;
+    if (!outRgba8) { setError("okrt_read_result_owned: null output"); return OKRT_ERR_INVALID_ARGUMENT; }
+    if (r->opt.shardMode != OKRT_SHARD_TILE || r->opt.shardCount <= 1) {
+        if (outBytes) *outBytes = (uint64_t)r->width * r->height * 4;
+        return okrt_read_result(r, outRgba8);
+    }
+    const size_t rowBytes = (size_t)r->width * 4;
+    const uint32_t band = r->opt.shardBandRows ? r->opt.shardBandRows : 8u, count = r->opt.shardCount, rank = r->opt.shardRank;
+    const uint32_t bands = (r->height + band - 1u) / band;
+    const uint32_t mine = bands / count + ((bands % count) > rank ? 1u : 0u);
+    uint64_t moved = 0;
+    if (mine) {
+        const uint32_t lastBand = rank + (mine - 1u) * count;
+        const uint32_t lastRows = std::min(band, r->height - lastBand * band);          /* the image's last band may be short */
+        const uint32_t fullBands = lastRows == band ? mine : mine - 1u;
+        const size_t first = (size_t)rank * band * rowBytes, pitch = (size_t)count * band * rowBytes;
+        if (fullBands) {
+            OKRT_CUDA(cudaMemcpy2DAsync(outRgba8 + first, pitch, (const uint8_t*)r->result + first, pitch, (size_t)band * rowBytes, fullBands,
+                                        cudaMemcpyDeviceToHost, r->stream));
+            moved += (uint64_t)fullBands * band * rowBytes;
+        }
+        if (fullBands != mine) {
+            const size_t at = (size_t)lastBand * band * rowBytes;
+            OKRT_CUDA(cudaMemcpyAsync(outRgba8 + at, (const uint8_t*)r->result + at, (size_t)lastRows * rowBytes, cudaMemcpyDeviceToHost, r->stream));
+            moved += (uint64_t)lastRows * rowBytes;
+        }
+    }
+    OKRT_CUDA(cudaStreamSynchronize(r->stream));
+    if (outBytes) *outBytes = moved;
+    return OKRT_OK;
+}
+
 int okrt_read_accumulation(okrt_renderer* r, float* outRgba32f)
 {
     int rc = checkHandle(r, "okrt_read_accumulation"); if (rc) return rc;

@@ -538,17 +538,34 @@ __device__ __forceinline__ bool boxPasses(V3 o, V3 idir, float4 lo, float4 hi, f
     return distFar >= distNear && distFar > 0.f && distNear < limit;
 }
 
+#ifndef OKRT_LD256
+#define OKRT_LD256 1
+#endif
+/* one 256-bit read-only load (LDG.E.ENL2.256.CONSTANT, sm_100+): two quads for one L1 tag lookup instead of two.
+ * p must be 32-byte aligned. */
+__device__ __forceinline__ void ldg256(const float4* p, float4& a, float4& b)
+{
+    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
+                 : "l"(p));
+}
+
 /* one child-pair node.  Empty children carry NaN boxes (okrt_accel.cpp), which never pass. */
 __device__ __forceinline__ void stepNode(const DeviceScene& s, StepLane& L, uint32_t* stack)
 {
     OKRT_CHECK(L.cur < s.numFastNodes);
     const float4* q = s.fastNodes + (size_t)L.cur * 4;
+#if OKRT_LD256
+    float4 q0, q1, q2, q3;
+    ldg256(q, q0, q1); ldg256(q + 2, q2, q3);
+#else
     const float4 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3);
+#endif
     const float limit = relaxedLimit(L.best);
     float n0, n1;
+    const uint32_t r0 = __float_as_uint(q0.w), r1 = __float_as_uint(q1.w);
     const bool h0 = boxPasses(L.ro, L.ridir, q0, q1, limit, n0);
     const bool h1 = boxPasses(L.ro, L.ridir, q2, q3, limit, n1);
-    const uint32_t r0 = __float_as_uint(q0.w), r1 = __float_as_uint(q1.w);
     const bool firstIs1 = h1 && (!h0 || n1 < n0);
     OKRT_CHECK(L.sp >= 1 && L.sp < (int)kFastStackCapacity);
     if (h0 && h1) stack[L.sp++] = firstIs1 ? r0 : r1;
@@ -581,8 +598,13 @@ __device__ __forceinline__ void stepTriangle(const DeviceScene& s, StepLane& L, 
 {
     const uint32_t j = L.triNext++;
     OKRT_CHECK(j < s.numTris);
-    const float4* tp = s.fastTris + (size_t)j * 3;
-    const float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);       /* p2 | E1 | E2 */
+    const float4* tp = s.fastTris + (size_t)j * kTriQuads;
+#if OKRT_LD256 && OKRT_TRI_QUADS == 4
+    float4 a, b, c, cPad;
+    ldg256(tp, a, b); ldg256(tp + 2, c, cPad);                              /* p2 | E1 | E2 | owner, padded to 64 B */
+#else
+    const float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);       /* p2 | E1 | E2 | owner */
+#endif
     float bu = 0.f, bv = 0.f;
     float t = rayAndTriangleEdges(L.ro, L.rd, v3(a.x, a.y, a.z), v3(a.w, b.x, b.y), v3(b.z, b.w, c.x), bu, bv);
     if (t > 0.f) {

@@ -390,6 +390,10 @@ OKRT_API uint32_t okrt_get_num_accumulation_frames(const okrt_renderer* r); /* R
 
 /* u0 / u1 read-back (reference: staging copy, DX11.cpp:196-230) */
 OKRT_API int okrt_read_result(okrt_renderer* r, uint8_t* outRgba8);            /* W*H*4 bytes */
+/* Tile-sharded renderer: copies only the row bands this rank owns into their place in a full-size W*H*4 image (other
+ * rows untouched), so N ranks fill one host image without moving N copies of it; *outBytes (may be NULL) = bytes moved.
+ * Unsharded renderers behave like okrt_read_result. */
+OKRT_API int okrt_read_result_owned(okrt_renderer* r, uint8_t* outRgba8, uint64_t* outBytes);
 OKRT_API int okrt_read_accumulation(okrt_renderer* r, float* outRgba32f);      /* W*H*4 floats */
 OKRT_API int okrt_read_aov(okrt_renderer* r, okrt_aov* out);                   /* W*H entries; needs writeAov */
 /* progressive-state restore / merge (new): replaces the accumulation buffer and frame counter */

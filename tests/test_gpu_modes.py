@@ -1,4 +1,6 @@
 """GPU tests of the modes around the hot path: sharding, progressive state, the RayTracer mirror, full-size runs."""
+import ctypes
+
 import numpy as np
 import pytest
 
@@ -23,10 +25,12 @@ def test_tile_sharding_union_equals_single(okrt, pipeline):
     single.options(maxBounces=4, coverAllPixels=1, pipeline=pipeline)
     single.render(host["rd"].copy(), frames=2)
     ref_acc = single.accumulation()
+    ref_img = single.result()
     total = int(single.stats()["raySegments"])
     for world, band in ((2, 8), (3, 16), (8, 8)):
         acc = np.zeros_like(ref_acc)
-        segs = 0
+        img = np.zeros_like(ref_img)          # one host image every rank drops its own bands into (okrt_read_result_owned)
+        segs = moved_total = 0
         for rank in range(world):
             r = helpers.Renderer(okrt, host, W, H, envFaces=env)
             r.options(maxBounces=4, coverAllPixels=1, pipeline=pipeline, **okrt.sharding.tile_options(rank, world, band))
@@ -36,9 +40,15 @@ def test_tile_sharding_union_equals_single(okrt, pipeline):
             other = np.setdiff1d(np.arange(H), rows)
             assert not a[other].any(), "a rank wrote outside its bands"
             acc[rows] = a[rows]
+            moved = ctypes.c_uint64(0)
+            before = img.copy()
+            okrt.abi.check(r.L.okrt_read_result_owned(r.h, okrt.abi.ptr(img), ctypes.byref(moved)))
+            assert moved.value == len(rows) * W * 4 and np.array_equal(img[other], before[other])
+            moved_total += moved.value
             segs += int(r.stats()["raySegments"])
             r.close()
         assert np.array_equal(acc.view(np.uint32), ref_acc.view(np.uint32))
+        assert np.array_equal(img, ref_img) and moved_total == W * H * 4
         assert segs == total
     single.close()
 
