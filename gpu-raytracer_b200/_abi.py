@@ -54,6 +54,10 @@ AOV = np.dtype([("hitKind", "<u4"), ("hitIdx", "<u4"), ("triIdx", "<u4"), ("bary
 STATS = np.dtype([("raySegments", "<u8"), ("fallbackSegments", "<u8"), ("pixelsTraced", "<u8"), ("kernelLaunches", "<u8"),
                   ("lastRenderMs", "<f4"), ("traceKernelMs", "<f4"), ("traceKernelLaunches", "<f4"), ("reserved", "<f4", 1)])
 
+LAYOUT_INFO = np.dtype([("numPairNodes", "<u4"), ("numFlattenedLeaves", "<u4"), ("numMergedInstances", "<u4"),
+                        ("numInstanceRecords", "<u4"), ("fastStackDepth", "<u4"), ("exactBvhDepth", "<u4"), ("exactOctDepth", "<u4"),
+                        ("reserved", "<u4"), ("sahCost", "<f8"), ("buildMs", "<f8")])
+
 WIRE_SIZES = {"TRIANGLE": 36, "VERTEX_INFO": 44, "TRIANGLE_INFO": 132, "AABB": 24, "BVH_NODE": 36, "OCTREE_NODE": 48,
               "MATERIAL": 68, "MESH_INSTANCE": 232, "SPHERE": 84, "DIRECTIONAL_LIGHT": 32, "POINT_LIGHT": 32,
               "SPOT_LIGHT": 48, "RENDER_DATA": 240, "AOV": 56}
@@ -112,6 +116,7 @@ SYMBOLS = [
     ("okrt_obj_num_meshes", _U, [_P]),
     ("okrt_obj_mesh", _I, [_P, _U, _P, ctypes.POINTER(ctypes.c_char_p)]),
     ("okrt_obj_texture_path", ctypes.c_char_p, [_P, _U, _U]),
+    ("okrt_layout_report", _I, [_P, _U, _P, _U, _P, _U, _P, _U, _P]),
     ("okrt_create", _I, [_I, _U, _U, ctypes.POINTER(_P)]),
     ("okrt_destroy", None, [_P]),
     ("okrt_resize", _I, [_P, _U, _U]),

@@ -4,10 +4,14 @@
  * resources/shaders/GPU-Structs.hlsli:95-98,113-125,159-179).  Host C++, runs once per scene change.
  */
 #include "okrt_accel.h"
+#include "okrt_internal.h"
 
 #include <algorithm>
 #include <cfloat>
+#include <chrono>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <functional>
 #include <string>
@@ -312,6 +316,8 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
     uint32_t topDepth = 0;
     constexpr int kBins = 32;
     constexpr uint32_t kSahDepthLimit = 44;
+    const char* sweepEnv = std::getenv("OKRT_TOP_SWEEP");
+    const size_t sweepBelow = sweepEnv ? (size_t)std::atoll(sweepEnv) : (size_t)-1;
     std::function<uint32_t(size_t, size_t, uint32_t, okrt_aabb&)> buildTop = [&](size_t lo, size_t hi, uint32_t level, okrt_aabb& box) -> uint32_t {
         double bl[3] = {DBL_MAX, DBL_MAX, DBL_MAX}, bh[3] = {-DBL_MAX, -DBL_MAX, -DBL_MAX};
         double cl[3] = {DBL_MAX, DBL_MAX, DBL_MAX}, ch[3] = {-DBL_MAX, -DBL_MAX, -DBL_MAX};
@@ -327,7 +333,35 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
         for (int k = 0; k < 3; k++) { box.min[k] = std::nextafterf(box.min[k], -INFINITY); box.max[k] = std::nextafterf(box.max[k], INFINITY); }
 
         size_t mid = lo;
-        if (hi - lo > 2 && level < kSahDepthLimit) {
+        if (hi - lo > 2 && hi - lo <= sweepBelow && level < kSahDepthLimit) {
+            /* small ranges: every split position of every axis (full sweep), not just the 31 bin borders */
+            auto area = [](const double* l, const double* h) { const double dx = h[0] - l[0], dy = h[1] - l[1], dz = h[2] - l[2]; return 2.0 * (dx * dy + dy * dz + dz * dx); };
+            const size_t n = hi - lo;
+            double bestCost = DBL_MAX; int bestAxis = -1; size_t bestCut = 0;
+            std::vector<double> rightArea(n); std::vector<uint64_t> rightW(n);
+            std::vector<TopLeaf> sorted(leaves.begin() + (ptrdiff_t)lo, leaves.begin() + (ptrdiff_t)hi), bestOrder;
+            for (int axis = 0; axis < 3; axis++) {
+                std::stable_sort(sorted.begin(), sorted.end(), [axis](const TopLeaf& a, const TopLeaf& c) { return a.lo[axis] + a.hi[axis] < c.lo[axis] + c.hi[axis]; });
+                double rl[3] = {DBL_MAX, DBL_MAX, DBL_MAX}, rh[3] = {-DBL_MAX, -DBL_MAX, -DBL_MAX}; uint64_t rw = 0;
+                for (size_t i = n - 1; i > 0; i--) {
+                    for (int k = 0; k < 3; k++) { rl[k] = std::min(rl[k], (double)sorted[i].lo[k]); rh[k] = std::max(rh[k], (double)sorted[i].hi[k]); }
+                    rw += sorted[i].weight; rightArea[i] = area(rl, rh); rightW[i] = rw;
+                }
+                double ll[3] = {DBL_MAX, DBL_MAX, DBL_MAX}, lh[3] = {-DBL_MAX, -DBL_MAX, -DBL_MAX}; uint64_t lw = 0;
+                bool improved = false;
+                for (size_t i = 0; i + 1 < n; i++) {
+                    for (int k = 0; k < 3; k++) { ll[k] = std::min(ll[k], (double)sorted[i].lo[k]); lh[k] = std::max(lh[k], (double)sorted[i].hi[k]); }
+                    lw += sorted[i].weight;
+                    const double cost = area(ll, lh) * (double)lw + rightArea[i + 1] * (double)rightW[i + 1];
+                    if (cost < bestCost) { bestCost = cost; bestAxis = axis; bestCut = i + 1; improved = true; }
+                }
+                if (improved) bestOrder = sorted;
+            }
+            if (bestAxis >= 0) {
+                std::copy(bestOrder.begin(), bestOrder.end(), leaves.begin() + (ptrdiff_t)lo);
+                mid = lo + bestCut;
+            }
+        } else if (hi - lo > 2 && level < kSahDepthLimit) {
             double bestCost = DBL_MAX; int bestAxis = -1, bestBin = -1;
             for (int axis = 0; axis < 3; axis++) {
                 const double ext = ch[axis] - cl[axis];
@@ -408,3 +442,53 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
 }
 
 } // namespace okrt
+
+/* ------------------------------------------------------------------ okrt_layout_report (include/okrt.h) */
+extern "C" OKRT_API int okrt_layout_report(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh_node* nodes, uint32_t numNodes,
+                                           const okrt_mesh_instance* instances, uint32_t numInstances,
+                                           const okrt_octree_node* octNodes, uint32_t numOctNodes, okrt_layout_info* out)
+{
+    using namespace okrt;
+    if (!out) { setError("okrt_layout_report: null output"); return OKRT_ERR_INVALID_ARGUMENT; }
+    std::memset(out, 0, sizeof(*out));
+    FastLayout fl;
+    const auto t0 = std::chrono::steady_clock::now();
+    if (!buildFastLayout(tris, numTris, nodes, numNodes, instances, numInstances, octNodes, numOctNodes, fl)) {
+        setError("scene rejected: " + fl.error);
+        return OKRT_ERR_INVALID_ARGUMENT;
+    }
+    out->buildMs = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    out->numPairNodes = (uint32_t)(fl.nodes.size() / 4);
+    out->numFlattenedLeaves = fl.numFlattenedLeaves; out->numMergedInstances = fl.numMerged;
+    out->numInstanceRecords = (uint32_t)(fl.instances.size() / kInstQuads);
+    out->fastStackDepth = fl.maxStackDepth; out->exactBvhDepth = fl.exactBvhDepth; out->exactOctDepth = fl.exactOctDepth;
+    /* expected work of a random ray through the tree reachable from topRef (an instance counts as one triangle) */
+    auto boxArea = [](const Float4& lo, const Float4& hi) {
+        const double dx = (double)hi.x - lo.x, dy = (double)hi.y - lo.y, dz = (double)hi.z - lo.z;
+        return (dx >= 0 && dy >= 0 && dz >= 0) ? 2.0 * (dx * dy + dy * dz + dz * dx) : 0.0;
+    };
+    if (fl.topRef != kRefNone && (fl.topRef & kRefTagMask) == kRefInterior) {
+        std::vector<uint32_t> stack{fl.topRef};
+        const Float4* rq = &fl.nodes[(size_t)fl.topRef * 4];
+        const Float4 rlo{std::fmin(rq[0].x, rq[2].x), std::fmin(rq[0].y, rq[2].y), std::fmin(rq[0].z, rq[2].z), 0.f};
+        const Float4 rhi{std::fmax(rq[1].x, rq[3].x), std::fmax(rq[1].y, rq[3].y), std::fmax(rq[1].z, rq[3].z), 0.f};
+        const double rootArea = boxArea(rlo, rhi);
+        double sum = 0.0, interior = 0.0;
+        while (!stack.empty() && rootArea > 0.0) {
+            const uint32_t p = stack.back(); stack.pop_back();
+            const Float4* q = &fl.nodes[(size_t)p * 4];
+            for (int c = 0; c < 2; c++) {
+                uint32_t ref; std::memcpy(&ref, c ? &q[1].w : &q[0].w, 4);
+                if (ref == kRefNone) continue;
+                const double a = boxArea(q[2 * c], q[2 * c + 1]) / rootArea;
+                const uint32_t tag = ref & kRefTagMask;
+                if (tag == kRefInterior) { sum += a; interior += a; stack.push_back(ref); }
+                else if (tag == kRefTriLeaf) sum += a * (double)(((ref >> 27) & 7u) + 1u);
+                else sum += a;
+            }
+        }
+        out->sahCost = sum;
+        if (std::getenv("OKRT_LAYOUT_VERBOSE")) std::fprintf(stderr, "[okrt] layout: interior term %.4f, leaf term %.4f\n", interior, sum - interior);
+    }
+    return OKRT_OK;
+}

@@ -47,10 +47,7 @@ constexpr uint32_t kRefNone = 0xFFFFFFFFu;        /* empty scene / empty child *
 constexpr uint32_t kMaxLeafTris = 8;
 constexpr uint32_t kInstQuads = 10;               /* float4 per instance record */
 constexpr uint32_t kMaxTriIndex = (1u << 27);
-#ifndef OKRT_TRI_QUADS
-#define OKRT_TRI_QUADS 3
-#endif
-constexpr uint32_t kTriQuads = OKRT_TRI_QUADS;      /* float4 per triangle record: 3 = 48 B packed, 4 = 64 B (two 256-bit loads) */
+constexpr uint32_t kTriQuads = 3;       /* float4 per triangle record (48 B: p2 | E1 | E2 | owner); 64-byte records measured slower */
 constexpr uint32_t kFastStackCapacity = 64;       /* entries; validated against tree depth at upload */
 constexpr uint32_t kExactBvhStackCapacity = 64;   /* reference: 50, RaytracerCS.hlsl:249 */
 constexpr uint32_t kExactOctStackCapacity = 32;   /* reference: 20, RaytracerCS.hlsl:244 */

@@ -115,6 +115,7 @@ struct okrt_renderer {
     DeviceBuffer triPos, triInfo, bvhNodes, octNodes, spheres, instances, dirLights, pointLights, spotLights;
     TextureArray textures, environment;
     DeviceBuffer fastNodes, fastTris, fastInstances, octParent;
+    cudaTextureObject_t fastTrisTex = 0;
 
     /* host copies needed to (re)build the fast layout */
     std::vector<okrt_triangle> hTris;
@@ -188,6 +189,15 @@ int rebuildLayout(okrt_renderer* r)
     if ((rc = r->fastTris.upload(fl.tris.data(), (uint32_t)fl.tris.size(), sizeof(Float4), r->stream))) return rc;
     if ((rc = r->fastInstances.upload(fl.instances.data(), (uint32_t)fl.instances.size(), sizeof(Float4), r->stream))) return rc;
     if ((rc = r->octParent.upload(fl.octParent.data(), (uint32_t)fl.octParent.size(), sizeof(uint32_t), r->stream))) return rc;
+    if (r->fastTrisTex) { cudaDestroyTextureObject(r->fastTrisTex); r->fastTrisTex = 0; }
+    if (r->fastTris.bytes) {            /* the triangle records as float4 texels: stepTriangle fetches them through the texture pipe */
+        cudaResourceDesc res; std::memset(&res, 0, sizeof(res));
+        res.resType = cudaResourceTypeLinear; res.res.linear.devPtr = r->fastTris.ptr; res.res.linear.sizeInBytes = r->fastTris.bytes;
+        res.res.linear.desc = cudaCreateChannelDesc<float4>();
+        cudaTextureDesc td; std::memset(&td, 0, sizeof(td));
+        td.readMode = cudaReadModeElementType; td.filterMode = cudaFilterModePoint; td.addressMode[0] = cudaAddressModeClamp;
+        OKRT_CUDA(cudaCreateTextureObject(&r->fastTrisTex, &res, &td, nullptr));
+    }
     r->topRef = fl.topRef;
     r->allRigid = fl.allRigid;
     r->fastStackNeed = fl.maxStackDepth; r->exactBvhNeed = fl.exactBvhDepth; r->exactOctNeed = fl.exactOctDepth;
@@ -218,6 +228,7 @@ DeviceScene sceneView(const okrt_renderer* r)
     s.envW = r->environment.width; s.envH = r->environment.height;
     s.fastNodes = (const float4*)r->fastNodes.ptr;
     s.fastTris = (const float4*)r->fastTris.ptr;
+    s.fastTrisTex = r->fastTrisTex;
     s.fastInstances = (const float4*)r->fastInstances.ptr;
     s.octParent = (const uint32_t*)r->octParent.ptr;
     s.topRef = r->topRef;
@@ -279,6 +290,9 @@ int launchWavefront(okrt_renderer* r, const FrameParams& fp, bool instrumented)
     generateKernel<<<flatGrid, 128, 0, r->stream>>>(fp, r->wb);
     r->launches++;
     const unsigned traceGrid = std::min<unsigned>((unsigned)(r->numSms * r->blocksPerSmTrace), std::max(1u, flatGrid));
+    const char* shadeWaves = std::getenv("OKRT_SHADE_WAVES");     /* tuning knob: resident-block multiples per SM */
+    const unsigned shadeGrid = std::min<unsigned>((unsigned)(r->numSms * OKRT_SHADE_MIN_BLOCKS * (shadeWaves ? std::max(1, std::atoi(shadeWaves)) : 16)),
+                                                  std::max(1u, flatGrid));
     const unsigned fallbackGrid = std::min<unsigned>((unsigned)(r->numSms * 8), std::max(1u, flatGrid));   /* 4 rays (warps) per block */
     for (uint32_t b = 0; b <= fp.maxBounces; b++) {
         const uint32_t* qin = r->wb.queue[b & 1u];
@@ -299,8 +313,8 @@ int launchWavefront(okrt_renderer* r, const FrameParams& fp, bool instrumented)
             traceFallbackKernel<<<fallbackGrid, 128, 0, r->stream>>>(scene, fp, r->wb, b);
             r->launches++;
         }
-        if (instrumented) shadeKernel<true><<<flatGrid, 128, 0, r->stream>>>(scene, fp, r->wb, qin, qout, b);
-        else shadeKernel<false><<<flatGrid, 128, 0, r->stream>>>(scene, fp, r->wb, qin, qout, b);
+        if (instrumented) shadeKernel<true><<<shadeGrid, 128, 0, r->stream>>>(scene, fp, r->wb, qin, qout, b);
+        else shadeKernel<false><<<shadeGrid, 128, 0, r->stream>>>(scene, fp, r->wb, qin, qout, b);
         r->launches += 2;
     }
     accumulateKernel<<<(unsigned)((slots + 127) / 128), 128, 0, r->stream>>>(fp, r->wb);
@@ -474,6 +488,7 @@ void okrt_destroy(okrt_renderer* r)
     if (r->stream) cudaStreamSynchronize(r->stream);
     r->triPos.release(); r->triInfo.release(); r->bvhNodes.release(); r->octNodes.release(); r->spheres.release();
     r->instances.release(); r->dirLights.release(); r->pointLights.release(); r->spotLights.release();
+    if (r->fastTrisTex) { cudaDestroyTextureObject(r->fastTrisTex); r->fastTrisTex = 0; }
     r->fastNodes.release(); r->fastTris.release(); r->fastInstances.release(); r->octParent.release();
     r->textures.release(); r->environment.release();
     if (r->accumulation) cudaFree(r->accumulation);

@@ -99,6 +99,8 @@ struct DeviceScene {
     uint32_t topRef;
     uint32_t numFastNodes, numFastInstances;
     uint32_t pad0;
+    cudaTextureObject_t fastTrisTex;          /* fastTris seen through the texture pipe (float4 texels) */
+    uint64_t pad1;
 };
 
 struct FrameParams {
@@ -541,6 +543,9 @@ __device__ __forceinline__ bool boxPasses(V3 o, V3 idir, float4 lo, float4 hi, f
 #ifndef OKRT_LD256
 #define OKRT_LD256 1
 #endif
+#ifndef OKRT_TRI_TEX
+#define OKRT_TRI_TEX 1          /* triangle records through the texture pipe (tex1Dfetch) instead of LDG */
+#endif
 /* one 256-bit read-only load (LDG.E.ENL2.256.CONSTANT, sm_100+): two quads for one L1 tag lookup instead of two.
  * p must be 32-byte aligned. */
 __device__ __forceinline__ void ldg256(const float4* p, float4& a, float4& b)
@@ -598,11 +603,13 @@ __device__ __forceinline__ void stepTriangle(const DeviceScene& s, StepLane& L, 
 {
     const uint32_t j = L.triNext++;
     OKRT_CHECK(j < s.numTris);
-    const float4* tp = s.fastTris + (size_t)j * kTriQuads;
-#if OKRT_LD256 && OKRT_TRI_QUADS == 4
-    float4 a, b, c, cPad;
-    ldg256(tp, a, b); ldg256(tp + 2, c, cPad);                              /* p2 | E1 | E2 | owner, padded to 64 B */
+#if OKRT_TRI_TEX
+    /* through the texture pipe: the LSU data stage (one 32-byte sector per cycle for divergent lanes) is the busiest unit
+     * of this kernel (80 %), the texture pipe is otherwise idle */
+    const int tj = (int)(j * kTriQuads);
+    const float4 a = tex1Dfetch<float4>(s.fastTrisTex, tj), b = tex1Dfetch<float4>(s.fastTrisTex, tj + 1), c = tex1Dfetch<float4>(s.fastTrisTex, tj + 2);
 #else
+    const float4* tp = s.fastTris + (size_t)j * kTriQuads;
     const float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);       /* p2 | E1 | E2 | owner */
 #endif
     float bu = 0.f, bv = 0.f;

@@ -302,7 +302,16 @@ shadeKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ Frame
 {
     const okrt_render_data& rd = fp.rd;
     const uint32_t count = wb.counts[2u * bounce];
-    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    __shared__ uint32_t warpSurvivors[4];
+    __shared__ uint32_t blockBase;
+    if (blockIdx.x == 0u && threadIdx.x == 0u) {
+        atomicAdd(fp.counters + 0, (unsigned long long)count);
+        if (bounce == 0u) atomicAdd(fp.counters + 2, (unsigned long long)count);
+    }
+    /* the grid is sized for the machine, not for the queue (whose length only the device knows): a block walks the
+     * queue in grid strides, the trip count is uniform within a block */
+    for (uint32_t first = blockIdx.x * blockDim.x; first < count; first += gridDim.x * blockDim.x) {
+    const uint32_t k = first + threadIdx.x;
     const bool active = k < count;
     bool survives = false;
     uint32_t path = 0u;
@@ -351,18 +360,23 @@ shadeKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ Frame
             survives = true;
         }
     }
-    /* surviving paths -> next queue, one atomic per warp */
+    /* surviving paths -> next queue, one atomic per block (every warp of every block adding to the same counter is
+     * half a million same-address atomics per launch) */
     const uint32_t mask = __ballot_sync(0xFFFFFFFFu, survives);
-    if (mask) {
-        uint32_t base = 0u;
-        const uint32_t lane = threadIdx.x & 31u;
-        if (lane == (uint32_t)(__ffs(mask) - 1)) base = atomicAdd(wb.counts + 2u * (bounce + 1u), (uint32_t)__popc(mask));
-        base = __shfl_sync(0xFFFFFFFFu, base, __ffs(mask) - 1);
-        if (survives) queueOut[base + __popc(mask & ((1u << lane) - 1u))] = path;
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    if (lane == 0u) warpSurvivors[warp] = (uint32_t)__popc(mask);
+    __syncthreads();
+    if (threadIdx.x == 0u) {
+        const uint32_t total = warpSurvivors[0] + warpSurvivors[1] + warpSurvivors[2] + warpSurvivors[3];
+        blockBase = total ? atomicAdd(wb.counts + 2u * (bounce + 1u), total) : 0u;
     }
-    if (k == 0u) {
-        atomicAdd(fp.counters + 0, (unsigned long long)count);
-        if (bounce == 0u) atomicAdd(fp.counters + 2, (unsigned long long)count);
+    __syncthreads();
+    if (survives) {
+        uint32_t base = blockBase;
+        for (uint32_t w = 0; w < warp; w++) base += warpSurvivors[w];
+        queueOut[base + __popc(mask & ((1u << lane) - 1u))] = path;
+    }
+    __syncthreads();                 /* warpSurvivors / blockBase are rewritten by the next trip */
     }
 }
 

@@ -358,6 +358,25 @@ OKRT_API uint32_t okrt_obj_num_meshes(const okrt_obj* a);
 OKRT_API int okrt_obj_mesh(const okrt_obj* a, uint32_t i, okrt_mesh_view* view, const char** name);
 OKRT_API const char* okrt_obj_texture_path(const okrt_obj* a, uint32_t mesh, uint32_t slot);   /* "" when the material binds none */
 
+/* Host-only report on the traversal layout okrt_render builds from the binding-table arrays (no GPU needed): lets a
+ * test or a tool check stack needs and compare tree quality.  sahCost = sum over child boxes of the scene-wide tree of
+ * area(box)/area(root) x (1 for an interior child, triangle count for a leaf child): the expected work of a random ray. */
+typedef struct okrt_layout_info {
+    uint32_t numPairNodes;          /* 64-byte child-pair nodes */
+    uint32_t numFlattenedLeaves;    /* reference BVH leaves that became primitives of the scene-wide tree */
+    uint32_t numMergedInstances;
+    uint32_t numInstanceRecords;
+    uint32_t fastStackDepth;        /* worst-case occupancy; capacity 64 */
+    uint32_t exactBvhDepth;
+    uint32_t exactOctDepth;
+    uint32_t reserved;
+    double   sahCost;
+    double   buildMs;
+} okrt_layout_info;
+OKRT_API int okrt_layout_report(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh_node* nodes, uint32_t numNodes,
+                                const okrt_mesh_instance* instances, uint32_t numInstances,
+                                const okrt_octree_node* octNodes, uint32_t numOctNodes, okrt_layout_info* out);
+
 /* ------------------------------------------------------- renderer (device) */
 OKRT_API int  okrt_create(int device, uint32_t width, uint32_t height, okrt_renderer** out); /* RayTracer::initiate :60 */
 OKRT_API void okrt_destroy(okrt_renderer* r);                                                 /* RayTracer::shutdown :34 */

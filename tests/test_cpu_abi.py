@@ -41,7 +41,8 @@ def test_library_is_built_for_sm100a_only(okrt):
     sass = subprocess.run(["cuobjdump", "-sass", "-arch", "sm_100a", okrt.abi.LIB_PATH], capture_output=True, text=True).stdout
     for kernel in ("traceFastKernel", "shadeKernel", "generateKernel", "pathTraceKernel", "traceExactKernel"):
         assert kernel in sass, kernel
-    assert "LDG.E.128" in sass                        # the 64-byte child-pair nodes are fetched as four 128-bit loads
+    assert "LDG.E.ENL2.256" in sass                   # the 64-byte child-pair nodes are fetched as two 256-bit loads
+    assert "TLD" in sass                              # triangle records go through the texture pipe
 
 
 def test_no_device_means_no_renderer(okrt):
