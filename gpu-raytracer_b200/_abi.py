@@ -116,6 +116,9 @@ SYMBOLS = [
     ("okrt_obj_num_meshes", _U, [_P]),
     ("okrt_obj_mesh", _I, [_P, _U, _P, ctypes.POINTER(ctypes.c_char_p)]),
     ("okrt_obj_texture_path", ctypes.c_char_p, [_P, _U, _U]),
+    ("okrt_write_png", _I, [ctypes.c_char_p, _P, _U, _U]),
+    ("okrt_write_accumulation_file", _I, [ctypes.c_char_p, _P, _U, _U, _U]),
+    ("okrt_read_accumulation_file", _I, [ctypes.c_char_p, _P, ctypes.POINTER(_U), ctypes.POINTER(_U), ctypes.POINTER(_U)]),
     ("okrt_layout_report", _I, [_P, _U, _P, _U, _P, _U, _P, _U, _P]),
     ("okrt_create", _I, [_I, _U, _U, ctypes.POINTER(_P)]),
     ("okrt_destroy", None, [_P]),

@@ -92,7 +92,105 @@ struct Builder {
     }
 };
 
+/* explicit node of the scene-wide tree while it is built and optimised; a leaf has left < 0 and carries `ref` */
+struct TopNode { double lo[3], hi[3]; int32_t left = -1, right = -1, parent = -1; uint32_t ref = kRefNone; };
 struct TopLeaf { double lo[3], hi[3]; uint32_t ref; uint32_t weight; };   /* weight: triangles below (SAH cost) */
+
+static inline double topArea(const TopNode& n)
+{
+    const double dx = n.hi[0] - n.lo[0], dy = n.hi[1] - n.lo[1], dz = n.hi[2] - n.lo[2];
+    return 2.0 * (dx * dy + dy * dz + dz * dx);
+}
+static inline double topUnionArea(const TopNode& a, const TopNode& c)
+{
+    const double dx = std::max(a.hi[0], c.hi[0]) - std::min(a.lo[0], c.lo[0]);
+    const double dy = std::max(a.hi[1], c.hi[1]) - std::min(a.lo[1], c.lo[1]);
+    const double dz = std::max(a.hi[2], c.hi[2]) - std::min(a.lo[2], c.lo[2]);
+    return 2.0 * (dx * dy + dy * dz + dz * dx);
+}
+static uint32_t topTreeDepth(const std::vector<TopNode>& tn, int32_t root)
+{
+    uint32_t deepest = 0;
+    std::vector<std::pair<int32_t, uint32_t>> st{{root, 0u}};
+    while (!st.empty()) {
+        const auto [n, level] = st.back(); st.pop_back();
+        if (tn[n].left < 0) continue;
+        deepest = std::max(deepest, level + 1);
+        st.push_back({tn[n].left, level + 1}); st.push_back({tn[n].right, level + 1});
+    }
+    return deepest;
+}
+
+/* Insertion-based optimisation of a binary BVH (after Bittner, Hapala, Havran 2013, restated): take a subtree out,
+ * let its sibling take the parent's place, and put it back where the total surface area of the tree grows least
+ * (branch-and-bound search from the root).  Interior boxes stay exact unions of their children, so everything the
+ * order-independence argument needs from the tree (conservative boxes) is untouched.  Deterministic: nodes are visited
+ * in order of decreasing area, no random numbers.  Returns the (possibly new) root. */
+static int32_t reinsertOptimize(std::vector<TopNode>& tn, int32_t root, int passes)
+{
+    auto refitUp = [&](int32_t n) {
+        while (n >= 0) {
+            const TopNode &l = tn[tn[n].left], &r = tn[tn[n].right];
+            bool changed = false;
+            for (int k = 0; k < 3; k++) {
+                const double lo = std::min(l.lo[k], r.lo[k]), hi = std::max(l.hi[k], r.hi[k]);
+                if (lo != tn[n].lo[k] || hi != tn[n].hi[k]) { tn[n].lo[k] = lo; tn[n].hi[k] = hi; changed = true; }
+            }
+            if (!changed) break;
+            n = tn[n].parent;
+        }
+    };
+    struct Entry { double induced; int32_t node; bool operator<(const Entry& o) const { return induced > o.induced; } };
+    std::vector<Entry> heap;
+    std::vector<int32_t> order;
+    for (int pass = 0; pass < passes; pass++) {
+        order.clear();
+        for (int32_t i = 0; i < (int32_t)tn.size(); i++) if (i != root && tn[i].parent >= 0 && tn[i].parent != root) order.push_back(i);
+        std::vector<double> areaAt(tn.size());
+        for (size_t i = 0; i < tn.size(); i++) areaAt[i] = topArea(tn[i]);
+        std::stable_sort(order.begin(), order.end(), [&](int32_t a, int32_t c) { return areaAt[a] > areaAt[c]; });
+        size_t moved = 0;
+        for (int32_t x : order) {
+            const int32_t parent = tn[x].parent;
+            if (parent < 0 || parent == root) continue;                     /* became a child of the root meanwhile */
+            const int32_t grand = tn[parent].parent;
+            const int32_t sibling = tn[parent].left == x ? tn[parent].right : tn[parent].left;
+            /* detach x: the sibling takes the parent's place */
+            if (tn[grand].left == parent) tn[grand].left = sibling; else tn[grand].right = sibling;
+            tn[sibling].parent = grand;
+            refitUp(grand);
+            /* best place for x */
+            const double areaX = topArea(tn[x]);
+            double best = DBL_MAX; int32_t bestNode = sibling;
+            heap.clear();
+            heap.push_back({0.0, root});
+            while (!heap.empty()) {
+                std::pop_heap(heap.begin(), heap.end());
+                const Entry e = heap.back(); heap.pop_back();
+                if (e.induced + areaX >= best) break;
+                const double direct = topUnionArea(tn[e.node], tn[x]);
+                const double total = e.induced + direct;
+                if (total < best) { best = total; bestNode = e.node; }
+                const double below = total - topArea(tn[e.node]);          /* what every ancestor-to-be already grows by */
+                if (tn[e.node].left >= 0 && below + areaX < best) {
+                    heap.push_back({below, tn[e.node].left}); std::push_heap(heap.begin(), heap.end());
+                    heap.push_back({below, tn[e.node].right}); std::push_heap(heap.begin(), heap.end());
+                }
+            }
+            /* attach: `parent` becomes the new interior node above bestNode and x */
+            const int32_t above = tn[bestNode].parent;
+            tn[parent].left = bestNode; tn[parent].right = x; tn[parent].parent = above;
+            tn[bestNode].parent = parent; tn[x].parent = parent;
+            if (above < 0) root = parent;
+            else if (tn[above].left == bestNode) tn[above].left = parent; else tn[above].right = parent;
+            for (int k = 0; k < 3; k++) { tn[parent].lo[k] = DBL_MAX; tn[parent].hi[k] = -DBL_MAX; }   /* force the refit */
+            refitUp(parent);
+            if (bestNode != sibling) moved++;
+        }
+        if (moved == 0) break;
+    }
+    return root;
+}
 
 /* true if every interior node's box contains both child boxes (component-wise, exactly) and nothing is NaN */
 bool flattenable(const okrt_bvh_node* nodes, uint32_t numNodes, uint32_t root)
@@ -318,7 +416,9 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
     constexpr uint32_t kSahDepthLimit = 44;
     const char* sweepEnv = std::getenv("OKRT_TOP_SWEEP");
     const size_t sweepBelow = sweepEnv ? (size_t)std::atoll(sweepEnv) : (size_t)-1;
-    std::function<uint32_t(size_t, size_t, uint32_t, okrt_aabb&)> buildTop = [&](size_t lo, size_t hi, uint32_t level, okrt_aabb& box) -> uint32_t {
+    std::vector<TopNode> tn;
+    tn.reserve(leaves.size() * 2);
+    std::function<int32_t(size_t, size_t, uint32_t)> buildTop = [&](size_t lo, size_t hi, uint32_t level) -> int32_t {
         double bl[3] = {DBL_MAX, DBL_MAX, DBL_MAX}, bh[3] = {-DBL_MAX, -DBL_MAX, -DBL_MAX};
         double cl[3] = {DBL_MAX, DBL_MAX, DBL_MAX}, ch[3] = {-DBL_MAX, -DBL_MAX, -DBL_MAX};
         for (size_t i = lo; i < hi; i++)
@@ -327,10 +427,10 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
                 const double c = 0.5 * (leaves[i].lo[k] + leaves[i].hi[k]);
                 cl[k] = std::min(cl[k], c); ch[k] = std::max(ch[k], c);
             }
-        for (int k = 0; k < 3; k++) { box.min[k] = roundDown(bl[k]); box.max[k] = roundUp(bh[k]); }
-        if (hi - lo == 1) return leaves[lo].ref;
-        /* unions of exact boxes are exact; one ulp outward keeps "child hit => parent hit" safe in every rounding case */
-        for (int k = 0; k < 3; k++) { box.min[k] = std::nextafterf(box.min[k], -INFINITY); box.max[k] = std::nextafterf(box.max[k], INFINITY); }
+        const int32_t self = (int32_t)tn.size();
+        tn.push_back(TopNode());
+        for (int k = 0; k < 3; k++) { tn[self].lo[k] = bl[k]; tn[self].hi[k] = bh[k]; }
+        if (hi - lo == 1) { tn[self].ref = leaves[lo].ref; return self; }
 
         size_t mid = lo;
         if (hi - lo > 2 && hi - lo <= sweepBelow && level < kSahDepthLimit) {
@@ -410,18 +510,38 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
             std::nth_element(leaves.begin() + (ptrdiff_t)lo, leaves.begin() + (ptrdiff_t)mid, leaves.begin() + (ptrdiff_t)hi,
                              [axis](const TopLeaf& a, const TopLeaf& c) { return a.lo[axis] + a.hi[axis] < c.lo[axis] + c.hi[axis]; });
         }
+        const int32_t l = buildTop(lo, mid, level + 1), r = buildTop(mid, hi, level + 1);
+        tn[self].left = l; tn[self].right = r;
+        tn[l].parent = self; tn[r].parent = self;
+        return self;
+    };
+    /* pair nodes in depth-first order; a leaf's box stays the reference's own floats, interior boxes (exact unions) go one
+     * ulp outward, which keeps "child hit => parent hit" safe in every rounding case */
+    std::function<uint32_t(int32_t, uint32_t, okrt_aabb&)> emitTop = [&](int32_t n, uint32_t level, okrt_aabb& box) -> uint32_t {
+        for (int k = 0; k < 3; k++) { box.min[k] = roundDown(tn[n].lo[k]); box.max[k] = roundUp(tn[n].hi[k]); }
+        if (tn[n].left < 0) return tn[n].ref;
+        for (int k = 0; k < 3; k++) { box.min[k] = std::nextafterf(box.min[k], -INFINITY); box.max[k] = std::nextafterf(box.max[k], INFINITY); }
         const uint32_t p = b.newPair();
         topDepth = std::max(topDepth, level + 1);
         okrt_aabb b0, b1;
-        const uint32_t r0 = buildTop(lo, mid, level + 1, b0);
-        const uint32_t r1 = buildTop(mid, hi, level + 1, b1);
+        const uint32_t r0 = emitTop(tn[n].left, level + 1, b0);
+        const uint32_t r1 = emitTop(tn[n].right, level + 1, b1);
         b.setChild(p, 0, b0, r0);
         b.setChild(p, 1, b1, r1);
         return p;
     };
     if (!leaves.empty()) {
         okrt_aabb rootBox;
-        out.topRef = buildTop(0, leaves.size(), 0, rootBox);
+        int32_t root = buildTop(0, leaves.size(), 0);
+        const char* passesEnv = std::getenv("OKRT_TOP_REINSERT");
+        const int passes = passesEnv ? std::atoi(passesEnv) : 0;
+        if (passes > 0 && leaves.size() > 2) {
+            const std::vector<TopNode> before = tn;
+            const int32_t rootBefore = root;
+            root = reinsertOptimize(tn, root, passes);
+            if (topTreeDepth(tn, root) > kSahDepthLimit + 4) { tn = before; root = rootBefore; }      /* stack budget */
+        }
+        out.topRef = emitTop(root, 0, rootBox);
         if (leaves.size() == 1) {
             /* single instance: wrap it in a pair node so the kernel always starts at an interior node (and tests its box) */
             const uint32_t p = b.newPair();

@@ -9,6 +9,7 @@ the EnTT registry (source/Scene): just enough to drive the path the way Applicat
 (Application.cpp:28-48,65-104).  Every computation happens in libokrt.so through the C ABI.
 """
 import ctypes
+import os
 
 import numpy as np
 
@@ -415,6 +416,27 @@ class RayTracer:
         out = np.zeros((h, w, 4), np.float32)
         abi.check(abi.lib().okrt_read_accumulation(self._handle, abi.ptr(out)))
         return out
+
+    def saveScreenshot(self, path="render.png"):
+        """Application::saveScreenshot (Application.cpp:661-674): the RGBA8 target as a PNG ("render.png" there)."""
+        img = self.readResult()
+        abi.check(abi.lib().okrt_write_png(os.fsencode(path), abi.ptr(img), img.shape[1], img.shape[0]))
+
+    def saveAccumulation(self, path):
+        """Progressive state to disk (row f3): RGBA32F accumulation + frame count; loadAccumulation resumes from it."""
+        acc = self.readAccumulation()
+        abi.check(abi.lib().okrt_write_accumulation_file(os.fsencode(path), abi.ptr(acc), acc.shape[1], acc.shape[0],
+                                                         self.getNumAccumulationFrames()))
+
+    def loadAccumulation(self, path):
+        w, h, n = ctypes.c_uint32(0), ctypes.c_uint32(0), ctypes.c_uint32(0)
+        L = abi.lib()
+        abi.check(L.okrt_read_accumulation_file(os.fsencode(path), None, ctypes.byref(w), ctypes.byref(h), ctypes.byref(n)))
+        if (w.value, h.value) != (int(self._rd[0]["textureDims"][0]), int(self._rd[0]["textureDims"][1])):
+            raise ValueError("accumulation file is %dx%d, the renderer %dx%d" % (w.value, h.value, *self._rd[0]["textureDims"]))
+        acc = np.zeros((h.value, w.value, 4), np.float32)
+        abi.check(L.okrt_read_accumulation_file(os.fsencode(path), abi.ptr(acc), ctypes.byref(w), ctypes.byref(h), ctypes.byref(n)))
+        abi.check(L.okrt_write_accumulation(self._handle, abi.ptr(acc), n.value))
 
     def readAov(self):
         w, h = int(self._rd[0]["textureDims"][0]), int(self._rd[0]["textureDims"][1])

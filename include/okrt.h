@@ -358,6 +358,16 @@ OKRT_API uint32_t okrt_obj_num_meshes(const okrt_obj* a);
 OKRT_API int okrt_obj_mesh(const okrt_obj* a, uint32_t i, okrt_mesh_view* view, const char** name);
 OKRT_API const char* okrt_obj_texture_path(const okrt_obj* a, uint32_t mesh, uint32_t slot);   /* "" when the material binds none */
 
+/* f3: Application::saveScreenshot (Application.cpp:661-674) = stbi_write_png(path, W, H, 4, data, W * 4) on the RGBA8
+ * target.  Own encoder (8-bit RGBA, filter 0, fixed-Huffman deflate); the decoded image equals the input bit for bit. */
+OKRT_API int okrt_write_png(const char* path, const uint8_t* rgba8, uint32_t width, uint32_t height);
+/* Progressive state on disk (checkpoint / resume, offline merge of sample shards): the RGBA32F accumulation (u1) and the
+ * frame count.  okrt_read_accumulation_file with rgba32f == NULL reads only the header. */
+OKRT_API int okrt_write_accumulation_file(const char* path, const float* rgba32f, uint32_t width, uint32_t height,
+                                          uint32_t numAccumulationFrames);
+OKRT_API int okrt_read_accumulation_file(const char* path, float* rgba32f, uint32_t* width, uint32_t* height,
+                                         uint32_t* numAccumulationFrames);
+
 /* Host-only report on the traversal layout okrt_render builds from the binding-table arrays (no GPU needed): lets a
  * test or a tool check stack needs and compare tree quality.  sahCost = sum over child boxes of the scene-wide tree of
  * area(box)/area(root) x (1 for an interior child, triangle count for a leaf child): the expected work of a random ray. */

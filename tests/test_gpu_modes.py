@@ -118,6 +118,38 @@ def _frame1(rd):
     return rd
 
 
+def test_screenshot_and_resume_from_accumulation_file(okrt, tmp_path):
+    """Row f3: saveScreenshot writes the RGBA8 target as a PNG (Application.cpp:661-674); the accumulation file resumes a
+    progressive render in a new renderer bit for bit (2 frames + file + 2 frames == 4 frames)."""
+    from tests.test_cpu_image import _decode_png
+    rm, sc, info = okrt.scenes.test_scene(with_textures=True)
+    W, H = 192, 108
+    env = okrt.scenes.procedural_sky_faces(32)
+
+    def fresh():
+        rt = okrt.RayTracer(0)
+        rt.initiate(W, H, rm, environmentMapFaces=env, maxBounces=3)
+        rt.setScene(sc)
+        rt.createOctTree(sc, 2, 50)
+        return rt
+
+    whole = fresh()
+    whole.render(frames=4)
+    first = fresh()
+    first.render(frames=2)
+    first.saveAccumulation(str(tmp_path / "state.okrtacc"))
+    first.shutdown()
+    second = fresh()
+    second.loadAccumulation(str(tmp_path / "state.okrtacc"))
+    assert second.getNumAccumulationFrames() == 2
+    second.render(frames=2)
+    assert np.array_equal(second.readAccumulation().view(np.uint32), whole.readAccumulation().view(np.uint32))
+    assert np.array_equal(second.readResult(), whole.readResult())
+    second.saveScreenshot(str(tmp_path / "render.png"))
+    assert np.array_equal(_decode_png(tmp_path / "render.png"), whole.readResult())
+    whole.shutdown(); second.shutdown()
+
+
 def test_raytracer_mirror_class(okrt, oracle):
     """The reference-facing class (raytracer.py mirrors RayTracer.h:82-116) end to end."""
     rm, sc, info = okrt.scenes.test_scene(with_textures=True)
