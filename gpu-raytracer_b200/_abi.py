@@ -119,6 +119,13 @@ SYMBOLS = [
     ("okrt_write_png", _I, [ctypes.c_char_p, _P, _U, _U]),
     ("okrt_write_accumulation_file", _I, [ctypes.c_char_p, _P, _U, _U, _U]),
     ("okrt_read_accumulation_file", _I, [ctypes.c_char_p, _P, ctypes.POINTER(_U), ctypes.POINTER(_U), ctypes.POINTER(_U)]),
+    ("okrt_overlay_build", _I, [_U, _P, _U, _U, _U, _P, _P, _U, _U, ctypes.POINTER(_P)]),
+    ("okrt_overlay_free", None, [_P]),
+    ("okrt_overlay_num_segments", _U, [_P]),
+    ("okrt_overlay_num_draws", _U, [_P]),
+    ("okrt_overlay_segments", _P, [_P]),
+    ("okrt_overlay_keys", _P, [_P]),
+    ("okrt_overlay_colours", _P, [_P]),
     ("okrt_layout_report", _I, [_P, _U, _P, _U, _P, _U, _P, _U, _P]),
     ("okrt_create", _I, [_I, _U, _U, ctypes.POINTER(_P)]),
     ("okrt_destroy", None, [_P]),
@@ -143,6 +150,7 @@ SYMBOLS = [
     ("okrt_reset_accumulation", _I, [_P]),
     ("okrt_get_num_accumulation_frames", _U, [_P]),
     ("okrt_read_result", _I, [_P, _P]),
+    ("okrt_draw_overlay", _I, [_P, _P]),
     ("okrt_read_result_owned", _I, [_P, _P, ctypes.POINTER(ctypes.c_uint64)]),
     ("okrt_read_accumulation", _I, [_P, _P]),
     ("okrt_read_aov", _I, [_P, _P]),

@@ -719,6 +719,73 @@ int okrt_read_result_owned(okrt_renderer* r, uint8_t* outRgba8, uint64_t* outByt
     return OKRT_OK;
 }
 
+/* ------------------------------------------------------------ debug overlay (row f4)
+ * One warp per line segment: lanes stride over the pixels of the major axis.  A pixel keeps the highest draw index that
+ * touched it (atomicMax), so overlapping boxes resolve like consecutive Draw calls; the resolve pass writes colours. */
+__global__ void overlayRasterKernel(const float4* __restrict__ segments, const uint32_t* __restrict__ keys, uint32_t numSegments,
+                                    uint32_t width, uint32_t height, uint32_t* __restrict__ pixelKey)
+{
+    const uint32_t seg = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
+    if (seg >= numSegments) return;
+    const float4 s = segments[seg];
+    const float dx = s.z - s.x, dy = s.w - s.y;
+    const bool xMajor = fabsf(dx) >= fabsf(dy);
+    const float a0 = xMajor ? s.x : s.y, a1 = xMajor ? s.z : s.w;          /* major axis */
+    const float b0 = xMajor ? s.y : s.x, db = xMajor ? dy : dx, da = xMajor ? dx : dy;
+    if (!(da != 0.f) || !isfinite(a0) || !isfinite(a1) || !isfinite(b0) || !isfinite(db)) return;
+    const float lo = fminf(a0, a1), hi = fmaxf(a0, a1);
+    const float majorLimit = (float)(xMajor ? width : height), minorLimit = (float)(xMajor ? height : width);
+    /* pixel centres c + 0.5 in [lo, hi), clamped to the image */
+    const float first = fmaxf(ceilf(lo - 0.5f), 0.f), last = fminf(ceilf(hi - 0.5f), majorLimit);   /* [first, last) */
+    const uint32_t key = keys[seg];
+    for (float c = first + (float)lane; c < last; c += 32.f) {
+        const float t = ((c + 0.5f) - a0) / da;
+        const float b = floorf(b0 + t * db);
+        if (!(b >= 0.f) || !(b < minorLimit)) continue;
+        const uint32_t x = xMajor ? (uint32_t)c : (uint32_t)b, y = xMajor ? (uint32_t)b : (uint32_t)c;
+        atomicMax(pixelKey + (size_t)y * width + x, key);
+    }
+}
+
+__global__ void overlayResolveKernel(const uint32_t* __restrict__ pixelKey, const uint32_t* __restrict__ colours, size_t pixels, uchar4* result)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= pixels) return;
+    const uint32_t k = pixelKey[i];
+    if (!k) return;
+    const uint32_t c = colours[k - 1u];
+    result[i] = make_uchar4((unsigned char)(c & 0xFFu), (unsigned char)((c >> 8) & 0xFFu), (unsigned char)((c >> 16) & 0xFFu), (unsigned char)(c >> 24));
+}
+
+int okrt_draw_overlay(okrt_renderer* r, const okrt_overlay* ov)
+{
+    int rc = checkHandle(r, "okrt_draw_overlay"); if (rc) return rc;
+    if (!ov) { setError("okrt_draw_overlay: null overlay"); return OKRT_ERR_INVALID_ARGUMENT; }
+    const uint32_t n = (uint32_t)ov->keys.size();
+    if (!n) return OKRT_OK;
+    const size_t pixels = (size_t)r->width * r->height;
+    float4* dSeg = nullptr; uint32_t *dKeys = nullptr, *dColours = nullptr, *dPixelKey = nullptr;
+    auto release = [&]() { cudaFree(dSeg); cudaFree(dKeys); cudaFree(dColours); cudaFree(dPixelKey); };
+    cudaError_t e = cudaMalloc(&dSeg, (size_t)n * sizeof(float4));
+    if (e == cudaSuccess) e = cudaMalloc(&dKeys, (size_t)n * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&dColours, ov->colours.size() * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&dPixelKey, pixels * 4);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dSeg, ov->segments.data(), (size_t)n * sizeof(float4), cudaMemcpyHostToDevice, r->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dKeys, ov->keys.data(), (size_t)n * 4, cudaMemcpyHostToDevice, r->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dColours, ov->colours.data(), ov->colours.size() * 4, cudaMemcpyHostToDevice, r->stream);
+    if (e == cudaSuccess) e = cudaMemsetAsync(dPixelKey, 0, pixels * 4, r->stream);
+    if (e == cudaSuccess) {
+        overlayRasterKernel<<<(unsigned)(((size_t)n * 32 + 127) / 128), 128, 0, r->stream>>>(dSeg, dKeys, n, r->width, r->height, dPixelKey);
+        overlayResolveKernel<<<(unsigned)((pixels + 255) / 256), 256, 0, r->stream>>>(dPixelKey, dColours, pixels, (uchar4*)r->result);
+        r->launches += 2;
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(r->stream);
+    release();
+    if (e != cudaSuccess) { setError(std::string("okrt_draw_overlay: ") + cudaGetErrorString(e)); return OKRT_ERR_CUDA; }
+    return OKRT_OK;
+}
+
 int okrt_read_accumulation(okrt_renderer* r, float* outRgba32f)
 {
     int rc = checkHandle(r, "okrt_read_accumulation"); if (rc) return rc;

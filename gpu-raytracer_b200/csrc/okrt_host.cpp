@@ -807,4 +807,113 @@ int okrt_environment_cross_to_faces(const uint8_t* cross, uint32_t imgW, uint32_
     return OKRT_OK;
 }
 
+/* ------------------------------------------------------------ debug overlay (row f4)
+ * DebugRenderer::renderBvhNodeBBs / renderOctTreeNodeBBs (DebugRenderer.cpp:264-303, 335-364) draw the 12 edges of
+ * node boxes as a line list through DebugBBVS.hlsl:13-33 (unit cube scaled to the box, object matrix, camera
+ * view-projection of updateCameraData :366-380), in the order executeDrawMode (:447-506) visits the nodes, with the
+ * colours of drawNodeBoundingBox / drawOctTreeNodeBoundingBox (:407-445), no depth test.  Here the host produces the
+ * clipped screen-space segments (double arithmetic, then float32) and the device rasterises them (okrt_draw_overlay). */
+int okrt_overlay_build(uint32_t kind, const void* nodeArray, uint32_t numNodes, uint32_t nodeIdx, uint32_t drawMode,
+                       const okrt_transform* objectTransform, const okrt_camera* cam, uint32_t width, uint32_t height, okrt_overlay** out)
+{
+    if (!out || !cam || !width || !height || kind > OKRT_OVERLAY_OCTREE || drawMode > OKRT_DRAW_WITH_DESCENDANTS || (!nodeArray && numNodes)) {
+        setError("okrt_overlay_build: bad argument"); return OKRT_ERR_INVALID_ARGUMENT;
+    }
+    okrt_overlay* ov = new okrt_overlay();
+    *out = ov;
+    if (drawMode == OKRT_DRAW_NONE || nodeIdx >= numNodes) return OKRT_OK;
+    const okrt_bvh_node* bvh = kind == OKRT_OVERLAY_BVH ? (const okrt_bvh_node*)nodeArray : nullptr;
+    const okrt_octree_node* oct = kind == OKRT_OVERLAY_OCTREE ? (const okrt_octree_node*)nodeArray : nullptr;
+    auto firstChild = [&](uint32_t i) { return bvh ? bvh[i].firstChildIdx : oct[i].firstChildIdx; };
+    auto childCount = [&](uint32_t i) { return bvh ? 2u : oct[i].numChildren; };
+    /* executeDrawMode: the node order of the draws */
+    std::vector<uint32_t> order;
+    if (drawMode == OKRT_DRAW_SINGLE) order.push_back(nodeIdx);
+    else if (drawMode == OKRT_DRAW_WITH_CHILDREN) {
+        order.push_back(nodeIdx);
+        /* the caller passes numChildren of the selected node (2 for a BVH node) :299,:359-360 */
+        if (firstChild(nodeIdx) != OKRT_INVALID_UINT) for (uint32_t c = 0; c < childCount(nodeIdx); c++) order.push_back(firstChild(nodeIdx) + c);
+    } else {
+        std::vector<uint32_t> st{nodeIdx};
+        while (!st.empty()) {
+            const uint32_t cur = st.back(); st.pop_back();
+            if (cur >= numNodes) { delete ov; *out = nullptr; setError("okrt_overlay_build: child index out of range"); return OKRT_ERR_INVALID_ARGUMENT; }
+            if (firstChild(cur) != OKRT_INVALID_UINT) for (uint32_t c = 0; c < childCount(cur); c++) st.push_back(firstChild(cur) + c);
+            order.push_back(cur);
+        }
+    }
+    /* camera: the float32 basis of updateCameraData, then double */
+    float R3[3][3];
+    rotationColumns(cam->rotation, R3);
+    float f[3] = {(cam->position[0] + R3[2][0]) - cam->position[0], (cam->position[1] + R3[2][1]) - cam->position[1], (cam->position[2] + R3[2][2]) - cam->position[2]};
+    normalize3(f);
+    float sv[3] = {1.f * f[2] - f[1] * 0.f, 0.f * f[0] - f[2] * 0.f, 0.f * f[1] - f[0] * 1.f};
+    normalize3(sv);
+    const float uv[3] = {f[1] * sv[2] - sv[1] * f[2], f[2] * sv[0] - sv[2] * f[0], f[0] * sv[1] - sv[0] * f[1]};
+    const float rad = radiansOf(cam->fov);
+    const float ph = std::cos(0.5f * rad) / std::sin(0.5f * rad);
+    const float pw = ph * (float)height / (float)width;
+    Mat4 M = identity();
+    if (objectTransform) M = composeTransform(*objectTransform);
+    const double zn = cam->nearZ, zf = cam->farZ, W = width, H = height;
+    static const int corner[12][2] = {{0, 1}, {2, 3}, {4, 5}, {6, 7}, {0, 2}, {1, 3}, {4, 6}, {5, 7}, {0, 4}, {1, 5}, {2, 6}, {3, 7}};
+    for (size_t k = 0; k < order.size(); k++) {
+        const uint32_t n = order[k];
+        if (n >= numNodes) { delete ov; *out = nullptr; setError("okrt_overlay_build: child index out of range"); return OKRT_ERR_INVALID_ARGUMENT; }
+        const okrt_aabb& box = bvh ? bvh[n].boundingBox : oct[n].boundingBox;
+        const float strength = 1.f - (float)n / (float)numNodes;
+        const float rgb[3] = {bvh ? 0.9f * strength : 0.4f, bvh ? 0.7f * strength : 0.7f, bvh ? 0.5f * strength : 0.4f};
+        uint32_t packed = 0xFF000000u;
+        for (int c = 0; c < 3; c++) packed |= (uint32_t)quantise(rgb[c]) << (8 * c);
+        ov->colours.push_back(packed);
+        double view[8][3];
+        for (int c = 0; c < 8; c++) {
+            /* DebugBBVS.hlsl:27-30: unit-cube vertex * half extent + centre, in float32 */
+            float local[3];
+            for (int a = 0; a < 3; a++) {
+                const float unit = ((c >> a) & 1) ? 1.f : -1.f;
+                local[a] = unit * ((box.max[a] - box.min[a]) * 0.5f) + (box.max[a] + box.min[a]) * 0.5f;
+            }
+            double world[3];
+            for (int r = 0; r < 3; r++) world[r] = (double)M.m[0][r] * local[0] + (double)M.m[1][r] * local[1] + (double)M.m[2][r] * local[2] + (double)M.m[3][r];
+            const double rel[3] = {world[0] - cam->position[0], world[1] - cam->position[1], world[2] - cam->position[2]};
+            view[c][0] = sv[0] * rel[0] + sv[1] * rel[1] + sv[2] * rel[2];
+            view[c][1] = uv[0] * rel[0] + uv[1] * rel[1] + uv[2] * rel[2];
+            view[c][2] = f[0] * rel[0] + f[1] * rel[1] + f[2] * rel[2];
+        }
+        for (int e = 0; e < 12; e++) {
+            double a[3] = {view[corner[e][0]][0], view[corner[e][0]][1], view[corner[e][0]][2]};
+            double c2[3] = {view[corner[e][1]][0], view[corner[e][1]][1], view[corner[e][1]][2]};
+            /* depth clip: nearZ <= view z <= farZ */
+            double t0 = 0.0, t1 = 1.0;
+            const double dz = c2[2] - a[2];
+            bool visible = true;
+            for (int side = 0; side < 2 && visible; side++) {
+                const double plane = side ? zf : zn, sign = side ? -1.0 : 1.0;
+                const double da = sign * (a[2] - plane), dc = sign * (c2[2] - plane);
+                if (da < 0 && dc < 0) visible = false;
+                else if (da < 0) t0 = std::max(t0, (plane - a[2]) / dz);
+                else if (dc < 0) t1 = std::min(t1, (plane - a[2]) / dz);
+            }
+            if (!visible || t0 > t1) continue;
+            float seg[4];
+            for (int end = 0; end < 2; end++) {
+                const double t = end ? t1 : t0;
+                const double x = a[0] + (c2[0] - a[0]) * t, y = a[1] + (c2[1] - a[1]) * t, z = a[2] + dz * t;
+                seg[2 * end + 0] = (float)((((double)pw * x / z) * 0.5 + 0.5) * W);
+                seg[2 * end + 1] = (float)((1.0 - (((double)ph * y / z) * 0.5 + 0.5)) * H);
+            }
+            ov->segments.insert(ov->segments.end(), seg, seg + 4);
+            ov->keys.push_back((uint32_t)k + 1u);
+        }
+    }
+    return OKRT_OK;
+}
+void okrt_overlay_free(okrt_overlay* ov) { delete ov; }
+uint32_t okrt_overlay_num_segments(const okrt_overlay* ov) { return ov ? (uint32_t)ov->keys.size() : 0; }
+uint32_t okrt_overlay_num_draws(const okrt_overlay* ov) { return ov ? (uint32_t)ov->colours.size() : 0; }
+const float* okrt_overlay_segments(const okrt_overlay* ov) { return ov ? ov->segments.data() : nullptr; }
+const uint32_t* okrt_overlay_keys(const okrt_overlay* ov) { return ov ? ov->keys.data() : nullptr; }
+const uint32_t* okrt_overlay_colours(const okrt_overlay* ov) { return ov ? ov->colours.data() : nullptr; }
+
 } // extern "C"

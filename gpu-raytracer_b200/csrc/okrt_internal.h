@@ -30,6 +30,14 @@ struct okrt_geometry {
     std::vector<okrt_aabb> bounds;
 };
 
+/* screen-space line list of a debug overlay (row f4): 4 floats per segment, the draw it belongs to (1-based; later draws
+ * win a pixel, like consecutive Draw calls), one RGBA8 colour per draw */
+struct okrt_overlay {
+    std::vector<float> segments;
+    std::vector<uint32_t> keys;
+    std::vector<uint32_t> colours;
+};
+
 namespace okrt {
 void setError(const std::string& msg);
 int buildBvh(const okrt_triangle* tris, uint32_t numTriangles, const okrt_aabb& rootBounds, uint32_t maxDepth,

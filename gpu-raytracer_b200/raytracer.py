@@ -417,6 +417,37 @@ class RayTracer:
         abi.check(abi.lib().okrt_read_accumulation(self._handle, abi.ptr(out)))
         return out
 
+    # ---- DebugRenderer's box overlays (row f4)
+    DrawMode_None, DrawMode_DrawSingle, DrawMode_DrawWithChildren, DrawMode_DrawWithDecendants = 0, 1, 2, 3
+
+    def getGlobalNodeIdx(self, meshEntityIdx, localNodeIdx):
+        """RayTracer::getGlobalNodeIdx (RayTracer.h:226-230)."""
+        mesh_id = self._scene.meshEntities[meshEntityIdx][2]
+        return int(self.geometry.meshDescs[mesh_id]["bvhTreeStartIdx"]) + int(localNodeIdx)
+
+    def _drawOverlay(self, kind, nodes, nodeIdx, drawMode, transform):
+        L = abi.lib()
+        cam = self._scene.cameraArray()
+        w, h = int(self._rd[0]["textureDims"][0]), int(self._rd[0]["textureDims"][1])
+        handle = ctypes.c_void_p()
+        abi.check(L.okrt_overlay_build(kind, abi.ptr(nodes), len(nodes), int(nodeIdx), int(drawMode),
+                                       abi.ptr(transform) if transform is not None else None, abi.ptr(cam), w, h, ctypes.byref(handle)))
+        try:
+            abi.check(L.okrt_draw_overlay(self._handle, handle))
+        finally:
+            L.okrt_overlay_free(handle)
+
+    def renderBvhNodeBBs(self, meshEntityIdx, localNodeIdx, drawMode):
+        """DebugRenderer::renderBvhNodeBBs (DebugRenderer.cpp:264-303) over the result image."""
+        tr = np.zeros(1, abi.TRANSFORM)
+        t = self._scene.meshEntities[meshEntityIdx][0]
+        tr[0]["position"], tr[0]["rotation"], tr[0]["scale"] = t["position"], t["rotation"], t["scale"]
+        self._drawOverlay(0, self.geometry.bvhNodes, self.getGlobalNodeIdx(meshEntityIdx, localNodeIdx), drawMode, tr)
+
+    def renderOctTreeNodeBBs(self, nodeIdx, drawMode):
+        """DebugRenderer::renderOctTreeNodeBBs (DebugRenderer.cpp:335-364)."""
+        self._drawOverlay(1, self.octTree.nodes, nodeIdx, drawMode, None)
+
     def saveScreenshot(self, path="render.png"):
         """Application::saveScreenshot (Application.cpp:661-674): the RGBA8 target as a PNG ("render.png" there)."""
         img = self.readResult()

@@ -368,6 +368,25 @@ OKRT_API int okrt_write_accumulation_file(const char* path, const float* rgba32f
 OKRT_API int okrt_read_accumulation_file(const char* path, float* rgba32f, uint32_t* width, uint32_t* height,
                                          uint32_t* numAccumulationFrames);
 
+/* f4: the box overlay of DebugRenderer::renderBvhNodeBBs / renderOctTreeNodeBBs (DebugRenderer.cpp:264-303, 335-364,
+ * DebugBBVS.hlsl:13-33, DebugBBPS.hlsl): the 12 edges of node boxes as lines over the result image, nodes in the order
+ * of executeDrawMode (:447-506), colours of :407-445, no depth test.  okrt_overlay_build (host) makes the clipped
+ * screen-space line list; okrt_draw_overlay (device) rasterises it into the RGBA8 result.  Rasterisation rule of this
+ * library (D3D11's own rasteriser is unavailable on this box): a line owns, in its major axis, every pixel whose
+ * centre lies in [start, end) and, in the minor axis, the pixel containing the interpolated coordinate. */
+typedef struct okrt_overlay okrt_overlay;
+enum { OKRT_OVERLAY_BVH = 0, OKRT_OVERLAY_OCTREE = 1 };                                   /* DBGRenderData.mode */
+enum { OKRT_DRAW_NONE = 0, OKRT_DRAW_SINGLE = 1, OKRT_DRAW_WITH_CHILDREN = 2, OKRT_DRAW_WITH_DESCENDANTS = 3 };  /* DrawMode */
+OKRT_API int okrt_overlay_build(uint32_t kind, const void* nodeArray, uint32_t numNodes, uint32_t nodeIdx, uint32_t drawMode,
+                                const okrt_transform* objectTransform /* NULL: identity */, const okrt_camera* cam,
+                                uint32_t width, uint32_t height, okrt_overlay** out);
+OKRT_API void okrt_overlay_free(okrt_overlay* ov);
+OKRT_API uint32_t okrt_overlay_num_segments(const okrt_overlay* ov);
+OKRT_API uint32_t okrt_overlay_num_draws(const okrt_overlay* ov);
+OKRT_API const float*    okrt_overlay_segments(const okrt_overlay* ov);   /* x0 y0 x1 y1 per segment, pixels */
+OKRT_API const uint32_t* okrt_overlay_keys(const okrt_overlay* ov);       /* draw (1-based) of each segment */
+OKRT_API const uint32_t* okrt_overlay_colours(const okrt_overlay* ov);    /* RGBA8 per draw */
+
 /* Host-only report on the traversal layout okrt_render builds from the binding-table arrays (no GPU needed): lets a
  * test or a tool check stack needs and compare tree quality.  sahCost = sum over child boxes of the scene-wide tree of
  * area(box)/area(root) x (1 for an interior child, triangle count for a leaf child): the expected work of a random ray. */
@@ -423,7 +442,11 @@ OKRT_API int okrt_read_result(okrt_renderer* r, uint8_t* outRgba8);            /
  * rows untouched), so N ranks fill one host image without moving N copies of it; *outBytes (may be NULL) = bytes moved.
  * Unsharded renderers behave like okrt_read_result. */
 OKRT_API int okrt_read_result_owned(okrt_renderer* r, uint8_t* outRgba8, uint64_t* outBytes);
-OKRT_API int okrt_read_accumulation(okrt_renderer* r, float* outRgba32f);      /* W*H*4 floats */
+OKRT_API int okrt_read_accumulation(okrt_renderer* r, float* outRgba32f);
+/* f4: rasterises the overlay's lines into the RGBA8 result (u0); the accumulation (u1) is untouched, the next
+ * okrt_render_frames rewrites u0. */
+OKRT_API int okrt_draw_overlay(okrt_renderer* r, const okrt_overlay* ov);
+      /* W*H*4 floats */
 OKRT_API int okrt_read_aov(okrt_renderer* r, okrt_aov* out);                   /* W*H entries; needs writeAov */
 /* progressive-state restore / merge (new): replaces the accumulation buffer and frame counter */
 OKRT_API int okrt_write_accumulation(okrt_renderer* r, const float* rgba32f, uint32_t numAccumulationFrames);
