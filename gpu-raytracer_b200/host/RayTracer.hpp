@@ -157,6 +157,51 @@ public:
     }
     okrt_renderer* handle() { return m_handle; }
 
+    /* RayTracer::getGlobalNodeIdx (RayTracer.h:226-230) */
+    uint32_t getGlobalNodeIdx(uint32_t meshID, uint32_t localNodeIdx) const
+    {
+        return okrt_geometry_mesh_descs(m_geometry)[meshID].bvhTreeStartIdx + localNodeIdx;
+    }
+
+    /* the "Rebuild BVH" path with the tree built on the GPU (row f2): reference node format, not the reference's tree */
+    float loadMeshAndBvhDataOnDevice(uint32_t maxLeafTriangles, int device = 0)
+    {
+        const auto& meshes = m_pResourceManager->meshes;
+        if (meshes.empty()) return 0.f;
+        std::vector<okrt_mesh_view> views(meshes.size());
+        for (size_t i = 0; i < meshes.size(); i++)
+            views[i] = okrt_mesh_view{meshes[i].trianglesPos.data(), meshes[i].trianglesInfo.data(),
+                                      (uint32_t)meshes[i].trianglesPos.size(), meshes[i].boundingBox};
+        if (m_geometry) okrt_geometry_free(m_geometry);
+        m_geometry = nullptr;
+        float ms = 0.f;
+        check(okrt_geometry_build_device(views.data(), (uint32_t)views.size(), maxLeafTriangles, device, &m_geometry, &ms));
+        check(okrt_set_triangles(m_handle, okrt_geometry_triangles_pos(m_geometry), okrt_geometry_triangles_info(m_geometry),
+                                 okrt_geometry_num_triangles(m_geometry)));
+        check(okrt_set_bvh_nodes(m_handle, okrt_geometry_bvh_nodes(m_geometry), okrt_geometry_num_nodes(m_geometry)));
+        return ms;
+    }
+
+    /* Application::saveScreenshot (Application.cpp:661-674) */
+    void saveScreenshot(const char* path = "render.png")
+    {
+        std::vector<uint8_t> rgba8;
+        readResult(rgba8);
+        check(okrt_write_png(path, rgba8.data(), m_renderData.textureDims[0], m_renderData.textureDims[1]));
+    }
+
+    /* DebugRenderer::renderBvhNodeBBs (DebugRenderer.cpp:264-303); drawMode = DrawMode enum value (0-3) */
+    void renderBvhNodeBBs(const okrt_mesh_entity& entity, uint32_t localNodeIdx, uint32_t drawMode)
+    {
+        okrt_overlay* ov = nullptr;
+        check(okrt_overlay_build(OKRT_OVERLAY_BVH, okrt_geometry_bvh_nodes(m_geometry), okrt_geometry_num_nodes(m_geometry),
+                                 getGlobalNodeIdx(entity.meshID, localNodeIdx), drawMode, &entity.transform, &m_pScene->camera,
+                                 m_renderData.textureDims[0], m_renderData.textureDims[1], &ov));
+        const int rc = okrt_draw_overlay(m_handle, ov);
+        okrt_overlay_free(ov);
+        check(rc);
+    }
+
 private:
     void loadTextureData()                                            /* RayTracer.cpp:310-342 */
     {
