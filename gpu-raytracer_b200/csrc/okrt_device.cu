@@ -191,6 +191,14 @@ int rebuildLayout(okrt_renderer* r)
     if ((rc = r->octParent.upload(fl.octParent.data(), (uint32_t)fl.octParent.size(), sizeof(uint32_t), r->stream))) return rc;
     if (r->fastTrisTex) { cudaDestroyTextureObject(r->fastTrisTex); r->fastTrisTex = 0; }
     if (r->fastTris.bytes) {            /* the triangle records as float4 texels: stepTriangle fetches them through the texture pipe */
+        int maxTexels = 0;
+        OKRT_CUDA(cudaDeviceGetAttribute(&maxTexels, cudaDevAttrMaxTexture1DLinearWidth, r->device));
+        if (r->fastTris.bytes / sizeof(Float4) > (size_t)maxTexels) {
+            char msg[160];
+            std::snprintf(msg, sizeof(msg), "scene too large: %zu triangles, the triangle texture holds %d", r->fastTris.bytes / sizeof(Float4) / kTriQuads, maxTexels / (int)kTriQuads);
+            setError(msg);
+            return OKRT_ERR_CAPACITY;
+        }
         cudaResourceDesc res; std::memset(&res, 0, sizeof(res));
         res.resType = cudaResourceTypeLinear; res.res.linear.devPtr = r->fastTris.ptr; res.res.linear.sizeInBytes = r->fastTris.bytes;
         res.res.linear.desc = cudaCreateChannelDesc<float4>();
