@@ -60,13 +60,16 @@ struct Builder {
         if (count == 0) return kRefNone;
         if ((uint64_t)start + count > numTris || start >= kMaxTriIndex) { fail("BVH leaf references triangles out of range"); return kRefNone; }
         if (count <= kMaxLeafTris) return kRefTriLeaf | ((count - 1u) << 27) | start;
-        /* oversized leaf: chain of pair nodes that repeat the leaf's box */
+        /* oversized leaf (depth-limited or maxLeafTriangles > 8 trees): a balanced tree of pair nodes that repeat the
+         * leaf's box over 8-triangle records — log2(count / 8) stack levels, not count / 8 */
         const uint32_t p = newPair();
         deepestPair = std::max(deepestPair, pairLevel + 1);
-        const uint32_t head = kRefTriLeaf | ((kMaxLeafTris - 1u) << 27) | start;
-        setChild(p, 0, box, head);
-        const uint32_t rest = leafRef(start + kMaxLeafTris, count - kMaxLeafTris, box, level, pairLevel + 1);
-        setChild(p, 1, box, rest);
+        const uint32_t records = (count + kMaxLeafTris - 1u) / kMaxLeafTris;
+        const uint32_t left = ((records + 1u) / 2u) * kMaxLeafTris;
+        const uint32_t r0 = leafRef(start, left, box, level, pairLevel + 1);
+        const uint32_t r1 = leafRef(start + left, count - left, box, level, pairLevel + 1);
+        setChild(p, 0, box, r0);
+        setChild(p, 1, box, r1);
         return p;
     }
 

@@ -176,3 +176,19 @@ def test_reference_struct_sizes_and_defaults(okrt):
     g = np.load(os.path.join(GOLD, "ref_structs.npz"))
     assert list(g["sizes"]) == [36, 44, 132, 24, 68, 232, 84, 32, 32, 48]          # sizeof() of the reference's CPU mirrors
     assert g["material"].tobytes() == np.array([okrt.abi.default_material()]).tobytes()   # Components.h:42-56
+
+
+def test_layout_report_and_oversized_leaves(okrt):
+    """okrt_layout_report (host-only): the traversal layout of a scene; a root-only BVH (one leaf of 1280 triangles)
+    becomes a balanced tree of 8-triangle records, so its stack need grows with log2, not with the triangle count."""
+    import sys
+    from tests import helpers
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
+    from layout_report import report
+    rm, sc, info = okrt.scenes.test_scene(num_spheres=0)
+    normal = report(helpers.build_host_side(okrt, rm, sc, info, 64, 36))
+    assert normal["numFlattenedLeaves"] > 100 and normal["numPairNodes"] >= normal["numFlattenedLeaves"] - 1
+    assert 0 < normal["fastStackDepth"] <= 40 and normal["sahCost"] > 0
+    flat = report(helpers.build_host_side(okrt, rm, sc, dict(info, bvh=(1, 1)), 64, 36))
+    assert flat["numFlattenedLeaves"] == 3                      # three meshes, each a single leaf
+    assert flat["fastStackDepth"] <= 16, int(flat["fastStackDepth"])
