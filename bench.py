@@ -27,7 +27,7 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 WIDTH, HEIGHT, MAX_BOUNCES = 1920, 1080, 8
-FRAMES_PER_STEP = 4
+FRAMES_PER_STEP = 16         # one wavefront pass at 1080p on one GPU: 2^25 path slots = 16 frames of 2 073 600 pixels
 METRIC = "Sponza 1080p 8-bounce Mrays/s (device-timed) at 1/2/4/8 B200 vs CPU ref"
 UNIT = "Mrays/s"
 
