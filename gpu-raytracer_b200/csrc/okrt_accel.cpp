@@ -7,6 +7,7 @@
 #include "okrt_internal.h"
 
 #include <algorithm>
+#include <atomic>
 #include <cfloat>
 #include <chrono>
 #include <cmath>
@@ -14,6 +15,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <functional>
+#include <future>
 #include <string>
 #include <unordered_map>
 #include <utility>
@@ -71,6 +73,22 @@ struct Builder {
         setChild(p, 0, box, r0);
         setChild(p, 1, box, r1);
         return p;
+    }
+
+    /* a reference BVH that passed flattenable(): records its depth (the reference-order stack bound) and says whether
+     * any leaf holds a triangle */
+    bool hasTriangles(uint32_t root)
+    {
+        bool any = false;
+        std::vector<std::pair<uint32_t, uint32_t>> st{{root, 0u}};
+        while (!st.empty()) {
+            const auto [idx, level] = st.back(); st.pop_back();
+            const okrt_bvh_node& n = nodes[idx];
+            if (n.firstChildIdx != OKRT_INVALID_UINT) { st.push_back({n.firstChildIdx, level + 1}); st.push_back({n.firstChildIdx + 1, level + 1}); continue; }
+            deepestLeafLevel = std::max(deepestLeafLevel, level);
+            any = any || (n.triStart != OKRT_INVALID_UINT && n.triEnd > n.triStart);
+        }
+        return any;
     }
 
     uint32_t convert(uint32_t nodeIdx, uint32_t level, uint32_t pairLevel)
@@ -229,6 +247,13 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
                      const okrt_octree_node* octNodes, uint32_t numOctNodes, FastLayout& out)
 {
     out = FastLayout();
+    const bool verbose = std::getenv("OKRT_LAYOUT_VERBOSE") != nullptr;
+    auto phaseStart = std::chrono::steady_clock::now();
+    auto phase = [&](const char* name) {
+        const auto now = std::chrono::steady_clock::now();
+        if (verbose) std::fprintf(stderr, "[okrt] layout: %-28s %8.1f ms\n", name, std::chrono::duration<double, std::milli>(now - phaseStart).count());
+        phaseStart = now;
+    };
 
     /* triangles: 3 x float4 */
     /* triangles: p2 | E1 = p0 - p2 | E2 = p1 - p2 (GPU-Utilities.hlsli:124: the same float32 subtractions, done once) */
@@ -242,6 +267,7 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
         out.tris[(size_t)t * kTriQuads + 2] = Float4{e[5], 0.f, 0.f, 0.f};
     }
 
+    phase("triangle records");
     /* oct-tree: parents, reachability, reference stack bound */
     out.octParent.assign(numOctNodes, 0xFFFFFFFFu);
     std::vector<uint8_t> reachable(numOctNodes, 0);
@@ -289,6 +315,7 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
         }
     }
 
+    phase("oct-tree checks");
     /* bottom level: one conversion per distinct BVH root */
     Builder b{tris, numTris, nodes, numNodes, out};
     std::unordered_map<uint32_t, uint32_t> rootRefOf;
@@ -302,21 +329,33 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
         if (instOct[i] == 0xFFFFFFFFu) continue;                 /* never visited by the reference either */
         const okrt_mesh_instance& inst = instances[i];
         if (inst.bvhNodeStartIdx >= numNodes) { out.error = "instance bvhNodeStartIdx out of range"; return false; }
-        auto it = rootRefOf.find(inst.bvhNodeStartIdx);
-        uint32_t rootRef;
-        if (it == rootRefOf.end()) {
+        /* pair-node copy of the instance's reference BVH: only instances that are walked as instances need it, so it
+         * is made on demand (a merged, flattened instance contributes its leaves to the scene-wide tree instead) */
+        auto convertedRoot = [&]() -> uint32_t {
+            auto it = rootRefOf.find(inst.bvhNodeStartIdx);
+            if (it != rootRefOf.end()) return it->second;
             const uint32_t before = b.deepestPair;
             b.deepestPair = 0;
-            rootRef = b.convert(inst.bvhNodeStartIdx, 0, 0);
-            if (b.failed) return false;
+            const uint32_t ref = b.convert(inst.bvhNodeStartIdx, 0, 0);
             b.deepestPair = std::max(before, b.deepestPair);
-            rootRefOf.emplace(inst.bvhNodeStartIdx, rootRef);
-        } else rootRef = it->second;
-        if (rootRef == kRefNone) continue;                       /* empty mesh */
-
+            rootRefOf.emplace(inst.bvhNodeStartIdx, ref);
+            return ref;
+        };
         const okrt_aabb& rb = nodes[inst.bvhNodeStartIdx].boundingBox;
         const float* T = inst.transformMatrix;
         const float* Ti = inst.inverseTransformMatrix;
+        static const float I16[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
+        bool identity = true;
+        for (int k = 0; k < 16; k++) identity = identity && T[k] == I16[k] && Ti[k] == I16[k];
+        const bool flatCandidate = identity && rootUsers[inst.bvhNodeStartIdx] == 1u && flattenable(nodes, numNodes, inst.bvhNodeStartIdx);
+        uint32_t rootRef = kRefNone;
+        if (flatCandidate) {
+            if (!b.hasTriangles(inst.bvhNodeStartIdx)) continue; /* empty mesh */
+        } else {
+            rootRef = convertedRoot();
+            if (b.failed) return false;
+            if (rootRef == kRefNone) continue;                   /* empty mesh */
+        }
         bool finite = true;
         for (int k = 0; k < 3; k++) finite = finite && std::isfinite(rb.min[k]) && std::isfinite(rb.max[k]) && rb.min[k] <= rb.max[k];
         for (int k = 0; k < 16; k++) finite = finite && std::isfinite(T[k]) && std::isfinite(Ti[k]);
@@ -330,10 +369,6 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
                 for (int r = 0; r < 3; r++) d += (double)T[r * 4 + a] * (double)T[r * 4 + c];
                 if (std::fabs(d - (a == c ? 1.0 : 0.0)) > 1e-4) out.allRigid = false;
             }
-        static const float I16[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
-        bool identity = true;
-        for (int k = 0; k < 16; k++) identity = identity && T[k] == I16[k] && Ti[k] == I16[k];
-
         const uint32_t rec = (uint32_t)(out.instances.size() / kInstQuads);
         out.instances.resize(out.instances.size() + kInstQuads);
         Float4* r = &out.instances[(size_t)rec * kInstQuads];
@@ -361,10 +396,15 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
                 ranges.emplace_back(n.triStart, n.triEnd);
             }
         }
+        if (!merged && rootRef == kRefNone) {                    /* a flat candidate whose triangles are shared after all */
+            rootRef = convertedRoot();
+            if (b.failed) return false;
+            r[7].x = bitsToFloat(rootRef);
+        }
         if (merged) {
             for (auto& rg : ranges) for (uint32_t j = rg.first; j < rg.second; j++) out.triOwner[j] = rec;
             out.numMerged++;
-            if (flattenable(nodes, numNodes, inst.bvhNodeStartIdx)) {
+            if (flatCandidate) {
                 /* every REFERENCE LEAF becomes a primitive of one scene-wide SAH tree.  Its box is the reference's own
                  * (bit copy) and is tested with the reference's arithmetic; a reference parent box contains its
                  * children's boxes exactly (BvhBuilder.cpp:209-222 takes min/max over the same points), and the slab
@@ -411,6 +451,7 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
         leaves.push_back(leaf);
     }
     out.exactBvhDepth = b.deepestLeafLevel + 1;
+    phase("instances and leaves");
 
     /* top level: binned SAH (32 bins per axis, cost = area x triangles below) over reference leaves and instances;
      * median split when the SAH finds nothing or the tree gets too deep for the traversal stack */
@@ -419,8 +460,11 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
     constexpr uint32_t kSahDepthLimit = 44;
     const char* sweepEnv = std::getenv("OKRT_TOP_SWEEP");
     const size_t sweepBelow = sweepEnv ? (size_t)std::atoll(sweepEnv) : (size_t)-1;
+    const char* sweepMinEnv = std::getenv("OKRT_TOP_SWEEP_MIN");
+    const size_t sweepAbove = sweepMinEnv ? (size_t)std::atoll(sweepMinEnv) : 8192;     /* smaller ranges use the 32-bin SAH: the sweep pays at the top levels only (measured) */
     std::vector<TopNode> tn;
-    tn.reserve(leaves.size() * 2);
+    tn.resize(leaves.size() * 2 + 2);                   /* slots are claimed with an atomic counter: subtrees are built in parallel */
+    std::atomic<int32_t> nextTopNode{0};
     std::function<int32_t(size_t, size_t, uint32_t)> buildTop = [&](size_t lo, size_t hi, uint32_t level) -> int32_t {
         double bl[3] = {DBL_MAX, DBL_MAX, DBL_MAX}, bh[3] = {-DBL_MAX, -DBL_MAX, -DBL_MAX};
         double cl[3] = {DBL_MAX, DBL_MAX, DBL_MAX}, ch[3] = {-DBL_MAX, -DBL_MAX, -DBL_MAX};
@@ -430,38 +474,42 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
                 const double c = 0.5 * (leaves[i].lo[k] + leaves[i].hi[k]);
                 cl[k] = std::min(cl[k], c); ch[k] = std::max(ch[k], c);
             }
-        const int32_t self = (int32_t)tn.size();
-        tn.push_back(TopNode());
+        const int32_t self = nextTopNode.fetch_add(1);
         for (int k = 0; k < 3; k++) { tn[self].lo[k] = bl[k]; tn[self].hi[k] = bh[k]; }
         if (hi - lo == 1) { tn[self].ref = leaves[lo].ref; return self; }
 
         size_t mid = lo;
-        if (hi - lo > 2 && hi - lo <= sweepBelow && level < kSahDepthLimit) {
+        if (hi - lo > 2 && hi - lo <= sweepBelow && hi - lo >= sweepAbove && level < kSahDepthLimit) {
             /* small ranges: every split position of every axis (full sweep), not just the 31 bin borders */
             auto area = [](const double* l, const double* h) { const double dx = h[0] - l[0], dy = h[1] - l[1], dz = h[2] - l[2]; return 2.0 * (dx * dy + dy * dz + dz * dx); };
             const size_t n = hi - lo;
             double bestCost = DBL_MAX; int bestAxis = -1; size_t bestCut = 0;
             std::vector<double> rightArea(n); std::vector<uint64_t> rightW(n);
-            std::vector<TopLeaf> sorted(leaves.begin() + (ptrdiff_t)lo, leaves.begin() + (ptrdiff_t)hi), bestOrder;
+            std::vector<std::pair<double, uint32_t>> keyed(n), bestOrder;          /* (centroid x 2, position in the range) */
             for (int axis = 0; axis < 3; axis++) {
-                std::stable_sort(sorted.begin(), sorted.end(), [axis](const TopLeaf& a, const TopLeaf& c) { return a.lo[axis] + a.hi[axis] < c.lo[axis] + c.hi[axis]; });
+                for (size_t i = 0; i < n; i++) keyed[i] = {leaves[lo + i].lo[axis] + leaves[lo + i].hi[axis], (uint32_t)i};
+                std::sort(keyed.begin(), keyed.end());                              /* ties by position: deterministic */
                 double rl[3] = {DBL_MAX, DBL_MAX, DBL_MAX}, rh[3] = {-DBL_MAX, -DBL_MAX, -DBL_MAX}; uint64_t rw = 0;
                 for (size_t i = n - 1; i > 0; i--) {
-                    for (int k = 0; k < 3; k++) { rl[k] = std::min(rl[k], (double)sorted[i].lo[k]); rh[k] = std::max(rh[k], (double)sorted[i].hi[k]); }
-                    rw += sorted[i].weight; rightArea[i] = area(rl, rh); rightW[i] = rw;
+                    const TopLeaf& q = leaves[lo + keyed[i].second];
+                    for (int k = 0; k < 3; k++) { rl[k] = std::min(rl[k], q.lo[k]); rh[k] = std::max(rh[k], q.hi[k]); }
+                    rw += q.weight; rightArea[i] = area(rl, rh); rightW[i] = rw;
                 }
                 double ll[3] = {DBL_MAX, DBL_MAX, DBL_MAX}, lh[3] = {-DBL_MAX, -DBL_MAX, -DBL_MAX}; uint64_t lw = 0;
                 bool improved = false;
                 for (size_t i = 0; i + 1 < n; i++) {
-                    for (int k = 0; k < 3; k++) { ll[k] = std::min(ll[k], (double)sorted[i].lo[k]); lh[k] = std::max(lh[k], (double)sorted[i].hi[k]); }
-                    lw += sorted[i].weight;
+                    const TopLeaf& q = leaves[lo + keyed[i].second];
+                    for (int k = 0; k < 3; k++) { ll[k] = std::min(ll[k], q.lo[k]); lh[k] = std::max(lh[k], q.hi[k]); }
+                    lw += q.weight;
                     const double cost = area(ll, lh) * (double)lw + rightArea[i + 1] * (double)rightW[i + 1];
                     if (cost < bestCost) { bestCost = cost; bestAxis = axis; bestCut = i + 1; improved = true; }
                 }
-                if (improved) bestOrder = sorted;
+                if (improved) bestOrder = keyed;
             }
             if (bestAxis >= 0) {
-                std::copy(bestOrder.begin(), bestOrder.end(), leaves.begin() + (ptrdiff_t)lo);
+                std::vector<TopLeaf> moved(n);
+                for (size_t i = 0; i < n; i++) moved[i] = leaves[lo + bestOrder[i].second];
+                std::copy(moved.begin(), moved.end(), leaves.begin() + (ptrdiff_t)lo);
                 mid = lo + bestCut;
             }
         } else if (hi - lo > 2 && level < kSahDepthLimit) {
@@ -513,7 +561,12 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
             std::nth_element(leaves.begin() + (ptrdiff_t)lo, leaves.begin() + (ptrdiff_t)mid, leaves.begin() + (ptrdiff_t)hi,
                              [axis](const TopLeaf& a, const TopLeaf& c) { return a.lo[axis] + a.hi[axis] < c.lo[axis] + c.hi[axis]; });
         }
-        const int32_t l = buildTop(lo, mid, level + 1), r = buildTop(mid, hi, level + 1);
+        int32_t l, r;
+        if (hi - lo > 8192 && level < 4) {                      /* disjoint ranges of `leaves`, disjoint slots of `tn` */
+            auto left = std::async(std::launch::async, [&]() { return buildTop(lo, mid, level + 1); });
+            r = buildTop(mid, hi, level + 1);
+            l = left.get();
+        } else { l = buildTop(lo, mid, level + 1); r = buildTop(mid, hi, level + 1); }
         tn[self].left = l; tn[self].right = r;
         tn[l].parent = self; tn[r].parent = self;
         return self;
@@ -536,6 +589,7 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
     if (!leaves.empty()) {
         okrt_aabb rootBox;
         int32_t root = buildTop(0, leaves.size(), 0);
+        tn.resize((size_t)nextTopNode.load());
         const char* passesEnv = std::getenv("OKRT_TOP_REINSERT");
         const int passes = passesEnv ? std::atoi(passesEnv) : 0;
         if (passes > 0 && leaves.size() > 2) {
@@ -544,7 +598,9 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
             root = reinsertOptimize(tn, root, passes);
             if (topTreeDepth(tn, root) > kSahDepthLimit + 4) { tn = before; root = rootBefore; }      /* stack budget */
         }
+        phase("scene-wide tree (SAH)");
         out.topRef = emitTop(root, 0, rootBox);
+        phase("pair-node emission");
         if (leaves.size() == 1) {
             /* single instance: wrap it in a pair node so the kernel always starts at an interior node (and tests its box) */
             const uint32_t p = b.newPair();
