@@ -274,12 +274,13 @@ def main():
             bseg_path, bseg = algorithmic_bytes_per_segment(visits, WIDTH * HEIGHT)
             peak, which = measured_peak_gbs()
             achieved = bseg * segments / (max(trace_ms, 1e-6) * 1e-3) / 1e9
-            traffic = None
+            traffic, units = None, None
             tpath = os.path.join(ROOT, "profiles", "traffic_bytes_per_launch.json")
             if os.path.exists(tpath):
                 try:
                     with open(tpath) as f:
                         tj = json.load(f)
+                        units = tj.get("traceFastKernel_units")
                         # DRAM bytes of the captured launch, scaled to this run's average launch by duration
                         traffic = tj["traceFastKernel"] * (trace_ms / max(1, trace_launches)) / tj["traceFastKernel_ms"]
                 except Exception:
@@ -289,6 +290,7 @@ def main():
                                 "kernel_launches": trace_launches, "kernel_ms_per_launch": trace_ms / max(1, trace_launches),
                                 "kernel_share_of_step": trace_ms / dev_ms,
                                 "algorithmic_bytes_per_launch": bseg * segments / max(1, trace_launches),
+                                "unit_utilisation_from_ncu": units,      # the ray-throughput view: how busy the kernel's busiest units are (committed capture, not live)
                                 "algorithmic_bytes_per_segment": bseg, "algorithmic_bytes_per_segment_whole_path": bseg_path,
                                 "note": "algorithmic bytes = what the reference's traversal order reads per segment (SURVEY.md 8d); the "
                                         "kernel visits far fewer nodes, and the scene is L2-resident, so DRAM traffic is much lower"}
