@@ -294,6 +294,20 @@ def main():
                                 "algorithmic_bytes_per_segment": bseg, "algorithmic_bytes_per_segment_whole_path": bseg_path,
                                 "note": "algorithmic bytes = what the reference's traversal order reads per segment (SURVEY.md 8d); the "
                                         "kernel visits far fewer nodes, and the scene is L2-resident, so DRAM traffic is much lower"}
+            # FP32-issue roofline.  Algorithmic flops per segment in REFERENCE order:
+            # 25 per box test (oct-tree, instance root and BVH node boxes), 51 per triangle test, 20 per accepted candidate
+            # (3x3 transform + length, counted once per hit segment); peak = SMs x 128 lanes x 2 x f_clk.
+            seg_n = max(1, visits["segments"])
+            flops_seg = (25.0 * (visits["bvhNodes"] + visits["instances"] + visits["octNodes"]) + 51.0 * visits["triangles"]
+                         + 20.0 * visits["hits"]) / seg_n
+            sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
+            peak_tf = 148 * 128 * 2 * sm_mhz * 1e6 / 1e12
+            ach_tf = flops_seg * segments / (max(trace_ms, 1e-6) * 1e-3) / 1e12
+            line["roofline_fp32"] = {"bound": "fp32-issue", "achieved": ach_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach_tf / peak_tf,
+                                     "algorithmic_flops_per_segment": flops_seg, "kernel": "traceFastKernel",
+                                     "visits_per_segment": {k: visits[k] / seg_n for k in ("bvhNodes", "triangles", "instances", "octNodes", "hits", "textureTaps")},
+                                     "note": "reference-order flops (SURVEY.md 8d) over the traversal kernel's event-timed launches; the kernel itself runs ~3x "
+                                             "fewer box tests than the reference order, so its executed FP32 rate is lower than this figure"}
         print(json.dumps(line))
     r.close()
     if dist is not None:

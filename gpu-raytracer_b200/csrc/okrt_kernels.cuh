@@ -476,6 +476,9 @@ constexpr uint32_t kTraceTop = 0xFFFFFFFFu;
  *   - the oct-tree chain of a merged instance is tested once, for the winning triangle, when the ray finishes
  *     (a failed chain or two candidates inside the window send the ray to the reference-order kernel).
  * Arithmetic per box and per triangle is unchanged, so are the results. */
+#ifndef OKRT_STACK_TOPREG
+#define OKRT_STACK_TOPREG 0
+#endif
 struct StepLane {
     V3 ro, rd, ridir;        /* current ray: identity-local at the top level, instance-local inside an instance */
     float best, second;
@@ -485,6 +488,10 @@ struct StepLane {
     uint32_t cur;            /* reference the lane stands on: interior / triangle leaf / instance / exit marker / done */
     uint32_t triNext;        /* next triangle of the leaf in `cur` */
     int sp;                  /* next free stack slot; slot 0 holds kTraceDone */
+#if OKRT_STACK_TOPREG
+    uint32_t top;            /* newest stack entry, kept in a register: a pop hands it out and re-loads it from memory, so the
+                              * load's latency is hidden behind the step that follows instead of stalling it */
+#endif
     uint32_t inst;           /* instance record inside a generic instance; kTraceTop at the top level */
     uint32_t path;
 };
@@ -510,17 +517,34 @@ __device__ __forceinline__ void stepEnter(StepLane& L, uint32_t ref)
     L.cur = ref;
     if ((ref & kRefTagMask) == kRefTriLeaf) L.triNext = ref & (kMaxTriIndex - 1u);
 }
-__device__ __forceinline__ void stepPop(StepLane& L, const uint32_t* stack)
+__device__ __forceinline__ void stackPush(StepLane& L, uint32_t* stack, uint32_t v)
+{
+    OKRT_CHECK(L.sp >= 1 && L.sp < (int)kFastStackCapacity);
+#if OKRT_STACK_TOPREG
+    stack[L.sp++] = L.top; L.top = v;
+#else
+    stack[L.sp++] = v;
+#endif
+}
+__device__ __forceinline__ uint32_t stackPop(StepLane& L, const uint32_t* stack)
 {
     OKRT_CHECK(L.sp >= 1 && L.sp <= (int)kFastStackCapacity);
-    stepEnter(L, stack[--L.sp]);
+#if OKRT_STACK_TOPREG
+    const uint32_t v = L.top; L.top = stack[--L.sp]; return v;
+#else
+    return stack[--L.sp];
+#endif
 }
+__device__ __forceinline__ void stepPop(StepLane& L, const uint32_t* stack) { stepEnter(L, stackPop(L, stack)); }
 
 __device__ __forceinline__ void stepInit(const DeviceScene& s, StepLane& L, uint32_t* stack, uint32_t numSpheres, V3 o, V3 d)
 {
     L.best = OKRT_FLT_MAX; L.second = OKRT_FLT_MAX;
     L.hitRec = 0x3FFFFFFFu; L.hitTri = 0xFFFFFFFFu; L.hitU = 0.f; L.hitV = 0.f;
     stack[0] = kTraceDone; L.sp = 1;
+#if OKRT_STACK_TOPREG
+    L.top = kTraceDone;
+#endif
     stepTopRay(L, o, d);
     for (uint32_t i = 0; i < numSpheres; i++) {                /* RaytracerCS.hlsl:232-242 */
         const okrt_sphere& sp = s.spheres[i];
@@ -572,10 +596,9 @@ __device__ __forceinline__ void stepNode(const DeviceScene& s, StepLane& L, uint
     const bool h0 = boxPasses(L.ro, L.ridir, q0, q1, limit, n0);
     const bool h1 = boxPasses(L.ro, L.ridir, q2, q3, limit, n1);
     const bool firstIs1 = h1 && (!h0 || n1 < n0);
-    OKRT_CHECK(L.sp >= 1 && L.sp < (int)kFastStackCapacity);
-    if (h0 && h1) stack[L.sp++] = firstIs1 ? r0 : r1;
+    if (h0 && h1) stackPush(L, stack, firstIs1 ? r0 : r1);
     uint32_t nxt = firstIs1 ? r1 : r0;
-    if (!(h0 || h1)) nxt = stack[--L.sp];
+    if (!(h0 || h1)) nxt = stackPop(L, stack);
     stepEnter(L, nxt);
 }
 
@@ -658,8 +681,7 @@ __device__ __forceinline__ void stepMisc(const DeviceScene& s, StepLane& L, uint
             const float4 a0 = __ldg(rec + 3), a1 = __ldg(rec + 4), a2 = __ldg(rec + 5);
             /* the mesh's root box (RaytracerCS.hlsl:285 on the first popped node) */
             if (rayAndAABBDist(lo, lidir, v3(a0.w, a1.w, a2.w), v3(r6.x, r6.y, r6.z)) < relaxedLimit(L.best)) {
-                OKRT_CHECK(L.sp >= 1 && L.sp < (int)kFastStackCapacity);
-                stack[L.sp++] = kTraceExitInstance;
+                stackPush(L, stack, kTraceExitInstance);
                 L.ro = lo; L.rd = ld; L.ridir = lidir;
                 L.inst = recIdx;
                 stepEnter(L, __float_as_uint(r7.x));

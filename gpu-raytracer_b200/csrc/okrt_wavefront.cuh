@@ -185,6 +185,9 @@ traceFastKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ F
     StepLane L;
     L.cur = kTraceDone; L.sp = 1; L.path = 0u; L.inst = kTraceTop; L.triNext = 0u;
     stack[0] = kTraceDone;
+#if OKRT_STACK_TOPREG
+    L.top = kTraceDone;
+#endif
     bool have = false;                        /* this lane owns a ray whose result is not written yet */
     uint32_t next = 0u, end = 0u;             /* warp-uniform: unclaimed part of the warp's current chunk */
     bool exhausted = false;                   /* warp-uniform */

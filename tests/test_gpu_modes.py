@@ -215,3 +215,33 @@ def test_full_size_8_bounces_properties(okrt):
 def test_cpp_mirror_on_gpu(okrt, tmp_path):
     from tests.test_cpu_host_mirror import test_cpp_mirror_builds_and_runs
     test_cpp_mirror_builds_and_runs(okrt, tmp_path)
+
+
+_DUAL_SCRIPT = """
+import importlib, sys, numpy as np
+sys.path.insert(0, {root!r})
+from tests import helpers
+okrt = importlib.import_module("gpu-raytracer_b200")
+rm, sc, info = okrt.scenes.sponza_standin(8000, texture_size=64)
+host = helpers.build_host_side(okrt, rm, sc, info, 160, 90)
+r = helpers.Renderer(okrt, host, 160, 90, envFaces=okrt.scenes.procedural_sky_faces(32))
+r.options(maxBounces=4)
+r.render(host["rd"].copy(), frames=5)
+np.save({out!r}, r.accumulation())
+r.close()
+"""
+
+
+def test_two_stream_halves_bit_identical(okrt, tmp_path):
+    """OKRT_DUAL_MIN_FRAMES (launchWavefront: the batch as two halves on two streams, one frame-ordered accumulate):
+    5 frames (halves of 3 and 2) give the same u1 bits as the single-stream batch."""
+    import os, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    outs = []
+    for name, val in (("single", "0"), ("dual", "2")):
+        out = str(tmp_path / (name + ".npy"))
+        env = dict(os.environ, OKRT_DUAL_MIN_FRAMES=val)
+        subprocess.run([sys.executable, "-c", _DUAL_SCRIPT.format(root=root, out=out)], check=True, env=env, cwd=root, timeout=300)
+        outs.append(np.load(out))
+    assert outs[0][..., 3].max() == 5.0
+    assert np.array_equal(outs[0].view(np.uint32), outs[1].view(np.uint32))
