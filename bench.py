@@ -264,7 +264,8 @@ def main():
                 "e2e": {"value": e2e_segments / e2e_s / 1e6, "unit": UNIT, "h2d_bytes_per_step": 240 + 64,
                         "d2h_bytes_per_step": d2h_bytes},
                 "gpu_launches": launches,
-                "ray_segments": segments, "fallback_segments": fallback, "traversal": args.traversal}
+                "ray_segments": segments, "fallback_segments": fallback, "traversal": args.traversal,
+                "trace_kernel_ms": trace_ms, "trace_kernel_launches": trace_launches}
         if world > 1:
             line["rank_ms"] = rank_ms                 # device time of each rank's K steps: shows the load balance of the tile split
             line["rank_segments"] = rank_segments

@@ -340,6 +340,8 @@ int launchWavefront(okrt_renderer* r, const FrameParams& fpWhole, bool instrumen
         generateKernel<<<flatGridH[h], 128, 0, st[h]>>>(fpH[h], wbH[h]);
         r->launches++;
     }
+    static const bool serialTrace = [] { const char* e = std::getenv("OKRT_DUAL_SERIAL_TRACE"); return e ? std::atoi(e) != 0 : true; }();
+    cudaEvent_t lastTraceEnd = nullptr;
     for (uint32_t b = 0; b <= fpWhole.maxBounces; b++) {
         for (int h = 0; h < halves; h++) {
             const FrameParams& fp = fpH[h];
@@ -356,9 +358,14 @@ int launchWavefront(okrt_renderer* r, const FrameParams& fpWhole, bool instrumen
                 }
                 e0 = r->traceEvents[r->traceEventsUsed]; e1 = r->traceEvents[r->traceEventsUsed + 1];
                 r->traceEventsUsed += 2;
+                /* the traversal kernels of the two halves take turns (each waits for the other half's previous one), so an
+                 * event pair never spans another traversal kernel; what overlaps with it is the other half's shade /
+                 * fallback / generate work */
+                if (dual && serialTrace && lastTraceEnd) OKRT_CUDA(cudaStreamWaitEvent(st[h], lastTraceEnd, 0));
                 OKRT_CUDA(cudaEventRecord(e0, st[h]));
                 traceFastKernel<<<traceGridH[h], kTraceBlockThreads, 0, st[h]>>>(scene, fp, wb, qin, b);
                 OKRT_CUDA(cudaEventRecord(e1, st[h]));
+                lastTraceEnd = e1;
                 traceFallbackKernel<<<fallbackGridH[h], 128, 0, st[h]>>>(scene, fp, wb, b);
                 r->launches++;
             }

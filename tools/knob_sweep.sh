@@ -7,7 +7,7 @@ for cfg in "$@"; do
 import sys,json
 t=sys.stdin.read()
 try:
-    d=json.loads(t); print('%.1f Mrays/s  %.3f ms/step  e2e %.1f  fallback %d' % (d['value'], d['ms_per_step'], d['e2e']['value'], d['fallback_segments']))
+    d=json.loads(t); print('%.1f Mrays/s  %.3f ms/step  e2e %.1f  fallback %d  trace share %.3f' % (d['value'], d['ms_per_step'], d['e2e']['value'], d['fallback_segments'], d.get('trace_kernel_ms', 0) / (d['ms_per_step'] * d['steps'])))
 except Exception: print('FAILED', t[-300:])
 " >> $out
 done
