@@ -295,6 +295,17 @@ def main():
                                 "algorithmic_bytes_per_segment": bseg, "algorithmic_bytes_per_segment_whole_path": bseg_path,
                                 "note": "algorithmic bytes = what the reference's traversal order reads per segment (SURVEY.md 8d); the "
                                         "kernel visits far fewer nodes, and the scene is L2-resident, so DRAM traffic is much lower"}
+            # north_star: "a fraction of the ray-throughput roofline".  The traversal kernel's busiest unit is the L1 data stage
+            # (one 32-byte sector per cycle per SM for divergent lanes); its utilisation in the committed ncu capture of this
+            # same command IS achieved / peak of that bound: peak = the traversal rate at which that unit would saturate
+            # with this kernel's sectors per ray.
+            if units and units.get("l1tex_data_stage_lsu_pct"):
+                rate = segments / (max(trace_ms, 1e-6) * 1e-3) / 1e6
+                f_l1 = units["l1tex_data_stage_lsu_pct"] / 100.0
+                line["roofline_rays"] = {"bound": "l1-data-stage", "achieved": rate, "peak": rate / f_l1, "unit": "Mrays/s (traversal kernel only)",
+                                         "frac": f_l1, "issue_slots_frac": units.get("issue_slots_pct", 0) / 100.0,
+                                         "lanes_per_instruction": units.get("lanes_per_instruction"), "source": units.get("source"),
+                                         "note": "frac = unit utilisation from the committed ncu --set full capture (not live); achieved = live, event-timed"}
             # FP32-issue roofline.  Algorithmic flops per segment in REFERENCE order:
             # 25 per box test (oct-tree, instance root and BVH node boxes), 51 per triangle test, 20 per accepted candidate
             # (3x3 transform + length, counted once per hit segment); peak = SMs x 128 lanes x 2 x f_clk.
