@@ -479,12 +479,23 @@ constexpr uint32_t kTraceTop = 0xFFFFFFFFu;
 #ifndef OKRT_STACK_TOPREG
 #define OKRT_STACK_TOPREG 0
 #endif
+#ifndef OKRT_COLD_IN_LOCAL
+#define OKRT_COLD_IN_LOCAL 0
+#endif
+/* OKRT_COLD_IN_LOCAL: the lane's hit record (written once or twice per ray, read when the ray finishes) lives in the slots
+ * behind the traversal stack instead of registers, which buys resident warps */
+constexpr uint32_t kColdSlots = 8;
+constexpr uint32_t kColdHitRec = kFastStackCapacity + 0, kColdHitTri = kFastStackCapacity + 1, kColdHitU = kFastStackCapacity + 2,
+                   kColdHitV = kFastStackCapacity + 3, kColdSecond = kFastStackCapacity + 4;
 struct StepLane {
     V3 ro, rd, ridir;        /* current ray: identity-local at the top level, instance-local inside an instance */
-    float best, second;
+    float best;
+#if !OKRT_COLD_IN_LOCAL
+    float second;
     uint32_t hitRec;         /* 1<<30 | sphere, or 2<<30 | instance record */
     uint32_t hitTri;
     float hitU, hitV;
+#endif
     uint32_t cur;            /* reference the lane stands on: interior / triangle leaf / instance / exit marker / done */
     uint32_t triNext;        /* next triangle of the leaf in `cur` */
     int sp;                  /* next free stack slot; slot 0 holds kTraceDone */
@@ -496,10 +507,17 @@ struct StepLane {
     uint32_t path;
 };
 
-__device__ __forceinline__ void stepCandidate(StepLane& L, float t, uint32_t rec, uint32_t tri, float u, float v)
+__device__ __forceinline__ void stepCandidate(StepLane& L, uint32_t* stack, float t, uint32_t rec, uint32_t tri, float u, float v)
 {
+#if OKRT_COLD_IN_LOCAL
+    if (t < L.best) {
+        stack[kColdSecond] = __float_as_uint(L.best); L.best = t;
+        stack[kColdHitRec] = rec; stack[kColdHitTri] = tri; stack[kColdHitU] = __float_as_uint(u); stack[kColdHitV] = __float_as_uint(v);
+    } else if (t < __uint_as_float(stack[kColdSecond])) stack[kColdSecond] = __float_as_uint(t);
+#else
     if (t < L.best) { L.second = L.best; L.best = t; L.hitRec = rec; L.hitTri = tri; L.hitU = u; L.hitV = v; }
     else if (t < L.second) L.second = t;
+#endif
 }
 
 __device__ __forceinline__ void stepTopRay(StepLane& L, V3 o, V3 d)
@@ -539,8 +557,14 @@ __device__ __forceinline__ void stepPop(StepLane& L, const uint32_t* stack) { st
 
 __device__ __forceinline__ void stepInit(const DeviceScene& s, StepLane& L, uint32_t* stack, uint32_t numSpheres, V3 o, V3 d)
 {
-    L.best = OKRT_FLT_MAX; L.second = OKRT_FLT_MAX;
+    L.best = OKRT_FLT_MAX;
+#if OKRT_COLD_IN_LOCAL
+    stack[kColdSecond] = __float_as_uint(OKRT_FLT_MAX);
+    stack[kColdHitRec] = 0x3FFFFFFFu; stack[kColdHitTri] = 0xFFFFFFFFu; stack[kColdHitU] = 0u; stack[kColdHitV] = 0u;
+#else
+    L.second = OKRT_FLT_MAX;
     L.hitRec = 0x3FFFFFFFu; L.hitTri = 0xFFFFFFFFu; L.hitU = 0.f; L.hitV = 0.f;
+#endif
     stack[0] = kTraceDone; L.sp = 1;
 #if OKRT_STACK_TOPREG
     L.top = kTraceDone;
@@ -549,7 +573,7 @@ __device__ __forceinline__ void stepInit(const DeviceScene& s, StepLane& L, uint
     for (uint32_t i = 0; i < numSpheres; i++) {                /* RaytracerCS.hlsl:232-242 */
         const okrt_sphere& sp = s.spheres[i];
         const float t = rayAndSphere(o, d, v3(sp.position), sp.radius);
-        if (t > 0.f) stepCandidate(L, t, (1u << 30) | i, 0xFFFFFFFFu, 0.f, 0.f);
+        if (t > 0.f) stepCandidate(L, stack, t, (1u << 30) | i, 0xFFFFFFFFu, 0.f, 0.f);
     }
     stepEnter(L, s.topRef == kRefNone ? kTraceDone : s.topRef);
 }
@@ -622,7 +646,7 @@ __device__ __forceinline__ float rayAndTriangleEdges(V3 o, V3 d, V3 p2, V3 E1, V
 }
 
 /* one triangle of the leaf the lane stands on */
-__device__ __forceinline__ void stepTriangle(const DeviceScene& s, StepLane& L, const uint32_t* stack)
+__device__ __forceinline__ void stepTriangle(const DeviceScene& s, StepLane& L, uint32_t* stack)
 {
     const uint32_t j = L.triNext++;
     OKRT_CHECK(j < s.numTris);
@@ -646,7 +670,7 @@ __device__ __forceinline__ void stepTriangle(const DeviceScene& s, StepLane& L, 
             rec = L.inst;
         }
         t = length(w);
-        stepCandidate(L, t, (2u << 30) | rec, j, bu, bv);
+        stepCandidate(L, stack, t, (2u << 30) | rec, j, bu, bv);
     }
     const uint32_t end = (L.cur & (kMaxTriIndex - 1u)) + ((L.cur >> 27) & 7u) + 1u;
     if (L.triNext == end) stepPop(L, stack);
@@ -694,14 +718,22 @@ __device__ __forceinline__ void stepMisc(const DeviceScene& s, StepLane& L, uint
 
 /* the finished lane's hit; returns true when the reference order has to decide.  `L` stands at the top level
  * again (the exit marker of an instance restores the top ray), so L.ro is the world origin. */
-__device__ __forceinline__ bool stepResult(const DeviceScene& s, const StepLane& L, const float4* rayD, Hit& hit, float& seed)
+__device__ __forceinline__ bool stepResult(const DeviceScene& s, const StepLane& L, const uint32_t* stack, const float4* rayD, Hit& hit, float& seed)
 {
+#if OKRT_COLD_IN_LOCAL
+    const uint32_t hitRec = stack[kColdHitRec];
+    const float second = __uint_as_float(stack[kColdSecond]);
+    hit.tri = stack[kColdHitTri]; hit.u = __uint_as_float(stack[kColdHitU]); hit.v = __uint_as_float(stack[kColdHitV]);
+#else
+    const uint32_t hitRec = L.hitRec;
+    const float second = L.second;
+    hit.tri = L.hitTri; hit.u = L.hitU; hit.v = L.hitV;
+#endif
     seed = L.best;                                               /* the reference's answer lies inside the window above it */
     hit.distance = L.best;
-    hit.kind = L.best < OKRT_FLT_MAX ? (L.hitRec >> 30) : 0u;
-    hit.idx = hit.kind ? (L.hitRec & 0x3FFFFFFFu) : 0xFFFFFFFFu;
-    hit.tri = L.hitTri; hit.u = L.hitU; hit.v = L.hitV;
-    bool ambiguous = L.second < relaxedLimit(L.best);
+    hit.kind = L.best < OKRT_FLT_MAX ? (hitRec >> 30) : 0u;
+    hit.idx = hit.kind ? (hitRec & 0x3FFFFFFFu) : 0xFFFFFFFFu;
+    bool ambiguous = second < relaxedLimit(L.best);
     if (hit.kind == 2u) {
         const uint32_t rec = hit.idx;
         OKRT_CHECK(rec < s.numFastInstances);
@@ -727,7 +759,7 @@ __device__ __forceinline__ bool stepResult(const DeviceScene& s, const StepLane&
 /* whole-ray form, used by the megakernel: the same steps, one ray per thread */
 __device__ __forceinline__ bool traverseFast(const DeviceScene& s, uint32_t numSpheres, V3 o, V3 d, Hit& hit, float& seed)
 {
-    uint32_t stack[kFastStackCapacity];
+    uint32_t stack[kFastStackCapacity + kColdSlots];
     StepLane L;
     L.path = 0u;
     stepInit(s, L, stack, numSpheres, o, d);
@@ -738,7 +770,7 @@ __device__ __forceinline__ bool traverseFast(const DeviceScene& s, uint32_t numS
         else stepMisc(s, L, stack, o, d);
     }
     const float4 dd = make_float4(d.x, d.y, d.z, 0.f);
-    return stepResult(s, L, &dd, hit, seed);
+    return stepResult(s, L, stack, &dd, hit, seed);
 }
 
 /* ------------------------------------------------------------ hit resolve
