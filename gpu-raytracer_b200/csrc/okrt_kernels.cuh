@@ -480,7 +480,7 @@ constexpr uint32_t kTraceTop = 0xFFFFFFFFu;
 #define OKRT_STACK_TOPREG 0
 #endif
 #ifndef OKRT_COLD_IN_LOCAL
-#define OKRT_COLD_IN_LOCAL 0
+#define OKRT_COLD_IN_LOCAL 1
 #endif
 /* OKRT_COLD_IN_LOCAL: the lane's hit record (written once or twice per ray, read when the ray finishes) lives in the slots
  * behind the traversal stack instead of registers, which buys resident warps */
@@ -598,7 +598,10 @@ __device__ __forceinline__ bool boxPasses(V3 o, V3 idir, float4 lo, float4 hi, f
  * p must be 32-byte aligned. */
 __device__ __forceinline__ void ldg256(const float4* p, float4& a, float4& b)
 {
-    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+#ifndef OKRT_NODE_LD_HINT
+#define OKRT_NODE_LD_HINT ""
+#endif
+    asm("ld.global.nc" OKRT_NODE_LD_HINT ".v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                  : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
                  : "l"(p));
 }

@@ -39,9 +39,13 @@ struct WavefrontBuffers {
 };
 constexpr uint32_t kMaxWavefrontBounces = 63;
 constexpr uint32_t kMaxQueueCounts = 2 * (kMaxWavefrontBounces + 2);
-constexpr int kTraceBlockThreads = 128;
+#ifndef OKRT_TRACE_BLOCK_THREADS
+#define OKRT_TRACE_BLOCK_THREADS 128
+#endif
+constexpr int kTraceBlockThreads = OKRT_TRACE_BLOCK_THREADS;
 #ifndef OKRT_TRACE_MIN_BLOCKS
-#define OKRT_TRACE_MIN_BLOCKS 9          /* 56 registers, no spills: 36 warps per SM (8 blocks / 63 registers: -4.4 % rays/s) */
+#define OKRT_TRACE_MIN_BLOCKS 12         /* 40 registers, 48 warps per SM, the lane's hit record behind its stack (OKRT_COLD_IN_LOCAL):
+                                         * 8 blocks / 63 registers 2540, 9 / 56 2655, 10 / 48 2677, 12 / 40 2704, 16 / 32 2434 Mrays/s */
 #endif
 #ifndef OKRT_KEEP_RUNNING
 #define OKRT_KEEP_RUNNING 16
