@@ -170,10 +170,10 @@ traceFallbackKernel(const __grid_constant__ DeviceScene s, const __grid_constant
 #define OKRT_REFILL_IDLE 16         /* refill as soon as this many lanes have no ray */
 #endif
 #ifndef OKRT_NODE_KEEP
-#define OKRT_NODE_KEEP 8            /* stay in the node phase while at least this many lanes want a node step */
+#define OKRT_NODE_KEEP 6            /* stay in the node phase while at least this many lanes want a node step */
 #endif
 #ifndef OKRT_TRI_KEEP
-#define OKRT_TRI_KEEP 8             /* stay in the triangle phase while at least this many lanes want a triangle step */
+#define OKRT_TRI_KEEP 6             /* stay in the triangle phase while at least this many lanes want a triangle step */
 #endif
 __global__ void __launch_bounds__(kTraceBlockThreads, OKRT_TRACE_MIN_BLOCKS)
 traceFastKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ FrameParams fp, const WavefrontBuffers wb,
