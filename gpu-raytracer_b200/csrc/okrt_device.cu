@@ -381,15 +381,15 @@ int launchWavefront(okrt_renderer* r, const FrameParams& fpWhole, bool instrumen
     accumulateKernel<<<(unsigned)((slots + 127) / 128), 128, 0, r->stream>>>(fpWhole, r->wb);
     r->launches++;
     OKRT_CUDA(cudaGetLastError());
-    if (std::getenv("OKRT_DEBUG_COUNTS")) {          /* diagnostic: rays per bounce of this batch */
+    if (std::getenv("OKRT_DEBUG_COUNTS")) {          /* diagnostic: rays per bounce of this batch (of each half) */
         const FrameParams& fp = fpWhole;
-        for (int hh = 0; hh < halves; hh++) {
-        std::vector<uint32_t> h(kCountWords);
-        cudaMemcpyAsync(h.data(), wbH[hh].counts, kCountWords * sizeof(uint32_t), cudaMemcpyDeviceToHost, r->stream);
-        cudaStreamSynchronize(r->stream);
-        std::fprintf(stderr, "okrt: batch of %u frames, rays per bounce:", fpH[hh].batchFrames);
-        for (uint32_t b = 0; b <= fp.maxBounces; b++) std::fprintf(stderr, " %u(fb %u)", h[2 * b], h[kMaxQueueCounts + b]);
-        std::fprintf(stderr, "\n");
+        for (int half = 0; half < halves; half++) {
+            std::vector<uint32_t> h(kCountWords);
+            cudaMemcpyAsync(h.data(), wbH[half].counts, kCountWords * sizeof(uint32_t), cudaMemcpyDeviceToHost, r->stream);
+            cudaStreamSynchronize(r->stream);
+            std::fprintf(stderr, "okrt: batch of %u frames, rays per bounce:", fpH[half].batchFrames);
+            for (uint32_t b = 0; b <= fp.maxBounces; b++) std::fprintf(stderr, " %u(fb %u)", h[2 * b], h[kMaxQueueCounts + b]);
+            std::fprintf(stderr, "\n");
         }
 #ifdef OKRT_TRACE_STATS
         const unsigned traceGrid = traceGridH[0];
