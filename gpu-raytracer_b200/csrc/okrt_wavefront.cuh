@@ -50,7 +50,10 @@ constexpr int kTraceBlockThreads = OKRT_TRACE_BLOCK_THREADS;
 #ifndef OKRT_KEEP_RUNNING
 #define OKRT_KEEP_RUNNING 16
 #endif
-constexpr uint32_t kTraceChunk = 64;         /* rays a warp claims per atomic */
+#ifndef OKRT_TRACE_CHUNK
+#define OKRT_TRACE_CHUNK 64
+#endif
+constexpr uint32_t kTraceChunk = OKRT_TRACE_CHUNK;         /* rays a warp claims per atomic */
 
 
 /* ---------------------------------------------------------------- generate
@@ -172,6 +175,12 @@ traceFallbackKernel(const __grid_constant__ DeviceScene s, const __grid_constant
 #ifndef OKRT_NODE_KEEP
 #define OKRT_NODE_KEEP 6            /* stay in the node phase while at least this many lanes want a node step */
 #endif
+#ifndef OKRT_KEEP_CONST
+#define OKRT_KEEP_CONST 0           /* 1: compile-time keep thresholds (measured slower: the register allocation changes) */
+#endif
+#ifndef OKRT_TRI_FIRST
+#define OKRT_TRI_FIRST 0
+#endif
 #ifndef OKRT_TRI_KEEP
 #define OKRT_TRI_KEEP 6             /* stay in the triangle phase while at least this many lanes want a triangle step */
 #endif
@@ -264,9 +273,17 @@ traceFastKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ F
             continue;
         }
 
+#if OKRT_TRI_FIRST
+        if (nNode > nTri) {
+#else
         if (nNode >= nTri) {
+#endif
             /* ---- node phase */
+#if OKRT_KEEP_CONST
+            constexpr uint32_t keep = (uint32_t)OKRT_NODE_KEEP;
+#else
             const uint32_t keep = min((uint32_t)OKRT_NODE_KEEP, nNode);
+#endif
             do {
 #ifdef OKRT_TRACE_STATS
                 stNodeIters++; if ((L.cur & kRefTagMask) == kRefInterior) stNodeSteps++;
@@ -275,7 +292,11 @@ traceFastKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ F
             } while ((uint32_t)__popc(__ballot_sync(0xFFFFFFFFu, (L.cur & kRefTagMask) == kRefInterior)) >= keep);
         } else {
             /* ---- triangle phase */
+#if OKRT_KEEP_CONST
+            constexpr uint32_t keep = (uint32_t)OKRT_TRI_KEEP;
+#else
             const uint32_t keep = min((uint32_t)OKRT_TRI_KEEP, nTri);
+#endif
             do {
 #ifdef OKRT_TRACE_STATS
                 stTriIters++; if ((L.cur & kRefTagMask) == kRefTriLeaf) stTriSteps++;
