@@ -296,15 +296,18 @@ int launchWavefront(okrt_renderer* r, const FrameParams& fpWhole, bool instrumen
 #ifdef OKRT_TRACE_STATS
     OKRT_CUDA(cudaMemsetAsync(r->wb.traceStats, 0, 8 * (kMaxWavefrontBounces + 2) * sizeof(unsigned long long), r->stream));
 #endif
-    /* Optional (OKRT_DUAL_MIN_FRAMES=n, off by default): two halves of the batch on two streams, each its own chain
+    /* Optional (OKRT_DUAL_MIN_FRAMES=n; 0 = off): two halves of the batch on two streams, each its own chain
      * generate -> (trace, fallback, shade) x bounces over its own slice of the path state, so that kernel tails, the
      * fallback launches and the launch gaps of one half are filled by the other half's kernels (every kernel pulls its
      * work from a device counter, so it makes progress with whatever share of the machine it gets).  The frames are
      * still added to u1 in frame order by ONE accumulateKernel over both slices, so results do not change (GPU parity
-     * suite green with it).  Measured +2.1 % (2541 -> 2595 Mrays/s, profiles/r1_k_experiments.txt); off by default
+     * suite green with it).  Measured +2.1 % (2541 -> 2595 Mrays/s, profiles/r1_k_experiments.txt); off by default on a single GPU
      * because the CUDA-event pairs around the traversal launches then overlap with the other half's kernels and the
      * per-kernel time bench.py's roofline is built on loses its meaning. */
-    static const int dualMin = [] { const char* e = std::getenv("OKRT_DUAL_MIN_FRAMES"); return e ? std::atoi(e) : 0; }();
+    static const int dualEnv = [] { const char* e = std::getenv("OKRT_DUAL_MIN_FRAMES"); return e ? std::atoi(e) : -1; }();
+    /* default: on for a tile-sharded rank (its kernels are small, tails and launch gaps weigh most there: 8 GPUs
+     * 19 667 -> 20 102 Mrays/s device-timed, 15 408 -> 16 054 end to end), off on a single GPU (see above) */
+    const int dualMin = dualEnv >= 0 ? dualEnv : (fpWhole.shardCount > 1u ? 2 : 0);
     const bool dual = !instrumented && fpWhole.traversal != OKRT_TRAVERSAL_EXACT && dualMin > 0 && fpWhole.batchFrames >= (uint32_t)dualMin &&
                       fpWhole.batchFrames >= 2u && r->stream2 != nullptr;
     const int halves = dual ? 2 : 1;
