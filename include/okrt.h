@@ -19,7 +19,8 @@
  * Map(WRITE_DISCARD)+memcpy, source/DirectX/DX11.cpp:104-156).
  * Errors: every call returns an int status (0 = OKRT_OK); the library never
  * aborts (reference: OKAY_ASSERT + bool, source/Utilities.h:12).
- * Threading: one host thread per renderer handle; one CUDA stream per handle;
+ * Threading: one host thread per renderer handle; one CUDA stream per handle
+ * (internal helper streams fork from and join it inside a call);
  * `okrt_render*` is asynchronous, `okrt_sync`/`okrt_read_*` synchronise.
  */
 #ifndef OKRT_H
