@@ -94,7 +94,14 @@ generateKernel(const __grid_constant__ FrameParams fp, const WavefrontBuffers wb
     const V3 target = mulPoint(pos, rd.cameraInverseProjectionMatrix);
     V3 o = v3(rd.cameraPosition);
     V3 d = mulDir(normalize(v3(target.x / target.z, target.y / target.z, target.z / target.z)), rd.cameraInverseViewMatrix);
-    const V2 jit = randomPointInCircle(seed);
+    /* applyDOF with dofStrength == 0: the disc sample is multiplied by zero, so the offset is (+-0, +-0, +-0) and
+     * o + offset == o bit for bit unless a camera coordinate is -0.0f (-0 + +0 = +0) — then, and for every non-zero
+     * strength, the full sample is evaluated.  The two RNG draws happen either way (the seed must advance). */
+    V2 jit;
+    const bool plainZeroOffset = rd.dofStrength == 0.f && __float_as_uint(rd.cameraPosition[0]) != 0x80000000u &&
+                                 __float_as_uint(rd.cameraPosition[1]) != 0x80000000u && __float_as_uint(rd.cameraPosition[2]) != 0x80000000u;
+    if (plainZeroOffset) { (void)randomFloat(seed); (void)randomFloat(seed); jit.x = 0.f; jit.y = 0.f; }
+    else jit = randomPointInCircle(seed);
     const float jx = jit.x * rd.dofStrength, jy = jit.y * rd.dofStrength;
     const V3 rayOffset = v3(rd.cameraRightDir) * jx + v3(rd.cameraUpDir) * jy;
     const V3 focusPoint = o + d * (rd.dofDistance + rd.cameraNearZ);
