@@ -192,3 +192,20 @@ def test_layout_report_and_oversized_leaves(okrt):
     flat = report(helpers.build_host_side(okrt, rm, sc, dict(info, bvh=(1, 1)), 64, 36))
     assert flat["numFlattenedLeaves"] == 3                      # three meshes, each a single leaf
     assert flat["fastStackDepth"] <= 16, int(flat["fastStackDepth"])
+
+
+def test_layout_build_is_deterministic(okrt):
+    """The scene-wide tree is built on several host threads (subtrees of large ranges, okrt_accel.cpp): the result must
+    not depend on their timing — same node count, stack need and area cost on every run."""
+    import sys
+    from tests import helpers
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
+    from layout_report import report
+    rm, sc, info = okrt.scenes.sponza_standin(60000, texture_size=16)
+    host = helpers.build_host_side(okrt, rm, sc, info, 64, 36)
+    runs = [report(host) for _ in range(3)]
+    keys = ("numPairNodes", "numFlattenedLeaves", "numMergedInstances", "fastStackDepth", "sahCost")
+    first = tuple(runs[0][k] for k in keys)
+    assert first[0] > 10000                                       # large enough for the parallel subtree path (ranges > 8192)
+    for r in runs[1:]:
+        assert tuple(r[k] for k in keys) == first
