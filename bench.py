@@ -44,7 +44,7 @@ def workload_config(n_gpus):
 
 
 def build_scene(okrt):
-    from tests import helpers
+    helpers = okrt.harness
     rm, sc, info = okrt.scenes.sponza_standin()
     host = helpers.build_host_side(okrt, rm, sc, info, WIDTH, HEIGHT)
     env = okrt.scenes.procedural_sky_faces(512)
@@ -111,9 +111,9 @@ def algorithmic_bytes_per_segment(visits, pixels_frames):
 
 def cpu_baseline_sample(okrt, host, env, threads=0):
     """The oracle (kind "port": scalar restatement of the HLSL) on one full 1080p frame, 1 spp, all host threads."""
-    from tests import helpers, oracle_binding
+    from oracle import binding as oracle_binding
     oracle = oracle_binding.load()
-    scene = helpers.oracle_scene(oracle, host, envFaces=env)
+    scene = oracle_binding.oracle_scene(oracle, host, envFaces=env)
     rd = host["rd"].copy()
     rd[0]["numAccumulationFrames"] = 1
     t0 = time.perf_counter()
@@ -131,10 +131,10 @@ def run_reference_arm(args):
     if rank != 0:
         return
     okrt = importlib.import_module("gpu-raytracer_b200")
-    from tests import helpers, oracle_binding
+    from oracle import binding as oracle_binding
     oracle = oracle_binding.load()
     host, env, info = build_scene(okrt)
-    scene = helpers.oracle_scene(oracle, host, envFaces=env)
+    scene = oracle_binding.oracle_scene(oracle, host, envFaces=env)
     rd = host["rd"].copy()
     rows = np.array([y for y in range(HEIGHT) if (y // 8) % 8 == 0], np.uint32)     # every 8th 8-row band: 1/8 of the frame
     cores = os.cpu_count() or 1
@@ -185,7 +185,7 @@ def main():
 
     okrt = importlib.import_module("gpu-raytracer_b200")
     abi = okrt.abi
-    from tests import helpers
+    helpers = okrt.harness
     if abi.lib().okrt_device_count() <= 0:
         raise SystemExit("bench.py: no CUDA device visible; the product path has no CPU fallback")
 

@@ -10,3 +10,4 @@ from .raytracer import environmentCrossToFaces, scaleTexturesToArray            
 from .raytracer import loadObjects, ObjectDescription                           # noqa: F401
 from . import scenes                           # noqa: F401
 from . import sharding                         # noqa: F401
+from . import harness                          # noqa: F401

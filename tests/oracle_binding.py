@@ -1,176 +1,3 @@
-"""ctypes binding of the CPU oracle (oracle/_build/libokrt_oracle.so) and of the compiled reference
-(oracle/_ref/libokrt_ref.so).  TEST INFRASTRUCTURE: imported only by tests/, __graft_entry__.smoke() and
-bench.py's CPU-baseline legs."""
-import ctypes
-import os
-import subprocess
-
-import numpy as np
-
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-ORACLE_DIR = os.path.join(ROOT, "oracle")
-ORACLE_LIB = os.path.join(ORACLE_DIR, "_build", "libokrt_oracle.so")
-REF_LIB = os.path.join(ORACLE_DIR, "_ref", "libokrt_ref.so")
-
-MATH_CANONICAL, MATH_LIBM = 0, 1
-
-
-class OracleScene(ctypes.Structure):
-    _fields_ = [(n, ctypes.c_void_p) for n in ("triPos", "triInfo", "bvhNodes", "textures", "envFaces", "octNodes", "spheres",
-                                              "meshes", "dirLights", "pointLights", "spotLights")] + \
-               [(n, ctypes.c_uint32) for n in ("numTris", "numBvhNodes", "texSize", "texLayers", "envW", "envH", "numOctNodes",
-                                              "numSpheres", "numMeshes", "numDirLights", "numPointLights", "numSpotLights")]
-
-
-def build_oracle(force=False):
-    srcs = [os.path.join(ORACLE_DIR, f) for f in ("okrt_oracle.cpp", "oracle_math.h")]
-    stale = force or not os.path.exists(ORACLE_LIB) or any(os.path.getmtime(s) > os.path.getmtime(ORACLE_LIB) for s in srcs)
-    if stale:
-        subprocess.run(["make", "-s", "-C", ORACLE_DIR, "oracle"], check=True)
-    return ORACLE_LIB
-
-
-def build_ref():
-    """Compiles the reference's BvhBuilder.cpp where /root/reference exists; otherwise keeps the prebuilt file."""
-    if os.path.exists("/root/reference/source/Graphics/BvhBuilder.cpp"):
-        shim = os.path.join(ORACLE_DIR, "ref_shim.cpp")
-        if not os.path.exists(REF_LIB) or os.path.getmtime(shim) > os.path.getmtime(REF_LIB):
-            subprocess.run(["make", "-s", "-C", ORACLE_DIR, "ref"], check=True)
-    return REF_LIB if os.path.exists(REF_LIB) else None
-
-
-_P, _U, _I, _F = ctypes.c_void_p, ctypes.c_uint32, ctypes.c_int, ctypes.c_float
-
-
-class Oracle:
-    def __init__(self, lib):
-        self.lib = lib
-        lib.oracle_render.restype = _U
-        lib.oracle_render.argtypes = [ctypes.POINTER(OracleScene), _P, _U, _U, _U, _P, _P, _P, _U, _U, _I, _I, ctypes.POINTER(ctypes.c_uint64)]
-        lib.oracle_render_rows.restype = _U
-        lib.oracle_render_rows.argtypes = [ctypes.POINTER(OracleScene), _P, _U, _U, _U, _P, _P, _P, _P, _U, _I, _I, ctypes.POINTER(ctypes.c_uint64)]
-        lib.oracle_last_visit_totals.restype = None
-        lib.oracle_last_visit_totals.argtypes = [_P]
-        lib.oracle_pcg_hash.restype = _U
-        lib.oracle_pcg_hash.argtypes = [ctypes.POINTER(_U)]
-        lib.oracle_random_float.restype = _F
-        lib.oracle_random_float.argtypes = [ctypes.POINTER(_U)]
-        lib.oracle_ray_triangle.restype = _F
-        lib.oracle_ray_triangle.argtypes = [_P] * 6
-        lib.oracle_ray_aabb_dist.restype = _F
-        lib.oracle_ray_aabb_dist.argtypes = [_P] * 4
-        lib.oracle_ray_sphere.restype = _F
-        lib.oracle_ray_sphere.argtypes = [_P, _P, _P, _F]
-        lib.oracle_math_eval.restype = None
-        lib.oracle_math_eval.argtypes = [_I, _P, _P, _P, _U]
-        lib.oracle_sample_texture.restype = None
-        lib.oracle_sample_texture.argtypes = [ctypes.POINTER(OracleScene), _U, _F, _F, _P]
-        lib.oracle_sample_environment.restype = None
-        lib.oracle_sample_environment.argtypes = [ctypes.POINTER(OracleScene), _P, _P]
-        lib.oracle_build_bvh.restype = _U
-        lib.oracle_build_bvh.argtypes = [_P, _U, _P, _P, _U, _U, _P, _P]
-        lib.oracle_transform_matrix.restype = None
-        lib.oracle_transform_matrix.argtypes = [_P, _P, _P, _P]
-        lib.oracle_calculate_projection_data.restype = None
-        lib.oracle_calculate_projection_data.argtypes = [_P, _P, _F, _F, _F, _U, _U, _P]
-        lib.oracle_build_octree.restype = _U
-        lib.oracle_build_octree.argtypes = [_P, _P, _U, _P, _U, _P, _U, _U, _U, _P, _U, _P, ctypes.POINTER(_U)]
-        lib.oracle_texture_array_size.restype = _U
-        lib.oracle_texture_array_size.argtypes = [_P, _P, _U]
-        lib.oracle_scale_texture.restype = None
-        lib.oracle_scale_texture.argtypes = [_P, _U, _U, _P, _U, _U]
-        lib.oracle_environment_cross_to_faces.restype = None
-        lib.oracle_environment_cross_to_faces.argtypes = [_P, _U, _U, _P]
-
-    # ---- helpers over numpy arrays (dtypes from the product's _abi module are byte-compatible) ----
-    @staticmethod
-    def _p(a):
-        return None if a is None or len(a) == 0 else a.ctypes.data_as(ctypes.c_void_p)
-
-    def make_scene(self, triPos, triInfo, bvhNodes, octNodes, instances, spheres=None, textures=None, envFaces=None,
-                   dirLights=None, pointLights=None, spotLights=None):
-        keep = dict(triPos=triPos, triInfo=triInfo, bvhNodes=bvhNodes, octNodes=octNodes, instances=instances, spheres=spheres,
-                    textures=textures, envFaces=envFaces, dirLights=dirLights, pointLights=pointLights, spotLights=spotLights)
-        s = OracleScene()
-        s.triPos, s.triInfo, s.bvhNodes = self._p(triPos), self._p(triInfo), self._p(bvhNodes)
-        s.octNodes, s.meshes, s.spheres = self._p(octNodes), self._p(instances), self._p(spheres)
-        s.textures = self._p(textures.reshape(-1)) if textures is not None and textures.size else None
-        s.envFaces = self._p(envFaces.reshape(-1)) if envFaces is not None and envFaces.size else None
-        s.dirLights, s.pointLights, s.spotLights = self._p(dirLights), self._p(pointLights), self._p(spotLights)
-        s.numTris, s.numBvhNodes, s.numOctNodes = len(triPos), len(bvhNodes), len(octNodes)
-        s.numMeshes = len(instances)
-        s.numSpheres = 0 if spheres is None else len(spheres)
-        s.numDirLights = 0 if dirLights is None else len(dirLights)
-        s.numPointLights = 0 if pointLights is None else len(pointLights)
-        s.numSpotLights = 0 if spotLights is None else len(spotLights)
-        if textures is not None and textures.size:
-            s.texLayers, s.texSize = textures.shape[0], textures.shape[1]
-        if envFaces is not None and envFaces.size:
-            s.envH, s.envW = envFaces.shape[1], envFaces.shape[2]
-        s._keep = keep
-        return s
-
-    def render(self, scene, rd, maxBounces, seedFrame=None, coverAll=0, accum=None, result=None, aov_dtype=None,
-               rows=None, threads=0, math=MATH_CANONICAL, row_list=None):
-        """One frame.  rd: 1-element RENDER_DATA array.  Returns dict(accum, result, aov, segments, overflow)."""
-        W, H = int(rd[0]["textureDims"][0]), int(rd[0]["textureDims"][1])
-        if accum is None:
-            accum = np.zeros((H, W, 4), np.float32)
-        if result is None:
-            result = np.zeros((H, W, 4), np.uint8)
-        aov = np.zeros((H, W), aov_dtype) if aov_dtype is not None else None
-        seg = ctypes.c_uint64(0)
-        if seedFrame is None:
-            seedFrame = int(rd[0]["numAccumulationFrames"])
-        if row_list is not None:
-            rl = np.ascontiguousarray(row_list, np.uint32)
-            ovf = self.lib.oracle_render_rows(ctypes.byref(scene), rd.ctypes.data_as(_P), maxBounces, seedFrame, coverAll,
-                                              accum.ctypes.data_as(_P), result.ctypes.data_as(_P),
-                                              None if aov is None else aov.ctypes.data_as(_P), rl.ctypes.data_as(_P), len(rl), threads, math, ctypes.byref(seg))
-        else:
-            y0, y1 = (0, H) if rows is None else rows
-            ovf = self.lib.oracle_render(ctypes.byref(scene), rd.ctypes.data_as(_P), maxBounces, seedFrame, coverAll,
-                                         accum.ctypes.data_as(_P), result.ctypes.data_as(_P),
-                                         None if aov is None else aov.ctypes.data_as(_P), y0, y1, threads, math, ctypes.byref(seg))
-        v = np.zeros(7, np.uint64)
-        self.lib.oracle_last_visit_totals(v.ctypes.data_as(_P))
-        visits = dict(zip(("segments", "octNodes", "instances", "bvhNodes", "triangles", "hits", "textureTaps"), (int(x) for x in v)))
-        return dict(accum=accum, result=result, aov=aov, segments=seg.value, overflow=ovf, visits=visits)
-
-
-_oracle = None
-
-
-def load():
-    global _oracle
-    if _oracle is None:
-        _oracle = Oracle(ctypes.CDLL(build_oracle()))
-    return _oracle
-
-
-_ref = None
-
-
-def load_ref():
-    global _ref
-    if _ref is None:
-        path = build_ref()
-        if path is None:
-            return None
-        lib = ctypes.CDLL(path)
-        lib.ref_build_bvh.restype = _U
-        lib.ref_build_bvh.argtypes = [_P, _U, _P, _P, _U, _U, _P, _U, _P]
-        lib.ref_transform_matrices.restype = None
-        lib.ref_transform_matrices.argtypes = [_P] * 5
-        lib.ref_projection_data.restype = None
-        lib.ref_projection_data.argtypes = [_P, _P, _F, _F, _F, _U, _U, _P, _P, _P, _P, _P]
-        lib.ref_aabb_area.restype = _F
-        lib.ref_aabb_area.argtypes = [_P, _P]
-        lib.ref_aabb_intersects.restype = _I
-        lib.ref_aabb_intersects.argtypes = [_P] * 4
-        lib.ref_struct_sizes.restype = None
-        lib.ref_struct_sizes.argtypes = [_P]
-        lib.ref_material_default.restype = None
-        lib.ref_material_default.argtypes = [_P]
-        _ref = lib
-    return _ref
+"""Kept for the tests' imports: the binding lives with the oracle (oracle/binding.py)."""
+from oracle.binding import *  # noqa: F401,F403
+from oracle.binding import load, load_ref, build_oracle, build_ref, MATH_CANONICAL, MATH_LIBM  # noqa: F401

@@ -13,10 +13,10 @@ pytestmark = pytest.mark.gpu
 @pytest.fixture(autouse=True, params=[0, 1], ids=["wavefront", "megakernel"])
 def pipeline(request):
     """Every parity test runs through both kernel organisations; they must agree with the oracle bit for bit."""
-    old = helpers.DEFAULT_PIPELINE
-    helpers.DEFAULT_PIPELINE = request.param
+    old = helpers.harness.DEFAULT_PIPELINE
+    helpers.harness.DEFAULT_PIPELINE = request.param
     yield request.param
-    helpers.DEFAULT_PIPELINE = old
+    helpers.harness.DEFAULT_PIPELINE = old
 
 
 def _require_gpu(okrt):

@@ -11,7 +11,7 @@ import numpy as np
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 okrt = importlib.import_module("gpu-raytracer_b200")
-from tests import helpers  # noqa: E402
+import importlib; helpers = importlib.import_module("gpu-raytracer_b200.harness")  # noqa: E402
 
 
 def main():

@@ -5,7 +5,7 @@ sys.path.insert(0, ROOT)
 import numpy as np
 okrt = importlib.import_module("gpu-raytracer_b200")
 abi = okrt.abi
-from tests import helpers
+import importlib; helpers = importlib.import_module("gpu-raytracer_b200.harness")
 import bench
 host, env, info = bench.build_scene(okrt)
 r = helpers.Renderer(okrt, host, bench.WIDTH, bench.HEIGHT, envFaces=env)

@@ -41,7 +41,7 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     okrt = importlib.import_module("gpu-raytracer_b200")
     abi = okrt.abi
-    from tests import helpers
+    import importlib; helpers = importlib.import_module("gpu-raytracer_b200.harness")
     W, H = args.width, args.height
     assert args.spp % world == 0 and args.check_spp % world == 0, "frames must split evenly over the ranks"
 
