@@ -531,3 +531,99 @@ def sponza_standin(target_triangles=262_267, seed=11, texture_size=1024):
     info = dict(name="sponza", stand_in=True, octree=(2, 50), bvh=(30, 5), triangles=total, entities=len(parts),
                 note="procedural Sponza-class stand-in: sponza.obj is listed in .MISSING_LARGE_BLOBS")
     return rm, sc, info
+
+
+# ------------------------------------------------------------------ adversarial scenes (differential stress test)
+def _flat_grid(p0, du, dv, nu, nv):
+    """nu x nv grid of exactly planar quads spanned by du, dv from p0 (float64 lattice, then float32 at upload)."""
+    p0, du, dv = np.asarray(p0, float), np.asarray(du, float), np.asarray(dv, float)
+    i, j = np.meshgrid(np.arange(nu), np.arange(nv), indexing="ij")
+    i, j = i.ravel()[:, None], j.ravel()[:, None]
+    a = p0 + du * (i / nu) + dv * (j / nv)
+    b = p0 + du * ((i + 1) / nu) + dv * (j / nv)
+    c = p0 + du * ((i + 1) / nu) + dv * ((j + 1) / nv)
+    d = p0 + du * (i / nu) + dv * ((j + 1) / nv)
+    return np.concatenate([np.stack([a, b, c], 1), np.stack([a, c, d], 1)])
+
+
+def adversarial_scene(kind, offset=(0.0, 0.0, 0.0), seed=5):
+    """Scenes built to break a near-first traversal that is not really order independent (tests/test_gpu_stress.py):
+
+    flat_room  axis-aligned, exactly planar floors / walls / boxes cut into many triangles: every leaf box is flat and its
+               triangles lie IN a box face; lots of corners, so bounce segments with t ~ 1e-3 next to large surfaces
+    layers     stacks of coplanar sheets 1e-7 ... 1e-4 apart (decals), straight and tilted, in different meshes and leaves
+    slivers    fans of long needle triangles (aspect 1e2 ... 1e5) in front of a wall
+    contact    one 4000-unit ground quad (two huge triangles) touched by finely tessellated spheres: tiny triangles against
+               huge ones along the contact curves
+    `offset` translates the whole scene (vertices and camera): 1e3 / 1e4 leave 2^-14 / 2^-10 of absolute resolution."""
+    rng = np.random.default_rng(seed)
+    rm, sc = ResourceManager(), Scene()
+    off = np.asarray(offset, float)
+
+    def add(pos, m, name):
+        pos = np.asarray(pos, float).reshape(-1, 3, 3) + off
+        sc.addMeshEntity(rm.addMesh(make_mesh(pos, name=name)), m)
+
+    grey = material(albedo=(0.75, 0.75, 0.7))
+    lamp = material(albedo=(0, 0, 0), emissionColour=(1.0, 0.9, 0.8), emissionPower=3.0)
+    mirror = material(albedo=(0.9, 0.9, 0.9), metallic=1.0, roughness=0.05)
+    if kind == "flat_room":
+        L = 16.0
+        faces = [((-L, 0, -L), (2 * L, 0, 0), (0, 0, 2 * L)), ((-L, 12, -L), (0, 0, 2 * L), (2 * L, 0, 0)),
+                 ((-L, 0, -L), (0, 12, 0), (2 * L, 0, 0)), ((-L, 0, L), (2 * L, 0, 0), (0, 12, 0)),
+                 ((-L, 0, -L), (0, 0, 2 * L), (0, 12, 0)), ((L, 0, -L), (0, 12, 0), (0, 0, 2 * L))]
+        for k, (p0, du, dv) in enumerate(faces):
+            add(_flat_grid(p0, du, dv, 24, 24), lamp if k == 1 else grey, "room_face_%d" % k)
+        for k in range(24):                                     # boxes standing on the floor, touching walls and each other
+            w = rng.integers(1, 4, 3).astype(float)
+            x, z = float(rng.integers(-14, 12)), float(rng.integers(-14, 12))
+            lo, hi = np.array([x, 0.0, z]), np.array([x + w[0], w[1], z + w[2]])
+            tris = []
+            for p0, du, dv in (((lo[0], lo[1], lo[2]), (hi[0] - lo[0], 0, 0), (0, hi[1] - lo[1], 0)), ((lo[0], lo[1], hi[2]), (hi[0] - lo[0], 0, 0), (0, hi[1] - lo[1], 0)),
+                               ((lo[0], lo[1], lo[2]), (0, 0, hi[2] - lo[2]), (0, hi[1] - lo[1], 0)), ((hi[0], lo[1], lo[2]), (0, 0, hi[2] - lo[2]), (0, hi[1] - lo[1], 0)),
+                               ((lo[0], hi[1], lo[2]), (hi[0] - lo[0], 0, 0), (0, 0, hi[2] - lo[2])), ((lo[0], lo[1], lo[2]), (hi[0] - lo[0], 0, 0), (0, 0, hi[2] - lo[2]))):
+                tris.append(_flat_grid(p0, du, dv, 3, 3))
+            add(np.concatenate(tris), mirror if k % 5 == 0 else grey, "box_%d" % k)
+        sc.setCamera(tuple(np.array([0.5, 5.0, -14.5]) + off), (8.0, 10.0, 0.0), 90.0, 0.1)
+    elif kind == "layers":
+        add(_flat_grid((-30, -10, 30), (60, 0, 0), (0, 40, 0), 8, 8), lamp, "back_wall")
+        add(_flat_grid((-30, -10, -30), (60, 0, 0), (0, 0, 60), 8, 8), grey, "floor")
+        k = 0
+        for gap in (1e-7, 1e-6, 1e-5, 1e-4):
+            for tilt in (0.0, 0.37):
+                c, s = np.cos(tilt), np.sin(tilt)
+                x0 = -24.0 + 6.0 * k
+                for layer in range(4):                          # four sheets `gap` apart along their common normal
+                    n = np.array([s, 0.0, -c]) * gap * layer
+                    p0 = np.array([x0, -6.0, 10.0 + 0.5 * k]) + n
+                    m = material(albedo=tuple(rng.uniform(0.2, 0.9, 3)), roughness=float(rng.uniform(0.1, 1.0)), metallic=float(layer % 2))
+                    add(_flat_grid(p0, (5.0 * c, 0, 5.0 * s), (0, 14.0, 0), 3 + layer, 5 + layer), m, "sheet_%d_%d" % (k, layer))
+                k += 1
+        sc.setCamera(tuple(np.array([0.0, 2.0, -14.0]) + off), (0.0, 0.0, 0.0), 90.0, 0.1)
+    elif kind == "slivers":
+        add(_flat_grid((-40, -20, 25), (80, 0, 0), (0, 60, 0), 4, 4), lamp, "back_wall")
+        add(_flat_grid((-40, -8, -30), (80, 0, 0), (0, 0, 60), 4, 4), grey, "floor")
+        tris = []
+        for k in range(6000):
+            c = np.array([rng.uniform(-18, 18), rng.uniform(-6, 14), rng.uniform(4, 18)])
+            d = rng.normal(0, 1, 3)
+            d /= np.linalg.norm(d)
+            e = np.cross(d, rng.normal(0, 1, 3))
+            e /= np.linalg.norm(e)
+            length, width = rng.uniform(4, 40), 10.0 ** rng.uniform(-4, -0.5)
+            tris.append([c - d * length * 0.5, c + d * length * 0.5, c + e * width])
+        add(np.array(tris), mirror, "needles")
+        sc.setCamera(tuple(np.array([0.0, 3.0, -16.0]) + off), (0.0, 0.0, 0.0), 90.0, 0.1)
+    elif kind == "contact":
+        add(_flat_grid((-2000, 0, -2000), (4000, 0, 0), (0, 0, 4000), 1, 1), grey, "ground")
+        for k in range(9):
+            r = 1.0 + 0.5 * (k % 3)
+            c = np.array([-9.0 + 4.5 * (k % 5), r - (0.0, 1e-3, 0.05)[k % 3], 2.0 + 5.0 * (k // 5)])
+            p, _, _ = icosphere(5, r, c)
+            add(p, mirror if k % 2 else material(albedo=tuple(rng.uniform(0.3, 0.9, 3))), "ball_%d" % k)
+        add(_flat_grid((-30, 30, -30), (0, 0, 60), (60, 0, 0), 2, 2), lamp, "sky_panel")
+        sc.setCamera(tuple(np.array([0.0, 1.2, -9.0]) + off), (5.0, 0.0, 0.0), 90.0, 0.1)
+    else:
+        raise ValueError(kind)
+    info = dict(name="adversarial_" + kind, stand_in=False, octree=(2, 50), bvh=(30, 5), offset=tuple(offset))
+    return rm, sc, info

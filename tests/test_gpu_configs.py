@@ -1,7 +1,7 @@
 """BASELINE.json configs[1], [2] and [4] on the GPU: the dragon-class mesh (metallic, env-lit, 4 bounces), the
 glass scene (transparency 1, IOR 1.5, 16 bounces: refraction and specular-probability paths) and the 4K
-sample-sharded progressive mode.  Small sizes are compared with the oracle bit for bit; the full sizes of the
-configs are checked through the oracle's primary rays and through size-independent properties."""
+sample-sharded progressive mode.  Small sizes and the full 1920x1080 sizes of configs[1] and [2] are compared with the oracle bit for bit (whole
+accumulation image); the 4K sample-sharded mode through its size-independent properties."""
 import numpy as np
 import pytest
 
@@ -64,33 +64,47 @@ def test_config3_real_glass_mesh_bit_exact(okrt, oracle):
     _bit_exact_against_oracle(okrt, oracle, rm, sc, info, 320, 180, 16, okrt.scenes.procedural_sky_faces(64), pipelines=(0,))
 
 
-def test_config2_full_size_dragon(okrt, oracle):
-    """configs[1] at full size: 871k triangles, 1920x1080, 4 bounces.  Primary rays equal the oracle's bit for bit;
-    the two pipelines and the two traversal orders agree on the 4-bounce image."""
-    rm, sc, info = okrt.scenes.dragon_scene()
+def _full_size_against_oracle(okrt, oracle, rm, sc, info, bounces, env, variants):
+    """One 1920x1080 frame at the config's bounce count: the whole RGBA32F accumulation image and the segment count
+    equal the oracle's, bit for bit, for every (pipeline, traversal) in `variants`."""
     W, H = 1920, 1080
-    env = okrt.scenes.procedural_sky_faces(256)
     host = helpers.build_host_side(okrt, rm, sc, info, W, H)
-    r = helpers.Renderer(okrt, host, W, H, envFaces=env)
-    r.options(maxBounces=0, writeAov=1)
-    r.render(host["rd"].copy())
-    g = r.aov()
-    o = oracle.render(helpers.oracle_scene(oracle, host, envFaces=env), _frame1(host["rd"]), 0, aov_dtype=okrt.abi.AOV)
-    assert np.array_equal(g["triIdx"], o["aov"]["triIdx"])
-    for f in ("baryU", "baryV", "distance"):
-        assert np.array_equal(g[f].view(np.uint32), o["aov"][f].view(np.uint32))
-    r.close()
-    outs = []
-    for pipeline, traversal in ((0, 0), (1, 0), (0, 1)):
+    o = oracle.render(helpers.oracle_scene(oracle, host, envFaces=env), _frame1(host["rd"]), bounces, aov_dtype=okrt.abi.AOV)
+    for pipeline, traversal in variants:
         r = helpers.Renderer(okrt, host, W, H, envFaces=env)
-        r.options(maxBounces=4, pipeline=pipeline, traversal=traversal)
-        r.render(host["rd"].copy(), frames=2)
+        r.options(maxBounces=bounces, pipeline=pipeline, traversal=traversal, writeAov=1 if (pipeline, traversal) == variants[0] else 0)
+        r.render(host["rd"].copy())
+        if (pipeline, traversal) == variants[0]:
+            g = r.aov()
+            assert np.array_equal(g["triIdx"], o["aov"]["triIdx"])
+            for f in ("baryU", "baryV", "distance"):
+                assert np.array_equal(g[f].view(np.uint32), o["aov"][f].view(np.uint32)), f
+        acc = r.accumulation()
         st = r.stats()
-        outs.append((r.accumulation(), int(st["raySegments"]), int(st["fallbackSegments"])))
         r.close()
-    for acc, seg, fb in outs[1:]:
-        assert np.array_equal(acc.view(np.uint32), outs[0][0].view(np.uint32)) and seg == outs[0][1]
-    assert outs[0][2] < 0.001 * outs[0][1]
+        bad = np.any(acc.view(np.uint32) != o["accum"].view(np.uint32), axis=2)
+        assert not bad.any(), "pipeline %d traversal %d: %d pixels differ from the oracle" % (pipeline, traversal, int(bad.sum()))
+        assert int(st["raySegments"]) == o["segments"]
+        assert int(st["fallbackSegments"]) < 0.01 * o["segments"]
+    return o
+
+
+def test_config2_full_size_dragon(okrt, oracle):
+    """configs[1] at full size: 871k triangles, 1920x1080, 4 bounces, against the oracle (primary AOVs and the image)."""
+    rm, sc, info = okrt.scenes.dragon_scene()
+    _full_size_against_oracle(okrt, oracle, rm, sc, info, 4, okrt.scenes.procedural_sky_faces(256), ((0, 0), (1, 0), (0, 1)))
+
+
+def test_config3_full_size_glass(okrt, oracle):
+    """configs[2] at full size: the reference's ikea_glass.obj (fixture), scale 10, 1920x1080, 16 bounces, against the oracle."""
+    import os
+    path = os.path.join(os.path.dirname(__file__), "golden", "ikea_glass_mesh.npz")
+    if os.path.exists(path):
+        rm, sc, info = okrt.scenes.glass_scene_from_fixture(path)
+    else:
+        rm, sc, info = okrt.scenes.glass_scene()
+    o = _full_size_against_oracle(okrt, oracle, rm, sc, info, 16, okrt.scenes.procedural_sky_faces(256), ((0, 0), (0, 1)))
+    assert int(o["aov"]["numSegments"].max()) >= 5
 
 
 def test_config5_4k_sample_sharded(okrt):
