@@ -165,6 +165,8 @@ SYMBOLS = [
     ("okrt_shard_seed_frame", _U, [_P, _U, _U]),
     ("okrt_get_stats", _I, [_P, _P]),
     ("okrt_reset_stats", _I, [_P]),
+    ("okrt_get_trace_stats", _I, [_P, _P, _U]),
+    ("okrt_trace_rays_host", _I, [_P, _U, _P, _U, _P, _U, _P, _U, _P, _U, _P]),
 ]
 
 

@@ -114,8 +114,10 @@ struct Builder {
 };
 
 /* explicit node of the scene-wide tree while it is built and optimised; a leaf has left < 0 and carries `ref` */
-struct TopNode { double lo[3], hi[3]; int32_t left = -1, right = -1, parent = -1; uint32_t ref = kRefNone; };
-struct TopLeaf { double lo[3], hi[3]; uint32_t ref; uint32_t weight; };   /* weight: triangles below (SAH cost) */
+/* wide-layout payload of a leaf: triangles [wstart, wstart + wcount) of a reference leaf and its slack, or (wcount == 0) the
+ * instance record wstart */
+struct TopNode { double lo[3], hi[3]; int32_t left = -1, right = -1, parent = -1; uint32_t ref = kRefNone; uint32_t wstart = 0, wcount = 0; float slack = 0.f; };
+struct TopLeaf { double lo[3], hi[3]; uint32_t ref; uint32_t weight; uint32_t wstart = 0, wcount = 0; float slack = 0.f; };   /* weight: triangles below (SAH cost) */
 
 static inline double topArea(const TopNode& n)
 {
@@ -237,6 +239,236 @@ bool flattenable(const okrt_bvh_node* nodes, uint32_t numNodes, uint32_t root)
     return true;
 }
 
+/* How far a triangle test may report a hit BEFORE the ray enters the triangle's (exact) leaf box, in distance along the ray,
+ * beyond the relative window: float32 Moeller-Trumbore has an absolute error of ~10 u |o - p2| / (|d.n| sin(phi)) in t (u = 2^-24,
+ * phi = angle between the edges), and |o - p2| <= t + longest edge.  The t-proportional part is what OKRT_DELTA covers; the
+ * edge-proportional part is this slack: 2^-13 x longest edge x |E1||E2| / |E1 x E2| (capped at 64), the largest over the
+ * leaf's triangles.  2^-13 ~ 1.2e-4 covers incidence down to ~0.3 degrees; every ACCEPTED hit is checked against it at run time. */
+float leafSlack(const okrt_triangle* tris, uint32_t start, uint32_t count)
+{
+    double worst = 0.0;
+    for (uint32_t t = start; t < start + count; t++) {
+        const float (*p)[3] = tris[t].position;
+        double e1[3], e2[3], e3[3];
+        for (int k = 0; k < 3; k++) { e1[k] = (double)p[0][k] - p[2][k]; e2[k] = (double)p[1][k] - p[2][k]; e3[k] = (double)p[0][k] - p[1][k]; }
+        const double l1 = std::sqrt(e1[0] * e1[0] + e1[1] * e1[1] + e1[2] * e1[2]), l2 = std::sqrt(e2[0] * e2[0] + e2[1] * e2[1] + e2[2] * e2[2]);
+        const double l3 = std::sqrt(e3[0] * e3[0] + e3[1] * e3[1] + e3[2] * e3[2]);
+        const double cx = e1[1] * e2[2] - e1[2] * e2[1], cy = e1[2] * e2[0] - e1[0] * e2[2], cz = e1[0] * e2[1] - e1[1] * e2[0];
+        const double area2 = std::sqrt(cx * cx + cy * cy + cz * cz);
+        const double shape = area2 > 0.0 ? std::min(64.0, std::max(1.0, l1 * l2 / area2)) : 64.0;
+        const double longest = std::max(l1, std::max(l2, l3));
+        if (std::isfinite(longest)) worst = std::max(worst, longest * shape);
+    }
+    const double s = worst * (1.0 / 8192.0);
+    return s < 3.0e38 ? (float)s : 3.0e38f;
+}
+
+
+/* ------------------------------------------------------------------ wide layout (okrt_accel.h)
+ * Collapses binary trees (the scene-wide SAH tree; the reference's own tree of an instance that is walked with a ray switch)
+ * into 8-wide nodes with quantised child boxes. */
+struct WideEmitter {
+    std::vector<TopNode>& tn;
+    const okrt_triangle* tris;
+    FastLayout& out;
+    std::vector<double> cull;          /* 6 per binary node: what a wide child box has to contain (leaf: exact box grown by its slack) */
+    uint32_t deepest = 0;
+    std::string error;
+
+    static double area(const double* b)
+    {
+        const double dx = b[3] - b[0], dy = b[4] - b[1], dz = b[5] - b[2];
+        return (dx < 0 || dy < 0 || dz < 0) ? 0.0 : 2.0 * (dx * dy + dy * dz + dz * dx);
+    }
+    /* leaves with more triangles than a leaf record can name are cut into a small subtree of records that repeat the box */
+    void splitOversized(int32_t n)
+    {
+        if (tn[n].wcount <= kWideMaxLeafTris) return;
+        const uint32_t half = tn[n].wcount / 2u;
+        TopNode a = tn[n], c = tn[n];
+        a.wcount = half; c.wstart = tn[n].wstart + half; c.wcount = tn[n].wcount - half;
+        a.parent = c.parent = n;
+        a.slack = leafSlack(tris, a.wstart, a.wcount); c.slack = leafSlack(tris, c.wstart, c.wcount);
+        const int32_t ia = (int32_t)tn.size(); tn.push_back(a);
+        const int32_t ic = (int32_t)tn.size(); tn.push_back(c);
+        tn[n].left = ia; tn[n].right = ic; tn[n].wcount = 0;
+        splitOversized(ia); splitOversized(ic);
+    }
+    void prepare(int32_t root)
+    {
+        /* post-order over the binary tree: culling boxes bottom-up */
+        std::vector<int32_t> order, st{root};
+        while (!st.empty()) {
+            const int32_t n = st.back(); st.pop_back();
+            if (tn[n].left < 0 && tn[n].wcount > kWideMaxLeafTris) splitOversized(n);
+            order.push_back(n);
+            if (tn[n].left >= 0) { st.push_back(tn[n].left); st.push_back(tn[n].right); }
+        }
+        cull.resize(tn.size() * 6);
+        for (size_t i = order.size(); i-- > 0;) {
+            const int32_t n = order[i];
+            double* c = &cull[(size_t)n * 6];
+            if (tn[n].left < 0) {
+                const double s = tn[n].wcount ? (double)tn[n].slack : 0.0;
+                for (int k = 0; k < 3; k++) { c[k] = tn[n].lo[k] - s; c[3 + k] = tn[n].hi[k] + s; }
+            } else {
+                const double *a = &cull[(size_t)tn[n].left * 6], *d = &cull[(size_t)tn[n].right * 6];
+                for (int k = 0; k < 3; k++) { c[k] = std::min(a[k], d[k]); c[3 + k] = std::max(a[3 + k], d[3 + k]); }
+            }
+        }
+    }
+    uint32_t newNodes(uint32_t k)
+    {
+        const uint32_t first = (uint32_t)(out.wideNodes.size() / kWideNodeWords);
+        out.wideNodes.resize(out.wideNodes.size() + (size_t)k * kWideNodeWords, 0u);
+        out.wideLeaves.resize(out.wideLeaves.size() + (size_t)k * 8u * kWideLeafWords, 0u);
+        return first;
+    }
+    bool fill(uint32_t node, int32_t bin, uint32_t level)
+    {
+        deepest = std::max(deepest, level + 1);
+        /* children: open the interior child of the largest area until there are eight */
+        int32_t child[8]; int n = 0;
+        if (tn[bin].left < 0) child[n++] = bin;
+        else { child[n++] = tn[bin].left; child[n++] = tn[bin].right; }
+        while (n < 8) {
+            int best = -1; double bestArea = -1.0;
+            for (int i = 0; i < n; i++)
+                if (tn[child[i]].left >= 0) { const double a = area(&cull[(size_t)child[i] * 6]); if (a > bestArea) { bestArea = a; best = i; } }
+            if (best < 0) break;
+            const int32_t open = child[best];
+            child[best] = tn[open].left; child[n++] = tn[open].right;
+        }
+        double box[6] = {DBL_MAX, DBL_MAX, DBL_MAX, -DBL_MAX, -DBL_MAX, -DBL_MAX};
+        for (int i = 0; i < n; i++) { const double* c = &cull[(size_t)child[i] * 6]; for (int k = 0; k < 3; k++) { box[k] = std::min(box[k], c[k]); box[3 + k] = std::max(box[3 + k], c[3 + k]); } }
+        /* slots: slot s is visited first by rays of direction octant s (bit 2: -x, bit 1: -y, bit 0: -z), so it should hold the
+         * child that lies farthest AGAINST that direction; greedy assignment of the cheapest (child, slot) pair */
+        int slotOf[8]; bool slotUsed[8] = {false, false, false, false, false, false, false, false};
+        {
+            double cost[8][8];
+            for (int i = 0; i < n; i++) {
+                const double* c = &cull[(size_t)child[i] * 6];
+                for (int s = 0; s < 8; s++) {
+                    double v = 0.0;
+                    for (int k = 0; k < 3; k++) { const double rel = 0.5 * (c[k] + c[3 + k]) - 0.5 * (box[k] + box[3 + k]); v += ((s >> (2 - k)) & 1) ? -rel : rel; }
+                    cost[i][s] = v;
+                }
+            }
+            bool done[8] = {false, false, false, false, false, false, false, false};
+            for (int round = 0; round < n; round++) {
+                int bi = -1, bs = -1; double bc = DBL_MAX;
+                for (int i = 0; i < n; i++) if (!done[i]) for (int s = 0; s < 8; s++) if (!slotUsed[s] && cost[i][s] < bc) { bc = cost[i][s]; bi = i; bs = s; }
+                if (bi < 0) { bi = 0; while (done[bi]) bi++; bs = 0; while (slotUsed[bs]) bs++; }       /* NaN boxes: any free slot */
+                done[bi] = true; slotUsed[bs] = true; slotOf[bi] = bs;
+            }
+        }
+        /* quantisation grid: cell 2^e per axis, origin a multiple of the cell, 255 cells cover the box, every plane exact in float32 */
+        float p[3]; uint32_t eb[3]; double cell[3];
+        for (int k = 0; k < 3; k++) {
+            const double lo = box[k], hi = box[3 + k];
+            if (!(lo <= hi) || !std::isfinite(lo) || !std::isfinite(hi)) { error = "wide layout: box is not finite"; return false; }
+            int e = -100;
+            if (hi > lo) e = std::max(e, (int)std::ceil(std::log2((hi - lo) / 255.0)));
+            for (;; e++) {
+                if (e > 100) { error = "wide layout: box too large to quantise"; return false; }
+                const double c = std::ldexp(1.0, e), origin = std::floor(lo / c) * c;
+                if ((hi - origin) / c > 255.0) continue;
+                if (std::fabs(origin) / c + 256.0 >= 16777216.0) continue;      /* origin + q * cell must be a float32 */
+                p[k] = (float)origin; cell[k] = c; eb[k] = (uint32_t)(e + 127);
+                if ((double)p[k] != origin) continue;
+                break;
+            }
+        }
+        uint32_t* w = &out.wideNodes[(size_t)node * kWideNodeWords];
+        uint8_t q[6][8];
+        for (int s = 0; s < 8; s++) { for (int a = 0; a < 3; a++) { q[a][s] = 255; q[3 + a][s] = 0; } }
+        uint32_t imask = 0u;
+        for (int i = 0; i < n; i++) {
+            const int s = slotOf[i];
+            const double* c = &cull[(size_t)child[i] * 6];
+            for (int k = 0; k < 3; k++) {
+                double ql = std::floor((c[k] - (double)p[k]) / cell[k]), qh = std::ceil((c[3 + k] - (double)p[k]) / cell[k]);
+                ql = std::min(255.0, std::max(0.0, ql)); qh = std::min(255.0, std::max(0.0, qh));
+                if ((double)p[k] + ql * cell[k] > c[k] || (double)p[k] + qh * cell[k] < c[3 + k]) { error = "wide layout: quantised box does not contain its child"; return false; }
+                q[k][s] = (uint8_t)ql; q[3 + k][s] = (uint8_t)qh;
+            }
+            if (tn[child[i]].left >= 0) imask |= 1u << s;
+        }
+        for (int k = 0; k < 3; k++) std::memcpy(&w[k], &p[k], 4);
+        w[3] = eb[0] | (eb[1] << 8) | (eb[2] << 16) | (imask << 24);
+        const uint32_t numInterior = (uint32_t)__builtin_popcount(imask);
+        const uint32_t childBase = numInterior ? newNodes(numInterior) : 0u;
+        w = &out.wideNodes[(size_t)node * kWideNodeWords];                     /* newNodes may have moved the array */
+        w[4] = childBase; w[5] = 0u;
+        for (int a = 0; a < 6; a++) {
+            w[6 + 2 * a] = (uint32_t)q[a][0] | ((uint32_t)q[a][1] << 8) | ((uint32_t)q[a][2] << 16) | ((uint32_t)q[a][3] << 24);
+            w[7 + 2 * a] = (uint32_t)q[a][4] | ((uint32_t)q[a][5] << 8) | ((uint32_t)q[a][6] << 16) | ((uint32_t)q[a][7] << 24);
+        }
+        for (int i = 0; i < n; i++) {
+            const int s = slotOf[i];
+            const TopNode& c = tn[child[i]];
+            if (c.left >= 0) continue;
+            uint32_t* lw = &out.wideLeaves[((size_t)node * 8u + (size_t)s) * kWideLeafWords];
+            for (int k = 0; k < 3; k++) {                                      /* a triangle leaf's box is float32 already; an instance's world box rounds outward */
+                float lo = (float)c.lo[k], hi = (float)c.hi[k];
+                if ((double)lo > c.lo[k]) lo = std::nextafterf(lo, -INFINITY);
+                if ((double)hi < c.hi[k]) hi = std::nextafterf(hi, INFINITY);
+                std::memcpy(&lw[k], &lo, 4); std::memcpy(&lw[3 + k], &hi, 4);
+            }
+            if (c.wcount) {
+                if (c.wstart >= (1u << 26)) { error = "wide layout: more than 2^26 triangles"; return false; }
+                lw[6] = (c.wcount << 26) | c.wstart;
+                std::memcpy(&lw[7], &c.slack, 4);
+                out.maxSlack = std::max(out.maxSlack, c.slack);
+            } else {
+                lw[6] = (kWideLeafInstance << 26) | c.wstart;
+                lw[7] = 0u;
+            }
+        }
+        for (int i = 0; i < n; i++) {
+            if (tn[child[i]].left < 0) continue;
+            const uint32_t rank = (uint32_t)__builtin_popcount(imask & ((1u << slotOf[i]) - 1u));
+            if (!fill(childBase + rank, child[i], level + 1)) return false;
+        }
+        return true;
+    }
+    /* returns the wide root of the binary tree under `root` and its depth in node levels */
+    bool emitTree(int32_t root, uint32_t& wideRoot, uint32_t& depth)
+    {
+        prepare(root);
+        deepest = 0;
+        wideRoot = newNodes(1);
+        if (!fill(wideRoot, root, 0)) return false;
+        depth = deepest;
+        return true;
+    }
+};
+
+/* the reference's own tree of one mesh as a binary tree of its LEAVES (interior boxes are rebuilt from the leaves: the
+ * reference's are supersets, flattenable() has checked that) */
+int32_t appendReferenceTree(std::vector<TopNode>& tn, const okrt_triangle* tris, const okrt_bvh_node* nodes, uint32_t idx)
+{
+    const okrt_bvh_node& n = nodes[idx];
+    if (n.firstChildIdx == OKRT_INVALID_UINT) {
+        if (n.triStart == OKRT_INVALID_UINT || n.triEnd <= n.triStart) return -1;
+        TopNode leaf;
+        for (int k = 0; k < 3; k++) { leaf.lo[k] = n.boundingBox.min[k]; leaf.hi[k] = n.boundingBox.max[k]; }
+        leaf.wstart = n.triStart; leaf.wcount = n.triEnd - n.triStart; leaf.slack = leafSlack(tris, n.triStart, n.triEnd - n.triStart);
+        tn.push_back(leaf);
+        return (int32_t)tn.size() - 1;
+    }
+    const int32_t l = appendReferenceTree(tn, tris, nodes, n.firstChildIdx), r = appendReferenceTree(tn, tris, nodes, n.firstChildIdx + 1);
+    if (l < 0) return r;
+    if (r < 0) return l;
+    TopNode in;
+    for (int k = 0; k < 3; k++) { in.lo[k] = std::min(tn[l].lo[k], tn[r].lo[k]); in.hi[k] = std::max(tn[l].hi[k], tn[r].hi[k]); }
+    in.left = l; in.right = r;
+    tn.push_back(in);
+    const int32_t self = (int32_t)tn.size() - 1;
+    tn[l].parent = self; tn[r].parent = self;
+    return self;
+}
+
 inline float roundDown(double v) { float f = (float)v; return (double)f > v ? std::nextafterf(f, -INFINITY) : f; }
 inline float roundUp(double v) { float f = (float)v; return (double)f < v ? std::nextafterf(f, INFINITY) : f; }
 
@@ -324,6 +556,7 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
         if (instOct[i] != 0xFFFFFFFFu) rootUsers[instances[i].bvhNodeStartIdx]++;
     out.triOwner.assign(numTris, 0xFFFFFFFFu);
     std::vector<TopLeaf> leaves;
+    std::vector<std::pair<uint32_t, uint32_t>> wideInstanceRoots;   /* (instance record, reference BVH root) walked with a ray switch */
     uint32_t chainDepth = 0;                                     /* pair levels of oversized-leaf chains below a flattened leaf */
     for (uint32_t i = 0; i < numInstances; i++) {
         if (instOct[i] == 0xFFFFFFFFu) continue;                 /* never visited by the reference either */
@@ -369,12 +602,38 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
                 for (int r = 0; r < 3; r++) d += (double)T[r * 4 + a] * (double)T[r * 4 + c];
                 if (std::fabs(d - (a == c ? 1.0 : 0.0)) > 1e-4) out.allRigid = false;
             }
+        /* world box of the root box (padded unless the transform is exactly the identity): a primitive of the scene-wide tree,
+         * and what the oct-tree boxes above the instance have to contain */
+        double worldLo[3], worldHi[3];
+        if (identity) { for (int k = 0; k < 3; k++) { worldLo[k] = rb.min[k]; worldHi[k] = rb.max[k]; } }
+        else {
+            for (int k = 0; k < 3; k++) { worldLo[k] = DBL_MAX; worldHi[k] = -DBL_MAX; }
+            for (int corner = 0; corner < 8; corner++) {
+                const double v[3] = {(corner & 1) ? rb.max[0] : rb.min[0], (corner & 2) ? rb.max[1] : rb.min[1], (corner & 4) ? rb.max[2] : rb.min[2]};
+                for (int row = 0; row < 3; row++) {
+                    const double p = (double)T[row * 4 + 0] * v[0] + (double)T[row * 4 + 1] * v[1] + (double)T[row * 4 + 2] * v[2] + (double)T[row * 4 + 3];
+                    worldLo[row] = std::min(worldLo[row], p); worldHi[row] = std::max(worldHi[row], p);
+                }
+            }
+            double diag = 0, mag = 0;
+            for (int k = 0; k < 3; k++) { diag += (worldHi[k] - worldLo[k]) * (worldHi[k] - worldLo[k]); mag = std::max(mag, std::max(std::fabs(worldLo[k]), std::fabs(worldHi[k]))); }
+            const double pad = 1e-4 * std::sqrt(diag) + 1e-5 * mag + 1e-6;
+            for (int k = 0; k < 3; k++) { worldLo[k] -= pad; worldHi[k] += pad; }
+        }
+        /* The reference culls an oct-tree node AND everything below it when the ray enters the node's box at or beyond the
+         * closest hit so far (RaytracerCS.hlsl:262-264), and createOctTree keeps untransformed occupant boxes (RayTracer.cpp:562)
+         * that are rounded through centre / extents: a node's box need not contain what it lists.  The traversal does not rely
+         * on containment: the distNear of every oct-tree box above the winning hit's instance joins the winner's gate
+         * (okrt_wide.cuh, wideResult / wideEnterInstance), a missed box sends the ray to the reference order.
+         * A BVH whose interior boxes do not contain their children (possible for uploaded arrays, never for BvhBuilder's) makes
+         * the reference's own culls order dependent inside the mesh: such an instance is walked by the reference order only. */
+        const bool orderDependent = !flattenable(nodes, numNodes, inst.bvhNodeStartIdx);
         const uint32_t rec = (uint32_t)(out.instances.size() / kInstQuads);
         out.instances.resize(out.instances.size() + kInstQuads);
         Float4* r = &out.instances[(size_t)rec * kInstQuads];
         for (int row = 0; row < 3; row++) r[row] = Float4{Ti[row * 4 + 0], Ti[row * 4 + 1], Ti[row * 4 + 2], Ti[row * 4 + 3]};
         for (int row = 0; row < 3; row++) r[3 + row] = Float4{T[row * 4 + 0], T[row * 4 + 1], T[row * 4 + 2], rb.min[row]};
-        r[6] = Float4{rb.max[0], rb.max[1], rb.max[2], bitsToFloat(identity ? 1u : 0u)};
+        r[6] = Float4{rb.max[0], rb.max[1], rb.max[2], bitsToFloat((identity ? 1u : 0u) | (orderDependent ? 2u : 0u))};
         r[7] = Float4{bitsToFloat(rootRef), bitsToFloat(instOct[i]), bitsToFloat(i), bitsToFloat(octNested[instOct[i]] ? 1u : 0u)};
         const okrt_aabb& ob = octNodes[instOct[i]].boundingBox;
         r[8] = Float4{ob.min[0], ob.min[1], ob.min[2], 0.f};
@@ -422,6 +681,7 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
                     b.deepestPair = before;
                     if (b.failed) return false;
                     leaf.weight = n.triEnd - n.triStart;
+                    leaf.wstart = n.triStart; leaf.wcount = n.triEnd - n.triStart; leaf.slack = leafSlack(tris, n.triStart, n.triEnd - n.triStart);
                     for (int k = 0; k < 3; k++) { leaf.lo[k] = n.boundingBox.min[k]; leaf.hi[k] = n.boundingBox.max[k]; }
                     leaves.push_back(leaf);
                     out.numFlattenedLeaves++;
@@ -429,25 +689,17 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
             } else {
                 TopLeaf leaf; leaf.ref = rootRef; leaf.weight = std::max<uint32_t>(1u, inst.triEnd > inst.triStart ? inst.triEnd - inst.triStart : 1u);
                 for (int k = 0; k < 3; k++) { leaf.lo[k] = rb.min[k]; leaf.hi[k] = rb.max[k]; }   /* exact: this IS the reference's root-box test */
+                leaf.wstart = rec; leaf.wcount = 0;              /* wide layout: an instance record (its tree is not nested: flagged order dependent) */
                 leaves.push_back(leaf);
             }
             continue;
         }
 
-        /* world box of the root box, padded: the top level only has to be conservative */
+        /* the (padded) world box: the top level only has to be conservative */
         TopLeaf leaf; leaf.ref = kRefInstance | rec; leaf.weight = std::max<uint32_t>(1u, inst.triEnd > inst.triStart ? inst.triEnd - inst.triStart : 1u);
-        for (int k = 0; k < 3; k++) { leaf.lo[k] = DBL_MAX; leaf.hi[k] = -DBL_MAX; }
-        for (int corner = 0; corner < 8; corner++) {
-            const double v[3] = {(corner & 1) ? rb.max[0] : rb.min[0], (corner & 2) ? rb.max[1] : rb.min[1], (corner & 4) ? rb.max[2] : rb.min[2]};
-            for (int row = 0; row < 3; row++) {
-                const double p = (double)T[row * 4 + 0] * v[0] + (double)T[row * 4 + 1] * v[1] + (double)T[row * 4 + 2] * v[2] + (double)T[row * 4 + 3];
-                leaf.lo[row] = std::min(leaf.lo[row], p); leaf.hi[row] = std::max(leaf.hi[row], p);
-            }
-        }
-        double diag = 0, mag = 0;
-        for (int k = 0; k < 3; k++) { diag += (leaf.hi[k] - leaf.lo[k]) * (leaf.hi[k] - leaf.lo[k]); mag = std::max(mag, std::max(std::fabs(leaf.lo[k]), std::fabs(leaf.hi[k]))); }
-        const double pad = 1e-4 * std::sqrt(diag) + 1e-5 * mag + 1e-6;
-        for (int k = 0; k < 3; k++) { leaf.lo[k] -= pad; leaf.hi[k] += pad; }
+        for (int k = 0; k < 3; k++) { leaf.lo[k] = worldLo[k]; leaf.hi[k] = worldHi[k]; }
+        leaf.wstart = rec; leaf.wcount = 0;
+        if (!orderDependent) wideInstanceRoots.emplace_back(rec, inst.bvhNodeStartIdx);
         leaves.push_back(leaf);
     }
     out.exactBvhDepth = b.deepestLeafLevel + 1;
@@ -476,7 +728,7 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
             }
         const int32_t self = nextTopNode.fetch_add(1);
         for (int k = 0; k < 3; k++) { tn[self].lo[k] = bl[k]; tn[self].hi[k] = bh[k]; }
-        if (hi - lo == 1) { tn[self].ref = leaves[lo].ref; return self; }
+        if (hi - lo == 1) { tn[self].ref = leaves[lo].ref; tn[self].wstart = leaves[lo].wstart; tn[self].wcount = leaves[lo].wcount; tn[self].slack = leaves[lo].slack; return self; }
 
         size_t mid = lo;
         if (hi - lo > 2 && hi - lo <= sweepBelow && hi - lo >= sweepAbove && level < kSahDepthLimit) {
@@ -586,6 +838,7 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
         b.setChild(p, 1, b1, r1);
         return p;
     };
+    int32_t wideBinaryRoot = -1;
     if (!leaves.empty()) {
         okrt_aabb rootBox;
         int32_t root = buildTop(0, leaves.size(), 0);
@@ -599,6 +852,7 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
             if (topTreeDepth(tn, root) > kSahDepthLimit + 4) { tn = before; root = rootBefore; }      /* stack budget */
         }
         phase("scene-wide tree (SAH)");
+        wideBinaryRoot = root;
         out.topRef = emitTop(root, 0, rootBox);
         phase("pair-node emission");
         if (leaves.size() == 1) {
@@ -610,6 +864,29 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
             out.topRef = p;
             topDepth = 1;
         }
+    }
+    /* wide layout: the same scene-wide tree collapsed into 8-wide quantised nodes; instances that are walked with a ray switch
+     * get their own wide tree (one per distinct mesh), its root in r8.w of the record */
+    if (!leaves.empty()) {
+        WideEmitter we{tn, tris, out};
+        uint32_t topWideDepth = 0, instWideDepth = 0;
+        if (!we.emitTree(wideBinaryRoot, out.wideRoot, topWideDepth)) { out.error = we.error; return false; }
+        std::unordered_map<uint32_t, uint32_t> wideRootOf;
+        for (const auto& ir : wideInstanceRoots) {
+            auto it = wideRootOf.find(ir.second);
+            if (it == wideRootOf.end()) {
+                const int32_t bin = appendReferenceTree(tn, tris, nodes, ir.second);
+                uint32_t wr = kRefNone, depth = 0;
+                if (bin >= 0 && !we.emitTree(bin, wr, depth)) { out.error = we.error; return false; }
+                instWideDepth = std::max(instWideDepth, depth);
+                it = wideRootOf.emplace(ir.second, wr).first;
+            }
+            out.instances[(size_t)ir.first * kInstQuads + 8].w = bitsToFloat(it->second);
+        }
+        out.wideDepth = topWideDepth;
+        /* sentinel + one deferred group per level + (at an instance: the two groups of the level, the exit marker) */
+        out.wideStackDepth = 1 + topWideDepth + 3 + instWideDepth;
+        phase("wide nodes");
     }
     if ((out.nodes.size() / 4) >= (1u << 30) || (out.instances.size() / kInstQuads) >= (1u << 30)) { out.error = "scene too large for 30-bit references"; return false; }
 

@@ -52,6 +52,29 @@ constexpr uint32_t kFastStackCapacity = 64;       /* entries; validated against 
 constexpr uint32_t kExactBvhStackCapacity = 64;   /* reference: 50, RaytracerCS.hlsl:249 */
 constexpr uint32_t kExactOctStackCapacity = 32;   /* reference: 20, RaytracerCS.hlsl:244 */
 
+
+/* ---- wide layout (8-wide nodes with quantised child boxes; leaf boxes stay exact) ----------------------------------
+ * Node, 96 B = 24 words, 32 B aligned (three 256-bit loads, three sectors):
+ *     w0..w2   p.xyz      origin of the node's quantisation grid (a multiple of the cell size: p + q*cell is exact in float32)
+ *     w3       e.x | e.y << 8 | e.z << 16 | imask << 24      cell size of axis k = 2^(e.k - 127); imask bit s: slot s is interior
+ *     w4       childBase  interior children are stored contiguously, in slot order: child of slot s = childBase + popc(imask & ((1<<s)-1))
+ *     w5       0
+ *     w6..w17  qlo.x[8] qlo.y[8] qlo.z[8] qhi.x[8] qhi.y[8] qhi.z[8]   one byte per slot; an empty slot has qlo = 255, qhi = 0
+ *     w18..23  0
+ * A child's quantised box CONTAINS the culling box of everything below it: the exact box of every leaf below, grown by that
+ * leaf's slack (below).  Slots are assigned so that visiting slots in the order (7 - octant) XOR priority is roughly near to far
+ * for a ray of that direction octant (after Ylitie, Karras, Laine 2017, restated): no sorting in the kernel.
+ * Leaf record, 32 B = 8 words, at index node * 8 + slot (one 256-bit load):
+ *     w0..w5   min.xyz, max.xyz: bit copy of the reference leaf's box — tested with the reference's own arithmetic
+ *     w6       count << 26 | first triangle (count 1..62), or 63 << 26 | instance record
+ *     w7       slack: how far (in distance along a ray) a triangle test of this leaf may report a hit before the ray enters the
+ *              leaf's box, beyond the relative window delta: 2^-13 x longest edge x edge-shape factor of its triangles */
+constexpr uint32_t kWideNodeWords = 24;
+constexpr uint32_t kWideLeafWords = 8;
+constexpr uint32_t kWideMaxLeafTris = 62;
+constexpr uint32_t kWideLeafInstance = 63;
+constexpr uint32_t kWideStackCapacity = 32;       /* 8-byte entries; validated against the tree depth at upload */
+
 struct Float4 { float x, y, z, w; };
 
 struct FastLayout {
@@ -67,6 +90,12 @@ struct FastLayout {
     uint32_t exactBvhDepth = 0;         /* worst-case reference BVH stack occupancy */
     uint32_t exactOctDepth = 0;         /* worst-case reference oct-tree stack occupancy */
     bool allRigid = true;               /* every instance transform has unit scale */
+    std::vector<uint32_t> wideNodes;    /* kWideNodeWords per node */
+    std::vector<uint32_t> wideLeaves;   /* kWideLeafWords per (node, slot) */
+    uint32_t wideRoot = kRefNone;       /* root node of the scene-wide tree */
+    uint32_t wideStackDepth = 0;        /* worst-case occupancy of the wide traversal's stack */
+    uint32_t wideDepth = 0;             /* node levels of the scene-wide tree */
+    float maxSlack = 0.f;               /* largest leaf slack of the scene */
     std::string error;
 };
 

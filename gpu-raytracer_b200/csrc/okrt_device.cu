@@ -10,6 +10,8 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <atomic>
+#include <thread>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -117,7 +119,9 @@ struct okrt_renderer {
 
     DeviceBuffer triPos, triInfo, bvhNodes, octNodes, spheres, instances, dirLights, pointLights, spotLights;
     TextureArray textures, environment;
-    DeviceBuffer fastNodes, fastTris, fastInstances, octParent;
+    DeviceBuffer fastNodes, fastTris, fastInstances, octParent, wideNodes, wideLeaves;
+    uint32_t wideRoot = kRefNone;
+    float maxSlack = 0.f;
     cudaTextureObject_t fastTrisTex = 0;
 
     /* host copies needed to (re)build the fast layout */
@@ -180,10 +184,10 @@ int rebuildLayout(okrt_renderer* r)
         setError("scene rejected: " + fl.error);
         return OKRT_ERR_INVALID_ARGUMENT;
     }
-    if (fl.maxStackDepth > kFastStackCapacity || fl.exactBvhDepth > kExactBvhStackCapacity || fl.exactOctDepth > kExactOctStackCapacity) {
+    if (fl.maxStackDepth > kFastStackCapacity || fl.wideStackDepth > kWideStackCapacity || fl.exactBvhDepth > kExactBvhStackCapacity || fl.exactOctDepth > kExactOctStackCapacity) {
         char msg[256];
-        std::snprintf(msg, sizeof(msg), "traversal stack would overflow: fast %u/%u, bvh %u/%u, oct-tree %u/%u",
-                      fl.maxStackDepth, kFastStackCapacity, fl.exactBvhDepth, kExactBvhStackCapacity, fl.exactOctDepth, kExactOctStackCapacity);
+        std::snprintf(msg, sizeof(msg), "traversal stack would overflow: pairs %u/%u, wide %u/%u, bvh %u/%u, oct-tree %u/%u",
+                      fl.maxStackDepth, kFastStackCapacity, fl.wideStackDepth, kWideStackCapacity, fl.exactBvhDepth, kExactBvhStackCapacity, fl.exactOctDepth, kExactOctStackCapacity);
         setError(msg);
         return OKRT_ERR_CAPACITY;
     }
@@ -192,6 +196,10 @@ int rebuildLayout(okrt_renderer* r)
     if ((rc = r->fastTris.upload(fl.tris.data(), (uint32_t)fl.tris.size(), sizeof(Float4), r->stream))) return rc;
     if ((rc = r->fastInstances.upload(fl.instances.data(), (uint32_t)fl.instances.size(), sizeof(Float4), r->stream))) return rc;
     if ((rc = r->octParent.upload(fl.octParent.data(), (uint32_t)fl.octParent.size(), sizeof(uint32_t), r->stream))) return rc;
+    if (fl.wideNodes.size() / kWideNodeWords >= (1u << 24) - 1u) { setError("scene too large: the wide layout names nodes with 24 bits"); return OKRT_ERR_CAPACITY; }
+    if ((rc = r->wideNodes.upload(fl.wideNodes.data(), (uint32_t)fl.wideNodes.size(), sizeof(uint32_t), r->stream))) return rc;
+    if ((rc = r->wideLeaves.upload(fl.wideLeaves.data(), (uint32_t)fl.wideLeaves.size(), sizeof(uint32_t), r->stream))) return rc;
+    r->wideRoot = fl.wideRoot; r->maxSlack = fl.maxSlack;
     if (r->fastTrisTex) { cudaDestroyTextureObject(r->fastTrisTex); r->fastTrisTex = 0; }
     if (r->fastTris.bytes) {            /* the triangle records as float4 texels: stepTriangle fetches them through the texture pipe */
         int maxTexels = 0;
@@ -244,6 +252,8 @@ DeviceScene sceneView(const okrt_renderer* r)
     s.octParent = (const uint32_t*)r->octParent.ptr;
     s.topRef = r->topRef;
     s.numFastNodes = r->fastNodes.count / 4u; s.numFastInstances = r->fastInstances.count / kInstQuads;
+    s.wideNodes = (const uint4*)r->wideNodes.ptr; s.wideLeaves = (const uint4*)r->wideLeaves.ptr;
+    s.wideRoot = r->wideRoot; s.numWideNodes = r->wideNodes.count / kWideNodeWords; s.maxSlack = r->maxSlack;
     return s;
 }
 
@@ -278,6 +288,7 @@ int ensureWavefront(okrt_renderer* r, size_t paths)
     OKRT_CUDA(cudaMalloc(&r->wb.queue[1], paths * sizeof(uint32_t)));
     OKRT_CUDA(cudaMalloc(&r->wb.fallbackQueue, paths * sizeof(uint32_t)));
     OKRT_CUDA(cudaMalloc(&r->wb.traceStats, 8 * (kMaxWavefrontBounces + 2) * sizeof(unsigned long long)));
+    OKRT_CUDA(cudaMemsetAsync(r->wb.traceStats, 0, 8 * (kMaxWavefrontBounces + 2) * sizeof(unsigned long long), r->stream));
     OKRT_CUDA(cudaMalloc(&r->wb.counts, kCountWords * sizeof(uint32_t)));
     r->wb.fallbackCounts = r->wb.counts + kMaxQueueCounts;
     r->wbPaths = paths;
@@ -293,9 +304,6 @@ int launchWavefront(okrt_renderer* r, const FrameParams& fpWhole, bool instrumen
     int rc = ensureWavefront(r, std::max(paths, r->wbReserve));
     if (rc) return rc;
     const DeviceScene scene = sceneView(r);
-#ifdef OKRT_TRACE_STATS
-    OKRT_CUDA(cudaMemsetAsync(r->wb.traceStats, 0, 8 * (kMaxWavefrontBounces + 2) * sizeof(unsigned long long), r->stream));
-#endif
     /* Optional (OKRT_DUAL_MIN_FRAMES=n; 0 = off): two halves of the batch on two streams, each its own chain
      * generate -> (trace, fallback, shade) x bounces over its own slice of the path state, so that kernel tails, the
      * fallback launches and the launch gaps of one half are filled by the other half's kernels (every kernel pulls its
@@ -366,7 +374,11 @@ int launchWavefront(okrt_renderer* r, const FrameParams& fpWhole, bool instrumen
                  * fallback / generate work */
                 if (dual && serialTrace && lastTraceEnd) OKRT_CUDA(cudaStreamWaitEvent(st[h], lastTraceEnd, 0));
                 OKRT_CUDA(cudaEventRecord(e0, st[h]));
+#if OKRT_WIDE
+                traceWideKernel<<<traceGridH[h], kTraceBlockThreads, 0, st[h]>>>(scene, fp, wb, qin, b);
+#else
                 traceFastKernel<<<traceGridH[h], kTraceBlockThreads, 0, st[h]>>>(scene, fp, wb, qin, b);
+#endif
                 OKRT_CUDA(cudaEventRecord(e1, st[h]));
                 lastTraceEnd = e1;
                 traceFallbackKernel<<<fallbackGridH[h], 128, 0, st[h]>>>(scene, fp, wb, b);
@@ -395,14 +407,13 @@ int launchWavefront(okrt_renderer* r, const FrameParams& fpWhole, bool instrumen
             std::fprintf(stderr, "\n");
         }
 #ifdef OKRT_TRACE_STATS
-        const unsigned traceGrid = traceGridH[0];
         std::vector<unsigned long long> st(8 * (fp.maxBounces + 1));
         cudaMemcpy(st.data(), r->wb.traceStats, st.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
         for (uint32_t b = 0; b <= fp.maxBounces; b++) {
             const unsigned long long* t = &st[8 * b];
-            std::fprintf(stderr, "  bounce %u: rays %llu  node steps/ray %.1f (lanes/iter %.1f)  tri steps/ray %.1f (lanes/iter %.1f)  refills/warp %.1f  warp clocks avg %.0f max %llu\n",
-                         b, t[0], (double)t[1] / std::max(1ull, t[0]), (double)t[1] / std::max(1ull, t[3]), (double)t[2] / std::max(1ull, t[0]), (double)t[2] / std::max(1ull, t[4]),
-                         (double)t[5] / (traceGrid * 4.0), (double)t[6] / (traceGrid * 4.0), t[7]);
+            const double rays = (double)std::max(1ull, t[0]);
+            std::fprintf(stderr, "  bounce %u (since reset): rays %llu  node steps/ray %.2f  leaf entries/ray %.2f  triangle tests/ray %.2f  lanes per node iteration %.1f  per triangle iteration %.1f\n",
+                         b, t[0], t[1] / rays, t[2] / rays, t[3] / rays, (double)t[6] / std::max(1ull, t[4]), (double)t[7] / std::max(1ull, t[5]));
         }
 #endif
     }
@@ -538,7 +549,11 @@ int okrt_create(int device, uint32_t width, uint32_t height, okrt_renderer** out
     if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess ||
         (e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&r->blocksPerSmLean, pathTraceKernel<false>, kBlockThreads, 0)) != cudaSuccess ||
         (e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&r->blocksPerSmInstrumented, pathTraceKernel<true>, kBlockThreads, 0)) != cudaSuccess ||
+#if OKRT_WIDE
+        (e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&r->blocksPerSmTrace, traceWideKernel, kTraceBlockThreads, 0)) != cudaSuccess) {
+#else
         (e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&r->blocksPerSmTrace, traceFastKernel, kTraceBlockThreads, 0)) != cudaSuccess) {
+#endif
         setError(std::string("okrt_create: ") + cudaGetErrorString(e));
         okrt_destroy(r);
         return OKRT_ERR_CUDA;
@@ -546,6 +561,7 @@ int okrt_create(int device, uint32_t width, uint32_t height, okrt_renderer** out
     if (const char* carve = std::getenv("OKRT_L1_CARVEOUT")) {     /* tuning knob: shared-memory share of the L1 (percent) */
         const int pct = std::atoi(carve);
         cudaFuncSetAttribute(traceFastKernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+        cudaFuncSetAttribute(traceWideKernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
         cudaFuncSetAttribute(shadeKernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
         cudaFuncSetAttribute(traceFallbackKernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
         cudaFuncSetAttribute(generateKernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
@@ -570,7 +586,7 @@ void okrt_destroy(okrt_renderer* r)
     r->triPos.release(); r->triInfo.release(); r->bvhNodes.release(); r->octNodes.release(); r->spheres.release();
     r->instances.release(); r->dirLights.release(); r->pointLights.release(); r->spotLights.release();
     if (r->fastTrisTex) { cudaDestroyTextureObject(r->fastTrisTex); r->fastTrisTex = 0; }
-    r->fastNodes.release(); r->fastTris.release(); r->fastInstances.release(); r->octParent.release();
+    r->fastNodes.release(); r->fastTris.release(); r->fastInstances.release(); r->octParent.release(); r->wideNodes.release(); r->wideLeaves.release();
     r->textures.release(); r->environment.release();
     if (r->accumulation) cudaFree(r->accumulation);
     if (r->result) cudaFree(r->result);
@@ -953,10 +969,79 @@ int okrt_get_stats(okrt_renderer* r, okrt_stats* out)
     return OKRT_OK;
 }
 
+/* Step counters of the traversal kernel since okrt_reset_stats, 8 per bounce (okrt_wavefront.cuh, traceWideKernel).  Only a
+ * library built with -DOKRT_TRACE_STATS counts (tools/: libokrt_stats.so); the product build returns OKRT_ERR_STATE. */
+int okrt_get_trace_stats(okrt_renderer* r, uint64_t* out, uint32_t bounces)
+{
+    int rc = checkHandle(r, "okrt_get_trace_stats"); if (rc) return rc;
+    if (!out || bounces > kMaxWavefrontBounces + 1) { setError("okrt_get_trace_stats: bad argument"); return OKRT_ERR_INVALID_ARGUMENT; }
+#ifdef OKRT_TRACE_STATS
+    if (!r->wb.traceStats) { std::memset(out, 0, (size_t)bounces * 8 * sizeof(uint64_t)); return OKRT_OK; }
+    OKRT_CUDA(cudaMemcpyAsync(out, r->wb.traceStats, (size_t)bounces * 8 * sizeof(uint64_t), cudaMemcpyDeviceToHost, r->stream));
+    OKRT_CUDA(cudaStreamSynchronize(r->stream));
+    return OKRT_OK;
+#else
+    setError("okrt_get_trace_stats: this library was built without -DOKRT_TRACE_STATS");
+    return OKRT_ERR_STATE;
+#endif
+}
+
+/* Host-only check of the wide traversal (no GPU): builds the traversal layout from the binding-table arrays and runs the
+ * kernels' own lane functions (okrt_wide.cuh, compiled for the host) over `numRays` rays (6 floats each: origin, direction).
+ * out: 12 words per ray — distance, u, v (float bits), triangle, kind, instance-or-sphere index, needs-reference-order flag,
+ * the bound left for the reference-order traversal (float bits), node steps, leaf entries, triangle tests, 0.
+ * The step counts need a -DOKRT_TRACE_STATS build (0 otherwise). */
+int okrt_trace_rays_host(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh_node* nodes, uint32_t numNodes,
+                         const okrt_mesh_instance* instances, uint32_t numInstances, const okrt_octree_node* octNodes, uint32_t numOctNodes,
+                         const float* rays, uint32_t numRays, uint32_t* out)
+{
+    if ((numRays && (!rays || !out))) { setError("okrt_trace_rays_host: null argument"); return OKRT_ERR_INVALID_ARGUMENT; }
+    FastLayout fl;
+    if (!buildFastLayout(tris, numTris, nodes, numNodes, instances, numInstances, octNodes, numOctNodes, fl)) {
+        setError("scene rejected: " + fl.error);
+        return OKRT_ERR_INVALID_ARGUMENT;
+    }
+    if (fl.wideStackDepth > kWideStackCapacity) { setError("traversal stack would overflow"); return OKRT_ERR_CAPACITY; }
+    if (!fl.allRigid) { setError("okrt_trace_rays_host: scaled instances use the reference order"); return OKRT_ERR_STATE; }
+    DeviceScene s;
+    std::memset(&s, 0, sizeof(s));
+    s.octNodes = octNodes; s.instances = instances; s.numOctNodes = numOctNodes; s.numInstances = numInstances; s.numTris = numTris;
+    s.fastTris = (const float4*)fl.tris.data(); s.fastInstances = (const float4*)fl.instances.data(); s.octParent = fl.octParent.data();
+    s.numFastInstances = (uint32_t)(fl.instances.size() / kInstQuads);
+    /* the node and leaf arrays are read with 32-byte loads */
+    std::vector<uint4> wn((fl.wideNodes.size() + 3) / 4), wl((fl.wideLeaves.size() + 3) / 4);
+    if (!fl.wideNodes.empty()) std::memcpy(wn.data(), fl.wideNodes.data(), fl.wideNodes.size() * 4);
+    if (!fl.wideLeaves.empty()) std::memcpy(wl.data(), fl.wideLeaves.data(), fl.wideLeaves.size() * 4);
+    s.wideNodes = wn.data(); s.wideLeaves = wl.data(); s.wideRoot = fl.wideRoot; s.numWideNodes = (uint32_t)(fl.wideNodes.size() / kWideNodeWords);
+    s.maxSlack = fl.maxSlack;
+    const unsigned nthreads = std::max(1u, std::thread::hardware_concurrency());
+    std::vector<std::thread> pool;
+    std::atomic<uint32_t> nextRay(0);
+    for (unsigned t = 0; t < nthreads; t++)
+        pool.emplace_back([&]() {
+            for (;;) {
+                const uint32_t begin = nextRay.fetch_add(1024u);
+                if (begin >= numRays) break;
+                for (uint32_t i = begin; i < std::min(numRays, begin + 1024u); i++) {
+                    const float* r6 = rays + (size_t)i * 6;
+                    Hit hit; float limit = 0.f; uint32_t counts[4] = {0u, 0u, 0u, 0u};
+                    const bool ambiguous = wideTraverse(s, 0u, v3(r6[0], r6[1], r6[2]), v3(r6[3], r6[4], r6[5]), hit, limit, counts);
+                    uint32_t* o = out + (size_t)i * 12;
+                    std::memcpy(o + 0, &hit.distance, 4); std::memcpy(o + 1, &hit.u, 4); std::memcpy(o + 2, &hit.v, 4);
+                    o[3] = hit.tri; o[4] = hit.kind; o[5] = hit.idx; o[6] = ambiguous ? 1u : 0u; std::memcpy(o + 7, &limit, 4);
+                    o[8] = counts[0]; o[9] = counts[1]; o[10] = counts[2]; o[11] = counts[3];
+                }
+            }
+        });
+    for (auto& th : pool) th.join();
+    return OKRT_OK;
+}
+
 int okrt_reset_stats(okrt_renderer* r)
 {
     int rc = checkHandle(r, "okrt_reset_stats"); if (rc) return rc;
     OKRT_CUDA(cudaMemsetAsync(r->counters, 0, 4 * sizeof(unsigned long long), r->stream));
+    if (r->wb.traceStats) OKRT_CUDA(cudaMemsetAsync(r->wb.traceStats, 0, 8 * (kMaxWavefrontBounces + 2) * sizeof(unsigned long long), r->stream));
     r->launches = 0;
     return OKRT_OK;
 }

@@ -22,24 +22,27 @@
 #include "okrt_accel.h"
 #include "okrt_math.cuh"
 
+/* functions the CPU check of the wide traversal (okrt_trace_rays_host) shares with the kernels */
+#define OKRT_HD __host__ __device__ __forceinline__
+
 namespace okrt {
 
 /* ------------------------------------------------------------------ shim */
 struct V3 { float x, y, z; };
 struct V2 { float x, y; };
 
-__device__ __forceinline__ V3 v3(float x, float y, float z) { V3 r; r.x = x; r.y = y; r.z = z; return r; }
-__device__ __forceinline__ V3 v3(const float* p) { return v3(p[0], p[1], p[2]); }
-__device__ __forceinline__ V3 operator+(V3 a, V3 b) { return v3(a.x + b.x, a.y + b.y, a.z + b.z); }
-__device__ __forceinline__ V3 operator-(V3 a, V3 b) { return v3(a.x - b.x, a.y - b.y, a.z - b.z); }
-__device__ __forceinline__ V3 operator*(V3 a, V3 b) { return v3(a.x * b.x, a.y * b.y, a.z * b.z); }
-__device__ __forceinline__ V3 operator*(V3 a, float s) { return v3(a.x * s, a.y * s, a.z * s); }
-__device__ __forceinline__ V3 operator*(float s, V3 a) { return v3(s * a.x, s * a.y, s * a.z); }
-__device__ __forceinline__ V3 operator-(V3 a) { return v3(-a.x, -a.y, -a.z); }
-__device__ __forceinline__ float dot(V3 a, V3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
-__device__ __forceinline__ V3 cross(V3 a, V3 b) { return v3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
-__device__ __forceinline__ float length(V3 a) { return sqrtf(dot(a, a)); }
-__device__ __forceinline__ V3 normalize(V3 a) { const float inv = 1.0f / sqrtf(dot(a, a)); return a * inv; }
+OKRT_HD V3 v3(float x, float y, float z) { V3 r; r.x = x; r.y = y; r.z = z; return r; }
+OKRT_HD V3 v3(const float* p) { return v3(p[0], p[1], p[2]); }
+OKRT_HD V3 operator+(V3 a, V3 b) { return v3(a.x + b.x, a.y + b.y, a.z + b.z); }
+OKRT_HD V3 operator-(V3 a, V3 b) { return v3(a.x - b.x, a.y - b.y, a.z - b.z); }
+OKRT_HD V3 operator*(V3 a, V3 b) { return v3(a.x * b.x, a.y * b.y, a.z * b.z); }
+OKRT_HD V3 operator*(V3 a, float s) { return v3(a.x * s, a.y * s, a.z * s); }
+OKRT_HD V3 operator*(float s, V3 a) { return v3(s * a.x, s * a.y, s * a.z); }
+OKRT_HD V3 operator-(V3 a) { return v3(-a.x, -a.y, -a.z); }
+OKRT_HD float dot(V3 a, V3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
+OKRT_HD V3 cross(V3 a, V3 b) { return v3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
+OKRT_HD float length(V3 a) { return sqrtf(dot(a, a)); }
+OKRT_HD V3 normalize(V3 a) { const float inv = 1.0f / sqrtf(dot(a, a)); return a * inv; }
 __device__ __forceinline__ float lerp1(float a, float b, float s) { return a + s * (b - a); }
 __device__ __forceinline__ V3 lerp3(V3 a, V3 b, float s) { return v3(lerp1(a.x, b.x, s), lerp1(a.y, b.y, s), lerp1(a.z, b.z, s)); }
 __device__ __forceinline__ V3 reflect(V3 i, V3 n) { const float d2 = 2.0f * dot(i, n); return i - n * d2; }
@@ -61,13 +64,13 @@ __device__ __forceinline__ V3 mulDir(V3 v, const float* m)
               (v.x * m[4] + v.y * m[5]) + v.z * m[6],
               (v.x * m[8] + v.y * m[9]) + v.z * m[10]);
 }
-__device__ __forceinline__ V3 mulPointRows(V3 v, float4 r0, float4 r1, float4 r2)
+OKRT_HD V3 mulPointRows(V3 v, float4 r0, float4 r1, float4 r2)
 {
     return v3(((v.x * r0.x + v.y * r0.y) + v.z * r0.z) + r0.w,
               ((v.x * r1.x + v.y * r1.y) + v.z * r1.z) + r1.w,
               ((v.x * r2.x + v.y * r2.y) + v.z * r2.z) + r2.w);
 }
-__device__ __forceinline__ V3 mulDirRows(V3 v, float4 r0, float4 r1, float4 r2)
+OKRT_HD V3 mulDirRows(V3 v, float4 r0, float4 r1, float4 r2)
 {
     return v3((v.x * r0.x + v.y * r0.y) + v.z * r0.z,
               (v.x * r1.x + v.y * r1.y) + v.z * r1.z,
@@ -100,7 +103,12 @@ struct DeviceScene {
     uint32_t numFastNodes, numFastInstances;
     uint32_t pad0;
     cudaTextureObject_t fastTrisTex;          /* fastTris seen through the texture pipe (float4 texels) */
-    uint64_t pad1;
+    /* wide layout (okrt_accel.h): 6 uint4 per node, 2 uint4 per leaf record */
+    const uint4* wideNodes;
+    const uint4* wideLeaves;
+    uint32_t wideRoot, numWideNodes;
+    float maxSlack;
+    uint32_t pad1;
 };
 
 struct FrameParams {
@@ -164,7 +172,7 @@ __device__ __forceinline__ V3 refractCustom(V3 direction, V3 normal, float refra
 }
 
 /* ----------------------------------------------------------- intersection */
-__device__ __forceinline__ float rayAndSphere(V3 o, V3 d, V3 c, float radius)   /* :98-114 [Q15] */
+OKRT_HD float rayAndSphere(V3 o, V3 d, V3 c, float radius)   /* :98-114 [Q15] */
 {
     const V3 rayToSphere = c - o;
     const float distToClosestPoint = dot(rayToSphere, d);
@@ -198,7 +206,7 @@ __device__ __forceinline__ float rayAndTriangle(V3 o, V3 d, V3 p0, V3 p1, V3 p2,
 }
 
 /* :183-197 with 1/direction hoisted (same value the shader recomputes per box) */
-__device__ __forceinline__ float rayAndAABBDist(V3 o, V3 idir, V3 bmin, V3 bmax)
+OKRT_HD float rayAndAABBDist(V3 o, V3 idir, V3 bmin, V3 bmax)
 {
     const V3 tMin = (bmin - o) * idir;
     const V3 tMax = (bmax - o) * idir;
@@ -207,7 +215,7 @@ __device__ __forceinline__ float rayAndAABBDist(V3 o, V3 idir, V3 bmin, V3 bmax)
     const bool didHit = distFar >= distNear && distFar > 0.f;
     return didHit ? distNear : OKRT_FLT_MAX;
 }
-__device__ __forceinline__ V3 rcp3(V3 d) { return v3(1.f / d.x, 1.f / d.y, 1.f / d.z); }
+OKRT_HD V3 rcp3(V3 d) { return v3(1.f / d.x, 1.f / d.y, 1.f / d.z); }
 
 /* --------------------------------------------------------------- textures */
 /* (float)k / 255.0f for k = 0..255, correctly rounded, without the IEEE division sequence: one Newton step on
@@ -630,7 +638,7 @@ __device__ __forceinline__ void stepNode(const DeviceScene& s, StepLane& L, uint
 }
 
 /* GPU-Utilities.hlsli:117-155 [Q6] with E1 = p0 - p2 and E2 = p1 - p2 formed at upload (the same float32 subtraction) */
-__device__ __forceinline__ float rayAndTriangleEdges(V3 o, V3 d, V3 p2, V3 E1, V3 E2, float& u, float& v)
+OKRT_HD float rayAndTriangleEdges(V3 o, V3 d, V3 p2, V3 E1, V3 E2, float& u, float& v)
 {
     const float EPSILON = 0.000001f;
     const V3 cross1 = cross(d, E2);
@@ -759,8 +767,29 @@ __device__ __forceinline__ bool stepResult(const DeviceScene& s, const StepLane&
     return ambiguous;
 }
 
-/* whole-ray form, used by the megakernel: the same steps, one ray per thread */
-__device__ __forceinline__ bool traverseFast(const DeviceScene& s, uint32_t numSpheres, V3 o, V3 d, Hit& hit, float& seed)
+} // namespace okrt
+#include "okrt_wide.cuh"
+namespace okrt {
+__device__ __forceinline__ bool traversePairs(const DeviceScene& s, uint32_t numSpheres, V3 o, V3 d, Hit& hit, float& seed);
+
+#ifndef OKRT_WIDE
+#define OKRT_WIDE 1          /* 1: the near-first traversal walks the wide layout (okrt_wide.cuh); 0: the child-pair layout below */
+#endif
+
+/* whole-ray form, used by the megakernel: the same steps, one ray per thread.  Returns true when the reference order has to
+ * decide; `limit` bounds that traversal. */
+__device__ __forceinline__ bool traverseFast(const DeviceScene& s, uint32_t numSpheres, V3 o, V3 d, Hit& hit, float& limit)
+{
+#if OKRT_WIDE
+    return wideTraverse(s, numSpheres, o, d, hit, limit);
+#else
+    float seed;
+    const bool ambiguous = traversePairs(s, numSpheres, o, d, hit, seed);
+    limit = relaxedLimit(seed);
+    return ambiguous;
+#endif
+}
+__device__ __forceinline__ bool traversePairs(const DeviceScene& s, uint32_t numSpheres, V3 o, V3 d, Hit& hit, float& seed)
 {
     uint32_t stack[kFastStackCapacity + kColdSlots];
     StepLane L;
@@ -1051,11 +1080,11 @@ pathTraceKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ F
             const uint32_t i = ps.bounce;
             Hit hit;
             bool usedFallback = false;
-            float fallbackSeed = OKRT_FLT_MAX;
+            float fallbackLimit = OKRT_FLT_MAX;
             if (exactMode) traverseExact(s, numSpheres, o, d, hit, bbCheckCount, triCheckCount);
-            else if (traverseFast(s, numSpheres, o, d, hit, fallbackSeed)) {
+            else if (traverseFast(s, numSpheres, o, d, hit, fallbackLimit)) {
                 uint32_t bb = 0u, tc = 0u;
-                traverseExact(s, numSpheres, o, d, hit, bb, tc, relaxedLimit(fallbackSeed));
+                traverseExact(s, numSpheres, o, d, hit, bb, tc, fallbackLimit);
                 usedFallback = true; fallbacks++;
             }
             segments++;

@@ -158,7 +158,7 @@ traceFallbackKernel(const __grid_constant__ DeviceScene s, const __grid_constant
     for (uint32_t k = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); k < count; k += warpsPerGrid) {
         const uint32_t path = wb.fallbackQueue[k];
         const float4 ro = wb.rayO[path], rdv = wb.rayD[path];
-        const float limit = relaxedLimit(wb.hitA[path].x);          /* the near-first traversal's closest distance */
+        const float limit = wb.hitA[path].x;                        /* the bound the near-first traversal left for this ray */
         Hit hit;
         traverseExactWarp(s, numSpheres, v3(ro.x, ro.y, ro.z), v3(rdv.x, rdv.y, rdv.z), hit, limit);
         __syncwarp();
@@ -240,7 +240,7 @@ traceFastKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ F
                 float seed;
                 if (stepResult(s, L, stack, wb.rayD + L.path, hit, seed)) {
                     wb.fallbackQueue[atomicAdd(wb.fallbackCounts + bounce, 1u)] = L.path;
-                    wb.hitA[L.path].x = seed;                            /* bounds the reference-order traversal's search */
+                    wb.hitA[L.path].x = relaxedLimit(seed);              /* bounds the reference-order traversal's search */
                 } else {
                     wb.hitA[L.path] = make_float4(hit.distance, hit.u, hit.v, __uint_as_float(hit.tri));
                     wb.hitB[L.path] = (hit.kind << 30) | (hit.idx & 0x3FFFFFFFu);
@@ -321,6 +321,143 @@ traceFastKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ F
             atomicAdd(st + 3, (unsigned long long)stNodeIters); atomicAdd(st + 4, (unsigned long long)stTriIters); atomicAdd(st + 5, (unsigned long long)stRefills);
             atomicAdd(st + 6, (unsigned long long)(clock64() - stStart)); atomicMax(st + 7, (unsigned long long)(clock64() - stStart));
         }
+    }
+#endif
+}
+
+
+/* ------------------------------------------------------------- trace, wide layout
+ * The same persistent-warp scheme as traceFastKernel over the wide layout (okrt_wide.cuh): a NODE phase (every lane with a
+ * pending node group visits one 8-wide node: three 256-bit loads, eight quantised slab tests) and a TRIANGLE phase (every lane
+ * with hit leaves enters one leaf — exact box test — and / or tests one triangle).  A lane's leaves are tested before it
+ * descends further (they belong to the node it just visited: the nearest geometry it knows). */
+#ifndef OKRT_WIDE_MIN_BLOCKS
+#define OKRT_WIDE_MIN_BLOCKS 8
+#endif
+#ifndef OKRT_WIDE_NODE_KEEP
+#define OKRT_WIDE_NODE_KEEP 8
+#endif
+#ifndef OKRT_WIDE_TRI_KEEP
+#define OKRT_WIDE_TRI_KEEP 8
+#endif
+#ifndef OKRT_WIDE_REFILL_IDLE
+#define OKRT_WIDE_REFILL_IDLE 12
+#endif
+__global__ void __launch_bounds__(kTraceBlockThreads, OKRT_WIDE_MIN_BLOCKS)
+traceWideKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ FrameParams fp, const WavefrontBuffers wb,
+                const uint32_t* __restrict__ queueIn, uint32_t bounce)
+{
+    const uint32_t count = wb.counts[2u * bounce];
+    uint32_t* workCounter = wb.counts + 2u * bounce + 1u;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t laneMaskLt = (1u << lane) - 1u;
+    const uint32_t numSpheres = fp.rd.numSpheres < s.numSpheres ? fp.rd.numSpheres : s.numSpheres;
+
+    uint32_t stack[kWideStackWords + kWideColdWords];
+    WideLane L;
+    L.sp = 0; L.path = 0u; L.inst = kTraceTop; L.lg = 0u; L.triNext = L.triEnd = 0u; L.ngHits = 0u; L.ngBase = 0u; L.flags = 0u;
+    L.best = L.lam = OKRT_FLT_MAX; L.leafNear = L.leafSlack = 0.f; L.octInv = 0u;
+    L.ro = L.rd = L.ridir = v3(0.f, 0.f, 0.f);
+#ifdef OKRT_TRACE_STATS
+    L.stNodes = L.stLeaves = L.stTris = 0u;
+    uint32_t stNodeIters = 0u, stTriIters = 0u, stRefills = 0u, stRays = 0u, stNodeSum = 0u, stLeafSum = 0u, stTriSum = 0u, stNodeLanes = 0u, stTriLanes = 0u;
+    const long long stStart = clock64();
+#endif
+    bool have = false;                        /* this lane owns a ray whose result is not written yet */
+    uint32_t next = 0u, end = 0u;             /* warp-uniform: unclaimed part of the warp's current chunk */
+    bool exhausted = false;                   /* warp-uniform */
+
+    for (;;) {
+        const bool wantsTri = have && wideWantsTri(L), wantsNode = have && wideWantsNode(L);
+        const uint32_t nNode = (uint32_t)__popc(__ballot_sync(0xFFFFFFFFu, wantsNode));
+        const uint32_t nTri = (uint32_t)__popc(__ballot_sync(0xFFFFFFFFu, wantsTri));
+        const uint32_t active = nNode + nTri;
+        if (active == 0u || (!exhausted && active <= 32u - (uint32_t)OKRT_WIDE_REFILL_IDLE)) {
+            /* ---- finished lanes write their hit record (or queue the ray for the reference order) */
+            if (have && wideDone(L)) {
+                Hit hit;
+                float limit;
+                if (wideResult(s, L, stack, wb.rayD + L.path, hit, limit)) {
+                    wb.fallbackQueue[atomicAdd(wb.fallbackCounts + bounce, 1u)] = L.path;
+                    wb.hitA[L.path].x = limit;                           /* bounds the reference-order traversal's search */
+                } else {
+                    wb.hitA[L.path] = make_float4(hit.distance, hit.u, hit.v, __uint_as_float(hit.tri));
+                    wb.hitB[L.path] = (hit.kind << 30) | (hit.idx & 0x3FFFFFFFu);
+                }
+#ifdef OKRT_TRACE_STATS
+                stNodeSum += L.stNodes; stLeafSum += L.stLeaves; stTriSum += L.stTris;
+#endif
+                have = false;
+            }
+            /* ---- refill */
+#ifdef OKRT_TRACE_STATS
+            stRefills++;
+#endif
+            uint32_t need = __ballot_sync(0xFFFFFFFFu, !have);
+            while (need != 0u && !exhausted) {
+                if (next == end) {
+                    uint32_t base = 0u;
+                    if (lane == 0u) base = atomicAdd(workCounter, kTraceChunk);
+                    base = __shfl_sync(0xFFFFFFFFu, base, 0);
+                    if (base >= count) { exhausted = true; break; }
+                    next = base; end = min(base + kTraceChunk, count);
+                }
+                const uint32_t want = __popc(need), avail = end - next;
+                const uint32_t take = want < avail ? want : avail;
+                const uint32_t rank = __popc(need & laneMaskLt);
+                if (!have && rank < take) {
+                    const uint32_t k = next + rank;
+                    L.path = queueIn ? __ldg(queueIn + k) : k;
+                    const float4 ro = wb.rayO[L.path], rdv = wb.rayD[L.path];
+                    wideInit(s, L, stack, numSpheres, v3(ro.x, ro.y, ro.z), v3(rdv.x, rdv.y, rdv.z));
+                    have = true;
+#ifdef OKRT_TRACE_STATS
+                    stRays++;
+#endif
+                }
+                next += take;
+                need = __ballot_sync(0xFFFFFFFFu, !have);
+            }
+            if (__ballot_sync(0xFFFFFFFFu, have) == 0u) break;
+            continue;
+        }
+        if (nNode >= nTri) {
+            const uint32_t keep = min((uint32_t)OKRT_WIDE_NODE_KEEP, nNode);
+            uint32_t left;
+            do {
+                const bool mine = have && wideWantsNode(L);
+#ifdef OKRT_TRACE_STATS
+                stNodeIters++; if (mine) stNodeLanes++;
+#endif
+                if (mine) wideNodeStep(s, L, stack, wb.rayO, wb.rayD);
+                left = (uint32_t)__popc(__ballot_sync(0xFFFFFFFFu, have && wideWantsNode(L)));
+            } while (left >= keep);
+        } else {
+            const uint32_t keep = min((uint32_t)OKRT_WIDE_TRI_KEEP, nTri);
+            uint32_t left;
+            do {
+                const bool mine = have && wideWantsTri(L);
+#ifdef OKRT_TRACE_STATS
+                stTriIters++; if (mine) stTriLanes++;
+#endif
+                if (mine) wideTriStep(s, L, stack, wb.rayO, wb.rayD);
+                left = (uint32_t)__popc(__ballot_sync(0xFFFFFFFFu, have && wideWantsTri(L)));
+            } while (left >= keep);
+        }
+    }
+#ifdef OKRT_TRACE_STATS
+    {
+        /* per bounce: [0] rays [1] node steps [2] leaf entries [3] triangle tests [4] node-phase iterations (warps) [5] triangle-phase
+         * iterations [6] lanes busy in node iterations [7] lanes busy in triangle iterations */
+        unsigned long long* st = wb.traceStats + 8u * bounce;
+        const uint32_t a0 = __reduce_add_sync(0xFFFFFFFFu, stRays), a1 = __reduce_add_sync(0xFFFFFFFFu, stNodeSum), a2 = __reduce_add_sync(0xFFFFFFFFu, stLeafSum);
+        const uint32_t a3 = __reduce_add_sync(0xFFFFFFFFu, stTriSum), a6 = __reduce_add_sync(0xFFFFFFFFu, stNodeLanes), a7 = __reduce_add_sync(0xFFFFFFFFu, stTriLanes);
+        if (lane == 0u) {
+            atomicAdd(st + 0, (unsigned long long)a0); atomicAdd(st + 1, (unsigned long long)a1); atomicAdd(st + 2, (unsigned long long)a2);
+            atomicAdd(st + 3, (unsigned long long)a3); atomicAdd(st + 4, (unsigned long long)stNodeIters); atomicAdd(st + 5, (unsigned long long)stTriIters);
+            atomicAdd(st + 6, (unsigned long long)a6); atomicAdd(st + 7, (unsigned long long)a7);
+        }
+        (void)stStart; (void)stRefills;
     }
 #endif
 }

@@ -627,3 +627,24 @@ def adversarial_scene(kind, offset=(0.0, 0.0, 0.0), seed=5):
         raise ValueError(kind)
     info = dict(name="adversarial_" + kind, stand_in=False, octree=(2, 50), bvh=(30, 5), offset=tuple(offset))
     return rm, sc, info
+
+
+def moved_props_scene(seed=17):
+    """24 props whose LOCAL boxes lie behind a wall (z 14..26) while two thirds of them are translated in front of it
+    (z -16..-4): createOctTree sorts occupants by their untransformed boxes (RayTracer.cpp:562), so the oct-tree nodes that
+    list the moved props do not contain them, and the reference culls those nodes against the wall."""
+    rng = np.random.default_rng(seed)
+    rm, sc = ResourceManager(), Scene()
+    for k in range(24):
+        c = np.array([rng.uniform(-10, 10), rng.uniform(-10, 10), rng.uniform(15, 25)])
+        if k % 2:
+            mesh = make_mesh(*box(c - 1.0, c + 1.0))
+        else:
+            p, n, uv = icosphere(2, 1.2, tuple(c))
+            mesh = make_mesh(p, n, uv)
+        sc.addMeshEntity(rm.addMesh(mesh), material(albedo=tuple(rng.uniform(0.3, 0.9, 3)), roughness=float(rng.uniform(0.1, 1.0)), metallic=float(k % 2)),
+                         position=(float(rng.uniform(-3, 3)), float(rng.uniform(-3, 3)), -30.0) if k % 3 else (0, 0, 0))
+    wall = make_mesh(*quad((-40, -40, 10), (40, -40, 10), (40, 40, 10), (-40, 40, 10)))
+    sc.addMeshEntity(rm.addMesh(wall), material(albedo=(0.9, 0.9, 0.9)))
+    sc.setCamera((0, 0, -30), (0, 0, 0), 80.0, 0.1)
+    return rm, sc, dict(name="moved_props", stand_in=False, bvh=(30, 5), octree=(3, 3))

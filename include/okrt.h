@@ -407,6 +407,16 @@ OKRT_API int okrt_layout_report(const okrt_triangle* tris, uint32_t numTris, con
                                 const okrt_mesh_instance* instances, uint32_t numInstances,
                                 const okrt_octree_node* octNodes, uint32_t numOctNodes, okrt_layout_info* out);
 
+/* Host-only check of the near-first traversal (no GPU): runs the traversal kernels' lane functions, compiled for the host,
+ * over arbitrary rays (6 floats per ray: origin, direction) on the layout okrt_render would build from the same arrays.
+ * out: 12 words per ray — distance, u, v (float bits), triangle, kind (0 miss / 2 mesh), instance index, 1 if the reference
+ * order has to decide, the bound left for that traversal (float bits), node steps, leaf entries, triangle tests, 0.
+ * Lets tests/ compare the traversal with the oracle's findClosestHit (RaytracerCS.hlsl:218-334) where no GPU exists. */
+OKRT_API int okrt_trace_rays_host(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh_node* nodes, uint32_t numNodes,
+                                  const okrt_mesh_instance* instances, uint32_t numInstances,
+                                  const okrt_octree_node* octNodes, uint32_t numOctNodes,
+                                  const float* rays, uint32_t numRays, uint32_t* out);
+
 /* ------------------------------------------------------- renderer (device) */
 OKRT_API int  okrt_create(int device, uint32_t width, uint32_t height, okrt_renderer** out); /* RayTracer::initiate :60 */
 OKRT_API void okrt_destroy(okrt_renderer* r);                                                 /* RayTracer::shutdown :34 */
@@ -469,6 +479,9 @@ OKRT_API uint32_t okrt_shard_owner_of_row(uint32_t y, uint32_t bandRows, uint32_
 OKRT_API uint32_t okrt_shard_seed_frame(const okrt_options* o, uint32_t localFrame, uint32_t accumulationEnabled);
 
 OKRT_API int okrt_get_stats(okrt_renderer* r, okrt_stats* out);   /* synchronises */
+/* step counters of the traversal kernel since okrt_reset_stats (8 x uint64 per bounce: rays, node steps, leaf entries, triangle
+ * tests, node-phase iterations, triangle-phase iterations, lanes busy in either); OKRT_ERR_STATE unless built with -DOKRT_TRACE_STATS */
+OKRT_API int okrt_get_trace_stats(okrt_renderer* r, uint64_t* out, uint32_t bounces);
 OKRT_API int okrt_reset_stats(okrt_renderer* r);
 
 #ifdef __cplusplus

@@ -50,6 +50,8 @@ class Oracle:
         lib.oracle_render.argtypes = [ctypes.POINTER(OracleScene), _P, _U, _U, _U, _P, _P, _P, _U, _U, _I, _I, ctypes.POINTER(ctypes.c_uint64)]
         lib.oracle_render_rows.restype = _U
         lib.oracle_render_rows.argtypes = [ctypes.POINTER(OracleScene), _P, _U, _U, _U, _P, _P, _P, _P, _U, _I, _I, ctypes.POINTER(ctypes.c_uint64)]
+        lib.oracle_trace_rays.restype = None
+        lib.oracle_trace_rays.argtypes = [ctypes.POINTER(OracleScene), _P, _P, _U, _P, _I]
         lib.oracle_last_visit_totals.restype = None
         lib.oracle_last_visit_totals.argtypes = [_P]
         lib.oracle_pcg_hash.restype = _U
@@ -110,6 +112,14 @@ class Oracle:
             s.envH, s.envW = envFaces.shape[1], envFaces.shape[2]
         s._keep = keep
         return s
+
+    def trace_rays(self, scene, rd, rays, threads=0):
+        """findClosestHit for an [n, 6] float32 array of rays; returns an [n, 6] uint32 array
+        (distance, u, v as float bits, triangle, kind, index)."""
+        rays = np.ascontiguousarray(rays, np.float32)
+        out = np.zeros((len(rays), 6), np.uint32)
+        self.lib.oracle_trace_rays(ctypes.byref(scene), rd.ctypes.data_as(_P), rays.ctypes.data_as(_P), len(rays), out.ctypes.data_as(_P), threads)
+        return out
 
     def render(self, scene, rd, maxBounces, seedFrame=None, coverAll=0, accum=None, result=None, aov_dtype=None,
                rows=None, threads=0, math=MATH_CANONICAL, row_list=None):

@@ -889,6 +889,36 @@ ORACLE_API uint32_t oracle_render(const OracleScene* scene, const RenderData* rd
     return renderRows(scene, rd, maxBounces, seedFrame, coverAll, accum, result, aov, nullptr, y0, y1, threads, mathMode, outSegments);
 }
 
+/* findClosestHit (RaytracerCS.hlsl:218-334) for arbitrary rays: 6 floats per ray in (origin, direction), 6 words per ray
+ * out (distance, u, v as float bits, triangle, kind 0/1/2, instance-or-sphere index).  Lets the tests compare a traversal of
+ * the product with the reference order ray by ray, without rendering. */
+ORACLE_API void oracle_trace_rays(const OracleScene* scene, const RenderData* rd, const float* rays, uint32_t numRays, uint32_t* out, int threads)
+{
+    unsigned nthreads = threads > 0 ? (unsigned)threads : std::max(1u, std::thread::hardware_concurrency());
+    std::atomic<uint32_t> nextRay(0);
+    auto worker = [&]() {
+        Ctx c;
+        c.s = scene; c.rd = rd; c.mathMode = ORACLE_MATH_CANONICAL; c.stackOverflow = 0;
+        for (;;) {
+            const uint32_t begin = nextRay.fetch_add(1024u);
+            if (begin >= numRays) break;
+            for (uint32_t i = begin; i < std::min(numRays, begin + 1024u); i++) {
+                const float* r = rays + (size_t)i * 6;
+                Ray ray; ray.origin = float3{r[0], r[1], r[2]}; ray.direction = float3{r[3], r[4], r[5]};
+                uint32_t bb = 0, tc = 0;
+                HitTap tap;
+                const Payload p = findClosestHit(c, ray, bb, tc, &tap);
+                uint32_t* o = out + (size_t)i * 6;
+                std::memcpy(o + 0, &p.distance, 4); std::memcpy(o + 1, &tap.u, 4); std::memcpy(o + 2, &tap.v, 4);
+                o[3] = tap.triIdx; o[4] = tap.hitKind; o[5] = tap.hitIdx;
+            }
+        }
+    };
+    std::vector<std::thread> pool;
+    for (unsigned t = 0; t < nthreads; t++) pool.emplace_back(worker);
+    for (auto& th : pool) th.join();
+}
+
 /* same, for an explicit list of image rows (bounded samples of a frame, tile-sharded ranks) */
 ORACLE_API uint32_t oracle_render_rows(const OracleScene* scene, const RenderData* rd, uint32_t maxBounces, uint32_t seedFrame,
                                        uint32_t coverAll, float* accum, uint8_t* result, Aov* aov,

@@ -157,6 +157,28 @@ def test_lights_and_transforms(okrt, oracle):
         r.close()
 
 
+def test_moved_props_under_child_oct_nodes(okrt, oracle):
+    """oct-tree nodes that do not contain the (translated) instances they list — the reference culls such a node,
+    and everything below it, against a FARTHER hit (RaytracerCS.hlsl:262-264).  The near-first path has to notice (the node's
+    distNear joins the winner's gate) and let the reference order decide those rays."""
+    _require_gpu(okrt)
+    abi = okrt.abi
+    rm, sc, info = okrt.scenes.moved_props_scene()
+    W, H = 256, 144
+    host = helpers.build_host_side(okrt, rm, sc, info, W, H)
+    assert len(host["octree"].nodes) > 1
+    env = okrt.scenes.procedural_sky_faces(16)
+    rdo = host["rd"].copy(); rdo[0]["numAccumulationFrames"] = 1
+    o = oracle.render(helpers.oracle_scene(oracle, host, envFaces=env), rdo, 4, aov_dtype=abi.AOV)
+    for traversal in (0, 1):
+        r = helpers.Renderer(okrt, host, W, H, envFaces=env)
+        r.options(maxBounces=4, traversal=traversal, writeAov=1)
+        r.render(host["rd"].copy())
+        _compare_aov(r.aov(), o["aov"], exact_counters=(traversal == 1))
+        assert np.array_equal(r.accumulation().view(np.uint32), o["accum"].view(np.uint32))
+        r.close()
+
+
 def test_scaled_instances_use_reference_order(okrt, oracle):
     """Non-unit scale makes the reference's local-vs-world culling order dependent [Q4]: the library must
     switch to the reference visiting order by itself and still match."""
