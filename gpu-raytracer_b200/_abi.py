@@ -70,7 +70,7 @@ class MeshView(ctypes.Structure):
                 ("numTriangles", ctypes.c_uint32), ("boundingBox", ctypes.c_float * 6)]
 
 
-TRAVERSAL_FAST, TRAVERSAL_EXACT = 0, 1
+TRAVERSAL_FAST, TRAVERSAL_EXACT, TRAVERSAL_WIDE = 0, 1, 2
 SHARD_NONE, SHARD_TILE = 0, 1
 PIPELINE_WAVEFRONT, PIPELINE_MEGAKERNEL = 0, 1
 
@@ -166,7 +166,7 @@ SYMBOLS = [
     ("okrt_get_stats", _I, [_P, _P]),
     ("okrt_reset_stats", _I, [_P]),
     ("okrt_get_trace_stats", _I, [_P, _P, _U]),
-    ("okrt_trace_rays_host", _I, [_P, _U, _P, _U, _P, _U, _P, _U, _P, _U, _P]),
+    ("okrt_trace_rays_host", _I, [_P, _U, _P, _U, _P, _U, _P, _U, _U, _P, _U, _P]),
 ]
 
 

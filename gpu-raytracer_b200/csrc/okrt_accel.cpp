@@ -476,7 +476,7 @@ inline float roundUp(double v) { float f = (float)v; return (double)f < v ? std:
 
 bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh_node* nodes, uint32_t numNodes,
                      const okrt_mesh_instance* instances, uint32_t numInstances,
-                     const okrt_octree_node* octNodes, uint32_t numOctNodes, FastLayout& out)
+                     const okrt_octree_node* octNodes, uint32_t numOctNodes, FastLayout& out, bool wantWide)
 {
     out = FastLayout();
     const bool verbose = std::getenv("OKRT_LAYOUT_VERBOSE") != nullptr;
@@ -628,6 +628,16 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
          * A BVH whose interior boxes do not contain their children (possible for uploaded arrays, never for BvhBuilder's) makes
          * the reference's own culls order dependent inside the mesh: such an instance is walked by the reference order only. */
         const bool orderDependent = !flattenable(nodes, numNodes, inst.bvhNodeStartIdx);
+        /* An identity instance is MERGED into the scene-wide tree only if the oct-tree boxes above it contain its root box up to
+         * the rounding of createOctTree's centre / extents arithmetic (a few ulp): then a ray enters those boxes no later than
+         * (1 + ~1e-6) x the hit, which the traversal's window covers.  Otherwise it is walked as an instance, whose oct-tree
+         * distNear is known before anything inside it is tested. */
+        bool octContains = true;
+        for (uint32_t on = instOct[i]; on != 0xFFFFFFFFu && octContains; on = out.octParent[on])
+            for (int k = 0; k < 3; k++) {
+                const double tol = 1e-5 * std::max(1.0, std::max(std::fabs(worldLo[k]), std::fabs(worldHi[k])));
+                octContains = octContains && (double)octNodes[on].boundingBox.min[k] <= worldLo[k] + tol && worldHi[k] - tol <= (double)octNodes[on].boundingBox.max[k];
+            }
         const uint32_t rec = (uint32_t)(out.instances.size() / kInstQuads);
         out.instances.resize(out.instances.size() + kInstQuads);
         Float4* r = &out.instances[(size_t)rec * kInstQuads];
@@ -643,7 +653,7 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
          * local ray is the same for all such instances (normalize(d*I), o*I), so the top-level tree can link
          * straight to its BVH root with the root's exact box — no ray switch, no exit marker.  Its triangles
          * remember their owner so that a hit can name the instance (and check its oct-tree chain). */
-        bool merged = identity && rootUsers[inst.bvhNodeStartIdx] == 1u;
+        bool merged = identity && rootUsers[inst.bvhNodeStartIdx] == 1u && octContains;
         std::vector<std::pair<uint32_t, uint32_t>> ranges;
         if (merged) {
             std::vector<uint32_t> st{inst.bvhNodeStartIdx};
@@ -867,7 +877,7 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
     }
     /* wide layout: the same scene-wide tree collapsed into 8-wide quantised nodes; instances that are walked with a ray switch
      * get their own wide tree (one per distinct mesh), its root in r8.w of the record */
-    if (!leaves.empty()) {
+    if (!leaves.empty() && wantWide) {
         WideEmitter we{tn, tris, out};
         uint32_t topWideDepth = 0, instWideDepth = 0;
         if (!we.emitTree(wideBinaryRoot, out.wideRoot, topWideDepth)) { out.error = we.error; return false; }

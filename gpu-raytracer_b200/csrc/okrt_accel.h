@@ -104,6 +104,6 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris,
                      const okrt_bvh_node* nodes, uint32_t numNodes,
                      const okrt_mesh_instance* instances, uint32_t numInstances,
                      const okrt_octree_node* octNodes, uint32_t numOctNodes,
-                     FastLayout& out);
+                     FastLayout& out, bool wantWide = false);
 
 } // namespace okrt

@@ -144,7 +144,8 @@ struct okrt_renderer {
     uint64_t launches = 0;
     float lastRenderMs = 0.f;
     int numSms = 0, blocksPerSmLean = 1, blocksPerSmInstrumented = 1;   /* persistent grid = SMs x resident blocks */
-    int blocksPerSmTrace = 1;
+    int blocksPerSmTrace = 1, blocksPerSmWide = 1;
+    bool layoutHasWide = false;                 /* the wide layout is built only for OKRT_TRAVERSAL_WIDE */
     WavefrontBuffers wb{};                      /* path state of the wavefront pipeline (sized for width x height) */
     size_t wbPaths = 0, wbReserve = 0;
 };
@@ -179,8 +180,9 @@ int ensureAov(okrt_renderer* r)
 int rebuildLayout(okrt_renderer* r)
 {
     FastLayout fl;
+    const bool wantWide = r->opt.traversal == OKRT_TRAVERSAL_WIDE;
     if (!buildFastLayout(r->hTris.data(), (uint32_t)r->hTris.size(), r->hNodes.data(), (uint32_t)r->hNodes.size(),
-                         r->hInstances.data(), (uint32_t)r->hInstances.size(), r->hOct.data(), (uint32_t)r->hOct.size(), fl)) {
+                         r->hInstances.data(), (uint32_t)r->hInstances.size(), r->hOct.data(), (uint32_t)r->hOct.size(), fl, wantWide)) {
         setError("scene rejected: " + fl.error);
         return OKRT_ERR_INVALID_ARGUMENT;
     }
@@ -199,7 +201,7 @@ int rebuildLayout(okrt_renderer* r)
     if (fl.wideNodes.size() / kWideNodeWords >= (1u << 24) - 1u) { setError("scene too large: the wide layout names nodes with 24 bits"); return OKRT_ERR_CAPACITY; }
     if ((rc = r->wideNodes.upload(fl.wideNodes.data(), (uint32_t)fl.wideNodes.size(), sizeof(uint32_t), r->stream))) return rc;
     if ((rc = r->wideLeaves.upload(fl.wideLeaves.data(), (uint32_t)fl.wideLeaves.size(), sizeof(uint32_t), r->stream))) return rc;
-    r->wideRoot = fl.wideRoot; r->maxSlack = fl.maxSlack;
+    r->wideRoot = fl.wideRoot; r->maxSlack = fl.maxSlack; r->layoutHasWide = wantWide;
     if (r->fastTrisTex) { cudaDestroyTextureObject(r->fastTrisTex); r->fastTrisTex = 0; }
     if (r->fastTris.bytes) {            /* the triangle records as float4 texels: stepTriangle fetches them through the texture pipe */
         int maxTexels = 0;
@@ -338,11 +340,12 @@ int launchWavefront(okrt_renderer* r, const FrameParams& fpWhole, bool instrumen
     const char* shadeWaves = std::getenv("OKRT_SHADE_WAVES");     /* tuning knob: resident-block multiples per SM */
     static const int traceBlocksEnv = [] { const char* e = std::getenv("OKRT_TRACE_BLOCKS"); return e ? std::max(1, std::atoi(e)) : 1 << 20; }();
     static const int shadeBlocksEnv = [] { const char* e = std::getenv("OKRT_SHADE_BLOCKS"); return e ? std::max(1, std::atoi(e)) : 0; }();
-    unsigned flatGridH[2], traceGridH[2], shadeGridH[2], fallbackGridH[2];
+    unsigned flatGridH[2], traceGridH[2], wideGridH[2], shadeGridH[2], fallbackGridH[2];
     for (int h = 0; h < halves; h++) {
         const size_t pathsH = slots * fpH[h].batchFrames;
         flatGridH[h] = (unsigned)((pathsH + 127) / 128);
         traceGridH[h] = std::min<unsigned>((unsigned)(r->numSms * std::min(r->blocksPerSmTrace, traceBlocksEnv)), std::max(1u, flatGridH[h]));
+        wideGridH[h] = std::min<unsigned>((unsigned)(r->numSms * std::min(r->blocksPerSmWide, traceBlocksEnv)), std::max(1u, flatGridH[h]));
         shadeGridH[h] = std::min<unsigned>((unsigned)(r->numSms * OKRT_SHADE_MIN_BLOCKS * (shadeWaves ? std::max(1, std::atoi(shadeWaves)) : 16)),
                                            std::max(1u, flatGridH[h]));
         if (shadeBlocksEnv) shadeGridH[h] = std::min<unsigned>((unsigned)(r->numSms * shadeBlocksEnv), std::max(1u, flatGridH[h]));
@@ -374,11 +377,8 @@ int launchWavefront(okrt_renderer* r, const FrameParams& fpWhole, bool instrumen
                  * fallback / generate work */
                 if (dual && serialTrace && lastTraceEnd) OKRT_CUDA(cudaStreamWaitEvent(st[h], lastTraceEnd, 0));
                 OKRT_CUDA(cudaEventRecord(e0, st[h]));
-#if OKRT_WIDE
-                traceWideKernel<<<traceGridH[h], kTraceBlockThreads, 0, st[h]>>>(scene, fp, wb, qin, b);
-#else
-                traceFastKernel<<<traceGridH[h], kTraceBlockThreads, 0, st[h]>>>(scene, fp, wb, qin, b);
-#endif
+                if (fp.traversal == OKRT_TRAVERSAL_WIDE) traceWideKernel<<<wideGridH[h], kTraceBlockThreads, 0, st[h]>>>(scene, fp, wb, qin, b);
+                else traceFastKernel<<<traceGridH[h], kTraceBlockThreads, 0, st[h]>>>(scene, fp, wb, qin, b);
                 OKRT_CUDA(cudaEventRecord(e1, st[h]));
                 lastTraceEnd = e1;
                 traceFallbackKernel<<<fallbackGridH[h], 128, 0, st[h]>>>(scene, fp, wb, b);
@@ -462,7 +462,7 @@ int launchFrames(okrt_renderer* r, uint32_t want, uint32_t& done)
     fp.batchFrames = done;
     /* scaled instances make the reference's local-vs-world culling order dependent; debug heat maps
      * display the reference's own visit counters: both need the reference visiting order */
-    fp.traversal = (r->opt.traversal == OKRT_TRAVERSAL_EXACT || !r->allRigid || r->rd.debugMode != 0u) ? OKRT_TRAVERSAL_EXACT : OKRT_TRAVERSAL_FAST;
+    fp.traversal = (r->opt.traversal == OKRT_TRAVERSAL_EXACT || !r->allRigid || r->rd.debugMode != 0u) ? OKRT_TRAVERSAL_EXACT : r->opt.traversal;
     coveredExtent(r, fp.coveredW, fp.coveredH);
     fp.accumulation = r->accumulation;
     fp.result = r->result;
@@ -549,11 +549,8 @@ int okrt_create(int device, uint32_t width, uint32_t height, okrt_renderer** out
     if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess ||
         (e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&r->blocksPerSmLean, pathTraceKernel<false>, kBlockThreads, 0)) != cudaSuccess ||
         (e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&r->blocksPerSmInstrumented, pathTraceKernel<true>, kBlockThreads, 0)) != cudaSuccess ||
-#if OKRT_WIDE
-        (e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&r->blocksPerSmTrace, traceWideKernel, kTraceBlockThreads, 0)) != cudaSuccess) {
-#else
-        (e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&r->blocksPerSmTrace, traceFastKernel, kTraceBlockThreads, 0)) != cudaSuccess) {
-#endif
+        (e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&r->blocksPerSmTrace, traceFastKernel, kTraceBlockThreads, 0)) != cudaSuccess ||
+        (e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&r->blocksPerSmWide, traceWideKernel, kTraceBlockThreads, 0)) != cudaSuccess) {
         setError(std::string("okrt_create: ") + cudaGetErrorString(e));
         okrt_destroy(r);
         return OKRT_ERR_CUDA;
@@ -571,6 +568,7 @@ int okrt_create(int device, uint32_t width, uint32_t height, okrt_renderer** out
     r->blocksPerSmLean = std::max(1, r->blocksPerSmLean);
     r->blocksPerSmInstrumented = std::max(1, r->blocksPerSmInstrumented);
     r->blocksPerSmTrace = std::max(1, r->blocksPerSmTrace);
+    r->blocksPerSmWide = std::max(1, r->blocksPerSmWide);
     const int rc = allocateImages(r);
     if (rc) { okrt_destroy(r); return rc; }
     *out = r;
@@ -716,7 +714,9 @@ int okrt_get_render_data(const okrt_renderer* r, okrt_render_data* out)
 int okrt_set_options(okrt_renderer* r, const okrt_options* o)
 {
     if (!r || !o) { setError("okrt_set_options: null argument"); return OKRT_ERR_INVALID_ARGUMENT; }
-    if (o->traversal > OKRT_TRAVERSAL_EXACT || o->shardMode > OKRT_SHARD_TILE || o->pipeline > OKRT_PIPELINE_MEGAKERNEL) { setError("okrt_set_options: unknown mode"); return OKRT_ERR_INVALID_ARGUMENT; }
+    if (o->traversal > OKRT_TRAVERSAL_WIDE || o->shardMode > OKRT_SHARD_TILE || o->pipeline > OKRT_PIPELINE_MEGAKERNEL) { setError("okrt_set_options: unknown mode"); return OKRT_ERR_INVALID_ARGUMENT; }
+    if (o->traversal == OKRT_TRAVERSAL_WIDE && o->pipeline != OKRT_PIPELINE_WAVEFRONT) { setError("okrt_set_options: OKRT_TRAVERSAL_WIDE needs the wavefront pipeline"); return OKRT_ERR_INVALID_ARGUMENT; }
+    if (o->traversal == OKRT_TRAVERSAL_WIDE && !r->layoutHasWide) r->layoutDirty = true;
     if (o->shardMode == OKRT_SHARD_TILE && (o->shardCount == 0u || o->shardRank >= o->shardCount)) { setError("okrt_set_options: shardRank/shardCount"); return OKRT_ERR_INVALID_ARGUMENT; }
     if (o->shardBandRows % kTileH) { setError("okrt_set_options: shardBandRows must be a multiple of 8"); return OKRT_ERR_INVALID_ARGUMENT; }
     const bool coverageChanged = (r->opt.coverAllPixels != 0u) != (o->coverAllPixels != 0u);
@@ -993,22 +993,27 @@ int okrt_get_trace_stats(okrt_renderer* r, uint64_t* out, uint32_t bounces)
  * The step counts need a -DOKRT_TRACE_STATS build (0 otherwise). */
 int okrt_trace_rays_host(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh_node* nodes, uint32_t numNodes,
                          const okrt_mesh_instance* instances, uint32_t numInstances, const okrt_octree_node* octNodes, uint32_t numOctNodes,
-                         const float* rays, uint32_t numRays, uint32_t* out)
+                         uint32_t traversal, const float* rays, uint32_t numRays, uint32_t* out)
 {
-    if ((numRays && (!rays || !out))) { setError("okrt_trace_rays_host: null argument"); return OKRT_ERR_INVALID_ARGUMENT; }
+    if ((numRays && (!rays || !out)) || (traversal != OKRT_TRAVERSAL_FAST && traversal != OKRT_TRAVERSAL_WIDE)) { setError("okrt_trace_rays_host: bad argument"); return OKRT_ERR_INVALID_ARGUMENT; }
+    const bool wide = traversal == OKRT_TRAVERSAL_WIDE;
     FastLayout fl;
-    if (!buildFastLayout(tris, numTris, nodes, numNodes, instances, numInstances, octNodes, numOctNodes, fl)) {
+    if (!buildFastLayout(tris, numTris, nodes, numNodes, instances, numInstances, octNodes, numOctNodes, fl, wide)) {
         setError("scene rejected: " + fl.error);
         return OKRT_ERR_INVALID_ARGUMENT;
     }
-    if (fl.wideStackDepth > kWideStackCapacity) { setError("traversal stack would overflow"); return OKRT_ERR_CAPACITY; }
+    if (fl.wideStackDepth > kWideStackCapacity || fl.maxStackDepth > kFastStackCapacity) { setError("traversal stack would overflow"); return OKRT_ERR_CAPACITY; }
     if (!fl.allRigid) { setError("okrt_trace_rays_host: scaled instances use the reference order"); return OKRT_ERR_STATE; }
     DeviceScene s;
     std::memset(&s, 0, sizeof(s));
     s.octNodes = octNodes; s.instances = instances; s.numOctNodes = numOctNodes; s.numInstances = numInstances; s.numTris = numTris;
     s.fastTris = (const float4*)fl.tris.data(); s.fastInstances = (const float4*)fl.instances.data(); s.octParent = fl.octParent.data();
     s.numFastInstances = (uint32_t)(fl.instances.size() / kInstQuads);
+    s.topRef = fl.topRef; s.numFastNodes = (uint32_t)(fl.nodes.size() / 4);
     /* the node and leaf arrays are read with 32-byte loads */
+    std::vector<uint4> pn((fl.nodes.size() * sizeof(Float4) + 31) / 32 * 2);
+    if (!fl.nodes.empty()) std::memcpy(pn.data(), fl.nodes.data(), fl.nodes.size() * sizeof(Float4));
+    s.fastNodes = (const float4*)pn.data();
     std::vector<uint4> wn((fl.wideNodes.size() + 3) / 4), wl((fl.wideLeaves.size() + 3) / 4);
     if (!fl.wideNodes.empty()) std::memcpy(wn.data(), fl.wideNodes.data(), fl.wideNodes.size() * 4);
     if (!fl.wideLeaves.empty()) std::memcpy(wl.data(), fl.wideLeaves.data(), fl.wideLeaves.size() * 4);
@@ -1025,7 +1030,8 @@ int okrt_trace_rays_host(const okrt_triangle* tris, uint32_t numTris, const okrt
                 for (uint32_t i = begin; i < std::min(numRays, begin + 1024u); i++) {
                     const float* r6 = rays + (size_t)i * 6;
                     Hit hit; float limit = 0.f; uint32_t counts[4] = {0u, 0u, 0u, 0u};
-                    const bool ambiguous = wideTraverse(s, 0u, v3(r6[0], r6[1], r6[2]), v3(r6[3], r6[4], r6[5]), hit, limit, counts);
+                    const V3 ro = v3(r6[0], r6[1], r6[2]), rd = v3(r6[3], r6[4], r6[5]);
+                    const bool ambiguous = wide ? wideTraverse(s, 0u, ro, rd, hit, limit, counts) : traverseFast(s, 0u, ro, rd, hit, limit);
                     uint32_t* o = out + (size_t)i * 12;
                     std::memcpy(o + 0, &hit.distance, 4); std::memcpy(o + 1, &hit.u, 4); std::memcpy(o + 2, &hit.v, 4);
                     o[3] = hit.tri; o[4] = hit.kind; o[5] = hit.idx; o[6] = ambiguous ? 1u : 0u; std::memcpy(o + 7, &limit, 4);

@@ -127,6 +127,110 @@ struct FrameParams {
     unsigned long long* counters;             /* [0] segments, [1] fallback segments, [2] pixels */
 };
 
+/* ------------------------------------------------------------------ portable intrinsics (host + device) */
+OKRT_HD uint32_t wBits(float f)
+{
+#ifdef __CUDA_ARCH__
+    return __float_as_uint(f);
+#else
+    uint32_t u; memcpy(&u, &f, 4); return u;
+#endif
+}
+OKRT_HD float wFloat(uint32_t u)
+{
+#ifdef __CUDA_ARCH__
+    return __uint_as_float(u);
+#else
+    float f; memcpy(&f, &u, 4); return f;
+#endif
+}
+OKRT_HD float wFma(float a, float b, float c)
+{
+#ifdef __CUDA_ARCH__
+    return __fmaf_rn(a, b, c);
+#else
+    return fmaf(a, b, c);
+#endif
+}
+OKRT_HD float wMax3(float a, float b, float c)
+{
+#ifdef __CUDA_ARCH__
+    float d; asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c)); return d;      /* FMNMX3 */
+#else
+    return fmaxf(fmaxf(a, b), c);
+#endif
+}
+OKRT_HD float wMin3(float a, float b, float c)
+{
+#ifdef __CUDA_ARCH__
+    float d; asm("min.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c)); return d;
+#else
+    return fminf(fminf(a, b), c);
+#endif
+}
+OKRT_HD uint32_t wPopc(uint32_t x)
+{
+#ifdef __CUDA_ARCH__
+    return (uint32_t)__popc(x);
+#else
+    return (uint32_t)__builtin_popcount(x);
+#endif
+}
+OKRT_HD uint32_t wHighBit(uint32_t x)       /* x != 0 */
+{
+#ifdef __CUDA_ARCH__
+    return 31u - (uint32_t)__clz((int)x);
+#else
+    return 31u - (uint32_t)__builtin_clz(x);
+#endif
+}
+OKRT_HD uint32_t wLowBit(uint32_t x)        /* x != 0 */
+{
+#ifdef __CUDA_ARCH__
+    return (uint32_t)__ffs((int)x) - 1u;
+#else
+    return (uint32_t)__builtin_ctz(x);
+#endif
+}
+/* 32768 + byte `k` of `w` as a float: one PRMT (the byte lands in bits 8..15 of 0x47000000 = 32768.0f, whose ulp is 2^-8) */
+template <int k>
+OKRT_HD float wPlane(uint32_t w)
+{
+#ifdef __CUDA_ARCH__
+    return __uint_as_float(__byte_perm(w, 0x47000000u, 0x7404 | (k << 4)));
+#else
+    return wFloat(0x47000000u | (((w >> (8 * k)) & 0xFFu) << 8));
+#endif
+}
+/* one 256-bit read-only load; p is 32-byte aligned */
+OKRT_HD void wLoad256(const uint4* p, uint4& a, uint4& b)
+{
+#ifdef __CUDA_ARCH__
+    asm("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w) : "l"(p));
+#else
+    a = p[0]; b = p[1];
+#endif
+}
+OKRT_HD float4 wLdg(const float4* p)
+{
+#ifdef __CUDA_ARCH__
+    return __ldg(p);
+#else
+    return *p;
+#endif
+}
+OKRT_HD void wTriangle(const DeviceScene& s, uint32_t j, float4& a, float4& b, float4& c)
+{
+#ifdef __CUDA_ARCH__
+    const int tj = (int)(j * kTriQuads);             /* through the texture pipe: the LSU data stage is the busier unit */
+    a = tex1Dfetch<float4>(s.fastTrisTex, tj); b = tex1Dfetch<float4>(s.fastTrisTex, tj + 1); c = tex1Dfetch<float4>(s.fastTrisTex, tj + 2);
+#else
+    const float4* tp = s.fastTris + (size_t)j * kTriQuads;
+    a = tp[0]; b = tp[1]; c = tp[2];
+#endif
+}
+
 /* ------------------------------------------------------------------- RNG */
 __device__ __forceinline__ uint32_t pcgHash(uint32_t& seed)           /* GPU-Utilities.hlsli:18-25 [F7] */
 {
@@ -468,7 +572,7 @@ __device__ __noinline__ void traverseExactWarp(const DeviceScene& s, uint32_t nu
  * re-traces the ray with traverseExact. */
 #define OKRT_DELTA 1.0e-4f
 /* a missed box reports FLT_MAX and must never pass, also while nothing has been hit yet */
-__device__ __forceinline__ float relaxedLimit(float best) { return fminf(best * (1.0f + OKRT_DELTA), OKRT_FLT_MAX); }
+OKRT_HD float relaxedLimit(float best) { return fminf(best * (1.0f + OKRT_DELTA), OKRT_FLT_MAX); }
 
 constexpr uint32_t kTraceDone = 0xFFFFFFFDu;
 constexpr uint32_t kTraceExitInstance = 0xFFFFFFFEu;
@@ -494,7 +598,9 @@ constexpr uint32_t kTraceTop = 0xFFFFFFFFu;
  * behind the traversal stack instead of registers, which buys resident warps */
 constexpr uint32_t kColdSlots = 8;
 constexpr uint32_t kColdHitRec = kFastStackCapacity + 0, kColdHitTri = kFastStackCapacity + 1, kColdHitU = kFastStackCapacity + 2,
-                   kColdHitV = kFastStackCapacity + 3, kColdSecond = kFastStackCapacity + 4;
+                   kColdHitV = kFastStackCapacity + 3, kColdSecond = kFastStackCapacity + 4,
+                   kColdGate = kFastStackCapacity + 5,        /* what the reference compares against before it tests the closest hit: see stepResult */
+                   kColdInstGate = kFastStackCapacity + 6;    /* largest distNear (>= 0) of the oct-tree boxes above the instance being walked */
 struct StepLane {
     V3 ro, rd, ridir;        /* current ray: identity-local at the top level, instance-local inside an instance */
     float best;
@@ -515,20 +621,27 @@ struct StepLane {
     uint32_t path;
 };
 
-__device__ __forceinline__ void stepCandidate(StepLane& L, uint32_t* stack, float t, uint32_t rec, uint32_t tri, float u, float v)
+OKRT_HD void stepCandidate(StepLane& L, uint32_t* stack, float t, uint32_t rec, uint32_t tri, float u, float v)
 {
 #if OKRT_COLD_IN_LOCAL
     if (t < L.best) {
-        stack[kColdSecond] = __float_as_uint(L.best); L.best = t;
-        stack[kColdHitRec] = rec; stack[kColdHitTri] = tri; stack[kColdHitU] = __float_as_uint(u); stack[kColdHitV] = __float_as_uint(v);
-    } else if (t < __uint_as_float(stack[kColdSecond])) stack[kColdSecond] = __float_as_uint(t);
+        stack[kColdSecond] = wBits(L.best); L.best = t;
+        stack[kColdHitRec] = rec; stack[kColdHitTri] = tri; stack[kColdHitU] = wBits(u); stack[kColdHitV] = wBits(v);
+        /* gate of this hit (stepResult): inside a ray-switched instance, the largest distNear of the oct-tree boxes above it.
+         * Sign bit set: those boxes are entered BEHIND the hit (they do not contain it: moved props, RayTracer.cpp:562) — the
+         * reference may cull the whole node against something farther that this traversal has already culled against the hit,
+         * so only the unbounded reference order can decide. */
+        uint32_t g = 0u;
+        if (L.inst != kTraceTop) { g = stack[kColdInstGate]; if (wFloat(g) > t) g |= 0x80000000u; }
+        stack[kColdGate] = g;
+    } else if (t < wFloat(stack[kColdSecond])) stack[kColdSecond] = wBits(t);
 #else
     if (t < L.best) { L.second = L.best; L.best = t; L.hitRec = rec; L.hitTri = tri; L.hitU = u; L.hitV = v; }
     else if (t < L.second) L.second = t;
 #endif
 }
 
-__device__ __forceinline__ void stepTopRay(StepLane& L, V3 o, V3 d)
+OKRT_HD void stepTopRay(StepLane& L, V3 o, V3 d)
 {
     const float4 i0 = make_float4(1, 0, 0, 0), i1 = make_float4(0, 1, 0, 0), i2 = make_float4(0, 0, 1, 0);
     L.ro = mulPointRows(o, i0, i1, i2);
@@ -538,12 +651,12 @@ __device__ __forceinline__ void stepTopRay(StepLane& L, V3 o, V3 d)
 }
 
 /* the lane moves to `ref`; a triangle leaf starts at its first triangle */
-__device__ __forceinline__ void stepEnter(StepLane& L, uint32_t ref)
+OKRT_HD void stepEnter(StepLane& L, uint32_t ref)
 {
     L.cur = ref;
     if ((ref & kRefTagMask) == kRefTriLeaf) L.triNext = ref & (kMaxTriIndex - 1u);
 }
-__device__ __forceinline__ void stackPush(StepLane& L, uint32_t* stack, uint32_t v)
+OKRT_HD void stackPush(StepLane& L, uint32_t* stack, uint32_t v)
 {
     OKRT_CHECK(L.sp >= 1 && L.sp < (int)kFastStackCapacity);
 #if OKRT_STACK_TOPREG
@@ -552,7 +665,7 @@ __device__ __forceinline__ void stackPush(StepLane& L, uint32_t* stack, uint32_t
     stack[L.sp++] = v;
 #endif
 }
-__device__ __forceinline__ uint32_t stackPop(StepLane& L, const uint32_t* stack)
+OKRT_HD uint32_t stackPop(StepLane& L, const uint32_t* stack)
 {
     OKRT_CHECK(L.sp >= 1 && L.sp <= (int)kFastStackCapacity);
 #if OKRT_STACK_TOPREG
@@ -561,13 +674,13 @@ __device__ __forceinline__ uint32_t stackPop(StepLane& L, const uint32_t* stack)
     return stack[--L.sp];
 #endif
 }
-__device__ __forceinline__ void stepPop(StepLane& L, const uint32_t* stack) { stepEnter(L, stackPop(L, stack)); }
+OKRT_HD void stepPop(StepLane& L, const uint32_t* stack) { stepEnter(L, stackPop(L, stack)); }
 
-__device__ __forceinline__ void stepInit(const DeviceScene& s, StepLane& L, uint32_t* stack, uint32_t numSpheres, V3 o, V3 d)
+OKRT_HD void stepInit(const DeviceScene& s, StepLane& L, uint32_t* stack, uint32_t numSpheres, V3 o, V3 d)
 {
     L.best = OKRT_FLT_MAX;
 #if OKRT_COLD_IN_LOCAL
-    stack[kColdSecond] = __float_as_uint(OKRT_FLT_MAX);
+    stack[kColdSecond] = wBits(OKRT_FLT_MAX);
     stack[kColdHitRec] = 0x3FFFFFFFu; stack[kColdHitTri] = 0xFFFFFFFFu; stack[kColdHitU] = 0u; stack[kColdHitV] = 0u;
 #else
     L.second = OKRT_FLT_MAX;
@@ -587,7 +700,7 @@ __device__ __forceinline__ void stepInit(const DeviceScene& s, StepLane& L, uint
 }
 
 /* GPU-Utilities.hlsli:183-197 for one box, as the three conditions the traversal needs: hit, in front, before `limit` */
-__device__ __forceinline__ bool boxPasses(V3 o, V3 idir, float4 lo, float4 hi, float limit, float& distNear)
+OKRT_HD bool boxPasses(V3 o, V3 idir, float4 lo, float4 hi, float limit, float& distNear)
 {
     const V3 tMin = (v3(lo.x, lo.y, lo.z) - o) * idir;
     const V3 tMax = (v3(hi.x, hi.y, hi.z) - o) * idir;
@@ -604,18 +717,22 @@ __device__ __forceinline__ bool boxPasses(V3 o, V3 idir, float4 lo, float4 hi, f
 #endif
 /* one 256-bit read-only load (LDG.E.ENL2.256.CONSTANT, sm_100+): two quads for one L1 tag lookup instead of two.
  * p must be 32-byte aligned. */
-__device__ __forceinline__ void ldg256(const float4* p, float4& a, float4& b)
+OKRT_HD void ldg256(const float4* p, float4& a, float4& b)
 {
 #ifndef OKRT_NODE_LD_HINT
 #define OKRT_NODE_LD_HINT ""
 #endif
+#ifdef __CUDA_ARCH__
     asm("ld.global.nc" OKRT_NODE_LD_HINT ".v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                  : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
                  : "l"(p));
+#else
+    a = p[0]; b = p[1];
+#endif
 }
 
 /* one child-pair node.  Empty children carry NaN boxes (okrt_accel.cpp), which never pass. */
-__device__ __forceinline__ void stepNode(const DeviceScene& s, StepLane& L, uint32_t* stack)
+OKRT_HD void stepNode(const DeviceScene& s, StepLane& L, uint32_t* stack)
 {
     OKRT_CHECK(L.cur < s.numFastNodes);
     const float4* q = s.fastNodes + (size_t)L.cur * 4;
@@ -623,11 +740,11 @@ __device__ __forceinline__ void stepNode(const DeviceScene& s, StepLane& L, uint
     float4 q0, q1, q2, q3;
     ldg256(q, q0, q1); ldg256(q + 2, q2, q3);
 #else
-    const float4 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3);
+    const float4 q0 = wLdg(q), q1 = wLdg(q + 1), q2 = wLdg(q + 2), q3 = wLdg(q + 3);
 #endif
     const float limit = relaxedLimit(L.best);
     float n0, n1;
-    const uint32_t r0 = __float_as_uint(q0.w), r1 = __float_as_uint(q1.w);
+    const uint32_t r0 = wBits(q0.w), r1 = wBits(q1.w);
     const bool h0 = boxPasses(L.ro, L.ridir, q0, q1, limit, n0);
     const bool h1 = boxPasses(L.ro, L.ridir, q2, q3, limit, n1);
     const bool firstIs1 = h1 && (!h0 || n1 < n0);
@@ -657,27 +774,22 @@ OKRT_HD float rayAndTriangleEdges(V3 o, V3 d, V3 p2, V3 E1, V3 E2, float& u, flo
 }
 
 /* one triangle of the leaf the lane stands on */
-__device__ __forceinline__ void stepTriangle(const DeviceScene& s, StepLane& L, uint32_t* stack)
+OKRT_HD void stepTriangle(const DeviceScene& s, StepLane& L, uint32_t* stack)
 {
     const uint32_t j = L.triNext++;
     OKRT_CHECK(j < s.numTris);
-#if OKRT_TRI_TEX
     /* through the texture pipe: the LSU data stage (one 32-byte sector per cycle for divergent lanes) is the busiest unit
      * of this kernel (80 %), the texture pipe is otherwise idle */
-    const int tj = (int)(j * kTriQuads);
-    const float4 a = tex1Dfetch<float4>(s.fastTrisTex, tj), b = tex1Dfetch<float4>(s.fastTrisTex, tj + 1), c = tex1Dfetch<float4>(s.fastTrisTex, tj + 2);
-#else
-    const float4* tp = s.fastTris + (size_t)j * kTriQuads;
-    const float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);       /* p2 | E1 | E2 | owner */
-#endif
+    float4 a, b, c;                                              /* p2 | E1 | E2 | owner */
+    wTriangle(s, j, a, b, c);
     float bu = 0.f, bv = 0.f;
     float t = rayAndTriangleEdges(L.ro, L.rd, v3(a.x, a.y, a.z), v3(a.w, b.x, b.y), v3(b.z, b.w, c.x), bu, bv);
     if (t > 0.f) {
         V3 w = L.rd * t;                                        /* RaytracerCS.hlsl:312-314; T == I for merged instances */
-        uint32_t rec = __float_as_uint(c.y);                    /* owner of a merged instance's triangle */
+        uint32_t rec = wBits(c.y);                    /* owner of a merged instance's triangle */
         if (L.inst != kTraceTop) {
             const float4* r = s.fastInstances + (size_t)L.inst * kInstQuads;
-            w = mulDirRows(w, __ldg(r + 3), __ldg(r + 4), __ldg(r + 5));
+            w = mulDirRows(w, wLdg(r + 3), wLdg(r + 4), wLdg(r + 5));
             rec = L.inst;
         }
         t = length(w);
@@ -687,19 +799,25 @@ __device__ __forceinline__ void stepTriangle(const DeviceScene& s, StepLane& L, 
     if (L.triNext == end) stepPop(L, stack);
 }
 
-/* oct-tree boxes on the way to an instance, world ray (RaytracerCS.hlsl:262): all must be HIT */
-__device__ __forceinline__ bool octChainHitWorld(const DeviceScene& s, V3 o, V3 d, uint32_t octNode)
+/* Oct-tree boxes on the way to an instance, world ray (RaytracerCS.hlsl:262-264).  The reference skips a node, and everything
+ * below it, when the box is missed OR entered at or beyond the closest hit so far — and createOctTree's boxes need not contain
+ * what they list (untransformed occupant boxes, RayTracer.cpp:562).  All boxes must be HIT; their largest distNear is returned
+ * and joins the GATE of whatever is found in the instance: nothing the reference tests earlier may be as close as the gate. */
+OKRT_HD bool octChainNear(const DeviceScene& s, V3 o, V3 d, uint32_t octNode, float& maxNear)
 {
     const V3 idirWorld = rcp3(d);
-    for (uint32_t on = octNode; on != 0xFFFFFFFFu; on = __ldg(s.octParent + on)) {
+    maxNear = 0.f;
+    for (uint32_t on = octNode; on != 0xFFFFFFFFu; on = s.octParent[on]) {
         const okrt_octree_node& node = s.octNodes[on];
-        if (!(rayAndAABBDist(o, idirWorld, v3(node.boundingBox.min), v3(node.boundingBox.max)) < OKRT_FLT_MAX)) return false;
+        const float n = rayAndAABBDist(o, idirWorld, v3(node.boundingBox.min), v3(node.boundingBox.max));
+        if (!(n < OKRT_FLT_MAX)) return false;
+        maxNear = fmaxf(maxNear, n);
     }
     return true;
 }
 
 /* the rare references: entering a generic (non-merged) instance, leaving one */
-__device__ __forceinline__ void stepMisc(const DeviceScene& s, StepLane& L, uint32_t* stack, V3 o, V3 d)
+OKRT_HD void stepMisc(const DeviceScene& s, StepLane& L, uint32_t* stack, V3 o, V3 d)
 {
     if (L.cur == kTraceExitInstance) {
         stepTopRay(L, o, d);
@@ -707,19 +825,23 @@ __device__ __forceinline__ void stepMisc(const DeviceScene& s, StepLane& L, uint
         const uint32_t recIdx = L.cur & ~kRefTagMask;
         OKRT_CHECK(recIdx < s.numFastInstances);
         const float4* rec = s.fastInstances + (size_t)recIdx * kInstQuads;
-        const float4 r6 = __ldg(rec + 6), r7 = __ldg(rec + 7);
-        if (octChainHitWorld(s, o, d, __float_as_uint(r7.y))) {
-            const float4 i0 = __ldg(rec), i1 = __ldg(rec + 1), i2 = __ldg(rec + 2);
+        const float4 r6 = wLdg(rec + 6), r7 = wLdg(rec + 7);
+        float octNear;
+        if (octChainNear(s, o, d, wBits(r7.y), octNear)) {
+            const float4 i0 = wLdg(rec), i1 = wLdg(rec + 1), i2 = wLdg(rec + 2);
             const V3 lo = mulPointRows(o, i0, i1, i2);
             const V3 ld = normalize(mulDirRows(d, i0, i1, i2));
             const V3 lidir = rcp3(ld);
-            const float4 a0 = __ldg(rec + 3), a1 = __ldg(rec + 4), a2 = __ldg(rec + 5);
+            const float4 a0 = wLdg(rec + 3), a1 = wLdg(rec + 4), a2 = wLdg(rec + 5);
             /* the mesh's root box (RaytracerCS.hlsl:285 on the first popped node) */
             if (rayAndAABBDist(lo, lidir, v3(a0.w, a1.w, a2.w), v3(r6.x, r6.y, r6.z)) < relaxedLimit(L.best)) {
                 stackPush(L, stack, kTraceExitInstance);
+#if OKRT_COLD_IN_LOCAL
+                stack[kColdInstGate] = wBits(octNear);
+#endif
                 L.ro = lo; L.rd = ld; L.ridir = lidir;
                 L.inst = recIdx;
-                stepEnter(L, __float_as_uint(r7.x));
+                stepEnter(L, wBits(r7.x));
                 return;
             }
         }
@@ -729,67 +851,63 @@ __device__ __forceinline__ void stepMisc(const DeviceScene& s, StepLane& L, uint
 
 /* the finished lane's hit; returns true when the reference order has to decide.  `L` stands at the top level
  * again (the exit marker of an instance restores the top ray), so L.ro is the world origin. */
-__device__ __forceinline__ bool stepResult(const DeviceScene& s, const StepLane& L, const uint32_t* stack, const float4* rayD, Hit& hit, float& seed)
+OKRT_HD bool stepResult(const DeviceScene& s, const StepLane& L, const uint32_t* stack, const float4* rayD, Hit& hit, float& seed)
 {
 #if OKRT_COLD_IN_LOCAL
     const uint32_t hitRec = stack[kColdHitRec];
-    const float second = __uint_as_float(stack[kColdSecond]);
-    hit.tri = stack[kColdHitTri]; hit.u = __uint_as_float(stack[kColdHitU]); hit.v = __uint_as_float(stack[kColdHitV]);
+    const float second = wFloat(stack[kColdSecond]);
+    hit.tri = stack[kColdHitTri]; hit.u = wFloat(stack[kColdHitU]); hit.v = wFloat(stack[kColdHitV]);
 #else
     const uint32_t hitRec = L.hitRec;
     const float second = L.second;
     hit.tri = L.hitTri; hit.u = L.hitU; hit.v = L.hitV;
 #endif
-    seed = L.best;                                               /* the reference's answer lies inside the window above it */
     hit.distance = L.best;
     hit.kind = L.best < OKRT_FLT_MAX ? (hitRec >> 30) : 0u;
     hit.idx = hit.kind ? (hitRec & 0x3FFFFFFFu) : 0xFFFFFFFFu;
-    bool ambiguous = second < relaxedLimit(L.best);
+    /* GATE of the closest hit W: the reference tests W unless something it tested earlier is at least as close as the distNear
+     * of a box on its way to W (it culls on `>= payload.distance`, RaytracerCS.hlsl:264,285).  The leaf box and the BVH boxes
+     * above it start before W (checked by the differential stress test, tests/test_gpu_stress.py); the oct-tree boxes need not
+     * (they need not even contain W's instance), so their distNear joins the gate. */
+    float gate = L.best;
+    bool chainMissed = false;
+#if OKRT_COLD_IN_LOCAL
+    if (hit.kind == 2u) {
+        const uint32_t g = stack[kColdGate];
+        gate = fmaxf(gate, wFloat(g & 0x7FFFFFFFu));
+        chainMissed = (g >> 31) != 0u;
+    }
+#endif
     if (hit.kind == 2u) {
         const uint32_t rec = hit.idx;
         OKRT_CHECK(rec < s.numFastInstances);
         const float4* r = s.fastInstances + (size_t)rec * kInstQuads;
-        const float4 r6 = __ldg(r + 6), r7 = __ldg(r + 7), lo = __ldg(r + 8), hi = __ldg(r + 9);
-        hit.idx = __float_as_uint(r7.z);
-        if ((__float_as_uint(r6.w) & 1u) != 0u) {
+        const float4 r6 = wLdg(r + 6), r7 = wLdg(r + 7), lo = wLdg(r + 8), hi = wLdg(r + 9);
+        hit.idx = wBits(r7.z);
+        if ((wBits(r6.w) & 1u) != 0u) {
             /* identity instance: the reference reaches it only through the oct-tree boxes above it (RaytracerCS.hlsl:262).
-             * An origin strictly inside a box hits it — both slabs of every axis have opposite signs, |1/d| >= 1/2 for
-             * the unit directions the shader produces, so distFar > 0 >= distNear — and the boxes above are nested. */
+             * An origin strictly inside a box hits it with distNear <= 0 — both slabs of every axis have opposite signs, |1/d| >= 1/2
+             * for the unit directions the shader produces — and the boxes above are nested. */
             const float m = 1.0e-20f;
-            const bool inside = (__float_as_uint(r7.w) & 1u) != 0u &&
+            const bool inside = (wBits(r7.w) & 1u) != 0u &&
                                 L.ro.x - lo.x > m && hi.x - L.ro.x > m && L.ro.y - lo.y > m && hi.y - L.ro.y > m && L.ro.z - lo.z > m && hi.z - L.ro.z > m;
             if (!inside) {
                 const float4 d = *rayD;
-                if (!octChainHitWorld(s, L.ro, v3(d.x, d.y, d.z), __float_as_uint(r7.y))) { ambiguous = true; seed = OKRT_FLT_MAX; }   /* no bound known */
+                float octNear;
+                if (!octChainNear(s, L.ro, v3(d.x, d.y, d.z), wBits(r7.y), octNear)) chainMissed = true;
+                else gate = fmaxf(gate, octNear);
             }
         }
     }
-    return ambiguous;
+    /* two candidates inside the window above the gate, or a box the reference never gets through: the reference order decides,
+     * searching up to the window (everything the reference could return lies inside it) or without a bound */
+    seed = chainMissed ? OKRT_FLT_MAX : gate;
+    return chainMissed || (hit.kind != 0u && second < relaxedLimit(gate));
 }
 
-} // namespace okrt
-#include "okrt_wide.cuh"
-namespace okrt {
-__device__ __forceinline__ bool traversePairs(const DeviceScene& s, uint32_t numSpheres, V3 o, V3 d, Hit& hit, float& seed);
-
-#ifndef OKRT_WIDE
-#define OKRT_WIDE 1          /* 1: the near-first traversal walks the wide layout (okrt_wide.cuh); 0: the child-pair layout below */
-#endif
-
-/* whole-ray form, used by the megakernel: the same steps, one ray per thread.  Returns true when the reference order has to
- * decide; `limit` bounds that traversal. */
-__device__ __forceinline__ bool traverseFast(const DeviceScene& s, uint32_t numSpheres, V3 o, V3 d, Hit& hit, float& limit)
-{
-#if OKRT_WIDE
-    return wideTraverse(s, numSpheres, o, d, hit, limit);
-#else
-    float seed;
-    const bool ambiguous = traversePairs(s, numSpheres, o, d, hit, seed);
-    limit = relaxedLimit(seed);
-    return ambiguous;
-#endif
-}
-__device__ __forceinline__ bool traversePairs(const DeviceScene& s, uint32_t numSpheres, V3 o, V3 d, Hit& hit, float& seed)
+/* whole-ray form of the near-first traversal over the child-pair layout, used by the megakernel and by the CPU check
+ * (okrt_trace_rays_host): the same steps, one ray per thread */
+OKRT_HD bool traversePairs(const DeviceScene& s, uint32_t numSpheres, V3 o, V3 d, Hit& hit, float& seed)
 {
     uint32_t stack[kFastStackCapacity + kColdSlots];
     StepLane L;
@@ -804,6 +922,19 @@ __device__ __forceinline__ bool traversePairs(const DeviceScene& s, uint32_t num
     const float4 dd = make_float4(d.x, d.y, d.z, 0.f);
     return stepResult(s, L, stack, &dd, hit, seed);
 }
+
+/* returns true when the reference order has to decide; `limit` bounds that traversal */
+OKRT_HD bool traverseFast(const DeviceScene& s, uint32_t numSpheres, V3 o, V3 d, Hit& hit, float& limit)
+{
+    float seed;
+    const bool ambiguous = traversePairs(s, numSpheres, o, d, hit, seed);
+    limit = relaxedLimit(seed);
+    return ambiguous;
+}
+
+} // namespace okrt
+#include "okrt_wide.cuh"          /* the same traversal over 8-wide quantised nodes (OKRT_TRAVERSAL_WIDE) */
+namespace okrt {
 
 /* ------------------------------------------------------------ hit resolve
  * RaytracerCS.hlsl:336-392 [Q8] */

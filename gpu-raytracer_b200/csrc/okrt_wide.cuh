@@ -12,7 +12,7 @@
  * down at WideLane / wideCandidate / wideResult.
  *
  * The lane functions are __host__ __device__: okrt_trace_rays_host (okrt_device.cu) runs the same code on the CPU so that the
- * layout and the certification logic can be compared with the oracle without a GPU (tests/test_cpu_wide.py).
+ * layout and the certification logic can be compared with the oracle without a GPU (tests/test_cpu_traversal.py).
  */
 #pragma once
 #include "okrt_kernels.cuh"
@@ -22,110 +22,6 @@ namespace okrt {
 #ifndef OKRT_DELTA
 #define OKRT_DELTA 1.0e-4f
 #endif
-
-/* ------------------------------------------------------------------ portable intrinsics */
-OKRT_HD uint32_t wBits(float f)
-{
-#ifdef __CUDA_ARCH__
-    return __float_as_uint(f);
-#else
-    uint32_t u; memcpy(&u, &f, 4); return u;
-#endif
-}
-OKRT_HD float wFloat(uint32_t u)
-{
-#ifdef __CUDA_ARCH__
-    return __uint_as_float(u);
-#else
-    float f; memcpy(&f, &u, 4); return f;
-#endif
-}
-OKRT_HD float wFma(float a, float b, float c)
-{
-#ifdef __CUDA_ARCH__
-    return __fmaf_rn(a, b, c);
-#else
-    return fmaf(a, b, c);
-#endif
-}
-OKRT_HD float wMax3(float a, float b, float c)
-{
-#ifdef __CUDA_ARCH__
-    float d; asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c)); return d;      /* FMNMX3 */
-#else
-    return fmaxf(fmaxf(a, b), c);
-#endif
-}
-OKRT_HD float wMin3(float a, float b, float c)
-{
-#ifdef __CUDA_ARCH__
-    float d; asm("min.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c)); return d;
-#else
-    return fminf(fminf(a, b), c);
-#endif
-}
-OKRT_HD uint32_t wPopc(uint32_t x)
-{
-#ifdef __CUDA_ARCH__
-    return (uint32_t)__popc(x);
-#else
-    return (uint32_t)__builtin_popcount(x);
-#endif
-}
-OKRT_HD uint32_t wHighBit(uint32_t x)       /* x != 0 */
-{
-#ifdef __CUDA_ARCH__
-    return 31u - (uint32_t)__clz((int)x);
-#else
-    return 31u - (uint32_t)__builtin_clz(x);
-#endif
-}
-OKRT_HD uint32_t wLowBit(uint32_t x)        /* x != 0 */
-{
-#ifdef __CUDA_ARCH__
-    return (uint32_t)__ffs((int)x) - 1u;
-#else
-    return (uint32_t)__builtin_ctz(x);
-#endif
-}
-/* 32768 + byte `k` of `w` as a float: one PRMT (the byte lands in bits 8..15 of 0x47000000 = 32768.0f, whose ulp is 2^-8) */
-template <int k>
-OKRT_HD float wPlane(uint32_t w)
-{
-#ifdef __CUDA_ARCH__
-    return __uint_as_float(__byte_perm(w, 0x47000000u, 0x7404 | (k << 4)));
-#else
-    return wFloat(0x47000000u | (((w >> (8 * k)) & 0xFFu) << 8));
-#endif
-}
-/* one 256-bit read-only load; p is 32-byte aligned */
-OKRT_HD void wLoad256(const uint4* p, uint4& a, uint4& b)
-{
-#ifdef __CUDA_ARCH__
-    asm("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-        : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w) : "l"(p));
-#else
-    a = p[0]; b = p[1];
-#endif
-}
-OKRT_HD float4 wLdg(const float4* p)
-{
-#ifdef __CUDA_ARCH__
-    return __ldg(p);
-#else
-    return *p;
-#endif
-}
-OKRT_HD void wTriangle(const DeviceScene& s, uint32_t j, float4& a, float4& b, float4& c)
-{
-#ifdef __CUDA_ARCH__
-    const int tj = (int)(j * kTriQuads);             /* through the texture pipe: the LSU data stage is the busier unit */
-    a = tex1Dfetch<float4>(s.fastTrisTex, tj); b = tex1Dfetch<float4>(s.fastTrisTex, tj + 1); c = tex1Dfetch<float4>(s.fastTrisTex, tj + 2);
-#else
-    const float4* tp = s.fastTris + (size_t)j * kTriQuads;
-    a = tp[0]; b = tp[1]; c = tp[2];
-#endif
-}
 
 /* ------------------------------------------------------------------ lane state
  * WINDOW AND CERTIFICATION.  n(l) is the reference's distNear of leaf l's box for this ray, s(l) the leaf's

@@ -218,7 +218,10 @@ typedef struct okrt_camera {            /* Transform + Camera, Components.h:130-
 
 enum { OKRT_TRAVERSAL_FAST = 0,   /* near-first traversal of the re-packed child-pair BVH with
                                      exact-arithmetic commit; falls back to reference order on ties */
-       OKRT_TRAVERSAL_EXACT = 1 };/* reference visit order, RaytracerCS.hlsl:244-334 (debug counters exact) */
+       OKRT_TRAVERSAL_EXACT = 1,  /* reference visit order, RaytracerCS.hlsl:244-334 (debug counters exact) */
+       OKRT_TRAVERSAL_WIDE = 2 }; /* near-first traversal of 8-wide nodes with quantised child boxes (wavefront pipeline only);
+                                    * same results; measured slower than OKRT_TRAVERSAL_FAST on B200, kept as the
+                                    * memory-lean alternative: 3 sectors per 8 children instead of 2 per 2 */
 
 enum { OKRT_PIPELINE_WAVEFRONT = 0,  /* generate / trace / shade kernels with ray queues in HBM (default) */
        OKRT_PIPELINE_MEGAKERNEL = 1 }; /* one persistent kernel with per-lane path regeneration */
@@ -415,7 +418,7 @@ OKRT_API int okrt_layout_report(const okrt_triangle* tris, uint32_t numTris, con
 OKRT_API int okrt_trace_rays_host(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh_node* nodes, uint32_t numNodes,
                                   const okrt_mesh_instance* instances, uint32_t numInstances,
                                   const okrt_octree_node* octNodes, uint32_t numOctNodes,
-                                  const float* rays, uint32_t numRays, uint32_t* out);
+                                  uint32_t traversal /* OKRT_TRAVERSAL_FAST or _WIDE */, const float* rays, uint32_t numRays, uint32_t* out);
 
 /* ------------------------------------------------------- renderer (device) */
 OKRT_API int  okrt_create(int device, uint32_t width, uint32_t height, okrt_renderer** out); /* RayTracer::initiate :60 */

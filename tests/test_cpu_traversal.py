@@ -1,5 +1,6 @@
-"""The near-first traversal's own lane functions (csrc/okrt_wide.cuh), compiled for the host and driven through
-okrt_trace_rays_host, against the oracle's findClosestHit (RaytracerCS.hlsl:218-334) ray by ray — no GPU involved.
+"""The near-first traversals' own lane functions (csrc/okrt_kernels.cuh: child-pair layout, the default; csrc/okrt_wide.cuh:
+8-wide quantised layout), compiled for the host and driven through okrt_trace_rays_host, against the oracle's
+findClosestHit (RaytracerCS.hlsl:218-334) ray by ray — no GPU involved.
 Every ray the traversal decides by itself must carry the reference's hit bit for bit (triangle, instance, u, v, distance);
 the rest must be flagged for the reference order, and stay rare."""
 import numpy as np
@@ -36,24 +37,24 @@ def _bounce_rays(host, rays, hits, seed, instances):
     return np.concatenate([(o + d * np.float32(0.001)).astype(np.float32), d], 1)
 
 
-def _trace_both(okrt, oracle, host, rays):
+def _trace_both(okrt, oracle, host, rays, traversal):
     abi = okrt.abi
     g, t = host["geometry"], host["octree"]
     ref = oracle.trace_rays(helpers.oracle_scene(oracle, host), host["rd"].copy(), rays)
     out = np.zeros((len(rays), 12), np.uint32)
     abi.check(abi.lib().okrt_trace_rays_host(abi.ptr(g.trianglesPos), len(g.trianglesPos), abi.ptr(g.bvhNodes), len(g.bvhNodes),
                                              abi.ptr(t.instances) if len(t.instances) else None, len(t.instances), abi.ptr(t.nodes), len(t.nodes),
-                                             abi.ptr(rays), len(rays), abi.ptr(out)))
+                                             traversal, abi.ptr(rays), len(rays), abi.ptr(out)))
     return ref, out
 
 
-def _check(okrt, oracle, host, n, generations=3, max_ambiguous=0.02, seed=1):
+def _check(okrt, oracle, host, n, traversal, generations=3, max_ambiguous=0.02, seed=1):
     rays = _random_rays(host, n, seed)
     total = 0
     for gen in range(generations):
         if len(rays) == 0:
             break
-        ref, out = _trace_both(okrt, oracle, host, rays)
+        ref, out = _trace_both(okrt, oracle, host, rays, traversal)
         decided = out[:, 6] == 0
         bad = decided & np.any(out[:, :6] != ref, axis=1)
         assert not bad.any(), "generation %d: %d of %d rays differ from the reference order (first: ray %s, reference %s, traversal %s)" % (
@@ -64,20 +65,26 @@ def _check(okrt, oracle, host, n, generations=3, max_ambiguous=0.02, seed=1):
     return total
 
 
-def test_wide_traversal_testscene_and_standin(okrt, oracle):
+TRAVERSALS = pytest.mark.parametrize("traversal", [0, 2], ids=["pairs", "wide"])      # OKRT_TRAVERSAL_FAST, OKRT_TRAVERSAL_WIDE
+
+
+@TRAVERSALS
+def test_traversal_testscene_and_standin(okrt, oracle, traversal):
     rm, sc, info = okrt.scenes.test_scene()
-    _check(okrt, oracle, helpers.build_host_side(okrt, rm, sc, info, 64, 64), 60_000)
+    _check(okrt, oracle, helpers.build_host_side(okrt, rm, sc, info, 64, 64), 60_000, traversal)
     rm, sc, info = okrt.scenes.sponza_standin(20_000, texture_size=16)
-    _check(okrt, oracle, helpers.build_host_side(okrt, rm, sc, info, 64, 64), 150_000)
+    _check(okrt, oracle, helpers.build_host_side(okrt, rm, sc, info, 64, 64), 150_000, traversal)
 
 
 @pytest.mark.parametrize("kind,offset,limit", [("flat_room", 0.0, 0.02), ("flat_room", 1.0e4, 0.05), ("layers", 0.0, 0.3), ("contact", 0.0, 0.02)])
-def test_wide_traversal_adversarial(okrt, oracle, kind, offset, limit):
+@TRAVERSALS
+def test_traversal_adversarial(okrt, oracle, kind, offset, limit, traversal):
     rm, sc, info = okrt.scenes.adversarial_scene(kind, offset=(offset, offset, offset))
-    _check(okrt, oracle, helpers.build_host_side(okrt, rm, sc, info, 64, 64), 80_000, max_ambiguous=limit)
+    _check(okrt, oracle, helpers.build_host_side(okrt, rm, sc, info, 64, 64), 80_000, traversal, max_ambiguous=limit)
 
 
-def test_wide_traversal_moved_props_under_child_oct_nodes(okrt, oracle):
+@TRAVERSALS
+def test_traversal_moved_props_under_child_oct_nodes(okrt, oracle, traversal):
     """createOctTree keeps UNtransformed occupant boxes (RayTracer.cpp:562), so the oct-tree box above a translated
     or rotated prop need not contain it, and the reference culls the prop's whole node against a farther hit.  Meshes with
     distinct local boxes + transforms give child oct nodes; a wall sits behind the props."""
@@ -92,7 +99,7 @@ def test_wide_traversal_moved_props_under_child_oct_nodes(okrt, oracle):
     d = target - o
     d /= np.linalg.norm(d, axis=1, keepdims=True)
     rays = np.concatenate([o, d], 1).astype(np.float32)
-    ref, out = _trace_both(okrt, oracle, host, rays)
+    ref, out = _trace_both(okrt, oracle, host, rays, traversal)
     decided = out[:, 6] == 0
     bad = decided & np.any(out[:, :6] != ref, axis=1)
     assert not bad.any(), "%d rays differ from the reference order" % int(bad.sum())
@@ -100,4 +107,4 @@ def test_wide_traversal_moved_props_under_child_oct_nodes(okrt, oracle):
     culled = ~decided & (out[:, 3] != ref[:, 3])
     assert culled.sum() > 10, "no ray met a node cull: %d" % int(culled.sum())
     assert (~decided).mean() < 0.6
-    _check(okrt, oracle, host, 60_000, max_ambiguous=0.6, seed=5)
+    _check(okrt, oracle, host, 60_000, traversal, max_ambiguous=0.6, seed=5)

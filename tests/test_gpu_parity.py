@@ -104,7 +104,9 @@ def test_sponza_standin_small_bit_exact(okrt, oracle):
     rd = host["rd"].copy()
     rd[0]["numAccumulationFrames"] = 1
     o = oracle.render(os_, rd, 8, aov_dtype=abi.AOV)
-    for traversal in (0, 1):
+    for traversal in (0, 1, 2):
+        if traversal == 2 and helpers.harness.DEFAULT_PIPELINE != 0:
+            continue                          # OKRT_TRAVERSAL_WIDE: wavefront pipeline only
         r = helpers.Renderer(okrt, host, W, H, envFaces=env)
         r.options(maxBounces=8, traversal=traversal, writeAov=1)
         r.render(host["rd"].copy())
@@ -113,7 +115,7 @@ def test_sponza_standin_small_bit_exact(okrt, oracle):
         assert np.array_equal(r.accumulation().view(np.uint32), o["accum"].view(np.uint32))
         st = r.stats()
         assert int(st["raySegments"]) == o["segments"]
-        if traversal == 0:
+        if traversal != 1:
             # the reference-order fallback must stay a rare path
             assert int(st["fallbackSegments"]) < 0.02 * int(st["raySegments"])
         r.close()
@@ -170,7 +172,9 @@ def test_moved_props_under_child_oct_nodes(okrt, oracle):
     env = okrt.scenes.procedural_sky_faces(16)
     rdo = host["rd"].copy(); rdo[0]["numAccumulationFrames"] = 1
     o = oracle.render(helpers.oracle_scene(oracle, host, envFaces=env), rdo, 4, aov_dtype=abi.AOV)
-    for traversal in (0, 1):
+    for traversal in (0, 1, 2):
+        if traversal == 2 and helpers.harness.DEFAULT_PIPELINE != 0:
+            continue                          # OKRT_TRAVERSAL_WIDE: wavefront pipeline only
         r = helpers.Renderer(okrt, host, W, H, envFaces=env)
         r.options(maxBounces=4, traversal=traversal, writeAov=1)
         r.render(host["rd"].copy())

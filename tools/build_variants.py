@@ -10,7 +10,7 @@ for arg in sys.argv[1:]:
     log = os.path.join(ROOT, "gpu-raytracer_b200", "_obj", "okrt_device.cu.ptxas.log")
     lines = open(log).read().splitlines()
     for i, l in enumerate(lines):
-        if "Compiling entry function" in l and ("traceFastKernel" in l or "shadeKernelILb0" in l):
+        if "Compiling entry function" in l and ("traceFastKernel" in l or "traceWideKernel" in l or "shadeKernelILb0" in l):
             print("  ", l.split("'")[1][:40], "|", lines[i + 2].strip(), "|", lines[i + 3].strip()[:60])
     print("built", name)
 b.build_library(force=True, out=os.path.join(ROOT, "gpu-raytracer_b200", "libokrt.so"))
