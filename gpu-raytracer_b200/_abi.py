@@ -54,6 +54,8 @@ AOV = np.dtype([("hitKind", "<u4"), ("hitIdx", "<u4"), ("triIdx", "<u4"), ("bary
 STATS = np.dtype([("raySegments", "<u8"), ("fallbackSegments", "<u8"), ("pixelsTraced", "<u8"), ("kernelLaunches", "<u8"),
                   ("lastRenderMs", "<f4"), ("traceKernelMs", "<f4"), ("traceKernelLaunches", "<f4"), ("reserved", "<f4", 1)])
 
+UNIT_PEAKS = np.dtype([("sectorsPerSecond", "<f8"), ("sectorsPerSecondL1", "<f8"), ("warpInstructionsPerSecond", "<f8"), ("smClockMHz", "<f8"), ("numSms", "<u4"), ("reserved", "<u4")])
+ALLREDUCE_FN = ctypes.CFUNCTYPE(ctypes.c_int, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p)
 LAYOUT_INFO = np.dtype([("numPairNodes", "<u4"), ("numFlattenedLeaves", "<u4"), ("numMergedInstances", "<u4"),
                         ("numInstanceRecords", "<u4"), ("fastStackDepth", "<u4"), ("exactBvhDepth", "<u4"), ("exactOctDepth", "<u4"),
                         ("reserved", "<u4"), ("sahCost", "<f8"), ("buildMs", "<f8")])
@@ -166,6 +168,10 @@ SYMBOLS = [
     ("okrt_get_stats", _I, [_P, _P]),
     ("okrt_reset_stats", _I, [_P]),
     ("okrt_get_trace_stats", _I, [_P, _P, _U]),
+    ("okrt_read_result_async", _I, [_P, _P, ctypes.POINTER(ctypes.c_uint64), _U]),
+    ("okrt_wait_read", _I, [_P, _U]),
+    ("okrt_reduce_accumulation", _I, [_P, _P, _P, _U]),
+    ("okrt_measure_unit_peaks", _I, [_I, _P]),
     ("okrt_trace_rays_host", _I, [_P, _U, _P, _U, _P, _U, _P, _U, _U, _P, _U, _P]),
 ]
 
@@ -174,6 +180,16 @@ class OkrtError(RuntimeError):
     def __init__(self, code, message):
         super().__init__("%s: %s" % (ERROR_NAMES.get(code, "error %d" % code), message))
         self.code = code
+
+
+def load_library(path):
+    """ctypes handle of a build of the library at `path` with every symbol typed (lib() below is the product build)."""
+    handle = ctypes.CDLL(path)
+    for name, restype, argtypes in SYMBOLS:
+        fn = getattr(handle, name)
+        fn.restype = restype
+        fn.argtypes = argtypes
+    return handle
 
 
 _lib = None
@@ -186,12 +202,7 @@ def lib():
         if not os.path.exists(LIB_PATH):
             raise ImportError("gpu-raytracer_b200/libokrt.so is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
                               "(or python gpu-raytracer_b200/build.py); there is no fallback implementation")
-        handle = ctypes.CDLL(LIB_PATH)
-        for name, restype, argtypes in SYMBOLS:
-            fn = getattr(handle, name)
-            fn.restype = restype
-            fn.argtypes = argtypes
-        _lib = handle
+        _lib = load_library(LIB_PATH)
     return _lib
 
 

@@ -42,10 +42,30 @@ def _stale(target, deps):
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build_library(force=False, verbose=False, extra_nvcc=(), out=None):
-    global OUT
-    if out:
-        OUT = out
+OUT_STATS = os.path.join(HERE, "libokrt_stats.so")
+
+
+def build_stats_library(force=False, verbose=False):
+    """The same library with -DOKRT_TRACE_STATS: the traversal kernel counts its node steps, triangle tests and busy lanes
+    (okrt_get_trace_stats).  bench.py renders one step through it to quote the kernel's executed work; the timed arms use
+    libokrt.so, which carries no counters."""
+    return build_library(force=force, verbose=verbose, extra_nvcc=("-DOKRT_TRACE_STATS",), out=OUT_STATS, obj_dir=OBJ + "_stats")
+
+
+def build_library(force=False, verbose=False, extra_nvcc=(), out=None, obj_dir=None):
+    global OUT, OBJ
+    saved = (OUT, OBJ)
+    try:
+        if out:
+            OUT = out
+        if obj_dir:
+            OBJ = obj_dir
+        return _build_library(force, verbose, extra_nvcc)
+    finally:
+        OUT, OBJ = saved
+
+
+def _build_library(force, verbose, extra_nvcc):
     os.makedirs(OBJ, exist_ok=True)
     inc = ["-I" + os.path.join(ROOT, "include"), "-I" + CSRC]
     common_deps = [os.path.join(ROOT, "include", "okrt.h")] + [os.path.join(CSRC, h) for h in HEADERS]
@@ -86,3 +106,4 @@ def build_library(force=False, verbose=False, extra_nvcc=(), out=None):
 
 if __name__ == "__main__":
     print(build_library(force="--force" in sys.argv, verbose=True))
+    print(build_stats_library(force="--force" in sys.argv, verbose=False))

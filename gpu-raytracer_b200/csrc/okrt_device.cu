@@ -110,6 +110,10 @@ struct okrt_renderer {
     int device = 0;
     cudaStream_t stream = nullptr;
     cudaStream_t stream2 = nullptr;            /* second half of a wavefront batch (launchWavefront) */
+    cudaStream_t streamCopy = nullptr;         /* okrt_read_result_async: device-to-host copies overlap the next frames */
+    uchar4* snapshot[2] = {nullptr, nullptr};  /* result image as of the call, one per slot */
+    cudaEvent_t evSnapshot[2] = {nullptr, nullptr}, evCopied[2] = {nullptr, nullptr};
+    bool copyPending[2] = {false, false};
     cudaEvent_t evFork = nullptr, evJoin = nullptr;
     uint32_t* counts2 = nullptr;               /* queue counters of the second half */
     cudaEvent_t evStart = nullptr, evStop = nullptr;
@@ -315,9 +319,9 @@ int launchWavefront(okrt_renderer* r, const FrameParams& fpWhole, bool instrumen
      * because the CUDA-event pairs around the traversal launches then overlap with the other half's kernels and the
      * per-kernel time bench.py's roofline is built on loses its meaning. */
     static const int dualEnv = [] { const char* e = std::getenv("OKRT_DUAL_MIN_FRAMES"); return e ? std::atoi(e) : -1; }();
-    /* default: on for a tile-sharded rank (its kernels are small, tails and launch gaps weigh most there: 8 GPUs
-     * 19 667 -> 20 102 Mrays/s device-timed, 15 408 -> 16 054 end to end), off on a single GPU (see above) */
-    const int dualMin = dualEnv >= 0 ? dualEnv : (fpWhole.shardCount > 1u ? 2 : 0);
+    /* default: off for every shard count, so that one GPU and N tile-sharded GPUs run the same code path (round 1 had it on for
+     * sharded ranks only: 8 GPUs 19 667 -> 20 102 Mrays/s device-timed, which flattered the scaling curve) */
+    const int dualMin = dualEnv >= 0 ? dualEnv : 0;
     const bool dual = !instrumented && fpWhole.traversal != OKRT_TRAVERSAL_EXACT && dualMin > 0 && fpWhole.batchFrames >= (uint32_t)dualMin &&
                       fpWhole.batchFrames >= 2u && r->stream2 != nullptr;
     const int halves = dual ? 2 : 1;
@@ -597,6 +601,12 @@ void okrt_destroy(okrt_renderer* r)
     if (r->evFork) cudaEventDestroy(r->evFork);
     if (r->evJoin) cudaEventDestroy(r->evJoin);
     if (r->counts2) cudaFree(r->counts2);
+    for (int k = 0; k < 2; k++) {
+        if (r->snapshot[k]) cudaFree(r->snapshot[k]);
+        if (r->evSnapshot[k]) cudaEventDestroy(r->evSnapshot[k]);
+        if (r->evCopied[k]) cudaEventDestroy(r->evCopied[k]);
+    }
+    if (r->streamCopy) { cudaStreamSynchronize(r->streamCopy); cudaStreamDestroy(r->streamCopy); }
     if (r->stream2) cudaStreamDestroy(r->stream2);
     if (r->stream) cudaStreamDestroy(r->stream);
     delete r;
@@ -607,6 +617,8 @@ int okrt_resize(okrt_renderer* r, uint32_t width, uint32_t height)
     int rc = checkHandle(r, "okrt_resize"); if (rc) return rc;
     if (!width || !height) { setError("okrt_resize: zero extent"); return OKRT_ERR_INVALID_ARGUMENT; }
     OKRT_CUDA(cudaStreamSynchronize(r->stream));
+    if (r->streamCopy) OKRT_CUDA(cudaStreamSynchronize(r->streamCopy));
+    for (int k = 0; k < 2; k++) { if (r->snapshot[k]) cudaFree(r->snapshot[k]); r->snapshot[k] = nullptr; r->copyPending[k] = false; }
     r->width = width; r->height = height;
     r->rd.textureDims[0] = width; r->rd.textureDims[1] = height;
     r->rd.numAccumulationFrames = 0u;                        /* onResize -> resetAccumulation, RayTracer.cpp:494-501 */
@@ -817,6 +829,177 @@ int okrt_read_result_owned(okrt_renderer* r, uint8_t* outRgba8, uint64_t* outByt
     }
     OKRT_CUDA(cudaStreamSynchronize(r->stream));
     if (outBytes) *outBytes = moved;
+    return OKRT_OK;
+}
+
+/* rows of the result this handle owns, as (offset, pitch, bytes per run, runs) + a short last band */
+static void ownedRuns(const okrt_renderer* r, size_t& first, size_t& pitch, size_t& runBytes, uint32_t& fullBands, size_t& tailAt, size_t& tailBytes)
+{
+    const size_t rowBytes = (size_t)r->width * 4;
+    first = 0; pitch = rowBytes * r->height; runBytes = rowBytes * r->height; fullBands = 1; tailAt = 0; tailBytes = 0;
+    if (r->opt.shardMode != OKRT_SHARD_TILE || r->opt.shardCount <= 1) return;
+    const uint32_t band = r->opt.shardBandRows ? r->opt.shardBandRows : 8u, count = r->opt.shardCount, rank = r->opt.shardRank;
+    const uint32_t bands = (r->height + band - 1u) / band;
+    const uint32_t mine = bands / count + ((bands % count) > rank ? 1u : 0u);
+    fullBands = 0; runBytes = (size_t)band * rowBytes; first = (size_t)rank * band * rowBytes; pitch = (size_t)count * band * rowBytes;
+    if (!mine) return;
+    const uint32_t lastBand = rank + (mine - 1u) * count;
+    const uint32_t lastRows = std::min(band, r->height - lastBand * band);
+    fullBands = lastRows == band ? mine : mine - 1u;
+    if (fullBands != mine) { tailAt = (size_t)lastBand * band * rowBytes; tailBytes = (size_t)lastRows * rowBytes; }
+}
+
+int okrt_read_result_async(okrt_renderer* r, uint8_t* outRgba8, uint64_t* outBytes, uint32_t slot)
+{
+    int rc = checkHandle(r, "okrt_read_result_async"); if (rc) return rc;
+    if (!outRgba8 || slot > 1u) { setError("okrt_read_result_async: bad argument"); return OKRT_ERR_INVALID_ARGUMENT; }
+    const size_t imageBytes = (size_t)r->width * r->height * 4;
+    if (!r->streamCopy) {
+        OKRT_CUDA(cudaStreamCreateWithFlags(&r->streamCopy, cudaStreamNonBlocking));
+        for (int k = 0; k < 2; k++) {
+            OKRT_CUDA(cudaEventCreateWithFlags(&r->evSnapshot[k], cudaEventDisableTiming));
+            OKRT_CUDA(cudaEventCreateWithFlags(&r->evCopied[k], cudaEventDisableTiming));
+        }
+    }
+    if (!r->snapshot[slot]) OKRT_CUDA(cudaMalloc(&r->snapshot[slot], imageBytes));
+    /* the snapshot of this slot may still be on its way to the host from two calls ago */
+    if (r->copyPending[slot]) OKRT_CUDA(cudaStreamWaitEvent(r->stream, r->evCopied[slot], 0));
+    size_t first, pitch, runBytes, tailAt, tailBytes; uint32_t fullBands;
+    ownedRuns(r, first, pitch, runBytes, fullBands, tailAt, tailBytes);
+    uint64_t moved = 0;
+    const uint8_t* src = (const uint8_t*)r->result;
+    uint8_t* snap = (uint8_t*)r->snapshot[slot];
+    if (fullBands) OKRT_CUDA(cudaMemcpy2DAsync(snap + first, pitch, src + first, pitch, runBytes, fullBands, cudaMemcpyDeviceToDevice, r->stream));
+    if (tailBytes) OKRT_CUDA(cudaMemcpyAsync(snap + tailAt, src + tailAt, tailBytes, cudaMemcpyDeviceToDevice, r->stream));
+    OKRT_CUDA(cudaEventRecord(r->evSnapshot[slot], r->stream));
+    OKRT_CUDA(cudaStreamWaitEvent(r->streamCopy, r->evSnapshot[slot], 0));
+    if (fullBands) { OKRT_CUDA(cudaMemcpy2DAsync(outRgba8 + first, pitch, snap + first, pitch, runBytes, fullBands, cudaMemcpyDeviceToHost, r->streamCopy)); moved += (uint64_t)fullBands * runBytes; }
+    if (tailBytes) { OKRT_CUDA(cudaMemcpyAsync(outRgba8 + tailAt, snap + tailAt, tailBytes, cudaMemcpyDeviceToHost, r->streamCopy)); moved += tailBytes; }
+    OKRT_CUDA(cudaEventRecord(r->evCopied[slot], r->streamCopy));
+    r->copyPending[slot] = true;
+    if (outBytes) *outBytes = moved;
+    return OKRT_OK;
+}
+
+int okrt_wait_read(okrt_renderer* r, uint32_t slot)
+{
+    int rc = checkHandle(r, "okrt_wait_read"); if (rc) return rc;
+    if (slot > 1u) { setError("okrt_wait_read: bad slot"); return OKRT_ERR_INVALID_ARGUMENT; }
+    if (!r->copyPending[slot]) return OKRT_OK;
+    OKRT_CUDA(cudaEventSynchronize(r->evCopied[slot]));
+    r->copyPending[slot] = false;
+    return OKRT_OK;
+}
+
+int okrt_reduce_accumulation(okrt_renderer* r, okrt_allreduce_fn allreduce, void* user, uint32_t totalFrames)
+{
+    int rc = checkHandle(r, "okrt_reduce_accumulation"); if (rc) return rc;
+    if (!allreduce || !totalFrames) { setError("okrt_reduce_accumulation: bad argument"); return OKRT_ERR_INVALID_ARGUMENT; }
+    if (allreduce((void*)r->accumulation, (size_t)r->width * r->height * 4, (void*)r->stream, user) != 0) {
+        setError("okrt_reduce_accumulation: the all-reduce callback failed");
+        return OKRT_ERR_STATE;
+    }
+    r->rd.numAccumulationFrames = totalFrames;
+    return okrt_resolve(r, totalFrames);
+}
+
+/* ------------------------------------------------------------ unit rates (bench.py's roofline denominators) */
+__global__ void __launch_bounds__(128) sectorRateKernel(const uint4* __restrict__ data, uint32_t mask, uint32_t blockWindow, uint32_t iters, uint32_t* sink)
+{
+    /* blockWindow != 0: each block stays inside its own window of that many sectors (L1-resident) */
+    if (blockWindow) { data += (size_t)(blockIdx.x % 64u) * blockWindow * 2u; mask = blockWindow - 1u; }
+    /* every lane walks its own pseudo-random chain of 32-byte sectors: the traversal kernel's access shape (two 256-bit loads per
+     * node, no two lanes in one sector) with enough independent loads in flight per lane to measure throughput, not latency */
+    uint32_t x = (blockIdx.x * blockDim.x + threadIdx.x) * 2654435761u + 12345u;
+    uint32_t acc = 0u;
+    for (uint32_t i = 0; i < iters; i++) {
+        uint4 a[4], b[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            x = x * 1664525u + 1013904223u;
+            const uint4* p = data + (size_t)((x >> 8) & mask) * 2u;
+            asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                         : "=r"(a[k].x), "=r"(a[k].y), "=r"(a[k].z), "=r"(a[k].w), "=r"(b[k].x), "=r"(b[k].y), "=r"(b[k].z), "=r"(b[k].w) : "l"(p));
+        }
+#pragma unroll
+        for (int k = 0; k < 4; k++) acc += a[k].x ^ b[k].w;
+    }
+    if (acc == 0x12345678u) *sink = acc;
+}
+
+__global__ void __launch_bounds__(128) issueRateKernel(uint32_t iters, float seed, float* sink, unsigned long long* cycles)
+{
+    float a0 = seed + threadIdx.x, a1 = a0 + 1.f, a2 = a0 + 2.f, a3 = a0 + 3.f, a4 = a0 + 4.f, a5 = a0 + 5.f, a6 = a0 + 6.f, a7 = a0 + 7.f;
+    const float m = 1.0000001f, c = 0.5f;
+    const long long t0 = clock64();
+    for (uint32_t i = 0; i < iters; i++) {
+#pragma unroll
+        for (int k = 0; k < 8; k++) {           /* 64 independent FFMA per trip: 8 chains x 8 */
+            a0 = __fmaf_rn(a0, m, c); a1 = __fmaf_rn(a1, m, c); a2 = __fmaf_rn(a2, m, c); a3 = __fmaf_rn(a3, m, c);
+            a4 = __fmaf_rn(a4, m, c); a5 = __fmaf_rn(a5, m, c); a6 = __fmaf_rn(a6, m, c); a7 = __fmaf_rn(a7, m, c);
+        }
+    }
+    const long long t1 = clock64();
+    const float sum = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
+    if (sum == 123.456f) *sink = sum;
+    if (blockIdx.x == 0 && threadIdx.x == 0) *cycles = (unsigned long long)(t1 - t0);
+}
+
+int okrt_measure_unit_peaks(int device, okrt_unit_peaks* out)
+{
+    if (!out) { setError("okrt_measure_unit_peaks: null output"); return OKRT_ERR_INVALID_ARGUMENT; }
+    std::memset(out, 0, sizeof(*out));
+    if (okrt_device_count() <= device || device < 0) { setError("okrt_measure_unit_peaks: no such CUDA device"); return OKRT_ERR_NO_DEVICE; }
+    OKRT_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    OKRT_CUDA(cudaGetDeviceProperties(&prop, device));
+    const uint32_t sectors = 1u << 19;                          /* 2^19 x 32 B = 16 MB: inside the 126 MB L2, far outside the L1 */
+    uint4* data = nullptr; uint32_t* sink = nullptr; float* fsink = nullptr; unsigned long long* cycles = nullptr;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    cudaError_t e = cudaMalloc(&data, (size_t)sectors * 32);
+    if (e == cudaSuccess) e = cudaMemset(data, 1, (size_t)sectors * 32);
+    if (e == cudaSuccess) e = cudaMalloc(&sink, 4);
+    if (e == cudaSuccess) e = cudaMalloc(&fsink, 4);
+    if (e == cudaSuccess) e = cudaMalloc(&cycles, 8);
+    if (e == cudaSuccess) e = cudaEventCreate(&e0);
+    if (e == cudaSuccess) e = cudaEventCreate(&e1);
+    const unsigned grid = (unsigned)prop.multiProcessorCount * 8u;
+    float msSector = 0.f, msSectorL1 = 0.f, msIssue = 0.f;
+    const uint32_t sIters = 256u, iIters = 4096u;
+    unsigned long long hCycles = 0;
+    if (e == cudaSuccess) {
+        for (int rep = 0; rep < 3 && e == cudaSuccess; rep++) {     /* the last repetition is the warm one */
+            cudaEventRecord(e0);
+            sectorRateKernel<<<grid, 128>>>(data, sectors - 1u, 0u, sIters, sink);
+            cudaEventRecord(e1);
+            e = cudaEventSynchronize(e1);
+            if (e == cudaSuccess) e = cudaEventElapsedTime(&msSector, e0, e1);
+        }
+        for (int rep = 0; rep < 3 && e == cudaSuccess; rep++) {
+            cudaEventRecord(e0);
+            sectorRateKernel<<<grid, 128>>>(data, sectors - 1u, 512u, sIters * 4u, sink);       /* 512 sectors = 16 KB per block, 8 blocks per SM */
+            cudaEventRecord(e1);
+            e = cudaEventSynchronize(e1);
+            if (e == cudaSuccess) e = cudaEventElapsedTime(&msSectorL1, e0, e1);
+        }
+        for (int rep = 0; rep < 3 && e == cudaSuccess; rep++) {
+            cudaEventRecord(e0);
+            issueRateKernel<<<grid, 128>>>(iIters, 1.0f, fsink, cycles);
+            cudaEventRecord(e1);
+            e = cudaEventSynchronize(e1);
+            if (e == cudaSuccess) e = cudaEventElapsedTime(&msIssue, e0, e1);
+        }
+        if (e == cudaSuccess) e = cudaMemcpy(&hCycles, cycles, 8, cudaMemcpyDeviceToHost);
+    }
+    if (data) cudaFree(data); if (sink) cudaFree(sink); if (fsink) cudaFree(fsink); if (cycles) cudaFree(cycles);
+    if (e0) cudaEventDestroy(e0); if (e1) cudaEventDestroy(e1);
+    if (e != cudaSuccess) { setError(std::string("okrt_measure_unit_peaks: ") + cudaGetErrorString(e)); return OKRT_ERR_CUDA; }
+    const double threads = (double)grid * 128.0;
+    out->sectorsPerSecond = threads * sIters * 4.0 * 2.0 / (msSector * 1e-3);         /* 4 loads x 2 sectors per trip */
+    out->sectorsPerSecondL1 = threads * (sIters * 4.0) * 4.0 * 2.0 / (msSectorL1 * 1e-3);
+    out->warpInstructionsPerSecond = (threads / 32.0) * iIters * 64.0 / (msIssue * 1e-3);
+    out->smClockMHz = msIssue > 0.f ? (double)hCycles / (msIssue * 1e-3) / 1e6 : 0.0;
+    out->numSms = (uint32_t)prop.multiProcessorCount;
     return OKRT_OK;
 }
 

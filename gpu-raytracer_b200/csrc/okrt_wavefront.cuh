@@ -314,17 +314,20 @@ traceFastKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ F
     }
 #ifdef OKRT_TRACE_STATS
     {
+        /* per bounce, the layout okrt_get_trace_stats documents: [0] rays [1] node steps [2] leaf entries (wide layout only)
+         * [3] triangle tests [4] node-phase iterations (warps) [5] triangle-phase iterations [6] lanes busy in node iterations
+         * [7] lanes busy in triangle iterations */
         unsigned long long* st = wb.traceStats + 8u * bounce;
         const uint32_t a0 = __reduce_add_sync(0xFFFFFFFFu, stRays), a1 = __reduce_add_sync(0xFFFFFFFFu, stNodeSteps), a2 = __reduce_add_sync(0xFFFFFFFFu, stTriSteps);
         if (lane == 0u) {
-            atomicAdd(st + 0, (unsigned long long)a0); atomicAdd(st + 1, (unsigned long long)a1); atomicAdd(st + 2, (unsigned long long)a2);
-            atomicAdd(st + 3, (unsigned long long)stNodeIters); atomicAdd(st + 4, (unsigned long long)stTriIters); atomicAdd(st + 5, (unsigned long long)stRefills);
-            atomicAdd(st + 6, (unsigned long long)(clock64() - stStart)); atomicMax(st + 7, (unsigned long long)(clock64() - stStart));
+            atomicAdd(st + 0, (unsigned long long)a0); atomicAdd(st + 1, (unsigned long long)a1); atomicAdd(st + 3, (unsigned long long)a2);
+            atomicAdd(st + 4, (unsigned long long)stNodeIters); atomicAdd(st + 5, (unsigned long long)stTriIters);
+            atomicAdd(st + 6, (unsigned long long)a1); atomicAdd(st + 7, (unsigned long long)a2);
         }
+        (void)stStart; (void)stRefills;
     }
 #endif
 }
-
 
 /* ------------------------------------------------------------- trace, wide layout
  * The same persistent-warp scheme as traceFastKernel over the wide layout (okrt_wide.cuh): a NODE phase (every lane with a

@@ -44,9 +44,10 @@ DEFAULT_PIPELINE = 0      # 0 wavefront, 1 persistent megakernel (the tests para
 class Renderer:
     """Low-level use of the C ABI (binding-table setters), as the parity tests drive it."""
 
-    def __init__(self, okrt, host, width, height, envFaces=None, device=0):
+    def __init__(self, okrt, host, width, height, envFaces=None, device=0, lib=None):
+        """lib: a ctypes handle from abi.load_library (e.g. the -DOKRT_TRACE_STATS build); default: the product library."""
         abi = okrt.abi
-        self.abi, self.L = abi, abi.lib()
+        self.abi, self.L = abi, (lib if lib is not None else abi.lib())
         self.W, self.H = width, height
         h = ctypes.c_void_p()
         abi.check(self.L.okrt_create(device, width, height, ctypes.byref(h)))
@@ -102,6 +103,14 @@ class Renderer:
         s = np.zeros(1, self.abi.STATS)
         self.abi.check(self.L.okrt_get_stats(self.h, self.abi.ptr(s)))
         return s[0]
+
+    def trace_stats(self, bounces):
+        """[bounces, 8] step counters of the traversal kernel since okrt_reset_stats (a -DOKRT_TRACE_STATS library only)."""
+        out = np.zeros((bounces, 8), np.uint64)
+        rc = self.L.okrt_get_trace_stats(self.h, self.abi.ptr(out), bounces)
+        if rc != self.abi.OK:
+            raise self.abi.OkrtError(rc, self.L.okrt_last_error().decode("utf-8", "replace"))
+        return out
 
     def close(self):
         if self.h:

@@ -156,6 +156,18 @@ public:
         check(okrt_read_result(m_handle, rgba8.data()));
     }
     okrt_renderer* handle() { return m_handle; }
+    /* new: `frames` frames in one call (okrt_render_frames), the non-blocking read-back, and the single exchange step of the
+     * sample-sharded mode (include/okrt.h: okrt_read_result_async, okrt_reduce_accumulation) */
+    void renderFrames(uint32_t frames)
+    {
+        calculateProjectionData();
+        updateBuffers();
+        check(okrt_render_frames(m_handle, frames));
+    }
+    void readResultAsync(uint8_t* pinnedRgba8, uint32_t slot) { check(okrt_read_result_async(m_handle, pinnedRgba8, nullptr, slot)); }
+    void waitRead(uint32_t slot) { check(okrt_wait_read(m_handle, slot)); }
+    void reduceAccumulation(okrt_allreduce_fn allreduce, void* user, uint32_t totalFrames) { check(okrt_reduce_accumulation(m_handle, allreduce, user, totalFrames)); }
+    void sync() { check(okrt_sync(m_handle)); }
 
     /* RayTracer::getGlobalNodeIdx (RayTracer.h:226-230) */
     uint32_t getGlobalNodeIdx(uint32_t meshID, uint32_t localNodeIdx) const

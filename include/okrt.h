@@ -456,6 +456,13 @@ OKRT_API int okrt_read_result(okrt_renderer* r, uint8_t* outRgba8);            /
  * rows untouched), so N ranks fill one host image without moving N copies of it; *outBytes (may be NULL) = bytes moved.
  * Unsharded renderers behave like okrt_read_result. */
 OKRT_API int okrt_read_result_owned(okrt_renderer* r, uint8_t* outRgba8, uint64_t* outBytes);
+/* Non-blocking form: snapshots the result image as of the frames submitted so far (device-to-device, on the renderer's
+ * stream) and starts the device-to-host copy of the rows this handle owns on a second stream; returns at once, so the caller
+ * can submit the next okrt_render_frames while the copy runs (the reference's render() is fire-and-forget on the device queue,
+ * RayTracer.cpp:219-260).  `slot` (0 or 1) names one of two snapshots; okrt_wait_read(slot) blocks until that copy has landed
+ * in outRgba8, which must stay valid (and should be page-locked, okrt_host_register) until then. */
+OKRT_API int okrt_read_result_async(okrt_renderer* r, uint8_t* outRgba8, uint64_t* outBytes, uint32_t slot);
+OKRT_API int okrt_wait_read(okrt_renderer* r, uint32_t slot);
 OKRT_API int okrt_read_accumulation(okrt_renderer* r, float* outRgba32f);
 /* f4: rasterises the overlay's lines into the RGBA8 result (u0); the accumulation (u1) is untouched, the next
  * okrt_render_frames rewrites u0. */
@@ -466,6 +473,28 @@ OKRT_API int okrt_read_aov(okrt_renderer* r, okrt_aov* out);                   /
 OKRT_API int okrt_write_accumulation(okrt_renderer* r, const float* rgba32f, uint32_t numAccumulationFrames);
 /* recompute u0 = saturate(u1 / frames) (RaytracerCS.hlsl:529) after an external reduction of u1 */
 OKRT_API int okrt_resolve(okrt_renderer* r, uint32_t totalFrames);
+
+/* Sample-sharded mode: every rank has rendered its own frames into u1; `allreduce` sums `count` floats in place
+ * across the ranks on `cudaStream` (ncclAllReduce(ptr, ptr, count, ncclFloat, ncclSum, comm, stream) in a C++ host —
+ * host/sample_sharded_nccl.cpp —, torch.distributed.all_reduce in bench.py); the library enqueues it on the renderer's stream
+ * after the frames submitted so far, then u0 = saturate(u1 / totalFrames) (RaytracerCS.hlsl:529).  Does not block.  The
+ * callback returns 0 on success.  NCCL itself stays out of the library's link line: the caller owns the communicator. */
+typedef int (*okrt_allreduce_fn)(void* deviceFloats, size_t count, void* cudaStream, void* user);
+OKRT_API int okrt_reduce_accumulation(okrt_renderer* r, okrt_allreduce_fn allreduce, void* user, uint32_t totalFrames);
+
+/* Unit rates of this device, measured by two small kernels (about 50 ms): what the traversal kernel's roofline is quoted
+ * against (bench.py).  sectorsPerSecond: 32-byte sectors per second that divergent 256-bit loads (every lane its own sector, an
+ * L2-resident 16 MB array, the traversal kernel's access shape) deliver over the whole device; warpInstructionsPerSecond: issue
+ * rate of a dependent-free FP32 instruction stream with 8 warps per scheduler. */
+typedef struct okrt_unit_peaks {
+    double sectorsPerSecond;       /* 16 MB window: every load misses the L1 and hits the L2 */
+    double sectorsPerSecondL1;     /* 16 KB window per block: every load hits the L1 — the LSU data stage's own rate */
+    double warpInstructionsPerSecond;
+    double smClockMHz;             /* (cycles of the issue kernel / its duration): the SM clock during the measurement */
+    uint32_t numSms;
+    uint32_t reserved;
+} okrt_unit_peaks;
+OKRT_API int okrt_measure_unit_peaks(int device, okrt_unit_peaks* out);
 
 /* device pointers for peer/NCCL exchange (sample-sharded mode reduces u1 in place) */
 /* Page-locks a caller-owned host buffer so that okrt_read_* / okrt_write_accumulation copy at full PCIe rate and
