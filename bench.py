@@ -171,8 +171,9 @@ def run_config(okrt, name, rm, sc, info, width, height, bounces, frames, env, de
     r.options(maxBounces=bounces, traversal=abi.TRAVERSAL_FAST, coverAllPixels=0)
     rd = host["rd"].copy()
     t0 = time.perf_counter()
-    r.render(rd, frames=frames)                      # warm-up: includes the traversal-layout build
+    r.render(rd, frames=frames)                      # warm-up: includes the traversal-layout build (on the device)
     first_ms = (time.perf_counter() - t0) * 1e3
+    lb = r.wait_layout()                             # ... and the host SAH tree that replaces the clustered one in the background
     abi.check(r.L.okrt_reset_stats(r.h))
     ms = 0.0
     for _ in range(steps):
@@ -184,7 +185,8 @@ def run_config(okrt, name, rm, sc, info, width, height, bounces, frames, env, de
     out = {"workload": "%s %dx%d maxBounces=%d, %d frames per call" % (info.get("name", name), width, height, bounces, frames),
            "value": seg / (ms * 1e-3) / 1e6, "unit": UNIT, "ms_per_frame": ms / (steps * frames), "ray_segments": seg,
            "fallback_segments": fb, "triangles": int(len(host["geometry"].trianglesPos)), "stand_in": bool(info.get("stand_in", False)),
-           "host_build_s": round(build_s, 2), "first_call_ms": round(first_ms, 1)}
+           "host_build_s": round(build_s, 2), "first_call_ms": round(first_ms, 1),
+           "layout": {"builder": int(lb["builder"]), "device_ms": round(float(lb["deviceMs"]), 2), "refine_ms": round(float(lb["refineMs"]), 1)}}
     if note:
         out["note"] = note
     return out
@@ -255,6 +257,7 @@ def run_c5(okrt, scene_parts, env, device, rank, world, dist):
         st = r.stats()
         return wall, float(st["lastRenderMs"]), int(st["raySegments"])
     one_run(4)                                               # warm-up: layout build, buffers, NCCL channels for this message size
+    r.wait_layout()
     reduce_events.clear()
     wall, render_ms, seg = one_run(C5_FRAMES_PER_RANK)
     ar_ms = float(reduce_events[-1][0].elapsed_time(reduce_events[-1][1])) if reduce_events else 0.0
@@ -304,6 +307,7 @@ def trace_roofline(okrt, host, env, device, trace_ms, trace_launches, dev_ms, se
     r.options(maxBounces=MAX_BOUNCES, traversal=abi.TRAVERSAL_FAST, coverAllPixels=0)
     rd = host["rd"].copy()
     r.render(rd, frames=FRAMES_PER_STEP)
+    r.wait_layout()
     abi.check(slib.okrt_reset_stats(r.h))
     r.render(rd, frames=FRAMES_PER_STEP)
     st = r.trace_stats(MAX_BOUNCES + 1).astype(np.float64)
@@ -408,6 +412,15 @@ def main():
     abi.check(r.L.okrt_render_frames(r.h, FRAMES_PER_STEP))                   # first call: builds the traversal layout
     abi.check(r.L.okrt_sync(r.h))
     first_call_ms = (time.perf_counter() - t_first) * 1e3
+    lb = np.zeros(1, abi.LAYOUT_BUILD)
+    abi.check(r.L.okrt_get_layout_build(r.h, abi.ptr(lb)))
+    layout_first = {"builder": int(lb[0]["builder"]), "device_ms": float(lb[0]["deviceMs"]), "wall_ms": float(lb[0]["wallMs"]),
+                    "pair_nodes": int(lb[0]["numPairNodes"]), "why": bytes(lb[0]["why"]).split(b"\0")[0].decode()}
+    t_wait = time.perf_counter()
+    abi.check(r.L.okrt_wait_layout(r.h))                                       # the background SAH build replaces the clustered tree
+    abi.check(r.L.okrt_get_layout_build(r.h, abi.ptr(lb)))
+    layout_now = {"builder": int(lb[0]["builder"]), "refine_ms": float(lb[0]["refineMs"]), "waited_ms": (time.perf_counter() - t_wait) * 1e3,
+                  "pair_nodes": int(lb[0]["numPairNodes"]), "stack": int(lb[0]["fastStackDepth"])}
     if args.warmup > 1:
         abi.check(r.L.okrt_render_frames(r.h, (args.warmup - 1) * FRAMES_PER_STEP))
     barrier()
@@ -485,7 +498,10 @@ def main():
                 "gpu_launches": launches,
                 "ray_segments": segments, "fallback_segments": fallback, "traversal": args.traversal,
                 "trace_kernel_ms": trace_ms, "trace_kernel_launches": trace_launches,
-                "first_call_ms": first_call_ms, "unit_peaks": peaks}
+                "first_call_ms": first_call_ms, "unit_peaks": peaks,
+                "layout_build": {"first_call": layout_first, "timed_region": layout_now,
+                                 "note": "builder 1: on the device (clustered tree, ready for the first frame after a scene edit); 2: the host SAH "
+                                         "builder's tree, built in the background and adopted before the timed region; 0: host builder, synchronous"}}
         if world > 1:
             line["rank_ms"] = rank_ms                 # device time of each rank's K steps: shows the load balance of the tile split
             line["rank_segments"] = rank_segments

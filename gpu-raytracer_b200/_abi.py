@@ -54,6 +54,8 @@ AOV = np.dtype([("hitKind", "<u4"), ("hitIdx", "<u4"), ("triIdx", "<u4"), ("bary
 STATS = np.dtype([("raySegments", "<u8"), ("fallbackSegments", "<u8"), ("pixelsTraced", "<u8"), ("kernelLaunches", "<u8"),
                   ("lastRenderMs", "<f4"), ("traceKernelMs", "<f4"), ("traceKernelLaunches", "<f4"), ("reserved", "<f4", 1)])
 
+LAYOUT_BUILD = np.dtype([("wallMs", "<f4"), ("deviceMs", "<f4"), ("refineMs", "<f4"), ("builder", "<u4"), ("numPairNodes", "<u4"),
+                         ("fastStackDepth", "<u4"), ("rounds", "<u4"), ("why", "S100")])
 UNIT_PEAKS = np.dtype([("sectorsPerSecond", "<f8"), ("sectorsPerSecondL1", "<f8"), ("warpInstructionsPerSecond", "<f8"), ("smClockMHz", "<f8"), ("numSms", "<u4"), ("reserved", "<u4")])
 ALLREDUCE_FN = ctypes.CFUNCTYPE(ctypes.c_int, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p)
 LAYOUT_INFO = np.dtype([("numPairNodes", "<u4"), ("numFlattenedLeaves", "<u4"), ("numMergedInstances", "<u4"),
@@ -172,6 +174,8 @@ SYMBOLS = [
     ("okrt_wait_read", _I, [_P, _U]),
     ("okrt_reduce_accumulation", _I, [_P, _P, _P, _U]),
     ("okrt_measure_unit_peaks", _I, [_I, _P]),
+    ("okrt_get_layout_build", _I, [_P, _P]),
+    ("okrt_wait_layout", _I, [_P]),
     ("okrt_trace_rays_host", _I, [_P, _U, _P, _U, _P, _U, _P, _U, _U, _P, _U, _P]),
 ]
 

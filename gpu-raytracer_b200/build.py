@@ -16,8 +16,8 @@ OUT = os.path.join(HERE, "libokrt.so")
 OBJ = os.path.join(HERE, "_obj")
 
 HOST_SOURCES = ["okrt_host.cpp", "okrt_accel.cpp", "okrt_obj.cpp", "okrt_image.cpp"]
-DEVICE_SOURCES = ["okrt_device.cu", "okrt_build_device.cu"]
-HEADERS = ["okrt_internal.h", "okrt_accel.h", "okrt_kernels.cuh", "okrt_wavefront.cuh", "okrt_math.cuh", "okrt_wide.cuh"]
+DEVICE_SOURCES = ["okrt_device.cu", "okrt_build_device.cu", "okrt_layout_device.cu"]
+HEADERS = ["okrt_internal.h", "okrt_accel.h", "okrt_kernels.cuh", "okrt_wavefront.cuh", "okrt_math.cuh", "okrt_wide.cuh", "okrt_layout_device.h"]
 
 
 def _nvcc():

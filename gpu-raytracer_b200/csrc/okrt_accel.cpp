@@ -474,6 +474,58 @@ inline float roundUp(double v) { float f = (float)v; return (double)f < v ? std:
 
 } // namespace
 
+
+/* Validates the oct-tree arrays and derives what both layout builders need: parent per node, whether every box on the way up
+ * from a node contains the one below it, which (reachable) node lists each instance, the reference traversal's stack need. */
+bool octTreeChecks(const okrt_octree_node* octNodes, uint32_t numOctNodes, uint32_t numInstances, std::vector<uint32_t>& octParent,
+                   std::vector<uint8_t>& octNested, std::vector<uint32_t>& instOct, uint32_t& exactOctDepth, std::string& error)
+{
+    octParent.assign(numOctNodes, 0xFFFFFFFFu);
+    std::vector<uint8_t> reachable(numOctNodes, 0);
+    exactOctDepth = 0;
+    if (numOctNodes) {
+        std::vector<uint32_t> stack{0u};
+        size_t maxOcc = 1, visited = 0;
+        while (!stack.empty()) {
+            const uint32_t n = stack.back(); stack.pop_back();
+            if (reachable[n]) { error = "oct-tree node reachable twice"; return false; }
+            reachable[n] = 1;
+            if (++visited > numOctNodes) { error = "oct-tree cycle"; return false; }
+            const okrt_octree_node& on = octNodes[n];
+            for (uint32_t c = 0; c < on.numChildren; c++) {
+                const uint64_t ci = (uint64_t)on.firstChildIdx + c;
+                if (ci >= numOctNodes) { error = "oct-tree child index out of range"; return false; }
+                octParent[ci] = n;
+                stack.push_back((uint32_t)ci);
+            }
+            maxOcc = std::max(maxOcc, stack.size());
+        }
+        exactOctDepth = (uint32_t)maxOcc;
+    }
+    /* octNested[n]: every box on the way from n up to the root contains the box below it (component-wise, exactly) */
+    octNested.assign(numOctNodes, 0);
+    for (uint32_t n = 0; n < numOctNodes; n++) {
+        if (!reachable[n]) continue;
+        bool nested = true;
+        for (uint32_t c = n, p = octParent[n]; p != 0xFFFFFFFFu && nested; c = p, p = octParent[p])
+            for (int k = 0; k < 3; k++)
+                nested = nested && octNodes[p].boundingBox.min[k] <= octNodes[c].boundingBox.min[k] && octNodes[c].boundingBox.max[k] <= octNodes[p].boundingBox.max[k];
+        octNested[n] = nested ? 1 : 0;
+    }
+    instOct.assign(numInstances, 0xFFFFFFFFu);
+    for (uint32_t n = 0; n < numOctNodes; n++) {
+        if (!reachable[n]) continue;
+        const okrt_octree_node& on = octNodes[n];
+        if (on.meshesStartIdx == OKRT_INVALID_UINT || on.meshesEndIdx == OKRT_INVALID_UINT) continue;
+        if (on.meshesEndIdx > numInstances && on.meshesStartIdx < on.meshesEndIdx) { error = "oct-tree node lists instances out of range"; return false; }
+        for (uint32_t i = on.meshesStartIdx; i < on.meshesEndIdx; i++) {
+            if (instOct[i] != 0xFFFFFFFFu) { error = "instance listed by two oct-tree nodes"; return false; }
+            instOct[i] = n;
+        }
+    }
+    return true;
+}
+
 bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh_node* nodes, uint32_t numNodes,
                      const okrt_mesh_instance* instances, uint32_t numInstances,
                      const okrt_octree_node* octNodes, uint32_t numOctNodes, FastLayout& out, bool wantWide)
@@ -500,53 +552,10 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
     }
 
     phase("triangle records");
-    /* oct-tree: parents, reachability, reference stack bound */
-    out.octParent.assign(numOctNodes, 0xFFFFFFFFu);
-    std::vector<uint8_t> reachable(numOctNodes, 0);
-    if (numOctNodes) {
-        std::vector<uint32_t> stack{0u};
-        size_t maxOcc = 1, visited = 0;
-        while (!stack.empty()) {
-            const uint32_t n = stack.back(); stack.pop_back();
-            if (reachable[n]) { out.error = "oct-tree node reachable twice"; return false; }
-            reachable[n] = 1;
-            if (++visited > numOctNodes) { out.error = "oct-tree cycle"; return false; }
-            const okrt_octree_node& on = octNodes[n];
-            for (uint32_t c = 0; c < on.numChildren; c++) {
-                const uint64_t ci = (uint64_t)on.firstChildIdx + c;
-                if (ci >= numOctNodes) { out.error = "oct-tree child index out of range"; return false; }
-                out.octParent[ci] = n;
-                stack.push_back((uint32_t)ci);
-            }
-            maxOcc = std::max(maxOcc, stack.size());
-        }
-        out.exactOctDepth = (uint32_t)maxOcc;
-    }
-
-    /* octNested[n]: every box on the way from n up to the root contains the box below it (component-wise, exactly) */
-    std::vector<uint8_t> octNested(numOctNodes, 0);
-    for (uint32_t n = 0; n < numOctNodes; n++) {
-        if (!reachable[n]) continue;
-        bool nested = true;
-        for (uint32_t c = n, p = out.octParent[n]; p != 0xFFFFFFFFu && nested; c = p, p = out.octParent[p])
-            for (int k = 0; k < 3; k++)
-                nested = nested && octNodes[p].boundingBox.min[k] <= octNodes[c].boundingBox.min[k] && octNodes[c].boundingBox.max[k] <= octNodes[p].boundingBox.max[k];
-        octNested[n] = nested ? 1 : 0;
-    }
-
-    /* which (reachable) oct-tree node lists each instance */
-    std::vector<uint32_t> instOct(numInstances, 0xFFFFFFFFu);
-    for (uint32_t n = 0; n < numOctNodes; n++) {
-        if (!reachable[n]) continue;
-        const okrt_octree_node& on = octNodes[n];
-        if (on.meshesStartIdx == OKRT_INVALID_UINT || on.meshesEndIdx == OKRT_INVALID_UINT) continue;
-        if (on.meshesEndIdx > numInstances && on.meshesStartIdx < on.meshesEndIdx) { out.error = "oct-tree node lists instances out of range"; return false; }
-        for (uint32_t i = on.meshesStartIdx; i < on.meshesEndIdx; i++) {
-            if (instOct[i] != 0xFFFFFFFFu) { out.error = "instance listed by two oct-tree nodes"; return false; }
-            instOct[i] = n;
-        }
-    }
-
+    /* oct-tree: parents, reachability, reference stack bound, which node lists each instance */
+    std::vector<uint8_t> octNested;
+    std::vector<uint32_t> instOct;
+    if (!octTreeChecks(octNodes, numOctNodes, numInstances, out.octParent, octNested, instOct, out.exactOctDepth, out.error)) return false;
     phase("oct-tree checks");
     /* bottom level: one conversion per distinct BVH root */
     Builder b{tris, numTris, nodes, numNodes, out};
@@ -691,7 +700,7 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris, const okrt_bvh
                     b.deepestPair = before;
                     if (b.failed) return false;
                     leaf.weight = n.triEnd - n.triStart;
-                    leaf.wstart = n.triStart; leaf.wcount = n.triEnd - n.triStart; leaf.slack = leafSlack(tris, n.triStart, n.triEnd - n.triStart);
+                    leaf.wstart = n.triStart; leaf.wcount = n.triEnd - n.triStart; leaf.slack = wantWide ? leafSlack(tris, n.triStart, n.triEnd - n.triStart) : 0.f;
                     for (int k = 0; k < 3; k++) { leaf.lo[k] = n.boundingBox.min[k]; leaf.hi[k] = n.boundingBox.max[k]; }
                     leaves.push_back(leaf);
                     out.numFlattenedLeaves++;

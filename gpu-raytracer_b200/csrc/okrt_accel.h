@@ -106,4 +106,7 @@ bool buildFastLayout(const okrt_triangle* tris, uint32_t numTris,
                      const okrt_octree_node* octNodes, uint32_t numOctNodes,
                      FastLayout& out, bool wantWide = false);
 
+bool octTreeChecks(const okrt_octree_node* octNodes, uint32_t numOctNodes, uint32_t numInstances, std::vector<uint32_t>& octParent,
+                   std::vector<uint8_t>& octNested, std::vector<uint32_t>& instOct, uint32_t& exactOctDepth, std::string& error);
+
 } // namespace okrt

@@ -11,6 +11,8 @@
 
 #include <algorithm>
 #include <atomic>
+#include <chrono>
+#include <memory>
 #include <thread>
 #include <cstdio>
 #include <cstdlib>
@@ -21,6 +23,7 @@
 #include "okrt.h"
 #include "okrt_accel.h"
 #include "okrt_internal.h"
+#include "okrt_layout_device.h"
 #include "okrt_kernels.cuh"
 #include "okrt_wavefront.cuh"
 
@@ -106,6 +109,21 @@ struct TextureArray {
 
 } // namespace
 
+/* The device builder's clustered tree is ready in milliseconds but costs ~18 % of the rays/s of the host builder's full-sweep SAH
+ * tree (measured).  After a device build the host builder therefore runs in the background on the same arrays;
+ * its layout replaces the clustered one at the next okrt_render* call after it finishes (okrt_wait_layout waits for it).
+ * Images do not change: both trees hold the reference's leaves, the visiting order is free. */
+struct RefineJob {
+    std::shared_ptr<const std::vector<okrt_triangle>> tris;
+    std::shared_ptr<const std::vector<okrt_bvh_node>> nodes;
+    std::shared_ptr<const std::vector<okrt_mesh_instance>> instances;
+    std::shared_ptr<const std::vector<okrt_octree_node>> oct;
+    FastLayout layout;
+    bool ok = false;
+    float ms = 0.f;
+    std::atomic<bool> done{false};
+};
+
 struct okrt_renderer {
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -129,10 +147,12 @@ struct okrt_renderer {
     cudaTextureObject_t fastTrisTex = 0;
 
     /* host copies needed to (re)build the fast layout */
-    std::vector<okrt_triangle> hTris;
-    std::vector<okrt_bvh_node> hNodes;
-    std::vector<okrt_mesh_instance> hInstances;
-    std::vector<okrt_octree_node> hOct;
+    /* shared, immutable once set: a background refinement (RefineJob) may still read the arrays of an older edit */
+    std::shared_ptr<const std::vector<okrt_triangle>> hTris = std::make_shared<std::vector<okrt_triangle>>();
+    std::shared_ptr<const std::vector<okrt_bvh_node>> hNodes = std::make_shared<std::vector<okrt_bvh_node>>();
+    std::shared_ptr<const std::vector<okrt_mesh_instance>> hInstances = std::make_shared<std::vector<okrt_mesh_instance>>();
+    std::shared_ptr<const std::vector<okrt_octree_node>> hOct = std::make_shared<std::vector<okrt_octree_node>>();
+    std::shared_ptr<struct RefineJob> refine;   /* host SAH build of the layout the device builder has just put in place */
     bool layoutDirty = true;
     uint32_t topRef = kRefNone;
     bool allRigid = true;
@@ -150,6 +170,7 @@ struct okrt_renderer {
     int numSms = 0, blocksPerSmLean = 1, blocksPerSmInstrumented = 1;   /* persistent grid = SMs x resident blocks */
     int blocksPerSmTrace = 1, blocksPerSmWide = 1;
     bool layoutHasWide = false;                 /* the wide layout is built only for OKRT_TRAVERSAL_WIDE */
+    okrt_layout_build layoutBuild{};            /* how the last rebuild went (okrt_get_layout_build) */
     WavefrontBuffers wb{};                      /* path state of the wavefront pipeline (sized for width x height) */
     size_t wbPaths = 0, wbReserve = 0;
 };
@@ -181,15 +202,72 @@ int ensureAov(okrt_renderer* r)
     return OKRT_OK;
 }
 
+int finishLayout(okrt_renderer* r);
+int installHostLayout(okrt_renderer* r, const FastLayout& fl, bool wantWide);
+void startRefine(okrt_renderer* r);
+
+/* the layout built on the device where the scene allows it (okrt_layout_device.cu) */
+int rebuildLayoutDevice(okrt_renderer* r, std::string& why)
+{
+    DeviceLayout dl;
+    const int rc = buildFastLayoutDevice((const okrt_triangle*)r->triPos.ptr, (uint32_t)r->hTris->size(), (const okrt_bvh_node*)r->bvhNodes.ptr, r->hNodes->data(),
+                                         (uint32_t)r->hNodes->size(), r->hInstances->data(), (uint32_t)r->hInstances->size(), r->hOct->data(), (uint32_t)r->hOct->size(),
+                                         r->stream, dl, why);
+    if (rc) return rc;
+    if (dl.exactBvhDepth > kExactBvhStackCapacity || dl.exactOctDepth > kExactOctStackCapacity) {
+        cudaFree(dl.nodes); cudaFree(dl.tris);
+        why = "reference-order stacks would overflow (the host builder reports it)";
+        return OKRT_ERR_STATE;
+    }
+    r->fastNodes.release(); r->fastTris.release();
+    r->fastNodes.ptr = dl.nodes; r->fastNodes.count = dl.numPairNodes * 4u; r->fastNodes.bytes = (size_t)r->fastNodes.count * sizeof(Float4);
+    r->fastTris.ptr = dl.tris; r->fastTris.count = (uint32_t)r->hTris->size() * kTriQuads; r->fastTris.bytes = (size_t)r->fastTris.count * sizeof(Float4);
+    int rc2;
+    if ((rc2 = r->fastInstances.upload(dl.instances.data(), (uint32_t)dl.instances.size(), sizeof(Float4), r->stream))) return rc2;
+    if ((rc2 = r->octParent.upload(dl.octParent.data(), (uint32_t)dl.octParent.size(), sizeof(uint32_t), r->stream))) return rc2;
+    r->wideNodes.release(); r->wideLeaves.release(); r->wideRoot = kRefNone; r->maxSlack = 0.f; r->layoutHasWide = false;
+    r->topRef = dl.topRef; r->allRigid = dl.allRigid;
+    r->fastStackNeed = dl.maxStackDepth; r->exactBvhNeed = dl.exactBvhDepth; r->exactOctNeed = dl.exactOctDepth;
+    r->layoutBuild.builder = 1u; r->layoutBuild.deviceMs = dl.deviceMs; r->layoutBuild.numPairNodes = dl.numPairNodes;
+    r->layoutBuild.fastStackDepth = dl.maxStackDepth; r->layoutBuild.rounds = dl.plocRounds;
+    return finishLayout(r);
+}
+
 int rebuildLayout(okrt_renderer* r)
 {
+    const auto t0 = std::chrono::steady_clock::now();
+    std::memset(&r->layoutBuild, 0, sizeof(r->layoutBuild));
+    r->refine.reset();                                                  /* a refinement of older arrays is of no use any more */
+    const char* hostEnv = std::getenv("OKRT_LAYOUT_HOST");            /* read at every rebuild: tests switch builders in one process */
+    const bool forceHost = hostEnv && std::atoi(hostEnv) != 0;
+    std::string why = forceHost ? "OKRT_LAYOUT_HOST=1" : (r->opt.traversal == OKRT_TRAVERSAL_WIDE ? "OKRT_TRAVERSAL_WIDE is laid out by the host builder" : "");
+    if (why.empty()) {
+        const int rc = rebuildLayoutDevice(r, why);
+        if (rc == OKRT_OK) {
+            r->layoutBuild.wallMs = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+            startRefine(r);
+            return OKRT_OK;
+        }
+        if (rc != OKRT_ERR_STATE) return rc;
+    }
+    std::snprintf(r->layoutBuild.why, sizeof(r->layoutBuild.why), "%s", why.c_str());
     FastLayout fl;
     const bool wantWide = r->opt.traversal == OKRT_TRAVERSAL_WIDE;
-    if (!buildFastLayout(r->hTris.data(), (uint32_t)r->hTris.size(), r->hNodes.data(), (uint32_t)r->hNodes.size(),
-                         r->hInstances.data(), (uint32_t)r->hInstances.size(), r->hOct.data(), (uint32_t)r->hOct.size(), fl, wantWide)) {
+    if (!buildFastLayout(r->hTris->data(), (uint32_t)r->hTris->size(), r->hNodes->data(), (uint32_t)r->hNodes->size(),
+                         r->hInstances->data(), (uint32_t)r->hInstances->size(), r->hOct->data(), (uint32_t)r->hOct->size(), fl, wantWide)) {
         setError("scene rejected: " + fl.error);
         return OKRT_ERR_INVALID_ARGUMENT;
     }
+    int rc = installHostLayout(r, fl, wantWide);
+    if (rc) return rc;
+    r->layoutBuild.builder = 0u;
+    r->layoutBuild.wallMs = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    return OKRT_OK;
+}
+
+/* uploads a layout the host builder made and makes it the one the kernels walk */
+int installHostLayout(okrt_renderer* r, const FastLayout& fl, bool wantWide)
+{
     if (fl.maxStackDepth > kFastStackCapacity || fl.wideStackDepth > kWideStackCapacity || fl.exactBvhDepth > kExactBvhStackCapacity || fl.exactOctDepth > kExactOctStackCapacity) {
         char msg[256];
         std::snprintf(msg, sizeof(msg), "traversal stack would overflow: pairs %u/%u, wide %u/%u, bvh %u/%u, oct-tree %u/%u",
@@ -206,8 +284,52 @@ int rebuildLayout(okrt_renderer* r)
     if ((rc = r->wideNodes.upload(fl.wideNodes.data(), (uint32_t)fl.wideNodes.size(), sizeof(uint32_t), r->stream))) return rc;
     if ((rc = r->wideLeaves.upload(fl.wideLeaves.data(), (uint32_t)fl.wideLeaves.size(), sizeof(uint32_t), r->stream))) return rc;
     r->wideRoot = fl.wideRoot; r->maxSlack = fl.maxSlack; r->layoutHasWide = wantWide;
+    r->topRef = fl.topRef;
+    r->allRigid = fl.allRigid;
+    r->fastStackNeed = fl.maxStackDepth; r->exactBvhNeed = fl.exactBvhDepth; r->exactOctNeed = fl.exactOctDepth;
+    r->layoutBuild.numPairNodes = (uint32_t)(fl.nodes.size() / 4); r->layoutBuild.fastStackDepth = fl.maxStackDepth;
+    return finishLayout(r);
+}
+
+/* starts the host builder in the background on the arrays of this edit (see RefineJob) */
+void startRefine(okrt_renderer* r)
+{
+    const char* e = std::getenv("OKRT_LAYOUT_REFINE");
+    if (e && std::atoi(e) == 0) { r->refine.reset(); return; }
+    auto job = std::make_shared<RefineJob>();
+    job->tris = r->hTris; job->nodes = r->hNodes; job->instances = r->hInstances; job->oct = r->hOct;
+    r->refine = job;
+    std::thread([job]() {
+        const auto t0 = std::chrono::steady_clock::now();
+        job->ok = buildFastLayout(job->tris->data(), (uint32_t)job->tris->size(), job->nodes->data(), (uint32_t)job->nodes->size(),
+                                  job->instances->data(), (uint32_t)job->instances->size(), job->oct->data(), (uint32_t)job->oct->size(), job->layout, false);
+        job->ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        job->done.store(true, std::memory_order_release);
+    }).detach();
+}
+
+/* installs the refined layout if it is ready (or waits for it); the job of an older edit was dropped when the edit arrived */
+int adoptRefined(okrt_renderer* r, bool wait)
+{
+    if (!r->refine) return OKRT_OK;
+    if (wait) while (!r->refine->done.load(std::memory_order_acquire)) std::this_thread::sleep_for(std::chrono::microseconds(200));
+    if (!r->refine->done.load(std::memory_order_acquire)) return OKRT_OK;
+    std::shared_ptr<RefineJob> job = r->refine;
+    r->refine.reset();
+    if (!job->ok || job->layout.maxStackDepth > kFastStackCapacity || !job->layout.allRigid) return OKRT_OK;       /* keep the clustered tree */
+    OKRT_CUDA(cudaStreamSynchronize(r->stream));
+    const int rc = installHostLayout(r, job->layout, false);
+    if (rc) return rc;
+    r->layoutBuild.builder = 2u;
+    r->layoutBuild.refineMs = job->ms;
+    return OKRT_OK;
+}
+
+/* the triangle records as float4 texels: stepTriangle fetches them through the texture pipe */
+int finishLayout(okrt_renderer* r)
+{
     if (r->fastTrisTex) { cudaDestroyTextureObject(r->fastTrisTex); r->fastTrisTex = 0; }
-    if (r->fastTris.bytes) {            /* the triangle records as float4 texels: stepTriangle fetches them through the texture pipe */
+    if (r->fastTris.bytes) {
         int maxTexels = 0;
         OKRT_CUDA(cudaDeviceGetAttribute(&maxTexels, cudaDevAttrMaxTexture1DLinearWidth, r->device));
         if (r->fastTris.bytes / sizeof(Float4) > (size_t)maxTexels) {
@@ -223,9 +345,6 @@ int rebuildLayout(okrt_renderer* r)
         td.readMode = cudaReadModeElementType; td.filterMode = cudaFilterModePoint; td.addressMode[0] = cudaAddressModeClamp;
         OKRT_CUDA(cudaCreateTextureObject(&r->fastTrisTex, &res, &td, nullptr));
     }
-    r->topRef = fl.topRef;
-    r->allRigid = fl.allRigid;
-    r->fastStackNeed = fl.maxStackDepth; r->exactBvhNeed = fl.exactBvhDepth; r->exactOctNeed = fl.exactOctDepth;
     r->layoutDirty = false;
     return OKRT_OK;
 }
@@ -631,7 +750,7 @@ int okrt_set_triangles(okrt_renderer* r, const okrt_triangle* pos, const okrt_tr
     if (n && (!pos || !info)) { setError("okrt_set_triangles: null array"); return OKRT_ERR_INVALID_ARGUMENT; }
     if ((rc = r->triPos.upload(pos, n, sizeof(okrt_triangle), r->stream))) return rc;
     if ((rc = r->triInfo.upload(info, n, sizeof(okrt_triangle_info), r->stream))) return rc;
-    r->hTris.assign(pos, pos + n);
+    r->hTris = std::make_shared<std::vector<okrt_triangle>>(pos, pos + n);
     r->layoutDirty = true;
     return OKRT_OK;
 }
@@ -641,7 +760,7 @@ int okrt_set_bvh_nodes(okrt_renderer* r, const okrt_bvh_node* nodes, uint32_t n)
     int rc = checkHandle(r, "okrt_set_bvh_nodes"); if (rc) return rc;
     if (n && !nodes) { setError("okrt_set_bvh_nodes: null array"); return OKRT_ERR_INVALID_ARGUMENT; }
     if ((rc = r->bvhNodes.upload(nodes, n, sizeof(okrt_bvh_node), r->stream))) return rc;
-    r->hNodes.assign(nodes, nodes + n);
+    r->hNodes = std::make_shared<std::vector<okrt_bvh_node>>(nodes, nodes + n);
     r->layoutDirty = true;
     return OKRT_OK;
 }
@@ -665,7 +784,7 @@ int okrt_set_octree(okrt_renderer* r, const okrt_octree_node* nodes, uint32_t n)
     int rc = checkHandle(r, "okrt_set_octree"); if (rc) return rc;
     if (n && !nodes) { setError("okrt_set_octree: null array"); return OKRT_ERR_INVALID_ARGUMENT; }
     if ((rc = r->octNodes.upload(nodes, n, sizeof(okrt_octree_node), r->stream))) return rc;
-    r->hOct.assign(nodes, nodes + n);
+    r->hOct = std::make_shared<std::vector<okrt_octree_node>>(nodes, nodes + n);
     r->layoutDirty = true;
     return OKRT_OK;
 }
@@ -682,7 +801,7 @@ int okrt_set_mesh_instances(okrt_renderer* r, const okrt_mesh_instance* inst, ui
     int rc = checkHandle(r, "okrt_set_mesh_instances"); if (rc) return rc;
     if (n && !inst) { setError("okrt_set_mesh_instances: null array"); return OKRT_ERR_INVALID_ARGUMENT; }
     if ((rc = r->instances.upload(inst, n, sizeof(okrt_mesh_instance), r->stream))) return rc;
-    r->hInstances.assign(inst, inst + n);
+    r->hInstances = std::make_shared<std::vector<okrt_mesh_instance>>(inst, inst + n);
     r->layoutDirty = true;
     return OKRT_OK;
 }
@@ -749,6 +868,7 @@ int okrt_render_frames(okrt_renderer* r, uint32_t frames)
 {
     int rc = checkHandle(r, "okrt_render"); if (rc) return rc;
     if (r->layoutDirty && (rc = rebuildLayout(r))) return rc;
+    if (r->refine && (rc = adoptRefined(r, false))) return rc;
     if (r->opt.writeAov && (rc = ensureAov(r))) return rc;
     r->traceEventsUsed = 0;
     OKRT_CUDA(cudaEventRecord(r->evStart, r->stream));
@@ -1223,6 +1343,20 @@ int okrt_trace_rays_host(const okrt_triangle* tris, uint32_t numTris, const okrt
             }
         });
     for (auto& th : pool) th.join();
+    return OKRT_OK;
+}
+
+int okrt_wait_layout(okrt_renderer* r)
+{
+    int rc = checkHandle(r, "okrt_wait_layout"); if (rc) return rc;
+    if (r->layoutDirty && (rc = rebuildLayout(r))) return rc;
+    return adoptRefined(r, true);
+}
+
+int okrt_get_layout_build(okrt_renderer* r, okrt_layout_build* out)
+{
+    if (!r || !out) { setError("okrt_get_layout_build: null argument"); return OKRT_ERR_INVALID_ARGUMENT; }
+    *out = r->layoutBuild;
     return OKRT_OK;
 }
 

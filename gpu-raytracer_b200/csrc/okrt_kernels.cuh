@@ -598,9 +598,7 @@ constexpr uint32_t kTraceTop = 0xFFFFFFFFu;
  * behind the traversal stack instead of registers, which buys resident warps */
 constexpr uint32_t kColdSlots = 8;
 constexpr uint32_t kColdHitRec = kFastStackCapacity + 0, kColdHitTri = kFastStackCapacity + 1, kColdHitU = kFastStackCapacity + 2,
-                   kColdHitV = kFastStackCapacity + 3, kColdSecond = kFastStackCapacity + 4,
-                   kColdGate = kFastStackCapacity + 5,        /* what the reference compares against before it tests the closest hit: see stepResult */
-                   kColdInstGate = kFastStackCapacity + 6;    /* largest distNear (>= 0) of the oct-tree boxes above the instance being walked */
+                   kColdHitV = kFastStackCapacity + 3, kColdSecond = kFastStackCapacity + 4;
 struct StepLane {
     V3 ro, rd, ridir;        /* current ray: identity-local at the top level, instance-local inside an instance */
     float best;
@@ -627,13 +625,6 @@ OKRT_HD void stepCandidate(StepLane& L, uint32_t* stack, float t, uint32_t rec, 
     if (t < L.best) {
         stack[kColdSecond] = wBits(L.best); L.best = t;
         stack[kColdHitRec] = rec; stack[kColdHitTri] = tri; stack[kColdHitU] = wBits(u); stack[kColdHitV] = wBits(v);
-        /* gate of this hit (stepResult): inside a ray-switched instance, the largest distNear of the oct-tree boxes above it.
-         * Sign bit set: those boxes are entered BEHIND the hit (they do not contain it: moved props, RayTracer.cpp:562) — the
-         * reference may cull the whole node against something farther that this traversal has already culled against the hit,
-         * so only the unbounded reference order can decide. */
-        uint32_t g = 0u;
-        if (L.inst != kTraceTop) { g = stack[kColdInstGate]; if (wFloat(g) > t) g |= 0x80000000u; }
-        stack[kColdGate] = g;
     } else if (t < wFloat(stack[kColdSecond])) stack[kColdSecond] = wBits(t);
 #else
     if (t < L.best) { L.second = L.best; L.best = t; L.hitRec = rec; L.hitTri = tri; L.hitU = u; L.hitV = v; }
@@ -836,9 +827,6 @@ OKRT_HD void stepMisc(const DeviceScene& s, StepLane& L, uint32_t* stack, V3 o, 
             /* the mesh's root box (RaytracerCS.hlsl:285 on the first popped node) */
             if (rayAndAABBDist(lo, lidir, v3(a0.w, a1.w, a2.w), v3(r6.x, r6.y, r6.z)) < relaxedLimit(L.best)) {
                 stackPush(L, stack, kTraceExitInstance);
-#if OKRT_COLD_IN_LOCAL
-                stack[kColdInstGate] = wBits(octNear);
-#endif
                 L.ro = lo; L.rd = ld; L.ridir = lidir;
                 L.inst = recIdx;
                 stepEnter(L, wBits(r7.x));
@@ -867,42 +855,34 @@ OKRT_HD bool stepResult(const DeviceScene& s, const StepLane& L, const uint32_t*
     hit.idx = hit.kind ? (hitRec & 0x3FFFFFFFu) : 0xFFFFFFFFu;
     /* GATE of the closest hit W: the reference tests W unless something it tested earlier is at least as close as the distNear
      * of a box on its way to W (it culls on `>= payload.distance`, RaytracerCS.hlsl:264,285).  The leaf box and the BVH boxes
-     * above it start before W (checked by the differential stress test, tests/test_gpu_stress.py); the oct-tree boxes need not
-     * (they need not even contain W's instance), so their distNear joins the gate. */
-    float gate = L.best;
+     * above it start before W (checked by the differential stress test, tests/test_gpu_stress.py); the oct-tree boxes need not —
+     * createOctTree sorts occupants by their UNtransformed boxes (RayTracer.cpp:562), so a node need not even contain what it
+     * lists.  A chain that is entered before W's window ends cannot be culled by anything beyond the window (and what lies in
+     * the window is known: `second`).  A chain that is MISSED, or entered BEHIND the window (moved props), is different: the reference never reaches W, or culls
+     * its node against something farther that this traversal has already culled against W — only the unbounded reference
+     * order can decide. */
     bool chainMissed = false;
-#if OKRT_COLD_IN_LOCAL
-    if (hit.kind == 2u) {
-        const uint32_t g = stack[kColdGate];
-        gate = fmaxf(gate, wFloat(g & 0x7FFFFFFFu));
-        chainMissed = (g >> 31) != 0u;
-    }
-#endif
     if (hit.kind == 2u) {
         const uint32_t rec = hit.idx;
         OKRT_CHECK(rec < s.numFastInstances);
         const float4* r = s.fastInstances + (size_t)rec * kInstQuads;
         const float4 r6 = wLdg(r + 6), r7 = wLdg(r + 7), lo = wLdg(r + 8), hi = wLdg(r + 9);
         hit.idx = wBits(r7.z);
-        if ((wBits(r6.w) & 1u) != 0u) {
-            /* identity instance: the reference reaches it only through the oct-tree boxes above it (RaytracerCS.hlsl:262).
-             * An origin strictly inside a box hits it with distNear <= 0 — both slabs of every axis have opposite signs, |1/d| >= 1/2
-             * for the unit directions the shader produces — and the boxes above are nested. */
-            const float m = 1.0e-20f;
-            const bool inside = (wBits(r7.w) & 1u) != 0u &&
-                                L.ro.x - lo.x > m && hi.x - L.ro.x > m && L.ro.y - lo.y > m && hi.y - L.ro.y > m && L.ro.z - lo.z > m && hi.z - L.ro.z > m;
-            if (!inside) {
-                const float4 d = *rayD;
-                float octNear;
-                if (!octChainNear(s, L.ro, v3(d.x, d.y, d.z), wBits(r7.y), octNear)) chainMissed = true;
-                else gate = fmaxf(gate, octNear);
-            }
+        /* An origin strictly inside the box of an identity instance's node hits it with distNear <= 0 — both slabs of every
+         * axis have opposite signs, |1/d| >= 1/2 for the unit directions the shader produces — and the boxes above are nested. */
+        const float m = 1.0e-20f;
+        const bool inside = (wBits(r6.w) & 1u) != 0u && (wBits(r7.w) & 1u) != 0u &&
+                            L.ro.x - lo.x > m && hi.x - L.ro.x > m && L.ro.y - lo.y > m && hi.y - L.ro.y > m && L.ro.z - lo.z > m && hi.z - L.ro.z > m;
+        if (!inside) {
+            const float4 d = *rayD;
+            float octNear;
+            if (!octChainNear(s, L.ro, v3(d.x, d.y, d.z), wBits(r7.y), octNear) || octNear >= relaxedLimit(L.best)) chainMissed = true;
         }
     }
-    /* two candidates inside the window above the gate, or a box the reference never gets through: the reference order decides,
-     * searching up to the window (everything the reference could return lies inside it) or without a bound */
-    seed = chainMissed ? OKRT_FLT_MAX : gate;
-    return chainMissed || (hit.kind != 0u && second < relaxedLimit(gate));
+    /* two candidates inside the window above the closest hit, or a box the reference never gets through: the reference order
+     * decides, searching up to the window (everything the reference could return lies inside it) or without a bound */
+    seed = chainMissed ? OKRT_FLT_MAX : L.best;
+    return chainMissed || (hit.kind != 0u && second < relaxedLimit(L.best));
 }
 
 /* whole-ray form of the near-first traversal over the child-pair layout, used by the megakernel and by the CPU check

@@ -84,6 +84,13 @@ class Renderer:
         self.abi.check(self.L.okrt_render_frames(self.h, frames))
         self.abi.check(self.L.okrt_sync(self.h))
 
+    def wait_layout(self):
+        """Adopts the background-refined traversal layout (okrt_wait_layout); returns the okrt_layout_build record."""
+        self.abi.check(self.L.okrt_wait_layout(self.h))
+        b = np.zeros(1, self.abi.LAYOUT_BUILD)
+        self.abi.check(self.L.okrt_get_layout_build(self.h, self.abi.ptr(b)))
+        return b[0]
+
     def result(self):
         out = np.zeros((self.H, self.W, 4), np.uint8)
         self.abi.check(self.L.okrt_read_result(self.h, self.abi.ptr(out)))

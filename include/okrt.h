@@ -410,6 +410,27 @@ OKRT_API int okrt_layout_report(const okrt_triangle* tris, uint32_t numTris, con
                                 const okrt_mesh_instance* instances, uint32_t numInstances,
                                 const okrt_octree_node* octNodes, uint32_t numOctNodes, okrt_layout_info* out);
 
+/* How the traversal layout the kernels walk right now was built.
+ *   builder 1: on the device (okrt_layout_device.cu), milliseconds after a scene edit: every instance identity and the only user
+ *              of its mesh — all BASELINE configs.  Its clustered tree costs rays/s against the host builder's SAH tree, so the
+ *              host builder starts in the background at once (OKRT_LAYOUT_REFINE=0: not) ...
+ *   builder 2: ... and its layout has replaced the clustered one (at an okrt_render* call after it finished, or in
+ *              okrt_wait_layout, which waits for it).  Images are the same with either tree.
+ *   builder 0: on host threads, synchronously (the complete path: instances with transforms, shared meshes,
+ *              OKRT_TRAVERSAL_WIDE, OKRT_LAYOUT_HOST=1); `why` says what sent it there. */
+typedef struct okrt_layout_build {
+    float    wallMs;             /* host wall clock of the synchronous part of the rebuild, uploads included */
+    float    deviceMs;           /* CUDA events around the device builder's kernels (0 for the host builder) */
+    float    refineMs;           /* builder 2: duration of the background host build */
+    uint32_t builder;
+    uint32_t numPairNodes;
+    uint32_t fastStackDepth;
+    uint32_t rounds;             /* clustering rounds of the device builder */
+    char     why[100];
+} okrt_layout_build;
+OKRT_API int okrt_get_layout_build(okrt_renderer* r, okrt_layout_build* out);
+OKRT_API int okrt_wait_layout(okrt_renderer* r);      /* builds the layout if an edit is pending and waits for its refinement */
+
 /* Host-only check of the near-first traversal (no GPU): runs the traversal kernels' lane functions, compiled for the host,
  * over arbitrary rays (6 floats per ray: origin, direction) on the layout okrt_render would build from the same arrays.
  * out: 12 words per ray — distance, u, v (float bits), triangle, kind (0 miss / 2 mesh), instance index, 1 if the reference

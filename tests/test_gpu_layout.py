@@ -1,0 +1,147 @@
+"""Row f2: the traversal layout built on the device (csrc/okrt_layout_device.cu) against the host builder
+(csrc/okrt_accel.cpp) and the oracle.  The trees differ; every image must not (the visiting order is free).
+Also the time budget of a scene edit: okrt_set_octree + first render (Application.cpp:312-317,405-411 rebuild on every
+interaction)."""
+import os
+import time
+
+import numpy as np
+import pytest
+
+from tests import helpers
+
+pytestmark = pytest.mark.gpu
+
+
+def _layout_build(okrt, r):
+    b = np.zeros(1, okrt.abi.LAYOUT_BUILD)
+    okrt.abi.check(r.L.okrt_get_layout_build(r.h, okrt.abi.ptr(b)))
+    return b[0]
+
+
+def _render(okrt, host, W, H, env, bounces, host_builder, frames=1, aov=False):
+    os.environ["OKRT_LAYOUT_HOST"] = "1" if host_builder else "0"
+    os.environ["OKRT_LAYOUT_REFINE"] = "0"                 # keep the device builder's own tree for the whole render
+    try:
+        r = helpers.Renderer(okrt, host, W, H, envFaces=env)
+        r.options(maxBounces=bounces, traversal=okrt.abi.TRAVERSAL_FAST, writeAov=1 if aov else 0)
+        r.render(host["rd"].copy(), frames=frames)
+        out = dict(acc=r.accumulation(), build=_layout_build(okrt, r), segments=int(r.stats()["raySegments"]),
+                   fallback=int(r.stats()["fallbackSegments"]), aov=r.aov() if aov else None)
+        r.close()
+        return out
+    finally:
+        os.environ.pop("OKRT_LAYOUT_HOST", None)
+        os.environ.pop("OKRT_LAYOUT_REFINE", None)
+
+
+def test_background_refinement_swaps_trees_without_changing_images(okrt):
+    """After a device build the host SAH builder runs in the background; okrt_wait_layout adopts its tree.  Frames rendered
+    before and after the swap accumulate into the same image as frames rendered with one tree throughout."""
+    rm, sc, info = okrt.scenes.sponza_standin(60000, texture_size=64)
+    W, H = 320, 180
+    host = helpers.build_host_side(okrt, rm, sc, info, W, H)
+    env = okrt.scenes.procedural_sky_faces(32)
+    r = helpers.Renderer(okrt, host, W, H, envFaces=env)
+    r.options(maxBounces=6)
+    r.render(host["rd"].copy(), frames=2)
+    first = _layout_build(okrt, r)
+    assert int(first["builder"]) in (1, 2)
+    okrt.abi.check(r.L.okrt_wait_layout(r.h))
+    after = _layout_build(okrt, r)
+    assert int(after["builder"]) == 2 and float(after["refineMs"]) > 0.0
+    rd = host["rd"].copy()
+    rd[0]["numAccumulationFrames"] = r.L.okrt_get_num_accumulation_frames(r.h)
+    r.render(rd, frames=2)
+    mixed = r.accumulation()
+    r.close()
+    ref = _render(okrt, host, W, H, env, 6, host_builder=True, frames=4)
+    assert np.array_equal(mixed.view(np.uint32), ref["acc"].view(np.uint32))
+
+
+def test_device_built_layout_equals_host_built_and_oracle(okrt, oracle):
+    rm, sc, info = okrt.scenes.sponza_standin(60000, texture_size=64)
+    W, H = 320, 180
+    host = helpers.build_host_side(okrt, rm, sc, info, W, H)
+    env = okrt.scenes.procedural_sky_faces(32)
+    rd = host["rd"].copy(); rd[0]["numAccumulationFrames"] = 1
+    o = oracle.render(helpers.oracle_scene(oracle, host, envFaces=env), rd, 8, aov_dtype=okrt.abi.AOV)
+    dev = _render(okrt, host, W, H, env, 8, host_builder=False, aov=True)
+    hst = _render(okrt, host, W, H, env, 8, host_builder=True)
+    assert int(dev["build"]["builder"]) == 1, dev["build"]["why"]
+    assert int(hst["build"]["builder"]) == 0
+    assert np.array_equal(dev["aov"]["triIdx"], o["aov"]["triIdx"])
+    assert np.array_equal(dev["acc"].view(np.uint32), o["accum"].view(np.uint32)), "device-built layout differs from the oracle"
+    assert np.array_equal(hst["acc"].view(np.uint32), o["accum"].view(np.uint32))
+    assert dev["segments"] == hst["segments"] == o["segments"]
+    assert dev["fallback"] < 0.02 * dev["segments"]
+
+
+@pytest.mark.parametrize("kind", ["flat_room", "contact"])
+def test_device_built_layout_adversarial(okrt, kind):
+    """the adversarial scenes of test_gpu_stress.py through the device-built tree: equal to the reference order"""
+    rm, sc, info = okrt.scenes.adversarial_scene(kind)
+    W = H = 512
+    host = helpers.build_host_side(okrt, rm, sc, info, W, H)
+    env = okrt.scenes.procedural_sky_faces(32)
+    os.environ["OKRT_LAYOUT_REFINE"] = "0"
+    try:
+        r = helpers.Renderer(okrt, host, W, H, envFaces=env)
+        r.options(maxBounces=5, traversal=okrt.abi.TRAVERSAL_FAST, coverAllPixels=1)
+        r.render(host["rd"].copy(), frames=3)
+        assert int(_layout_build(okrt, r)["builder"]) == 1
+        fast = r.accumulation()
+        r.close()
+    finally:
+        os.environ.pop("OKRT_LAYOUT_REFINE", None)
+    r = helpers.Renderer(okrt, host, W, H, envFaces=env)
+    r.options(maxBounces=5, traversal=okrt.abi.TRAVERSAL_EXACT, coverAllPixels=1)
+    r.render(host["rd"].copy(), frames=3)
+    exact = r.accumulation()
+    r.close()
+    assert np.array_equal(fast.view(np.uint32), exact.view(np.uint32))
+
+
+def test_scenes_with_transforms_fall_back_to_the_host_builder(okrt):
+    rm, sc, info = okrt.scenes.moved_props_scene()
+    host = helpers.build_host_side(okrt, rm, sc, info, 128, 72)
+    r = helpers.Renderer(okrt, host, 128, 72)
+    r.options(maxBounces=2)
+    r.render(host["rd"].copy())
+    b = _layout_build(okrt, r)
+    assert int(b["builder"]) == 0 and b"transform" in bytes(b["why"])
+    r.close()
+
+
+def test_scene_edit_budget_full_size(okrt):
+    """BASELINE C4 scene (262k triangles, 354 instances): a scene edit (okrt_set_octree again) followed by one frame.
+    Device builder: the layout rebuild must stay within 10 ms of device time; the dragon (871k triangles) within 40 ms."""
+    import bench
+    host, env, info = bench.build_scene(okrt)
+    r = helpers.Renderer(okrt, host, bench.WIDTH, bench.HEIGHT, envFaces=env)
+    r.options(maxBounces=8)
+    r.render(host["rd"].copy())
+    t = host["octree"]
+    walls = []
+    for _ in range(3):
+        okrt.abi.check(r.L.okrt_set_octree(r.h, okrt.abi.ptr(t.nodes), len(t.nodes)))          # marks the layout dirty
+        t0 = time.perf_counter()
+        r.render(host["rd"].copy())
+        walls.append((time.perf_counter() - t0) * 1e3)
+    b = _layout_build(okrt, r)
+    print("C4 scene edit: layout rebuild %.2f ms device / %.2f ms wall, edit + frame %.1f ms wall, %d pair nodes, stack %d, %d rounds" % (
+        float(b["deviceMs"]), float(b["wallMs"]), min(walls), int(b["numPairNodes"]), int(b["fastStackDepth"]), int(b["rounds"])))
+    assert int(b["builder"]) in (1, 2), b["why"]
+    assert float(b["deviceMs"]) <= 10.0
+    r.close()
+    rm, sc, info = okrt.scenes.dragon_scene()
+    host = helpers.build_host_side(okrt, rm, sc, info, 1920, 1080)
+    r = helpers.Renderer(okrt, host, 1920, 1080, envFaces=okrt.scenes.procedural_sky_faces(64))
+    r.options(maxBounces=4)
+    r.render(host["rd"].copy())
+    b = _layout_build(okrt, r)
+    print("dragon: layout build %.2f ms device / %.2f ms wall, %d pair nodes, stack %d, %d rounds" % (
+        float(b["deviceMs"]), float(b["wallMs"]), int(b["numPairNodes"]), int(b["fastStackDepth"]), int(b["rounds"])))
+    assert int(b["builder"]) in (1, 2), b["why"]
+    assert float(b["deviceMs"]) <= 40.0
+    r.close()
