@@ -176,6 +176,8 @@ SYMBOLS = [
     ("okrt_measure_unit_peaks", _I, [_I, _P]),
     ("okrt_get_layout_build", _I, [_P, _P]),
     ("okrt_wait_layout", _I, [_P]),
+    ("okrt_set_shard_bands", _I, [_P, _P, _U]),
+    ("okrt_shard_balance", _I, [_P, _U, _U, _P]),
     ("okrt_trace_rays_host", _I, [_P, _U, _P, _U, _P, _U, _P, _U, _U, _P, _U, _P]),
 ]
 

@@ -170,6 +170,8 @@ struct okrt_renderer {
     int numSms = 0, blocksPerSmLean = 1, blocksPerSmInstrumented = 1;   /* persistent grid = SMs x resident blocks */
     int blocksPerSmTrace = 1, blocksPerSmWide = 1;
     bool layoutHasWide = false;                 /* the wide layout is built only for OKRT_TRAVERSAL_WIDE */
+    std::vector<uint32_t> ownedBands;           /* okrt_set_shard_bands: this rank's bands (ascending); empty: interleaved by arithmetic */
+    DeviceBuffer dOwnedBands;
     okrt_layout_build layoutBuild{};            /* how the last rebuild went (okrt_get_layout_build) */
     WavefrontBuffers wb{};                      /* path state of the wavefront pipeline (sized for width x height) */
     size_t wbPaths = 0, wbReserve = 0;
@@ -504,11 +506,27 @@ int launchWavefront(okrt_renderer* r, const FrameParams& fpWhole, bool instrumen
                 else traceFastKernel<<<traceGridH[h], kTraceBlockThreads, 0, st[h]>>>(scene, fp, wb, qin, b);
                 OKRT_CUDA(cudaEventRecord(e1, st[h]));
                 lastTraceEnd = e1;
-                traceFallbackKernel<<<fallbackGridH[h], 128, 0, st[h]>>>(scene, fp, wb, b);
+                /* The reference-order kernel decides a few hundred rays per launch and lasts one bounded traversal (~100 us of
+                 * dependent loads): on a second stream it runs BESIDE the main shade launch, which skips its paths (kHitPending);
+                 * a late shade launch over the fallback queue follows.  (Two-stream halves keep everything on the half's stream.) */
+                const bool beside = !dual && r->stream2 != nullptr;
+                if (beside) {
+                    OKRT_CUDA(cudaEventRecord(r->evFork, st[h]));
+                    OKRT_CUDA(cudaStreamWaitEvent(r->stream2, r->evFork, 0));
+                    traceFallbackKernel<<<fallbackGridH[h], 128, 0, r->stream2>>>(scene, fp, wb, b);
+                    OKRT_CUDA(cudaEventRecord(r->evJoin, r->stream2));
+                } else traceFallbackKernel<<<fallbackGridH[h], 128, 0, st[h]>>>(scene, fp, wb, b);
                 r->launches++;
+                if (instrumented) shadeKernel<true><<<shadeGridH[h], 128, 0, st[h]>>>(scene, fp, wb, qin, qout, b, 0u);
+                else shadeKernel<false><<<shadeGridH[h], 128, 0, st[h]>>>(scene, fp, wb, qin, qout, b, 0u);
+                if (beside) OKRT_CUDA(cudaStreamWaitEvent(st[h], r->evJoin, 0));
+                if (instrumented) shadeKernel<true><<<fallbackGridH[h], 128, 0, st[h]>>>(scene, fp, wb, qin, qout, b, 1u);
+                else shadeKernel<false><<<fallbackGridH[h], 128, 0, st[h]>>>(scene, fp, wb, qin, qout, b, 1u);
+                r->launches += 3;                              /* traversal, main shade, late shade (+ the fallback above) */
+                continue;
             }
-            if (instrumented) shadeKernel<true><<<shadeGridH[h], 128, 0, st[h]>>>(scene, fp, wb, qin, qout, b);
-            else shadeKernel<false><<<shadeGridH[h], 128, 0, st[h]>>>(scene, fp, wb, qin, qout, b);
+            if (instrumented) shadeKernel<true><<<shadeGridH[h], 128, 0, st[h]>>>(scene, fp, wb, qin, qout, b, 0u);
+            else shadeKernel<false><<<shadeGridH[h], 128, 0, st[h]>>>(scene, fp, wb, qin, qout, b, 0u);
             r->launches += 2;
         }
     }
@@ -559,7 +577,7 @@ int launchFrames(okrt_renderer* r, uint32_t want, uint32_t& done)
     if (r->opt.shardMode == OKRT_SHARD_TILE && r->opt.shardCount > 1u) {
         const uint32_t band = r->opt.shardBandRows ? r->opt.shardBandRows : 8u;
         const uint32_t bands = (r->height + band - 1u) / band;
-        ownedRows = (bands / r->opt.shardCount + ((bands % r->opt.shardCount) > r->opt.shardRank ? 1u : 0u)) * band;
+        ownedRows = (r->ownedBands.empty() ? bands / r->opt.shardCount + ((bands % r->opt.shardCount) > r->opt.shardRank ? 1u : 0u) : (uint32_t)r->ownedBands.size()) * band;
     }
     const size_t slotsPerFrame = (size_t)((r->width + kTileW - 1) / kTileW) * ((ownedRows + kTileH - 1) / kTileH) * kTilePixels;
     r->wbReserve = slotsPerFrame;
@@ -601,8 +619,12 @@ int launchFrames(okrt_renderer* r, uint32_t want, uint32_t& done)
         fp.shardCount = r->opt.shardCount; fp.shardRank = r->opt.shardRank;
         fp.bandRows = r->opt.shardBandRows ? r->opt.shardBandRows : 8u;
         const uint32_t bands = (r->height + fp.bandRows - 1u) / fp.bandRows;
-        const uint32_t mine = bands / fp.shardCount + ((bands % fp.shardCount) > fp.shardRank ? 1u : 0u);
+        const uint32_t mine = r->ownedBands.empty() ? bands / fp.shardCount + ((bands % fp.shardCount) > fp.shardRank ? 1u : 0u) : (uint32_t)r->ownedBands.size();
         rows = mine * fp.bandRows;
+        if (!r->ownedBands.empty()) {
+            if (r->ownedBands.back() >= bands) { setError("okrt_set_shard_bands: a band lies outside the image"); return OKRT_ERR_INVALID_ARGUMENT; }
+            fp.ownedBands = (const uint32_t*)r->dOwnedBands.ptr;
+        }
     }
     /* the reference clears the whole target to (0.2,0.4,0.6,1) every frame (RayTracer.cpp:227-228) and then
      * overwrites every covered pixel; uncovered pixels [Q9] are cleared once, when the images are created
@@ -630,6 +652,54 @@ int checkHandle(const okrt_renderer* r, const char* fn)
     if (e != cudaSuccess) { setError(std::string(fn) + ": cudaSetDevice: " + cudaGetErrorString(e)); return OKRT_ERR_CUDA; }
     return OKRT_OK;
 }
+
+/* rows of the result this handle owns, as contiguous byte runs of the image (a strided family + extra runs) */
+struct OwnedRuns {
+    size_t first = 0, pitch = 0, runBytes = 0; uint32_t regular = 0;      /* `regular` runs of runBytes at first + k * pitch */
+    std::vector<std::pair<size_t, size_t>> extra;                         /* (offset, bytes) */
+};
+OwnedRuns ownedRuns(const okrt_renderer* r)
+{
+    OwnedRuns o;
+    const size_t rowBytes = (size_t)r->width * 4;
+    if (r->opt.shardMode != OKRT_SHARD_TILE || r->opt.shardCount <= 1) { o.pitch = o.runBytes = rowBytes * r->height; o.regular = 1; return o; }
+    const uint32_t band = r->opt.shardBandRows ? r->opt.shardBandRows : 8u, count = r->opt.shardCount, rank = r->opt.shardRank;
+    const uint32_t bands = (r->height + band - 1u) / band;
+    if (!r->ownedBands.empty()) {                                         /* explicit table: neighbouring bands merge into one run */
+        for (size_t i = 0; i < r->ownedBands.size();) {
+            size_t j = i + 1;
+            while (j < r->ownedBands.size() && r->ownedBands[j] == r->ownedBands[j - 1] + 1u) j++;
+            const size_t rowStart = (size_t)r->ownedBands[i] * band, rowEnd = std::min<size_t>((size_t)(r->ownedBands[j - 1] + 1u) * band, r->height);
+            if (rowEnd > rowStart) o.extra.emplace_back(rowStart * rowBytes, (rowEnd - rowStart) * rowBytes);
+            i = j;
+        }
+        return o;
+    }
+    const uint32_t mine = bands / count + ((bands % count) > rank ? 1u : 0u);
+    o.runBytes = (size_t)band * rowBytes; o.first = (size_t)rank * band * rowBytes; o.pitch = (size_t)count * band * rowBytes;
+    if (!mine) return o;
+    const uint32_t lastBand = rank + (mine - 1u) * count;
+    const uint32_t lastRows = std::min(band, r->height - lastBand * band);
+    o.regular = lastRows == band ? mine : mine - 1u;
+    if (o.regular != mine) o.extra.emplace_back((size_t)lastBand * band * rowBytes, (size_t)lastRows * rowBytes);
+    return o;
+}
+/* copies the owned runs from `src` to `dst` (same layout: full-size images) */
+cudaError_t copyOwned(const OwnedRuns& o, uint8_t* dst, const uint8_t* src, cudaMemcpyKind kind, cudaStream_t stream, uint64_t* moved)
+{
+    cudaError_t e = cudaSuccess;
+    if (o.regular) {
+        e = cudaMemcpy2DAsync(dst + o.first, o.pitch, src + o.first, o.pitch, o.runBytes, o.regular, kind, stream);
+        if (moved) *moved += (uint64_t)o.regular * o.runBytes;
+    }
+    for (const auto& run : o.extra) {
+        if (e != cudaSuccess) break;
+        e = cudaMemcpyAsync(dst + run.first, src + run.first, run.second, kind, stream);
+        if (moved) *moved += run.second;
+    }
+    return e;
+}
+
 
 } // namespace
 
@@ -708,6 +778,7 @@ void okrt_destroy(okrt_renderer* r)
     r->instances.release(); r->dirLights.release(); r->pointLights.release(); r->spotLights.release();
     if (r->fastTrisTex) { cudaDestroyTextureObject(r->fastTrisTex); r->fastTrisTex = 0; }
     r->fastNodes.release(); r->fastTris.release(); r->fastInstances.release(); r->octParent.release(); r->wideNodes.release(); r->wideLeaves.release();
+    r->dOwnedBands.release();
     r->textures.release(); r->environment.release();
     if (r->accumulation) cudaFree(r->accumulation);
     if (r->result) cudaFree(r->result);
@@ -926,47 +997,24 @@ int okrt_read_result_owned(okrt_renderer* r, uint8_t* outRgba8, uint64_t* outByt
         if (outBytes) *outBytes = (uint64_t)r->width * r->height * 4;
         return okrt_read_result(r, outRgba8);
     }
-    const size_t rowBytes = (size_t)r->width * 4;
-    const uint32_t band = r->opt.shardBandRows ? r->opt.shardBandRows : 8u, count = r->opt.shardCount, rank = r->opt.shardRank;
-    const uint32_t bands = (r->height + band - 1u) / band;
-    const uint32_t mine = bands / count + ((bands % count) > rank ? 1u : 0u);
     uint64_t moved = 0;
-    if (mine) {
-        const uint32_t lastBand = rank + (mine - 1u) * count;
-        const uint32_t lastRows = std::min(band, r->height - lastBand * band);          /* the image's last band may be short */
-        const uint32_t fullBands = lastRows == band ? mine : mine - 1u;
-        const size_t first = (size_t)rank * band * rowBytes, pitch = (size_t)count * band * rowBytes;
-        if (fullBands) {
-            OKRT_CUDA(cudaMemcpy2DAsync(outRgba8 + first, pitch, (const uint8_t*)r->result + first, pitch, (size_t)band * rowBytes, fullBands,
-                                        cudaMemcpyDeviceToHost, r->stream));
-            moved += (uint64_t)fullBands * band * rowBytes;
-        }
-        if (fullBands != mine) {
-            const size_t at = (size_t)lastBand * band * rowBytes;
-            OKRT_CUDA(cudaMemcpyAsync(outRgba8 + at, (const uint8_t*)r->result + at, (size_t)lastRows * rowBytes, cudaMemcpyDeviceToHost, r->stream));
-            moved += (uint64_t)lastRows * rowBytes;
-        }
-    }
+    OKRT_CUDA(copyOwned(ownedRuns(r), outRgba8, (const uint8_t*)r->result, cudaMemcpyDeviceToHost, r->stream, &moved));
     OKRT_CUDA(cudaStreamSynchronize(r->stream));
     if (outBytes) *outBytes = moved;
     return OKRT_OK;
 }
 
-/* rows of the result this handle owns, as (offset, pitch, bytes per run, runs) + a short last band */
-static void ownedRuns(const okrt_renderer* r, size_t& first, size_t& pitch, size_t& runBytes, uint32_t& fullBands, size_t& tailAt, size_t& tailBytes)
+/* Tile sharding with an explicit band table: `bands` = the global band indices (ascending, no duplicates) this handle traces,
+ * instead of every shardCount-th band.  Lets the host balance ranks by measured band cost (okrt_shard_balance); n = 0 restores
+ * the interleave.  Takes effect with the next okrt_render* call; shardBandRows must be set first. */
+int okrt_set_shard_bands(okrt_renderer* r, const uint32_t* bands, uint32_t n)
 {
-    const size_t rowBytes = (size_t)r->width * 4;
-    first = 0; pitch = rowBytes * r->height; runBytes = rowBytes * r->height; fullBands = 1; tailAt = 0; tailBytes = 0;
-    if (r->opt.shardMode != OKRT_SHARD_TILE || r->opt.shardCount <= 1) return;
-    const uint32_t band = r->opt.shardBandRows ? r->opt.shardBandRows : 8u, count = r->opt.shardCount, rank = r->opt.shardRank;
-    const uint32_t bands = (r->height + band - 1u) / band;
-    const uint32_t mine = bands / count + ((bands % count) > rank ? 1u : 0u);
-    fullBands = 0; runBytes = (size_t)band * rowBytes; first = (size_t)rank * band * rowBytes; pitch = (size_t)count * band * rowBytes;
-    if (!mine) return;
-    const uint32_t lastBand = rank + (mine - 1u) * count;
-    const uint32_t lastRows = std::min(band, r->height - lastBand * band);
-    fullBands = lastRows == band ? mine : mine - 1u;
-    if (fullBands != mine) { tailAt = (size_t)lastBand * band * rowBytes; tailBytes = (size_t)lastRows * rowBytes; }
+    int rc = checkHandle(r, "okrt_set_shard_bands"); if (rc) return rc;
+    if (n && !bands) { setError("okrt_set_shard_bands: null array"); return OKRT_ERR_INVALID_ARGUMENT; }
+    for (uint32_t i = 1; i < n; i++) if (bands[i] <= bands[i - 1]) { setError("okrt_set_shard_bands: bands must ascend"); return OKRT_ERR_INVALID_ARGUMENT; }
+    OKRT_CUDA(cudaStreamSynchronize(r->stream));
+    r->ownedBands.assign(bands, bands + n);
+    return r->dOwnedBands.upload(bands, n, sizeof(uint32_t), r->stream);
 }
 
 int okrt_read_result_async(okrt_renderer* r, uint8_t* outRgba8, uint64_t* outBytes, uint32_t slot)
@@ -984,17 +1032,14 @@ int okrt_read_result_async(okrt_renderer* r, uint8_t* outRgba8, uint64_t* outByt
     if (!r->snapshot[slot]) OKRT_CUDA(cudaMalloc(&r->snapshot[slot], imageBytes));
     /* the snapshot of this slot may still be on its way to the host from two calls ago */
     if (r->copyPending[slot]) OKRT_CUDA(cudaStreamWaitEvent(r->stream, r->evCopied[slot], 0));
-    size_t first, pitch, runBytes, tailAt, tailBytes; uint32_t fullBands;
-    ownedRuns(r, first, pitch, runBytes, fullBands, tailAt, tailBytes);
+    const OwnedRuns runs = ownedRuns(r);
     uint64_t moved = 0;
     const uint8_t* src = (const uint8_t*)r->result;
     uint8_t* snap = (uint8_t*)r->snapshot[slot];
-    if (fullBands) OKRT_CUDA(cudaMemcpy2DAsync(snap + first, pitch, src + first, pitch, runBytes, fullBands, cudaMemcpyDeviceToDevice, r->stream));
-    if (tailBytes) OKRT_CUDA(cudaMemcpyAsync(snap + tailAt, src + tailAt, tailBytes, cudaMemcpyDeviceToDevice, r->stream));
+    OKRT_CUDA(copyOwned(runs, snap, src, cudaMemcpyDeviceToDevice, r->stream, nullptr));
     OKRT_CUDA(cudaEventRecord(r->evSnapshot[slot], r->stream));
     OKRT_CUDA(cudaStreamWaitEvent(r->streamCopy, r->evSnapshot[slot], 0));
-    if (fullBands) { OKRT_CUDA(cudaMemcpy2DAsync(outRgba8 + first, pitch, snap + first, pitch, runBytes, fullBands, cudaMemcpyDeviceToHost, r->streamCopy)); moved += (uint64_t)fullBands * runBytes; }
-    if (tailBytes) { OKRT_CUDA(cudaMemcpyAsync(outRgba8 + tailAt, snap + tailAt, tailBytes, cudaMemcpyDeviceToHost, r->streamCopy)); moved += tailBytes; }
+    OKRT_CUDA(copyOwned(runs, outRgba8, snap, cudaMemcpyDeviceToHost, r->streamCopy, &moved));
     OKRT_CUDA(cudaEventRecord(r->evCopied[slot], r->streamCopy));
     r->copyPending[slot] = true;
     if (outBytes) *outBytes = moved;

@@ -732,6 +732,23 @@ int okrt_calculate_projection_data(const okrt_camera* cam, uint32_t width, uint3
 }
 
 /* ------------------------------------------------------------ sharding */
+/* longest-processing-time-first: bands by decreasing cost (ties: lower band first), each to the least-loaded rank (ties: lower rank) */
+int okrt_shard_balance(const double* bandCost, uint32_t numBands, uint32_t shardCount, uint32_t* ownerOfBand)
+{
+    if (!bandCost || !ownerOfBand || shardCount == 0u) { okrt::setError("okrt_shard_balance: bad argument"); return OKRT_ERR_INVALID_ARGUMENT; }
+    std::vector<uint32_t> order(numBands);
+    for (uint32_t b = 0; b < numBands; b++) order[b] = b;
+    std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t c) { return bandCost[a] > bandCost[c]; });
+    std::vector<double> load(shardCount, 0.0);
+    for (uint32_t b : order) {
+        uint32_t best = 0;
+        for (uint32_t r = 1; r < shardCount; r++) if (load[r] < load[best]) best = r;
+        ownerOfBand[b] = best;
+        load[best] += bandCost[b] > 0.0 ? bandCost[b] : 0.0;
+    }
+    return OKRT_OK;
+}
+
 uint32_t okrt_shard_owner_of_row(uint32_t y, uint32_t bandRows, uint32_t shardCount)
 {
     if (bandRows == 0u) bandRows = 8u;

@@ -119,6 +119,7 @@ struct FrameParams {
     uint32_t traversal;
     uint32_t coveredW, coveredH;              /* [Q9] */
     uint32_t bandRows, shardRank, shardCount; /* tile sharding: row band b belongs to rank b % shardCount */
+    const uint32_t* ownedBands;               /* tile sharding with an explicit table (okrt_set_shard_bands): global band of this rank's k-th band */
     uint32_t tilesX, numTiles;                /* 16x8 tiles this launch owns */
     uint32_t* workCounter;                    /* next tile to hand out (zeroed before the launch) */
     float4* accumulation;                     /* u1 */
@@ -229,6 +230,16 @@ OKRT_HD void wTriangle(const DeviceScene& s, uint32_t j, float4& a, float4& b, f
     const float4* tp = s.fastTris + (size_t)j * kTriQuads;
     a = tp[0]; b = tp[1]; c = tp[2];
 #endif
+}
+
+/* tile sharding: image tile row of this rank's local tile row (its k-th band is global band k*shardCount + shardRank, or the
+ * k-th entry of the explicit band table) */
+__device__ __forceinline__ uint32_t ownedTileRow(const FrameParams& fp, uint32_t tileRowLocal)
+{
+    const uint32_t tilesPerBand = fp.bandRows / 8u;
+    const uint32_t k = tileRowLocal / tilesPerBand;
+    const uint32_t band = fp.ownedBands ? fp.ownedBands[k] : k * fp.shardCount + fp.shardRank;
+    return band * tilesPerBand + tileRowLocal % tilesPerBand;
 }
 
 /* ------------------------------------------------------------------- RNG */
@@ -1152,9 +1163,7 @@ pathTraceKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ F
                 const uint32_t slot = slotNext + rank;
                 const uint32_t tile = slot / kTilePixels, j = slot % kTilePixels;
                 const uint32_t tileX = tile % fp.tilesX, tileRowLocal = tile / fp.tilesX;
-                /* tile sharding: this rank's k-th band is global band k*shardCount + shardRank */
-                const uint32_t tilesPerBand = fp.bandRows / kTileH;
-                const uint32_t tileRow = ((tileRowLocal / tilesPerBand) * fp.shardCount + fp.shardRank) * tilesPerBand + tileRowLocal % tilesPerBand;
+                const uint32_t tileRow = ownedTileRow(fp, tileRowLocal);
                 const uint32_t px = tileX * kTileW + j % kTileW, py = tileRow * kTileH + j / kTileW;
                 if (px < fp.coveredW && py < fp.coveredH) {
                     /* [Q3] seed, createRay :177-206 [Q2], applyDOF :208-216 */

@@ -38,6 +38,9 @@ struct WavefrontBuffers {
     uint32_t* fallbackCounts;  /* [bounce]; zeroed per frame (lives behind counts) */
 };
 constexpr uint32_t kMaxWavefrontBounces = 63;
+/* hitB of a path whose hit the reference-order kernel is still deciding: the main shade launch skips it, the late one (after
+ * traceFallbackKernel, which may run beside the main shade launch on a second stream) shades it */
+constexpr uint32_t kHitPending = 0xFFFFFFFFu;
 constexpr uint32_t kMaxQueueCounts = 2 * (kMaxWavefrontBounces + 2);
 #ifndef OKRT_TRACE_BLOCK_THREADS
 #define OKRT_TRACE_BLOCK_THREADS 128
@@ -68,8 +71,7 @@ generateKernel(const __grid_constant__ FrameParams fp, const WavefrontBuffers wb
     if (frame >= fp.batchFrames) return;
     const uint32_t tile = slot / kTilePixels, j = slot % kTilePixels;
     const uint32_t tileX = tile % fp.tilesX, tileRowLocal = tile / fp.tilesX;
-    const uint32_t tilesPerBand = fp.bandRows / kTileH;
-    const uint32_t tileRow = ((tileRowLocal / tilesPerBand) * fp.shardCount + fp.shardRank) * tilesPerBand + tileRowLocal % tilesPerBand;
+    const uint32_t tileRow = ownedTileRow(fp, tileRowLocal);
     const uint32_t px = tileX * kTileW + j % kTileW, py = tileRow * kTileH + j / kTileW;
     const bool covered = px < fp.coveredW && py < fp.coveredH;
 
@@ -163,8 +165,10 @@ traceFallbackKernel(const __grid_constant__ DeviceScene s, const __grid_constant
         traverseExactWarp(s, numSpheres, v3(ro.x, ro.y, ro.z), v3(rdv.x, rdv.y, rdv.z), hit, limit);
         __syncwarp();
         if ((threadIdx.x & 31u) == 0u) {
+            /* hitB keeps its pending marker — the main shade launch may be reading it at this moment; kind | index travel in the
+             * spare word of the path's throughput */
             wb.hitA[path] = make_float4(hit.distance, hit.u, hit.v, __uint_as_float(hit.tri));
-            wb.hitB[path] = (hit.kind << 30) | (hit.idx & 0x3FFFFFFFu);
+            wb.throughput[path].w = __uint_as_float((hit.kind << 30) | (hit.idx & 0x3FFFFFFFu));
             if (fp.aov && bounce == 0u) fp.aov[__float_as_uint(rdv.w)].flags = 1u;
         }
     }
@@ -241,6 +245,7 @@ traceFastKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ F
                 if (stepResult(s, L, stack, wb.rayD + L.path, hit, seed)) {
                     wb.fallbackQueue[atomicAdd(wb.fallbackCounts + bounce, 1u)] = L.path;
                     wb.hitA[L.path].x = relaxedLimit(seed);              /* bounds the reference-order traversal's search */
+                    wb.hitB[L.path] = kHitPending;
                 } else {
                     wb.hitA[L.path] = make_float4(hit.distance, hit.u, hit.v, __uint_as_float(hit.tri));
                     wb.hitB[L.path] = (hit.kind << 30) | (hit.idx & 0x3FFFFFFFu);
@@ -383,6 +388,7 @@ traceWideKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ F
                 if (wideResult(s, L, stack, wb.rayD + L.path, hit, limit)) {
                     wb.fallbackQueue[atomicAdd(wb.fallbackCounts + bounce, 1u)] = L.path;
                     wb.hitA[L.path].x = limit;                           /* bounds the reference-order traversal's search */
+                    wb.hitB[L.path] = kHitPending;
                 } else {
                     wb.hitA[L.path] = make_float4(hit.distance, hit.u, hit.v, __uint_as_float(hit.tri));
                     wb.hitB[L.path] = (hit.kind << 30) | (hit.idx & 0x3FFFFFFFu);
@@ -473,13 +479,15 @@ traceWideKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ F
 template <bool kInstrumented>
 __global__ void __launch_bounds__(128, OKRT_SHADE_MIN_BLOCKS)
 shadeKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ FrameParams fp, const WavefrontBuffers wb,
-            const uint32_t* __restrict__ queueIn, uint32_t* __restrict__ queueOut, uint32_t bounce)
+            const uint32_t* __restrict__ queueIn, uint32_t* __restrict__ queueOut, uint32_t bounce, uint32_t late)
 {
+    /* late == 0: every path of the bounce's queue except those still with the reference-order kernel (kHitPending);
+     * late == 1: exactly those, from the fallback queue, once that kernel is done */
     const okrt_render_data& rd = fp.rd;
-    const uint32_t count = wb.counts[2u * bounce];
+    const uint32_t count = late ? wb.fallbackCounts[bounce] : wb.counts[2u * bounce];
     __shared__ uint32_t warpSurvivors[4];
     __shared__ uint32_t blockBase;
-    if (blockIdx.x == 0u && threadIdx.x == 0u) {
+    if (blockIdx.x == 0u && threadIdx.x == 0u && !late) {
         atomicAdd(fp.counters + 0, (unsigned long long)count);
         if (bounce == 0u) atomicAdd(fp.counters + 2, (unsigned long long)count);
     }
@@ -490,11 +498,15 @@ shadeKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ Frame
     const bool active = k < count;
     bool survives = false;
     uint32_t path = 0u;
+    uint32_t hbEarly = 0u;
     if (active) {
-        path = queueIn ? __ldg(queueIn + k) : k;
+        path = late ? wb.fallbackQueue[k] : (queueIn ? __ldg(queueIn + k) : k);
+        hbEarly = wb.hitB[path];
+    }
+    if (active && (late || hbEarly != kHitPending)) {
         const float4 ro = wb.rayO[path], rdv = wb.rayD[path], li = wb.radiance[path], th = wb.throughput[path];
         const float4 ha = wb.hitA[path];
-        const uint32_t hb = wb.hitB[path];
+        const uint32_t hb = late ? __float_as_uint(th.w) : hbEarly;
         PathState ps;
         ps.o = v3(ro.x, ro.y, ro.z); ps.seed = __float_as_uint(ro.w);
         ps.d = v3(rdv.x, rdv.y, rdv.z); ps.pixel = __float_as_uint(rdv.w);
@@ -567,8 +579,7 @@ accumulateKernel(const __grid_constant__ FrameParams fp, const WavefrontBuffers 
     if (slot >= numSlots) return;
     const uint32_t tile = slot / kTilePixels, j = slot % kTilePixels;
     const uint32_t tileX = tile % fp.tilesX, tileRowLocal = tile / fp.tilesX;
-    const uint32_t tilesPerBand = fp.bandRows / kTileH;
-    const uint32_t tileRow = ((tileRowLocal / tilesPerBand) * fp.shardCount + fp.shardRank) * tilesPerBand + tileRowLocal % tilesPerBand;
+    const uint32_t tileRow = ownedTileRow(fp, tileRowLocal);
     const uint32_t px = tileX * kTileW + j % kTileW, py = tileRow * kTileH + j / kTileW;
     if (px >= fp.coveredW || py >= fp.coveredH) return;
     const size_t pi = (size_t)py * rd.textureDims[0] + px;

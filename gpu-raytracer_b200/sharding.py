@@ -34,6 +34,22 @@ def seed_frames_of_rank(rank, world, local_frames):
     return [int(L.okrt_shard_seed_frame(abi.ptr(o), k, 1)) for k in range(1, local_frames + 1)]
 
 
+def balanced_bands(band_cost, world):
+    """Cost-weighted tile sharding: owner rank of every band (okrt_shard_balance: longest-processing-time-first, deterministic).
+    band_cost: one number per band, e.g. the ray segments of one calibration frame (aov numSegments summed over the band's rows)."""
+    cost = np.ascontiguousarray(band_cost, np.float64)
+    owner = np.zeros(len(cost), np.uint32)
+    abi.check(abi.lib().okrt_shard_balance(abi.ptr(cost), len(cost), world, abi.ptr(owner)))
+    return owner
+
+
+def band_costs_from_segments(num_segments, band_rows=8):
+    """Per-band sums of a per-pixel segment count image (okrt_aov.numSegments of one frame)."""
+    h = num_segments.shape[0]
+    bands = (h + band_rows - 1) // band_rows
+    return np.array([float(num_segments[b * band_rows:(b + 1) * band_rows].sum()) for b in range(bands)], np.float64)
+
+
 def all_reduce_accumulation(tensor):
     """In-place sum of the RGBA32F accumulation image over all ranks (the single exchange step of sample mode)."""
     import torch.distributed as dist

@@ -485,6 +485,12 @@ OKRT_API int okrt_read_result_owned(okrt_renderer* r, uint8_t* outRgba8, uint64_
 OKRT_API int okrt_read_result_async(okrt_renderer* r, uint8_t* outRgba8, uint64_t* outBytes, uint32_t slot);
 OKRT_API int okrt_wait_read(okrt_renderer* r, uint32_t slot);
 OKRT_API int okrt_read_accumulation(okrt_renderer* r, float* outRgba32f);
+/* Tile sharding with an explicit band table: `bands` = the global band indices (ascending) this handle traces, instead of every
+ * shardCount-th band; n = 0 restores the interleave.  okrt_shard_balance (host-only) assigns bands to ranks from measured band
+ * costs (e.g. ray segments per band of one calibration frame) by longest-processing-time-first, deterministically, so that
+ * every rank computes the same table without talking to the others. */
+OKRT_API int okrt_set_shard_bands(okrt_renderer* r, const uint32_t* bands, uint32_t n);
+OKRT_API int okrt_shard_balance(const double* bandCost, uint32_t numBands, uint32_t shardCount, uint32_t* ownerOfBand);
 /* f4: rasterises the overlay's lines into the RGBA8 result (u0); the accumulation (u1) is untouched, the next
  * okrt_render_frames rewrites u0. */
 OKRT_API int okrt_draw_overlay(okrt_renderer* r, const okrt_overlay* ov);

@@ -53,6 +53,45 @@ def test_tile_sharding_union_equals_single(okrt, pipeline):
     single.close()
 
 
+def test_cost_balanced_band_table_union_equals_single(okrt):
+    """Tile mode with an explicit band table (okrt_set_shard_bands), bands assigned by okrt_shard_balance from the ray
+    segments of a calibration frame: the ranks' rows still tile the image exactly, images equal the single-GPU one."""
+    W, H, world = 320, 184, 3
+    host, env = _scene(okrt, W, H)
+    single = helpers.Renderer(okrt, host, W, H, envFaces=env)
+    single.options(maxBounces=4, coverAllPixels=1, writeAov=1)
+    single.render(host["rd"].copy(), frames=1)
+    cost = okrt.sharding.band_costs_from_segments(single.aov()["numSegments"], 8)
+    single.close()
+    owner = okrt.sharding.balanced_bands(cost, world)
+    assert set(owner.tolist()) == set(range(world)) and len(owner) == (H + 7) // 8
+    loads = [cost[owner == k].sum() for k in range(world)]
+    assert max(loads) / min(loads) < 1.1
+    single = helpers.Renderer(okrt, host, W, H, envFaces=env)
+    single.options(maxBounces=4, coverAllPixels=1)
+    single.render(host["rd"].copy(), frames=2)
+    ref_acc, ref_img = single.accumulation(), single.result()
+    single.close()
+    acc, img, moved_total = np.zeros_like(ref_acc), np.zeros_like(ref_img), 0
+    for rank in range(world):
+        bands = np.ascontiguousarray(np.nonzero(owner == rank)[0], np.uint32)
+        r = helpers.Renderer(okrt, host, W, H, envFaces=env)
+        r.options(maxBounces=4, coverAllPixels=1, **okrt.sharding.tile_options(rank, world, 8))
+        okrt.abi.check(r.L.okrt_set_shard_bands(r.h, okrt.abi.ptr(bands), len(bands)))
+        r.render(host["rd"].copy(), frames=2)
+        rows = np.concatenate([np.arange(b * 8, min((b + 1) * 8, H)) for b in bands])
+        a = r.accumulation()
+        assert not a[np.setdiff1d(np.arange(H), rows)].any()
+        acc[rows] = a[rows]
+        moved = ctypes.c_uint64(0)
+        okrt.abi.check(r.L.okrt_read_result_async(r.h, okrt.abi.ptr(img), ctypes.byref(moved), 0))
+        okrt.abi.check(r.L.okrt_wait_read(r.h, 0))
+        assert moved.value == len(rows) * W * 4
+        moved_total += moved.value
+        r.close()
+    assert np.array_equal(acc.view(np.uint32), ref_acc.view(np.uint32)) and np.array_equal(img, ref_img) and moved_total == W * H * 4
+
+
 def test_sample_sharding_matches_sequential(okrt):
     """Sample mode: rank r renders frames r+1, r+1+G, ...; summed u1 == sequential u1 up to float summation order."""
     W, H, total, world = 256, 144, 8, 4
