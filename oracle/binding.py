@@ -12,6 +12,7 @@ ORACLE_DIR = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(ORACLE_DIR)
 ORACLE_LIB = os.path.join(ORACLE_DIR, "_build", "libokrt_oracle.so")
 REF_LIB = os.path.join(ORACLE_DIR, "_ref", "libokrt_ref.so")
+REF_OCTREE_LIB = os.path.join(ORACLE_DIR, "_ref", "libokrt_ref_octree.so")
 
 MATH_CANONICAL, MATH_LIBM = 0, 1
 
@@ -34,8 +35,10 @@ def build_oracle(force=False):
 def build_ref():
     """Compiles the reference's BvhBuilder.cpp where /root/reference exists; otherwise keeps the prebuilt file."""
     if os.path.exists("/root/reference/source/Graphics/BvhBuilder.cpp"):
-        shim = os.path.join(ORACLE_DIR, "ref_shim.cpp")
-        if not os.path.exists(REF_LIB) or os.path.getmtime(shim) > os.path.getmtime(REF_LIB):
+        shims = [os.path.join(ORACLE_DIR, f) for f in ("ref_shim.cpp", "ref_octree_shim.cpp", "Makefile")]
+        stale = not os.path.exists(REF_LIB) or not os.path.exists(REF_OCTREE_LIB)
+        stale = stale or any(os.path.getmtime(f) > min(os.path.getmtime(REF_LIB), os.path.getmtime(REF_OCTREE_LIB)) for f in shims)
+        if stale:
             subprocess.run(["make", "-s", "-C", ORACLE_DIR, "ref"], check=True)
     return REF_LIB if os.path.exists(REF_LIB) else None
 
@@ -165,6 +168,24 @@ def load():
     if _oracle is None:
         _oracle = Oracle(ctypes.CDLL(build_oracle()))
     return _oracle
+
+
+_ref_octree = None
+
+
+def load_ref_octree():
+    """The reference's own RayTracer::createOctTree / loadOctTree / refitOctTreeNode (oracle/ref_octree_shim.cpp); None where
+    neither /root/reference nor a prebuilt oracle/_ref/libokrt_ref_octree.so exists."""
+    global _ref_octree
+    if _ref_octree is None:
+        build_ref()
+        if not os.path.exists(REF_OCTREE_LIB):
+            return None
+        lib = ctypes.CDLL(REF_OCTREE_LIB)
+        lib.ref_build_octree.restype = _U
+        lib.ref_build_octree.argtypes = [_P, _P, _U, _P, _U, _P, _U, _U, _U, _P, _U, _P, _U, ctypes.POINTER(_U)]
+        _ref_octree = lib
+    return _ref_octree
 
 
 _ref = None

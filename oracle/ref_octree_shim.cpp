@@ -1,0 +1,107 @@
+/*
+ * ref_octree_shim.cpp — TEST INFRASTRUCTURE.  C entry point around the REFERENCE's own oct-tree builder.
+ *
+ * This file is ours; it contains no reference source.  oracle/Makefile extracts the text of
+ *   RayTracer::refitOctTreeNode / createOctTree / loadOctTree   (/root/reference/source/Graphics/RayTracer.cpp:503-788)
+ * at build time into oracle/_ref/octree_extract.inc (git-ignored, deleted after the compile) and compiles it here, unmodified,
+ * as members of the reference's own `class RayTracer` (its header is included as it lies), together with the reference's
+ * Scene.cpp, EnTT (vendored header), glm, Components.h, Mesh.h, ResourceManager.h.  What is NOT the reference's: <d3d11.h> and
+ * <DirectXCollision.h> (oracle/ref_stubs: opaque types, BoundingBox::GetCorners) and the handful of D3D-side definitions below
+ * that the three functions link against but whose effects are irrelevant here (GPUStorage::updateRaw, Okay::updateBuffer).
+ * The rest of RayTracer.cpp (D3D11 device code) is not compiled.
+ * Result: row a11 of SURVEY.md §8 is pinned to the reference itself (tests/test_cpu_builders.py, tests/golden/octree_*.npz).
+ */
+#include <chrono>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <stack>
+#include <vector>
+
+#define private public          /* the shim fills ResourceManager::m_meshes / RayTracer::m_meshDescs and reads the results */
+#include "Graphics/ResourceManager.h"
+#include "Graphics/RayTracer.h"
+#undef private
+#include "Scene/Scene.h"
+#include "Scene/Components.h"
+#include "glm/gtc/matrix_transform.hpp"
+#include "glm/gtx/quaternion.hpp"
+#include <DirectXCollision.h>
+
+/* ---- D3D-side symbols the class needs to link; none of them does anything */
+namespace Okay {
+ID3D11DeviceContext* getDeviceContext() { static ID3D11DeviceContext ctx; return &ctx; }
+void updateBuffer(ID3D11Buffer*, const void*, size_t) {}
+}
+GPUStorage::GPUStorage() : m_pBuffer(nullptr), m_pSRV(nullptr), m_capacity(0), m_elementByteWidth(0) {}
+GPUStorage::~GPUStorage() {}
+void GPUStorage::updateRaw(uint32_t, const void*) {}
+RenderTexture::RenderTexture() {}
+RenderTexture::~RenderTexture() {}
+RayTracer::RayTracer() : m_pScene(nullptr), m_pResourceManager(nullptr), m_pTargetTexture(nullptr), m_pRenderDataBuffer(nullptr),
+                         m_pMainRaytracingCS(nullptr), m_pTextures(nullptr), m_pEnvironmentMapSRV(nullptr) {}
+RayTracer::~RayTracer() {}
+
+/* ---- the reference's own text: RayTracer.cpp:503-788 */
+static int okrt_silent_printf(const char*, ...) { return 0; }
+#define printf okrt_silent_printf
+#include "octree_extract.inc"
+#undef printf
+
+#define REF_API extern "C" __attribute__((visibility("default")))
+
+struct ShimMeshEntity { float position[3], rotation[3], scale[3]; Material material; uint32_t meshID; };
+struct ShimSphereEntity { float position[3], rotation[3], scale[3]; Material material; float radius; };
+struct ShimMeshDesc { uint32_t startIdx, endIdx, bvhTreeStartIdx, numBvhNodes; };
+static_assert(sizeof(GPU_OctTreeNode) == 48 && sizeof(GPU_MeshComponent) == 232, "wire structs");
+
+/* Same arguments as oracle_build_octree (oracle/okrt_oracle.cpp) and okrt_octree_build's inputs.  Returns the node count
+ * (~0u if a capacity is too small). */
+REF_API uint32_t ref_build_octree(const ShimMeshDesc* descs, const float* meshBounds /* 6 per mesh */, uint32_t numMeshes,
+                                  const ShimMeshEntity* meshEnts, uint32_t numMeshEnts, const ShimSphereEntity* sphereEnts, uint32_t numSphereEnts,
+                                  uint32_t maxDepth, uint32_t maxLeafObjects, void* outNodes, uint32_t nodeCapacity,
+                                  void* outInstances, uint32_t instanceCapacity, uint32_t* outNumInstances)
+{
+    ResourceManager rm;
+    for (uint32_t m = 0; m < numMeshes; m++) {
+        MeshData md;
+        md.boundingBox.min = glm::vec3(meshBounds[m * 6 + 0], meshBounds[m * 6 + 1], meshBounds[m * 6 + 2]);
+        md.boundingBox.max = glm::vec3(meshBounds[m * 6 + 3], meshBounds[m * 6 + 4], meshBounds[m * 6 + 5]);
+        rm.m_meshes.emplace_back(md, "shim");
+    }
+    Scene scene;
+    /* The arrays are given in the order the registry views ENUMERATE the entities (the contract of okrt_octree_build, include/okrt.h).
+     * EnTT walks a pool from its newest element to its oldest, so the entities are created last-to-first. */
+    for (uint32_t e = numMeshEnts; e-- > 0u;) {
+        Entity ent = scene.createEntity();
+        Transform& t = ent.getComponent<Transform>();
+        t.position = glm::vec3(meshEnts[e].position[0], meshEnts[e].position[1], meshEnts[e].position[2]);
+        t.rotation = glm::vec3(meshEnts[e].rotation[0], meshEnts[e].rotation[1], meshEnts[e].rotation[2]);
+        t.scale = glm::vec3(meshEnts[e].scale[0], meshEnts[e].scale[1], meshEnts[e].scale[2]);
+        MeshComponent& mc = ent.addComponent<MeshComponent>();
+        mc.meshID = meshEnts[e].meshID;
+        mc.material = meshEnts[e].material;
+    }
+    for (uint32_t e = numSphereEnts; e-- > 0u;) {
+        Entity ent = scene.createEntity();
+        Transform& t = ent.getComponent<Transform>();
+        t.position = glm::vec3(sphereEnts[e].position[0], sphereEnts[e].position[1], sphereEnts[e].position[2]);
+        Sphere& sp = ent.addComponent<Sphere>();
+        sp.material = sphereEnts[e].material;
+        sp.radius = sphereEnts[e].radius;
+    }
+    RayTracer rt;
+    rt.m_pResourceManager = &rm;
+    rt.setScene(scene);
+    rt.m_meshDescs.resize(numMeshes);
+    for (uint32_t m = 0; m < numMeshes; m++) {
+        rt.m_meshDescs[m].startIdx = descs[m].startIdx; rt.m_meshDescs[m].endIdx = descs[m].endIdx;
+        rt.m_meshDescs[m].bvhTreeStartIdx = descs[m].bvhTreeStartIdx; rt.m_meshDescs[m].numBvhNodes = descs[m].numBvhNodes;
+    }
+    rt.createOctTree(scene, maxDepth, maxLeafObjects);
+    if (rt.m_octTreeNodes.size() > nodeCapacity || rt.m_gpuMeshes.size() > instanceCapacity) return ~0u;
+    std::memcpy(outNodes, rt.m_octTreeNodes.data(), rt.m_octTreeNodes.size() * sizeof(GPU_OctTreeNode));
+    std::memcpy(outInstances, rt.m_gpuMeshes.data(), rt.m_gpuMeshes.size() * sizeof(GPU_MeshComponent));
+    *outNumInstances = (uint32_t)rt.m_gpuMeshes.size();
+    return (uint32_t)rt.m_octTreeNodes.size();
+}

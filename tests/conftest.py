@@ -37,3 +37,13 @@ def ref():
     if lib is None:
         pytest.skip("oracle/_ref/libokrt_ref.so not available")
     return lib
+
+
+@pytest.fixture(scope="session")
+def ref_octree():
+    """The reference's own oct-tree builder (RayTracer.cpp:503-788) behind oracle/_ref/libokrt_ref_octree.so."""
+    from oracle import binding
+    lib = binding.load_ref_octree()
+    if lib is None:
+        pytest.skip("oracle/_ref/libokrt_ref_octree.so not available")
+    return lib

@@ -150,6 +150,65 @@ def test_octree_product_equals_oracle(okrt, oracle):
         assert sum(int(n["meshesEndIdx"] - n["meshesStartIdx"]) for n in t.nodes) == len(me)
 
 
+def _octree_cases(okrt):
+    rng = np.random.default_rng(23)
+    rm, sc, info = okrt.scenes.moved_props_scene()
+    for k in range(6):                                  # spheres take part in the split (RayTracer.cpp:561-571)
+        sc.addSphereEntity(float(rng.uniform(0.5, 3.0)), okrt.scenes.material(), tuple(rng.uniform(-20, 20, 3)))
+    return [(okrt.scenes.test_scene(), (2, 50)), (okrt.scenes.test_scene(), (3, 2)), (okrt.scenes.sponza_standin(8000, texture_size=32), (2, 50)),
+            (okrt.scenes.sponza_standin(8000, texture_size=32), (3, 10)), ((rm, sc, info), (3, 3)), ((rm, sc, info), (4, 1))]
+
+
+def _ref_octree(okrt, ref_octree, geo, sc, depth, leaf):
+    abi = okrt.abi
+    me, se = sc.meshEntityArray(), sc.sphereEntityArray()
+    nodes = np.zeros(8192, abi.OCTREE_NODE); inst = np.zeros(max(1, len(me)), abi.MESH_INSTANCE); ni = ctypes.c_uint32()
+    bounds = np.ascontiguousarray(geo.meshBounds)
+    nn = ref_octree.ref_build_octree(abi.ptr(geo.meshDescs), abi.ptr(bounds), len(geo.meshDescs), abi.ptr(me), len(me),
+                                     abi.ptr(se) if len(se) else None, len(se), depth, leaf, abi.ptr(nodes), len(nodes),
+                                     abi.ptr(inst), len(inst), ctypes.byref(ni))
+    assert nn != 0xFFFFFFFF
+    return nodes[:nn], inst[:ni.value]
+
+
+def test_octree_product_equals_reference(okrt, oracle, ref_octree):
+    """Row a11 pinned to the reference itself: RayTracer::createOctTree / loadOctTree / refitOctTreeNode (RayTracer.cpp:503-788),
+    compiled from the reference's own source text with its own class header, EnTT, glm and Scene.cpp (oracle/ref_octree_shim.cpp),
+    against okrt_octree_build and against the oracle's restatement, byte for byte: GPU_OctTreeNode[] and GPU_MeshComponent[]."""
+    abi = okrt.abi
+    for (rm, sc, info), (depth, leaf) in _octree_cases(okrt):
+        geo = okrt.Geometry(rm.meshes, 30, 5)
+        t = okrt.OctTree(geo, sc, depth, leaf)
+        rn, ri = _ref_octree(okrt, ref_octree, geo, sc, depth, leaf)
+        assert len(rn) == len(t.nodes) and len(ri) == len(t.instances), (info.get("name"), depth, leaf, len(rn), len(t.nodes))
+        assert rn.tobytes() == t.nodes.tobytes(), (info.get("name"), depth, leaf)
+        assert ri.tobytes() == t.instances.tobytes(), (info.get("name"), depth, leaf)
+        me, se = sc.meshEntityArray(), sc.sphereEntityArray()
+        nodes = np.zeros(8192, abi.OCTREE_NODE); inst = np.zeros(max(1, len(me)), abi.MESH_INSTANCE); ni = ctypes.c_uint32()
+        nn = oracle.lib.oracle_build_octree(abi.ptr(geo.meshDescs), abi.ptr(geo.meshBounds), len(geo.meshDescs), abi.ptr(me), len(me),
+                                            abi.ptr(se) if len(se) else None, len(se), depth, leaf, abi.ptr(nodes), len(nodes), abi.ptr(inst), ctypes.byref(ni))
+        assert nodes[:nn].tobytes() == rn.tobytes() and inst[:ni.value].tobytes() == ri.tobytes()
+
+
+def test_octree_golden_fixtures(okrt):
+    """The same pin without /root/reference: tests/golden/octree_*.npz hold the reference builder's own outputs
+    (tests/golden/make_golden_octree.py); okrt_octree_build must reproduce them byte for byte."""
+    import glob
+    import os
+    from tests.golden.make_golden_octree import box_meshes, EntityArrays
+    abi = okrt.abi
+    paths = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "octree_*.npz")))
+    assert len(paths) >= 3
+    for path in paths:
+        z = np.load(path)
+        geo = okrt.Geometry(box_meshes(okrt, z["boxes"]), 30, 5)
+        me = np.ascontiguousarray(z["meshEntities"]).view(abi.MESH_ENTITY)
+        se = np.ascontiguousarray(z["sphereEntities"]).view(abi.SPHERE_ENTITY)
+        t = okrt.OctTree(geo, EntityArrays(me, se), int(z["maxDepth"]), int(z["maxLeafObjects"]))
+        assert t.nodes.tobytes() == z["nodes"].tobytes(), path
+        assert t.instances.tobytes() == z["instances"].tobytes(), path
+
+
 def test_texture_array_and_environment(okrt, oracle):
     """Row a13: N = uint(sqrt(total area / count)) (RayTracer.cpp:318-324), bilinear CLAMP rescale, cross -> 6 faces."""
     abi = okrt.abi
