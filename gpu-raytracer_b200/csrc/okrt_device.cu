@@ -172,6 +172,7 @@ struct okrt_renderer {
     bool layoutHasWide = false;                 /* the wide layout is built only for OKRT_TRAVERSAL_WIDE */
     std::vector<uint32_t> ownedBands;           /* okrt_set_shard_bands: this rank's bands (ascending); empty: interleaved by arithmetic */
     DeviceBuffer dOwnedBands;
+    DeviceBuffer ovSegments, ovKeys, ovColours, ovPixelKey;   /* okrt_draw_overlay scratch */
     okrt_layout_build layoutBuild{};            /* how the last rebuild went (okrt_get_layout_build) */
     WavefrontBuffers wb{};                      /* path state of the wavefront pipeline (sized for width x height) */
     size_t wbPaths = 0, wbReserve = 0;
@@ -779,6 +780,7 @@ void okrt_destroy(okrt_renderer* r)
     if (r->fastTrisTex) { cudaDestroyTextureObject(r->fastTrisTex); r->fastTrisTex = 0; }
     r->fastNodes.release(); r->fastTris.release(); r->fastInstances.release(); r->octParent.release(); r->wideNodes.release(); r->wideLeaves.release();
     r->dOwnedBands.release();
+    r->ovSegments.release(); r->ovKeys.release(); r->ovColours.release(); r->ovPixelKey.release();
     r->textures.release(); r->environment.release();
     if (r->accumulation) cudaFree(r->accumulation);
     if (r->result) cudaFree(r->result);
@@ -1213,12 +1215,20 @@ int okrt_draw_overlay(okrt_renderer* r, const okrt_overlay* ov)
     const uint32_t n = (uint32_t)ov->keys.size();
     if (!n) return OKRT_OK;
     const size_t pixels = (size_t)r->width * r->height;
-    float4* dSeg = nullptr; uint32_t *dKeys = nullptr, *dColours = nullptr, *dPixelKey = nullptr;
-    auto release = [&]() { cudaFree(dSeg); cudaFree(dKeys); cudaFree(dColours); cudaFree(dPixelKey); };
-    cudaError_t e = cudaMalloc(&dSeg, (size_t)n * sizeof(float4));
-    if (e == cudaSuccess) e = cudaMalloc(&dKeys, (size_t)n * 4);
-    if (e == cudaSuccess) e = cudaMalloc(&dColours, ov->colours.size() * 4);
-    if (e == cudaSuccess) e = cudaMalloc(&dPixelKey, pixels * 4);
+    /* scratch kept with the renderer (grown on demand): the reference redraws its overlays every frame (DebugRenderer.cpp:264-364) */
+    auto grow = [](DeviceBuffer& b, size_t bytes) -> cudaError_t {
+        if (b.bytes >= bytes) return cudaSuccess;
+        if (b.ptr) cudaFree(b.ptr);
+        b.ptr = nullptr; b.bytes = 0;
+        const cudaError_t err = cudaMalloc(&b.ptr, bytes);
+        if (err == cudaSuccess) b.bytes = bytes;
+        return err;
+    };
+    cudaError_t e = grow(r->ovSegments, (size_t)n * sizeof(float4));
+    if (e == cudaSuccess) e = grow(r->ovKeys, (size_t)n * 4);
+    if (e == cudaSuccess) e = grow(r->ovColours, ov->colours.size() * 4);
+    if (e == cudaSuccess) e = grow(r->ovPixelKey, pixels * 4);
+    float4* dSeg = (float4*)r->ovSegments.ptr; uint32_t *dKeys = (uint32_t*)r->ovKeys.ptr, *dColours = (uint32_t*)r->ovColours.ptr, *dPixelKey = (uint32_t*)r->ovPixelKey.ptr;
     if (e == cudaSuccess) e = cudaMemcpyAsync(dSeg, ov->segments.data(), (size_t)n * sizeof(float4), cudaMemcpyHostToDevice, r->stream);
     if (e == cudaSuccess) e = cudaMemcpyAsync(dKeys, ov->keys.data(), (size_t)n * 4, cudaMemcpyHostToDevice, r->stream);
     if (e == cudaSuccess) e = cudaMemcpyAsync(dColours, ov->colours.data(), ov->colours.size() * 4, cudaMemcpyHostToDevice, r->stream);
@@ -1229,8 +1239,7 @@ int okrt_draw_overlay(okrt_renderer* r, const okrt_overlay* ov)
         r->launches += 2;
         e = cudaGetLastError();
     }
-    if (e == cudaSuccess) e = cudaStreamSynchronize(r->stream);
-    release();
+    if (e == cudaSuccess) e = cudaStreamSynchronize(r->stream);          /* the overlay's host arrays may go away on return */
     if (e != cudaSuccess) { setError(std::string("okrt_draw_overlay: ") + cudaGetErrorString(e)); return OKRT_ERR_CUDA; }
     return OKRT_OK;
 }
