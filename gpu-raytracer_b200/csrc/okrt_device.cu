@@ -139,7 +139,7 @@ struct okrt_renderer {
     size_t traceEventsUsed = 0;
     uint32_t width = 0, height = 0;
 
-    DeviceBuffer triPos, triInfo, bvhNodes, octNodes, spheres, instances, dirLights, pointLights, spotLights;
+    DeviceBuffer triPos, triInfo, shadeInfo, bvhNodes, octNodes, spheres, instances, dirLights, pointLights, spotLights;
     TextureArray textures, environment;
     DeviceBuffer fastNodes, fastTris, fastInstances, octParent, wideNodes, wideLeaves;
     uint32_t wideRoot = kRefNone;
@@ -358,6 +358,7 @@ DeviceScene sceneView(const okrt_renderer* r)
     std::memset(&s, 0, sizeof(s));
     s.triPos = (const float*)r->triPos.ptr;
     s.triInfo = (const float*)r->triInfo.ptr;
+    s.shadeInfo = (const float4*)r->shadeInfo.ptr;
     s.bvhNodes = (const okrt_bvh_node*)r->bvhNodes.ptr;
     s.textures = r->textures.object;
     s.environment = r->environment.object;
@@ -775,7 +776,7 @@ void okrt_destroy(okrt_renderer* r)
     cudaSetDevice(r->device);
     if (r->stream) cudaStreamSynchronize(r->stream);
     if (r->stream2) cudaStreamSynchronize(r->stream2);
-    r->triPos.release(); r->triInfo.release(); r->bvhNodes.release(); r->octNodes.release(); r->spheres.release();
+    r->triPos.release(); r->triInfo.release(); r->shadeInfo.release(); r->bvhNodes.release(); r->octNodes.release(); r->spheres.release();
     r->instances.release(); r->dirLights.release(); r->pointLights.release(); r->spotLights.release();
     if (r->fastTrisTex) { cudaDestroyTextureObject(r->fastTrisTex); r->fastTrisTex = 0; }
     r->fastNodes.release(); r->fastTris.release(); r->fastInstances.release(); r->octParent.release(); r->wideNodes.release(); r->wideLeaves.release();
@@ -817,12 +818,37 @@ int okrt_resize(okrt_renderer* r, uint32_t width, uint32_t height)
     return allocateImages(r);
 }
 
+/* DeviceScene::shadeInfo from t1 (TriangleInfo = 3 x VertexInfo of 11 floats: normal 0-2, uv 3-4), bit copies */
+__global__ void packShadeInfoKernel(const float* __restrict__ triInfo, float4* __restrict__ out, uint32_t n)
+{
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    const float* ti = triInfo + (size_t)t * 33;
+    out[4 * (size_t)t + 0] = make_float4(ti[0], ti[1], ti[2], ti[3]);
+    out[4 * (size_t)t + 1] = make_float4(ti[11], ti[12], ti[13], ti[4]);
+    out[4 * (size_t)t + 2] = make_float4(ti[22], ti[23], ti[24], ti[14]);
+    out[4 * (size_t)t + 3] = make_float4(ti[15], ti[25], ti[26], 0.f);
+}
+
 int okrt_set_triangles(okrt_renderer* r, const okrt_triangle* pos, const okrt_triangle_info* info, uint32_t n)
 {
     int rc = checkHandle(r, "okrt_set_triangles"); if (rc) return rc;
     if (n && (!pos || !info)) { setError("okrt_set_triangles: null array"); return OKRT_ERR_INVALID_ARGUMENT; }
     if ((rc = r->triPos.upload(pos, n, sizeof(okrt_triangle), r->stream))) return rc;
     if ((rc = r->triInfo.upload(info, n, sizeof(okrt_triangle_info), r->stream))) return rc;
+    {
+        const size_t need = (size_t)n * 4 * sizeof(float4);
+        if (need != r->shadeInfo.bytes) {
+            r->shadeInfo.release();
+            if (need) OKRT_CUDA(cudaMalloc(&r->shadeInfo.ptr, need));
+            r->shadeInfo.bytes = need;
+        }
+        r->shadeInfo.count = n;
+        if (n) {
+            packShadeInfoKernel<<<(n + 255u) / 256u, 256, 0, r->stream>>>((const float*)r->triInfo.ptr, (float4*)r->shadeInfo.ptr, n);
+            OKRT_CUDA(cudaGetLastError());
+        }
+    }
     r->hTris = std::make_shared<std::vector<okrt_triangle>>(pos, pos + n);
     r->layoutDirty = true;
     return OKRT_OK;

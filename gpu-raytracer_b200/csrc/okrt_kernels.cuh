@@ -109,6 +109,10 @@ struct DeviceScene {
     uint32_t wideRoot, numWideNodes;
     float maxSlack;
     uint32_t pad1;
+    /* shading record, 64 B per triangle (4 float4), packed on the device from t1 when the triangles are set: what every mesh hit
+     * reads (3 vertex normals, 3 uvs) in two sectors instead of six; tangents / bitangents stay in t1 for normal-mapped hits.
+     *   {n0.xyz, uv0.x} {n1.xyz, uv0.y} {n2.xyz, uv1.x} {uv1.y, uv2.x, uv2.y, 0} */
+    const float4* shadeInfo;
 };
 
 struct FrameParams {
@@ -981,11 +985,13 @@ __device__ __forceinline__ void resolveHit(const DeviceScene& s, V3 o, V3 d, con
         const okrt_mesh_instance& inst = s.instances[hit.idx];
         loadMaterial(sf.material, &inst.material);
         const float* ti = s.triInfo + (size_t)hit.tri * 33;   /* VertexInfo: normal 0-2, uv 3-4, tangent 5-7, bitangent 8-10 */
+        const float4* si = s.shadeInfo + (size_t)hit.tri * 4;  /* bit copies of the same floats (DeviceScene::shadeInfo) */
+        const float4 s0 = __ldg(si), s1 = __ldg(si + 1), s2 = __ldg(si + 2), s3 = __ldg(si + 3);
         const float bu = hit.u, bv = hit.v, bw = 1.f - (hit.u + hit.v);
         V2 uv;
-        uv.x = (__ldg(ti + 3) * bu + __ldg(ti + 14) * bv) + __ldg(ti + 25) * bw;
-        uv.y = (__ldg(ti + 4) * bu + __ldg(ti + 15) * bv) + __ldg(ti + 26) * bw;
-        const V3 n0 = v3(__ldg(ti + 0), __ldg(ti + 1), __ldg(ti + 2)), n1 = v3(__ldg(ti + 11), __ldg(ti + 12), __ldg(ti + 13)), n2 = v3(__ldg(ti + 22), __ldg(ti + 23), __ldg(ti + 24));
+        uv.x = (s0.w * bu + s2.w * bv) + s3.y * bw;
+        uv.y = (s1.w * bu + s3.x * bv) + s3.z * bw;
+        const V3 n0 = v3(s0.x, s0.y, s0.z), n1 = v3(s1.x, s1.y, s1.z), n2 = v3(s2.x, s2.y, s2.z);
         V3 normal = normalize(mulDir((n0 * bu + n1 * bv) + n2 * bw, inst.transformMatrix));
         if (sf.material.normalMapIdx != 0xFFFFFFFFu) {
             const V3 g0 = v3(__ldg(ti + 5), __ldg(ti + 6), __ldg(ti + 7)), g1 = v3(__ldg(ti + 16), __ldg(ti + 17), __ldg(ti + 18)), g2 = v3(__ldg(ti + 27), __ldg(ti + 28), __ldg(ti + 29));

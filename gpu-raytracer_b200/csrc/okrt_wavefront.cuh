@@ -485,8 +485,9 @@ shadeKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ Frame
      * late == 1: exactly those, from the fallback queue, once that kernel is done */
     const okrt_render_data& rd = fp.rd;
     const uint32_t count = late ? wb.fallbackCounts[bounce] : wb.counts[2u * bounce];
-    __shared__ uint32_t warpSurvivors[4];
-    __shared__ uint32_t blockBase;
+    __shared__ uint32_t warpSurvivors[2][4];     /* two copies, used by alternate trips: a trip's readers and the next trip's */
+    __shared__ uint32_t blockBase[2];            /* writers are a barrier apart without a third barrier per trip */
+    uint32_t trip = 0u;
     if (blockIdx.x == 0u && threadIdx.x == 0u && !late) {
         atomicAdd(fp.counters + 0, (unsigned long long)count);
         if (bounce == 0u) atomicAdd(fp.counters + 2, (unsigned long long)count);
@@ -551,19 +552,20 @@ shadeKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ Frame
      * half a million same-address atomics per launch) */
     const uint32_t mask = __ballot_sync(0xFFFFFFFFu, survives);
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    if (lane == 0u) warpSurvivors[warp] = (uint32_t)__popc(mask);
+    uint32_t* const ws = warpSurvivors[trip & 1u];
+    if (lane == 0u) ws[warp] = (uint32_t)__popc(mask);
     __syncthreads();
     if (threadIdx.x == 0u) {
-        const uint32_t total = warpSurvivors[0] + warpSurvivors[1] + warpSurvivors[2] + warpSurvivors[3];
-        blockBase = total ? atomicAdd(wb.counts + 2u * (bounce + 1u), total) : 0u;
+        const uint32_t total = ws[0] + ws[1] + ws[2] + ws[3];
+        blockBase[trip & 1u] = total ? atomicAdd(wb.counts + 2u * (bounce + 1u), total) : 0u;
     }
     __syncthreads();
     if (survives) {
-        uint32_t base = blockBase;
-        for (uint32_t w = 0; w < warp; w++) base += warpSurvivors[w];
+        uint32_t base = blockBase[trip & 1u];
+        for (uint32_t w = 0; w < warp; w++) base += ws[w];
         queueOut[base + __popc(mask & ((1u << lane) - 1u))] = path;
     }
-    __syncthreads();                 /* warpSurvivors / blockBase are rewritten by the next trip */
+    trip++;                          /* the next trip writes the other copy; the one after it is two barriers away */
     }
 }
 
