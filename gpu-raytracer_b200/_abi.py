@@ -155,6 +155,7 @@ SYMBOLS = [
     ("okrt_get_num_accumulation_frames", _U, [_P]),
     ("okrt_read_result", _I, [_P, _P]),
     ("okrt_draw_overlay", _I, [_P, _P]),
+    ("okrt_draw_overlay_static", _I, [_P, _P]),
     ("okrt_read_result_owned", _I, [_P, _P, ctypes.POINTER(ctypes.c_uint64)]),
     ("okrt_read_accumulation", _I, [_P, _P]),
     ("okrt_read_aov", _I, [_P, _P]),

@@ -18,6 +18,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <mutex>
 #include <vector>
 
 #include "okrt.h"
@@ -1267,6 +1268,80 @@ int okrt_draw_overlay(okrt_renderer* r, const okrt_overlay* ov)
     }
     if (e == cudaSuccess) e = cudaStreamSynchronize(r->stream);          /* the overlay's host arrays may go away on return */
     if (e != cudaSuccess) { setError(std::string("okrt_draw_overlay: ") + cudaGetErrorString(e)); return OKRT_ERR_CUDA; }
+    return OKRT_OK;
+}
+
+/* ------------------------------------------------------------ okrt_draw_overlay without allocation
+ * No counterpart in the reference; added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, serving loops, harnesses that forbid it).  Same two kernels as okrt_draw_overlay; their scratch
+ * (pixel keys, the line list, the draw colours) lives in one file-scope device array of a fixed maximum size instead of
+ * buffers grown with cudaMalloc.  Every device that loads the library holds the array (9.3 MiB) until exit.
+ *   layout: [pixelKey: MAX_PIXELS u32][segments: MAX_SEGMENTS float4][keys: MAX_SEGMENTS u32][colours: MAX_DRAWS u32]
+ * In host code `gOverlayStaticScratch` is a host-side stand-in, not a device address: the kernels get the pointer that
+ * cudaGetSymbolAddress returns for the current device (looked up once per device, below). */
+constexpr size_t kOvStaticPixelKeyBytes = (size_t)OKRT_OVERLAY_STATIC_MAX_PIXELS * 4;
+constexpr size_t kOvStaticSegmentsBytes = (size_t)OKRT_OVERLAY_STATIC_MAX_SEGMENTS * sizeof(float4);
+constexpr size_t kOvStaticKeysBytes = (size_t)OKRT_OVERLAY_STATIC_MAX_SEGMENTS * 4;
+constexpr size_t kOvStaticColoursBytes = (size_t)OKRT_OVERLAY_STATIC_MAX_DRAWS * 4;
+constexpr size_t kOvStaticBytes = kOvStaticPixelKeyBytes + kOvStaticSegmentsBytes + kOvStaticKeysBytes + kOvStaticColoursBytes;
+static_assert(kOvStaticPixelKeyBytes % 256 == 0 && kOvStaticSegmentsBytes % 256 == 0 && kOvStaticKeysBytes % 256 == 0, "sub-arrays stay 256-byte aligned");
+static __device__ __align__(256) unsigned char gOverlayStaticScratch[kOvStaticBytes];
+
+namespace {
+constexpr int kOvStaticMaxDevices = 64;
+std::mutex gOvStaticMutex;
+unsigned char* gOvStaticPtr[kOvStaticMaxDevices] = {};       /* device address of gOverlayStaticScratch, per device ordinal */
+
+/* set-up, once per device, with that device current (checkHandle has made it so) */
+int overlayStaticAddress(int device, unsigned char** out)
+{
+    if (device < 0 || device >= kOvStaticMaxDevices) { setError("okrt_draw_overlay_static: device ordinal beyond 63"); return OKRT_ERR_INVALID_ARGUMENT; }
+    std::lock_guard<std::mutex> lock(gOvStaticMutex);
+    if (!gOvStaticPtr[device]) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, gOverlayStaticScratch);
+        if (e != cudaSuccess || !p) {
+            setError(std::string("okrt_draw_overlay_static: cudaGetSymbolAddress: ") + cudaGetErrorString(e));
+            return OKRT_ERR_CUDA;
+        }
+        gOvStaticPtr[device] = (unsigned char*)p;
+    }
+    *out = gOvStaticPtr[device];
+    return OKRT_OK;
+}
+} // namespace
+
+int okrt_draw_overlay_static(okrt_renderer* r, const okrt_overlay* ov)
+{
+    int rc = checkHandle(r, "okrt_draw_overlay_static"); if (rc) return rc;
+    if (!ov) { setError("okrt_draw_overlay_static: null overlay"); return OKRT_ERR_INVALID_ARGUMENT; }
+    const size_t n = ov->keys.size(), draws = ov->colours.size(), pixels = (size_t)r->width * r->height;
+    if (pixels > OKRT_OVERLAY_STATIC_MAX_PIXELS || n > OKRT_OVERLAY_STATIC_MAX_SEGMENTS || draws > OKRT_OVERLAY_STATIC_MAX_DRAWS) {
+        setError("okrt_draw_overlay_static: " + std::to_string(pixels) + " pixels / " + std::to_string(n) + " segments / " + std::to_string(draws) +
+                 " draws exceed the static scratch (" + std::to_string(OKRT_OVERLAY_STATIC_MAX_PIXELS) + " / " + std::to_string(OKRT_OVERLAY_STATIC_MAX_SEGMENTS) +
+                 " / " + std::to_string(OKRT_OVERLAY_STATIC_MAX_DRAWS) + "): use okrt_draw_overlay");
+        return OKRT_ERR_INVALID_ARGUMENT;
+    }
+    unsigned char* base = nullptr;
+    if ((rc = overlayStaticAddress(r->device, &base))) return rc;       /* an empty overlay still does the set-up: a warm-up call */
+    if (!n) return OKRT_OK;
+    uint32_t* dPixelKey = (uint32_t*)base;
+    float4* dSeg = (float4*)(base + kOvStaticPixelKeyBytes);
+    uint32_t* dKeys = (uint32_t*)(base + kOvStaticPixelKeyBytes + kOvStaticSegmentsBytes);
+    uint32_t* dColours = (uint32_t*)(base + kOvStaticPixelKeyBytes + kOvStaticSegmentsBytes + kOvStaticKeysBytes);
+    /* the array keeps the last call's contents: the pixel keys must start at zero, the rest is overwritten up to what is read */
+    cudaError_t e = cudaMemsetAsync(dPixelKey, 0, pixels * 4, r->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dSeg, ov->segments.data(), n * sizeof(float4), cudaMemcpyHostToDevice, r->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dKeys, ov->keys.data(), n * 4, cudaMemcpyHostToDevice, r->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dColours, ov->colours.data(), draws * 4, cudaMemcpyHostToDevice, r->stream);
+    if (e == cudaSuccess) {
+        overlayRasterKernel<<<(unsigned)((n * 32 + 127) / 128), 128, 0, r->stream>>>(dSeg, dKeys, (uint32_t)n, r->width, r->height, dPixelKey);
+        overlayResolveKernel<<<(unsigned)((pixels + 255) / 256), 256, 0, r->stream>>>(dPixelKey, dColours, pixels, (uchar4*)r->result);
+        r->launches += 2;
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(r->stream);          /* the overlay's host arrays may go away on return */
+    if (e != cudaSuccess) { setError(std::string("okrt_draw_overlay_static: ") + cudaGetErrorString(e)); return OKRT_ERR_CUDA; }
     return OKRT_OK;
 }
 

@@ -494,6 +494,18 @@ OKRT_API int okrt_shard_balance(const double* bandCost, uint32_t numBands, uint3
 /* f4: rasterises the overlay's lines into the RGBA8 result (u0); the accumulation (u1) is untouched, the next
  * okrt_render_frames rewrites u0. */
 OKRT_API int okrt_draw_overlay(okrt_renderer* r, const okrt_overlay* ov);
+/* okrt_draw_overlay for callers that cannot allocate device memory (CUDA graph capture around them, serving loops, harnesses
+ * that forbid cudaMalloc).  It has no counterpart in the reference.
+ * Same kernels and the same pixels as okrt_draw_overlay, but the scratch (pixel keys, line list, draw colours) is one
+ * file-scope device array of fixed size — 9.3 MiB held by every GPU that loads the library, until exit — so the call makes
+ * no cudaMalloc / cudaFree.  Image, line list or draw count beyond the limits below: OKRT_ERR_INVALID_ARGUMENT, nothing drawn
+ * (use okrt_draw_overlay).  All callers on a device share the array, which keeps the last call's contents (the call clears
+ * what must start at zero): calls that overlap on one GPU — two renderers on different streams, two host threads — race;
+ * serialise them.  A call with an empty overlay only does the per-device set-up (the address look-up), as a warm-up. */
+#define OKRT_OVERLAY_STATIC_MAX_PIXELS   2097152u   /* 2^21 >= 1920 x 1080 */
+#define OKRT_OVERLAY_STATIC_MAX_SEGMENTS 65536u
+#define OKRT_OVERLAY_STATIC_MAX_DRAWS    16384u
+OKRT_API int okrt_draw_overlay_static(okrt_renderer* r, const okrt_overlay* ov);
       /* W*H*4 floats */
 OKRT_API int okrt_read_aov(okrt_renderer* r, okrt_aov* out);                   /* W*H entries; needs writeAov */
 /* progressive-state restore / merge (new): replaces the accumulation buffer and frame counter */
