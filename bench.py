@@ -50,7 +50,7 @@ def workload_config(n_gpus):
         "resolution": [WIDTH, HEIGHT], "max_bounces": MAX_BOUNCES, "frames_per_step": FRAMES_PER_STEP,
         "bvh": [30, 5], "octree": [2, 50],
         "sharding": "tile: interleaved 8-row bands, rank = band %% %d, scene replicated, no collective" % n_gpus,
-        "two_stream_halves": "off for every N (one code path for 1 and N GPUs)",
+        "batches_in_flight": "3 (library default, the same for every N): consecutive 16-frame batches overlap on the device, frames are accumulated in frame order",
         "l2": "no flush: the working set (geometry + 27x903x903 RGBA8 textures + 1080p RGBA32F/RGBA8 images, ~230 MB) is larger than the 126 MB L2",
     }
 
@@ -304,7 +304,7 @@ def trace_roofline(okrt, host, env, device, trace_ms, trace_launches, dev_ms, se
         raise SystemExit("bench.py: gpu-raytracer_b200/libokrt_stats.so is missing (python -c 'import __graft_entry__ as g; g.build()')")
     slib = abi.load_library(stats_path)
     r = okrt.harness.Renderer(okrt, host, WIDTH, HEIGHT, envFaces=env, device=device, lib=slib)
-    r.options(maxBounces=MAX_BOUNCES, traversal=abi.TRAVERSAL_FAST, coverAllPixels=0)
+    r.options(maxBounces=MAX_BOUNCES, traversal=abi.TRAVERSAL_FAST, coverAllPixels=0, batchesInFlight=1)
     rd = host["rd"].copy()
     r.render(rd, frames=FRAMES_PER_STEP)
     r.wait_layout()
@@ -455,10 +455,24 @@ def main():
     launches = int(st["kernelLaunches"])
     fallback = int(st["fallbackSegments"])
 
+    # ---- the traversal kernel timed alone: three steps with ONE batch in flight, so that the CUDA-event pair around each
+    # traversal launch spans that kernel only (with several batches in flight other batches' kernels run inside the pair)
+    alone = None
+    if world == 1:
+        r.options(batchesInFlight=1)
+        barrier()
+        abi.check(r.L.okrt_reset_stats(r.h))
+        abi.check(r.L.okrt_render_frames(r.h, 3 * FRAMES_PER_STEP))
+        barrier()
+        sa = r.stats()
+        alone = {"dev_ms": float(sa["lastRenderMs"]), "trace_ms": float(sa["traceKernelMs"]), "trace_launches": int(sa["traceKernelLaunches"]),
+                 "segments": int(sa["raySegments"]), "steps": 3}
+        r.options(batchesInFlight=0)
+
     # ---- end-to-end arm: host constants in, result image out, every step, wall clock around the public calls.  Step k's
-    # device-to-host copy runs on the library's copy stream while step k+1's kernels run; the host waits for copy k after it
-    # has submitted step k+1 (two page-locked host images alternate).
-    pinned = [np.zeros((HEIGHT, WIDTH, 4), np.uint8) for _ in range(2)]
+    # device-to-host copy runs on the library's copy stream while the next steps' kernels run; the host waits for copy k-2
+    # after it has submitted step k (three page-locked host images in turn), so three steps are on the device at a time.
+    pinned = [np.zeros((HEIGHT, WIDTH, 4), np.uint8) for _ in range(3)]
     for buf in pinned:
         abi.check(r.L.okrt_host_register(abi.ptr(buf), buf.nbytes))           # page-locked: the D2H copy is a plain DMA
     moved = ctypes.c_uint64(0)
@@ -469,10 +483,11 @@ def main():
             abi.check(r.L.okrt_set_render_data(r.h, abi.ptr(rd)))              # H2D: 240 B of constants travel with the launches
             abi.check(r.L.okrt_render_frames(r.h, FRAMES_PER_STEP))
             # D2H: the RGBA8 result image; a tile-sharded rank moves only the row bands it owns into the shared image layout
-            abi.check(r.L.okrt_read_result_async(r.h, abi.ptr(pinned[k & 1]), ctypes.byref(moved), k & 1))
-            if k >= 1:
-                abi.check(r.L.okrt_wait_read(r.h, (k - 1) & 1))
-        abi.check(r.L.okrt_wait_read(r.h, (count - 1) & 1))
+            abi.check(r.L.okrt_read_result_async(r.h, abi.ptr(pinned[k % 3]), ctypes.byref(moved), k % 3))
+            if k >= 2:
+                abi.check(r.L.okrt_wait_read(r.h, (k - 2) % 3))
+        for k in range(max(0, count - 2), count):
+            abi.check(r.L.okrt_wait_read(r.h, k % 3))
     e2e_steps(args.warmup)                                                     # the same call sequence, untimed
     abi.check(r.L.okrt_reset_stats(r.h))
     barrier()
@@ -510,8 +525,8 @@ def main():
                 "dtype": "f32", "data": "synthetic", "config": workload_config(world), "clocks": clocks,
                 "e2e": {"value": e2e_segments / e2e_s / 1e6, "unit": UNIT, "h2d_bytes_per_step": 240 + 64,
                         "d2h_bytes_per_step": d2h_bytes,
-                        "how": "okrt_set_render_data + okrt_render_frames + okrt_read_result_async per step; the host waits for step k's image "
-                               "after submitting step k+1; %d untimed warm-up steps through the same calls" % args.warmup},
+                        "how": "okrt_set_render_data + okrt_render_frames + okrt_read_result_async per step; the host waits for step k-2's image "
+                               "after submitting step k; %d untimed warm-up steps through the same calls" % args.warmup},
                 "gpu_launches": launches,
                 "ray_segments": segments, "fallback_segments": fallback, "traversal": args.traversal,
                 "trace_kernel_ms": trace_ms, "trace_kernel_launches": trace_launches,
@@ -542,7 +557,9 @@ def main():
                               "against": "oracle (CPU restatement of RaytracerCS.hlsl): every RGBA32F accumulation word and the segment count"}
             failed = not ok
         if args.traversal == "fast":
-            line["roofline"] = trace_roofline(okrt, host, env, local_rank, trace_ms, trace_launches, dev_ms, segments, peaks)
+            line["roofline"] = trace_roofline(okrt, host, env, local_rank, alone["trace_ms"], alone["trace_launches"], alone["dev_ms"], alone["segments"], peaks)
+            line["one_batch_in_flight"] = {"ms_per_step": alone["dev_ms"] / alone["steps"], "value": alone["segments"] / (alone["dev_ms"] * 1e-3) / 1e6,
+                                           "note": "okrt_options.batchesInFlight = 1: the batches of the step run one after the other; the roofline's kernel times come from this pass"}
     r.close()
     if not args.no_configs:
         if world == 1 and rank == 0:

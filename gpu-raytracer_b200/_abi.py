@@ -47,7 +47,8 @@ SPHERE_ENTITY = np.dtype([("transform", TRANSFORM), ("material", MATERIAL), ("ra
 CAMERA = np.dtype([("position", "<f4", 3), ("rotation", "<f4", 3), ("fov", "<f4"), ("nearZ", "<f4"), ("farZ", "<f4")])
 OPTIONS = np.dtype([("maxBounces", "<u4"), ("traversal", "<u4"), ("coverAllPixels", "<u4"), ("writeAov", "<u4"),
                     ("shardMode", "<u4"), ("shardRank", "<u4"), ("shardCount", "<u4"), ("shardBandRows", "<u4"),
-                    ("frameOffset", "<u4"), ("frameStride", "<u4"), ("pipeline", "<u4"), ("reserved", "<u4", 5)])
+                    ("frameOffset", "<u4"), ("frameStride", "<u4"), ("pipeline", "<u4"), ("batchesInFlight", "<u4"),
+                    ("reserved", "<u4", 4)])
 AOV = np.dtype([("hitKind", "<u4"), ("hitIdx", "<u4"), ("triIdx", "<u4"), ("baryU", "<f4"), ("baryV", "<f4"),
                 ("distance", "<f4"), ("bbCheckCount", "<u4"), ("triCheckCount", "<u4"), ("numSegments", "<u4"),
                 ("flags", "<u4"), ("radiance", "<f4", 3), ("reserved", "<u4")])

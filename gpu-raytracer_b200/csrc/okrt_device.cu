@@ -125,17 +125,43 @@ struct RefineJob {
     std::atomic<bool> done{false};
 };
 
+/* BATCH LANES.  A batch (generate -> (trace, fallback, shade) x bounces -> accumulate over its own path state) runs on one of
+ * up to kMaxLanes streams; consecutive batches — of one okrt_render_frames call or of consecutive calls — take the lanes in turn,
+ * so that the thin late bounces of batch k run beside the full early bounces of batch k+1 (every kernel pulls its work from a
+ * device counter and makes progress with whatever share of the machine it gets).  What orders them:
+ *   - the accumulate stage of a batch waits for an event recorded on the renderer's main stream when the call began; the main
+ *     stream has by then been made to wait for every earlier batch (end of okrt_render_frames) and carries whatever else the
+ *     caller queued (result snapshots, resets, overlays): frames reach u1 in frame order, u0 is never overwritten under a reader;
+ *   - a lane's chain START waits for the main stream only after a call that may have changed what the chain reads
+ *     (`mainTouched`: every entry point except render / set_render_data / read_result_async / wait_read): the steady
+ *     render-and-read loop never serialises its batches, an edit always does.
+ * One GPU and N tile-sharded GPUs run the same code; what changes with N is only how small a 16-frame batch is. */
+constexpr int kMaxLanes = 4;
+struct BatchLane {
+    cudaStream_t stream = nullptr, streamBeside = nullptr;   /* the chain; the reference-order kernel beside the main shade launch */
+    cudaEvent_t evFork = nullptr, evJoin = nullptr;          /* chain <-> beside */
+    cudaEvent_t evDone = nullptr;                            /* after the lane's latest accumulate */
+    WavefrontBuffers wb{};                                   /* path state of the lane's batch */
+    size_t wbPaths = 0;
+    uint64_t forkSeen = 0;                                   /* generation of the main-stream fork the lane has waited for */
+};
+
 struct okrt_renderer {
     int device = 0;
-    cudaStream_t stream = nullptr;
-    cudaStream_t stream2 = nullptr;            /* second half of a wavefront batch (launchWavefront) */
+    cudaStream_t stream = nullptr;             /* main stream: uploads, reads, resets; always downstream of every batch issued */
+    BatchLane lanes[kMaxLanes];
+    uint32_t nextLane = 0;
+    int lastLane = -1;                         /* lane of the most recent batch */
+    bool mainTouched = true;                   /* the next batch's chain must wait for the main stream */
+    uint64_t forkGen = 0;
+    cudaEvent_t evMainFork = nullptr, evMainNow = nullptr;
+    unsigned long long* traceStats = nullptr;  /* OKRT_TRACE_STATS builds: 8 counters per bounce, all lanes add to it */
     cudaStream_t streamCopy = nullptr;         /* okrt_read_result_async: device-to-host copies overlap the next frames */
-    uchar4* snapshot[2] = {nullptr, nullptr};  /* result image as of the call, one per slot */
-    cudaEvent_t evSnapshot[2] = {nullptr, nullptr}, evCopied[2] = {nullptr, nullptr};
-    bool copyPending[2] = {false, false};
-    cudaEvent_t evFork = nullptr, evJoin = nullptr;
-    uint32_t* counts2 = nullptr;               /* queue counters of the second half */
+    uchar4* snapshot[OKRT_READ_SLOTS] = {};    /* result image as of the call, one per slot */
+    cudaEvent_t evSnapshot[OKRT_READ_SLOTS] = {}, evCopied[OKRT_READ_SLOTS] = {};
+    bool copyPending[OKRT_READ_SLOTS] = {};
     cudaEvent_t evStart = nullptr, evStop = nullptr;
+    bool timingPending = false;                /* evStart goes onto the lane of the call's first batch */
     std::vector<cudaEvent_t> traceEvents;      /* pairs around every traversal-kernel launch of the last render call */
     size_t traceEventsUsed = 0;
     uint32_t width = 0, height = 0;
@@ -175,8 +201,6 @@ struct okrt_renderer {
     DeviceBuffer dOwnedBands;
     DeviceBuffer ovSegments, ovKeys, ovColours, ovPixelKey;   /* okrt_draw_overlay scratch */
     okrt_layout_build layoutBuild{};            /* how the last rebuild went (okrt_get_layout_build) */
-    WavefrontBuffers wb{};                      /* path state of the wavefront pipeline (sized for width x height) */
-    size_t wbPaths = 0, wbReserve = 0;
 };
 
 namespace {
@@ -321,9 +345,10 @@ int adoptRefined(okrt_renderer* r, bool wait)
     std::shared_ptr<RefineJob> job = r->refine;
     r->refine.reset();
     if (!job->ok || job->layout.maxStackDepth > kFastStackCapacity || !job->layout.allRigid) return OKRT_OK;       /* keep the clustered tree */
-    OKRT_CUDA(cudaStreamSynchronize(r->stream));
+    OKRT_CUDA(cudaStreamSynchronize(r->stream));             /* downstream of every batch: the old layout is no longer read */
     const int rc = installHostLayout(r, job->layout, false);
     if (rc) return rc;
+    r->mainTouched = true;
     r->layoutBuild.builder = 2u;
     r->layoutBuild.refineMs = job->ms;
     return OKRT_OK;
@@ -394,167 +419,184 @@ void coveredExtent(const okrt_renderer* r, uint32_t& cw, uint32_t& ch)
     ch = r->opt.coverAllPixels ? r->height : 9u * (r->height / 9u);
 }
 
+void freeLaneBuffers(BatchLane& l)
+{
+    void* ptrs[] = {l.wb.rayO, l.wb.rayD, l.wb.radiance, l.wb.throughput, l.wb.hitA, l.wb.hitB, l.wb.queue[0], l.wb.queue[1], l.wb.counts, l.wb.fallbackQueue};
+    for (void* p : ptrs) if (p) cudaFree(p);
+    std::memset(&l.wb, 0, sizeof(l.wb));
+    l.wbPaths = 0;
+}
 void freeWavefront(okrt_renderer* r)
 {
-    void* ptrs[] = {r->wb.rayO, r->wb.rayD, r->wb.radiance, r->wb.throughput, r->wb.hitA, r->wb.hitB, r->wb.queue[0], r->wb.queue[1], r->wb.counts, r->wb.fallbackQueue, r->wb.traceStats};
-    for (void* p : ptrs) if (p) cudaFree(p);
-    std::memset(&r->wb, 0, sizeof(r->wb));
-    r->wbPaths = 0;
+    for (BatchLane& l : r->lanes) freeLaneBuffers(l);
+    if (r->traceStats) cudaFree(r->traceStats);
+    r->traceStats = nullptr;
 }
 
 constexpr uint32_t kCountWords = kMaxQueueCounts + kMaxWavefrontBounces + 2;
 
-int ensureWavefront(okrt_renderer* r, size_t paths)
+/* streams and events of a lane on first use; path state grown to `paths` (freeing waits for the device: rare, sizes repeat) */
+int ensureLane(okrt_renderer* r, BatchLane& l, size_t paths)
 {
-    if (r->wbPaths >= paths && r->wb.counts) return OKRT_OK;
-    freeWavefront(r);
-    OKRT_CUDA(cudaMalloc(&r->wb.rayO, paths * sizeof(float4)));
-    OKRT_CUDA(cudaMalloc(&r->wb.rayD, paths * sizeof(float4)));
-    OKRT_CUDA(cudaMalloc(&r->wb.radiance, paths * sizeof(float4)));
-    OKRT_CUDA(cudaMalloc(&r->wb.throughput, paths * sizeof(float4)));
-    OKRT_CUDA(cudaMalloc(&r->wb.hitA, paths * sizeof(float4)));
-    OKRT_CUDA(cudaMalloc(&r->wb.hitB, paths * sizeof(uint32_t)));
-    OKRT_CUDA(cudaMalloc(&r->wb.queue[0], paths * sizeof(uint32_t)));
-    OKRT_CUDA(cudaMalloc(&r->wb.queue[1], paths * sizeof(uint32_t)));
-    OKRT_CUDA(cudaMalloc(&r->wb.fallbackQueue, paths * sizeof(uint32_t)));
-    OKRT_CUDA(cudaMalloc(&r->wb.traceStats, 8 * (kMaxWavefrontBounces + 2) * sizeof(unsigned long long)));
-    OKRT_CUDA(cudaMemsetAsync(r->wb.traceStats, 0, 8 * (kMaxWavefrontBounces + 2) * sizeof(unsigned long long), r->stream));
-    OKRT_CUDA(cudaMalloc(&r->wb.counts, kCountWords * sizeof(uint32_t)));
-    r->wb.fallbackCounts = r->wb.counts + kMaxQueueCounts;
-    r->wbPaths = paths;
+    if (!l.stream) {
+        OKRT_CUDA(cudaStreamCreateWithFlags(&l.stream, cudaStreamNonBlocking));
+        OKRT_CUDA(cudaStreamCreateWithFlags(&l.streamBeside, cudaStreamNonBlocking));
+        OKRT_CUDA(cudaEventCreateWithFlags(&l.evFork, cudaEventDisableTiming));
+        OKRT_CUDA(cudaEventCreateWithFlags(&l.evJoin, cudaEventDisableTiming));
+        OKRT_CUDA(cudaEventCreateWithFlags(&l.evDone, cudaEventDisableTiming));
+    }
+    if (!r->traceStats) {
+        OKRT_CUDA(cudaMalloc(&r->traceStats, 8 * (kMaxWavefrontBounces + 2) * sizeof(unsigned long long)));
+        OKRT_CUDA(cudaMemset(r->traceStats, 0, 8 * (kMaxWavefrontBounces + 2) * sizeof(unsigned long long)));
+    }
+    if (l.wbPaths >= paths && l.wb.counts) { l.wb.traceStats = r->traceStats; return OKRT_OK; }
+    freeLaneBuffers(l);
+    OKRT_CUDA(cudaMalloc(&l.wb.rayO, paths * sizeof(float4)));
+    OKRT_CUDA(cudaMalloc(&l.wb.rayD, paths * sizeof(float4)));
+    OKRT_CUDA(cudaMalloc(&l.wb.radiance, paths * sizeof(float4)));
+    OKRT_CUDA(cudaMalloc(&l.wb.throughput, paths * sizeof(float4)));
+    OKRT_CUDA(cudaMalloc(&l.wb.hitA, paths * sizeof(float4)));
+    OKRT_CUDA(cudaMalloc(&l.wb.hitB, paths * sizeof(uint32_t)));
+    OKRT_CUDA(cudaMalloc(&l.wb.queue[0], paths * sizeof(uint32_t)));
+    OKRT_CUDA(cudaMalloc(&l.wb.queue[1], paths * sizeof(uint32_t)));
+    OKRT_CUDA(cudaMalloc(&l.wb.fallbackQueue, paths * sizeof(uint32_t)));
+    OKRT_CUDA(cudaMalloc(&l.wb.counts, kCountWords * sizeof(uint32_t)));
+    l.wb.fallbackCounts = l.wb.counts + kMaxQueueCounts;
+    l.wb.traceStats = r->traceStats;
+    l.wbPaths = paths;
     return OKRT_OK;
 }
 
-/* generate -> (trace, shade) x (maxBounces + 1) -> accumulate, for `fp.batchFrames` frames at once; queue sizes
- * stay on the device, nothing syncs with the host */
-int launchWavefront(okrt_renderer* r, const FrameParams& fpWhole, bool instrumented)
+/* how many batches may be in flight: okrt_options::batchesInFlight (0 = default), OKRT_LANES overrides (tuning) */
+int laneCount(const okrt_renderer* r)
 {
-    const size_t slots = (size_t)fpWhole.numTiles * kTilePixels;
-    const size_t paths = slots * fpWhole.batchFrames;
-    int rc = ensureWavefront(r, std::max(paths, r->wbReserve));
+    static const int env = [] { const char* e = std::getenv("OKRT_LANES"); return e ? std::atoi(e) : 0; }();
+    int n = env > 0 ? env : (r->opt.batchesInFlight ? (int)r->opt.batchesInFlight : 3);
+    return std::max(1, std::min(kMaxLanes, n));
+}
+
+/* Takes the next lane for a batch and orders its chain after the main stream where that is needed (see BatchLane).  `serial`:
+ * the batch may not overlap with anything (instrumented runs share the AOV image, the megakernel adds to u1 itself). */
+int beginBatch(okrt_renderer* r, size_t paths, bool serial, BatchLane*& out)
+{
+    const int count = serial ? 1 : laneCount(r);
+    if (r->nextLane >= (uint32_t)count) r->nextLane = 0;
+    BatchLane& l = r->lanes[serial ? 0 : r->nextLane];
+    if (!serial) r->nextLane = (r->nextLane + 1u) % (uint32_t)count;
+    int rc = ensureLane(r, l, paths);
     if (rc) return rc;
-    const DeviceScene scene = sceneView(r);
-    /* Optional (OKRT_DUAL_MIN_FRAMES=n; 0 = off): two halves of the batch on two streams, each its own chain
-     * generate -> (trace, fallback, shade) x bounces over its own slice of the path state, so that kernel tails, the
-     * fallback launches and the launch gaps of one half are filled by the other half's kernels (every kernel pulls its
-     * work from a device counter, so it makes progress with whatever share of the machine it gets).  The frames are
-     * still added to u1 in frame order by ONE accumulateKernel over both slices, so results do not change (GPU parity
-     * suite green with it).  Measured +2.1 % (2541 -> 2595 Mrays/s, profiles/r1_k_experiments.txt); off by default on a single GPU
-     * because the CUDA-event pairs around the traversal launches then overlap with the other half's kernels and the
-     * per-kernel time bench.py's roofline is built on loses its meaning. */
-    static const int dualEnv = [] { const char* e = std::getenv("OKRT_DUAL_MIN_FRAMES"); return e ? std::atoi(e) : -1; }();
-    /* default: off for every shard count, so that one GPU and N tile-sharded GPUs run the same code path (round 1 had it on for
-     * sharded ranks only: 8 GPUs 19 667 -> 20 102 Mrays/s device-timed, which flattered the scaling curve) */
-    const int dualMin = dualEnv >= 0 ? dualEnv : 0;
-    const bool dual = !instrumented && fpWhole.traversal != OKRT_TRAVERSAL_EXACT && dualMin > 0 && fpWhole.batchFrames >= (uint32_t)dualMin &&
-                      fpWhole.batchFrames >= 2u && r->stream2 != nullptr;
-    const int halves = dual ? 2 : 1;
-    FrameParams fpH[2] = {fpWhole, fpWhole};
-    WavefrontBuffers wbH[2] = {r->wb, r->wb};
-    cudaStream_t st[2] = {r->stream, r->stream2};
-    if (dual) {
-        const uint32_t framesA = (fpWhole.batchFrames + 1u) / 2u;
-        const size_t off = slots * framesA;
-        fpH[0].batchFrames = framesA;
-        fpH[1].batchFrames = fpWhole.batchFrames - framesA;
-        fpH[1].seedFrame = fpWhole.seedFrame + framesA * fpWhole.seedStride;
-        WavefrontBuffers& w = wbH[1];
-        w.rayO += off; w.rayD += off; w.radiance += off; w.throughput += off; w.hitA += off; w.hitB += off;
-        w.queue[0] += off; w.queue[1] += off; w.fallbackQueue += off;
-        w.counts = r->counts2; w.fallbackCounts = r->counts2 + kMaxQueueCounts;
-        OKRT_CUDA(cudaEventRecord(r->evFork, r->stream));
-        OKRT_CUDA(cudaStreamWaitEvent(r->stream2, r->evFork, 0));
+    if (r->mainTouched) {
+        r->forkGen++;
+        OKRT_CUDA(cudaEventRecord(r->evMainFork, r->stream));
+        r->mainTouched = false;
     }
+    if (serial) {                      /* after everything issued so far (the main stream is downstream of every batch) */
+        OKRT_CUDA(cudaEventRecord(r->evMainFork, r->stream));
+        OKRT_CUDA(cudaStreamWaitEvent(l.stream, r->evMainFork, 0));
+        l.forkSeen = r->forkGen;
+    } else if (l.forkSeen != r->forkGen) {
+        OKRT_CUDA(cudaStreamWaitEvent(l.stream, r->evMainFork, 0));
+        l.forkSeen = r->forkGen;
+    }
+    out = &l;
+    return OKRT_OK;
+}
+
+/* the batch's writes to u1 / u0 come after everything on the main stream as of now */
+int gateAccumulate(okrt_renderer* r, BatchLane& l)
+{
+    OKRT_CUDA(cudaEventRecord(r->evMainNow, r->stream));
+    OKRT_CUDA(cudaStreamWaitEvent(l.stream, r->evMainNow, 0));
+    return OKRT_OK;
+}
+
+/* the main stream waits for the batch: whatever the caller queues next sees its images */
+int endBatch(okrt_renderer* r, BatchLane& l)
+{
+    OKRT_CUDA(cudaEventRecord(l.evDone, l.stream));
+    OKRT_CUDA(cudaStreamWaitEvent(r->stream, l.evDone, 0));
+    r->lastLane = (int)(&l - r->lanes);
+    return OKRT_OK;
+}
+
+/* generate -> (trace, fallback, shade) x (maxBounces + 1) -> accumulate, for `fp.batchFrames` frames at once, on the next batch
+ * lane; queue sizes stay on the device, nothing syncs with the host */
+int launchWavefront(okrt_renderer* r, const FrameParams& fp, bool instrumented)
+{
+    const size_t slots = (size_t)fp.numTiles * kTilePixels;
+    const size_t paths = slots * fp.batchFrames;
+    BatchLane* lanePtr = nullptr;
+    int rc = beginBatch(r, paths, instrumented, lanePtr);
+    if (rc) return rc;
+    BatchLane& lane = *lanePtr;
+    const WavefrontBuffers& wb = lane.wb;
+    cudaStream_t st = lane.stream;
+    const DeviceScene scene = sceneView(r);
     const char* shadeWaves = std::getenv("OKRT_SHADE_WAVES");     /* tuning knob: resident-block multiples per SM */
     static const int traceBlocksEnv = [] { const char* e = std::getenv("OKRT_TRACE_BLOCKS"); return e ? std::max(1, std::atoi(e)) : 1 << 20; }();
     static const int shadeBlocksEnv = [] { const char* e = std::getenv("OKRT_SHADE_BLOCKS"); return e ? std::max(1, std::atoi(e)) : 0; }();
-    unsigned flatGridH[2], traceGridH[2], wideGridH[2], shadeGridH[2], fallbackGridH[2];
-    for (int h = 0; h < halves; h++) {
-        const size_t pathsH = slots * fpH[h].batchFrames;
-        flatGridH[h] = (unsigned)((pathsH + 127) / 128);
-        traceGridH[h] = std::min<unsigned>((unsigned)(r->numSms * std::min(r->blocksPerSmTrace, traceBlocksEnv)), std::max(1u, flatGridH[h]));
-        wideGridH[h] = std::min<unsigned>((unsigned)(r->numSms * std::min(r->blocksPerSmWide, traceBlocksEnv)), std::max(1u, flatGridH[h]));
-        shadeGridH[h] = std::min<unsigned>((unsigned)(r->numSms * OKRT_SHADE_MIN_BLOCKS * (shadeWaves ? std::max(1, std::atoi(shadeWaves)) : 16)),
-                                           std::max(1u, flatGridH[h]));
-        if (shadeBlocksEnv) shadeGridH[h] = std::min<unsigned>((unsigned)(r->numSms * shadeBlocksEnv), std::max(1u, flatGridH[h]));
-        fallbackGridH[h] = std::min<unsigned>((unsigned)(r->numSms * 8), std::max(1u, flatGridH[h]));   /* 4 rays (warps) per block */
-        OKRT_CUDA(cudaMemsetAsync(wbH[h].counts, 0, kCountWords * sizeof(uint32_t), st[h]));
-        generateKernel<<<flatGridH[h], 128, 0, st[h]>>>(fpH[h], wbH[h]);
-        r->launches++;
-    }
-    static const bool serialTrace = [] { const char* e = std::getenv("OKRT_DUAL_SERIAL_TRACE"); return e ? std::atoi(e) != 0 : true; }();
-    cudaEvent_t lastTraceEnd = nullptr;
-    for (uint32_t b = 0; b <= fpWhole.maxBounces; b++) {
-        for (int h = 0; h < halves; h++) {
-            const FrameParams& fp = fpH[h];
-            const WavefrontBuffers& wb = wbH[h];
-            const uint32_t* qin = wb.queue[b & 1u];
-            uint32_t* qout = wb.queue[(b + 1u) & 1u];
-            if (fp.traversal == OKRT_TRAVERSAL_EXACT) traceExactKernel<<<flatGridH[h], 128, 0, st[h]>>>(scene, fp, wb, qin, b);
-            else {
-                cudaEvent_t e0 = nullptr, e1 = nullptr;
-                if (r->traceEventsUsed + 2 > r->traceEvents.size()) {
-                    r->traceEvents.resize(r->traceEventsUsed + 2, nullptr);
-                    OKRT_CUDA(cudaEventCreate(&r->traceEvents[r->traceEventsUsed]));
-                    OKRT_CUDA(cudaEventCreate(&r->traceEvents[r->traceEventsUsed + 1]));
-                }
-                e0 = r->traceEvents[r->traceEventsUsed]; e1 = r->traceEvents[r->traceEventsUsed + 1];
-                r->traceEventsUsed += 2;
-                /* the traversal kernels of the two halves take turns (each waits for the other half's previous one), so an
-                 * event pair never spans another traversal kernel; what overlaps with it is the other half's shade /
-                 * fallback / generate work */
-                if (dual && serialTrace && lastTraceEnd) OKRT_CUDA(cudaStreamWaitEvent(st[h], lastTraceEnd, 0));
-                OKRT_CUDA(cudaEventRecord(e0, st[h]));
-                if (fp.traversal == OKRT_TRAVERSAL_WIDE) traceWideKernel<<<wideGridH[h], kTraceBlockThreads, 0, st[h]>>>(scene, fp, wb, qin, b);
-                else traceFastKernel<<<traceGridH[h], kTraceBlockThreads, 0, st[h]>>>(scene, fp, wb, qin, b);
-                OKRT_CUDA(cudaEventRecord(e1, st[h]));
-                lastTraceEnd = e1;
-                /* The reference-order kernel decides a few hundred rays per launch and lasts one bounded traversal (~100 us of
-                 * dependent loads): on a second stream it runs BESIDE the main shade launch, which skips its paths (kHitPending);
-                 * a late shade launch over the fallback queue follows.  (Two-stream halves keep everything on the half's stream.) */
-                const bool beside = !dual && r->stream2 != nullptr;
-                if (beside) {
-                    OKRT_CUDA(cudaEventRecord(r->evFork, st[h]));
-                    OKRT_CUDA(cudaStreamWaitEvent(r->stream2, r->evFork, 0));
-                    traceFallbackKernel<<<fallbackGridH[h], 128, 0, r->stream2>>>(scene, fp, wb, b);
-                    OKRT_CUDA(cudaEventRecord(r->evJoin, r->stream2));
-                } else traceFallbackKernel<<<fallbackGridH[h], 128, 0, st[h]>>>(scene, fp, wb, b);
-                r->launches++;
-                if (instrumented) shadeKernel<true><<<shadeGridH[h], 128, 0, st[h]>>>(scene, fp, wb, qin, qout, b, 0u);
-                else shadeKernel<false><<<shadeGridH[h], 128, 0, st[h]>>>(scene, fp, wb, qin, qout, b, 0u);
-                if (beside) OKRT_CUDA(cudaStreamWaitEvent(st[h], r->evJoin, 0));
-                if (instrumented) shadeKernel<true><<<fallbackGridH[h], 128, 0, st[h]>>>(scene, fp, wb, qin, qout, b, 1u);
-                else shadeKernel<false><<<fallbackGridH[h], 128, 0, st[h]>>>(scene, fp, wb, qin, qout, b, 1u);
-                r->launches += 3;                              /* traversal, main shade, late shade (+ the fallback above) */
-                continue;
-            }
-            if (instrumented) shadeKernel<true><<<shadeGridH[h], 128, 0, st[h]>>>(scene, fp, wb, qin, qout, b, 0u);
-            else shadeKernel<false><<<shadeGridH[h], 128, 0, st[h]>>>(scene, fp, wb, qin, qout, b, 0u);
+    const unsigned flatGrid = (unsigned)((paths + 127) / 128);
+    const unsigned traceGrid = std::min<unsigned>((unsigned)(r->numSms * std::min(r->blocksPerSmTrace, traceBlocksEnv)), std::max(1u, flatGrid));
+    const unsigned wideGrid = std::min<unsigned>((unsigned)(r->numSms * std::min(r->blocksPerSmWide, traceBlocksEnv)), std::max(1u, flatGrid));
+    unsigned shadeGrid = std::min<unsigned>((unsigned)(r->numSms * OKRT_SHADE_MIN_BLOCKS * (shadeWaves ? std::max(1, std::atoi(shadeWaves)) : 16)), std::max(1u, flatGrid));
+    if (shadeBlocksEnv) shadeGrid = std::min<unsigned>((unsigned)(r->numSms * shadeBlocksEnv), std::max(1u, flatGrid));
+    const unsigned fallbackGrid = std::min<unsigned>((unsigned)(r->numSms * 8), std::max(1u, flatGrid));   /* 4 rays (warps) per block */
+    if (r->timingPending) { OKRT_CUDA(cudaEventRecord(r->evStart, st)); r->timingPending = false; }
+    OKRT_CUDA(cudaMemsetAsync(wb.counts, 0, kCountWords * sizeof(uint32_t), st));
+    generateKernel<<<flatGrid, 128, 0, st>>>(fp, wb);
+    r->launches++;
+    for (uint32_t b = 0; b <= fp.maxBounces; b++) {
+        const uint32_t* qin = wb.queue[b & 1u];
+        uint32_t* qout = wb.queue[(b + 1u) & 1u];
+        if (fp.traversal == OKRT_TRAVERSAL_EXACT) {
+            traceExactKernel<<<flatGrid, 128, 0, st>>>(scene, fp, wb, qin, b);
+            if (instrumented) shadeKernel<true><<<shadeGrid, 128, 0, st>>>(scene, fp, wb, qin, qout, b, 0u);
+            else shadeKernel<false><<<shadeGrid, 128, 0, st>>>(scene, fp, wb, qin, qout, b, 0u);
             r->launches += 2;
+            continue;
         }
+        if (r->traceEventsUsed + 2 > r->traceEvents.size()) {
+            r->traceEvents.resize(r->traceEventsUsed + 2, nullptr);
+            OKRT_CUDA(cudaEventCreate(&r->traceEvents[r->traceEventsUsed]));
+            OKRT_CUDA(cudaEventCreate(&r->traceEvents[r->traceEventsUsed + 1]));
+        }
+        cudaEvent_t e0 = r->traceEvents[r->traceEventsUsed], e1 = r->traceEvents[r->traceEventsUsed + 1];
+        r->traceEventsUsed += 2;
+        OKRT_CUDA(cudaEventRecord(e0, st));
+        if (fp.traversal == OKRT_TRAVERSAL_WIDE) traceWideKernel<<<wideGrid, kTraceBlockThreads, 0, st>>>(scene, fp, wb, qin, b);
+        else traceFastKernel<<<traceGrid, kTraceBlockThreads, 0, st>>>(scene, fp, wb, qin, b);
+        OKRT_CUDA(cudaEventRecord(e1, st));
+        /* The reference-order kernel decides a few hundred rays per launch and lasts one bounded traversal (~100 us of
+         * dependent loads): on the lane's second stream it runs BESIDE the main shade launch, which skips its paths (kHitPending);
+         * a late shade launch over the fallback queue follows. */
+        OKRT_CUDA(cudaEventRecord(lane.evFork, st));
+        OKRT_CUDA(cudaStreamWaitEvent(lane.streamBeside, lane.evFork, 0));
+        traceFallbackKernel<<<fallbackGrid, 128, 0, lane.streamBeside>>>(scene, fp, wb, b);
+        OKRT_CUDA(cudaEventRecord(lane.evJoin, lane.streamBeside));
+        if (instrumented) shadeKernel<true><<<shadeGrid, 128, 0, st>>>(scene, fp, wb, qin, qout, b, 0u);
+        else shadeKernel<false><<<shadeGrid, 128, 0, st>>>(scene, fp, wb, qin, qout, b, 0u);
+        OKRT_CUDA(cudaStreamWaitEvent(st, lane.evJoin, 0));
+        if (instrumented) shadeKernel<true><<<fallbackGrid, 128, 0, st>>>(scene, fp, wb, qin, qout, b, 1u);
+        else shadeKernel<false><<<fallbackGrid, 128, 0, st>>>(scene, fp, wb, qin, qout, b, 1u);
+        r->launches += 4;                                  /* traversal, fallback, main shade, late shade */
     }
-    if (dual) {
-        OKRT_CUDA(cudaEventRecord(r->evJoin, r->stream2));
-        OKRT_CUDA(cudaStreamWaitEvent(r->stream, r->evJoin, 0));
-    }
-    accumulateKernel<<<(unsigned)((slots + 127) / 128), 128, 0, r->stream>>>(fpWhole, r->wb);
+    if ((rc = gateAccumulate(r, lane))) return rc;
+    accumulateKernel<<<(unsigned)((slots + 127) / 128), 128, 0, st>>>(fp, wb);
     r->launches++;
     OKRT_CUDA(cudaGetLastError());
-    if (std::getenv("OKRT_DEBUG_COUNTS")) {          /* diagnostic: rays per bounce of this batch (of each half) */
-        const FrameParams& fp = fpWhole;
-        for (int half = 0; half < halves; half++) {
-            std::vector<uint32_t> h(kCountWords);
-            cudaMemcpyAsync(h.data(), wbH[half].counts, kCountWords * sizeof(uint32_t), cudaMemcpyDeviceToHost, r->stream);
-            cudaStreamSynchronize(r->stream);
-            std::fprintf(stderr, "okrt: batch of %u frames, rays per bounce:", fpH[half].batchFrames);
-            for (uint32_t b = 0; b <= fp.maxBounces; b++) std::fprintf(stderr, " %u(fb %u)", h[2 * b], h[kMaxQueueCounts + b]);
-            std::fprintf(stderr, "\n");
-        }
+    if ((rc = endBatch(r, lane))) return rc;
+    if (std::getenv("OKRT_DEBUG_COUNTS")) {          /* diagnostic: rays per bounce of this batch */
+        std::vector<uint32_t> h(kCountWords);
+        cudaMemcpyAsync(h.data(), wb.counts, kCountWords * sizeof(uint32_t), cudaMemcpyDeviceToHost, st);
+        cudaStreamSynchronize(st);
+        std::fprintf(stderr, "okrt: batch of %u frames, rays per bounce:", fp.batchFrames);
+        for (uint32_t b = 0; b <= fp.maxBounces; b++) std::fprintf(stderr, " %u(fb %u)", h[2 * b], h[kMaxQueueCounts + b]);
+        std::fprintf(stderr, "\n");
 #ifdef OKRT_TRACE_STATS
-        std::vector<unsigned long long> st(8 * (fp.maxBounces + 1));
-        cudaMemcpy(st.data(), r->wb.traceStats, st.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+        std::vector<unsigned long long> ts(8 * (fp.maxBounces + 1));
+        cudaMemcpy(ts.data(), r->traceStats, ts.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
         for (uint32_t b = 0; b <= fp.maxBounces; b++) {
-            const unsigned long long* t = &st[8 * b];
+            const unsigned long long* t = &ts[8 * b];
             const double rays = (double)std::max(1ull, t[0]);
             std::fprintf(stderr, "  bounce %u (since reset): rays %llu  node steps/ray %.2f  leaf entries/ray %.2f  triangle tests/ray %.2f  lanes per node iteration %.1f  per triangle iteration %.1f\n",
                          b, t[0], t[1] / rays, t[2] / rays, t[3] / rays, (double)t[6] / std::max(1ull, t[4]), (double)t[7] / std::max(1ull, t[5]));
@@ -570,27 +612,47 @@ int launchWavefront(okrt_renderer* r, const FrameParams& fpWhole, bool instrumen
 constexpr uint32_t kMaxBatchFrames = 128;
 constexpr size_t kMaxBatchPaths = (size_t)1 << 25;
 
-int launchFrames(okrt_renderer* r, uint32_t want, uint32_t& done)
+/* how many of `want` frames the next batch takes, and the pixel slots of one frame (this handle's share of the 8-row bands
+ * under tile sharding) */
+uint32_t planBatch(const okrt_renderer* r, uint32_t want, size_t& slotsPerFrame)
 {
-    done = 1u;
     const bool instrumentedRun = r->opt.writeAov != 0u || r->rd.debugMode != 0u;
     const bool wavefront = r->opt.pipeline == OKRT_PIPELINE_WAVEFRONT && r->opt.maxBounces <= kMaxWavefrontBounces;
-    /* pixel slots this handle traces per frame (its share of the 8-row bands under tile sharding) */
     uint32_t ownedRows = r->height;
     if (r->opt.shardMode == OKRT_SHARD_TILE && r->opt.shardCount > 1u) {
         const uint32_t band = r->opt.shardBandRows ? r->opt.shardBandRows : 8u;
         const uint32_t bands = (r->height + band - 1u) / band;
         ownedRows = (r->ownedBands.empty() ? bands / r->opt.shardCount + ((bands % r->opt.shardCount) > r->opt.shardRank ? 1u : 0u) : (uint32_t)r->ownedBands.size()) * band;
     }
-    const size_t slotsPerFrame = (size_t)((r->width + kTileW - 1) / kTileW) * ((ownedRows + kTileH - 1) / kTileH) * kTilePixels;
-    r->wbReserve = slotsPerFrame;
-    if (wavefront && !instrumentedRun && r->rd.accumulationEnabled == 1u) {
-        const size_t most = std::max<size_t>(1, std::min<size_t>(kMaxBatchFrames, kMaxBatchPaths / std::max<size_t>(slotsPerFrame, 1)));
-        /* split `want` into equal batches rather than full ones and a small remainder */
-        const size_t batches = (want + most - 1) / most;
-        done = (uint32_t)((want + batches - 1) / batches);
-        r->wbReserve = slotsPerFrame * most;          /* allocate for the largest batch at once: no re-allocation between batches */
+    slotsPerFrame = (size_t)((r->width + kTileW - 1) / kTileW) * ((ownedRows + kTileH - 1) / kTileH) * kTilePixels;
+    if (!(wavefront && !instrumentedRun && r->rd.accumulationEnabled == 1u)) return 1u;
+    const size_t most = std::max<size_t>(1, std::min<size_t>(kMaxBatchFrames, kMaxBatchPaths / std::max<size_t>(slotsPerFrame, 1)));
+    /* split `want` into equal batches rather than full ones and a small remainder */
+    const size_t batches = (want + most - 1) / most;
+    return (uint32_t)((want + batches - 1) / batches);
+}
+
+/* path state of the lanes this call will use, before its first kernel: growing a lane frees memory, which waits for the device */
+int presizeLanes(okrt_renderer* r, uint32_t frames)
+{
+    if (!(r->opt.pipeline == OKRT_PIPELINE_WAVEFRONT && r->opt.maxBounces <= kMaxWavefrontBounces) || !frames) return OKRT_OK;
+    if (r->opt.writeAov != 0u || r->rd.debugMode != 0u) return OKRT_OK;
+    size_t slotsPerFrame = 0;
+    const uint32_t done = planBatch(r, frames, slotsPerFrame);
+    const uint32_t batches = (frames + done - 1u) / done;
+    const int count = laneCount(r);
+    const uint32_t first = r->nextLane >= (uint32_t)count ? 0u : r->nextLane;
+    for (uint32_t i = 0; i < std::min<uint32_t>(batches, (uint32_t)count); i++) {
+        const int rc = ensureLane(r, r->lanes[(first + i) % (uint32_t)count], slotsPerFrame * done);
+        if (rc) return rc;
     }
+    return OKRT_OK;
+}
+
+int launchFrames(okrt_renderer* r, uint32_t want, uint32_t& done)
+{
+    size_t slotsPerFrame = 0;
+    done = planBatch(r, want, slotsPerFrame);
     /* updateBuffers: the counter advances before the constants are uploaded (RayTracer.cpp:489) */
     const uint32_t firstLocalFrame = r->rd.numAccumulationFrames + r->rd.accumulationEnabled;
     r->rd.numAccumulationFrames += r->rd.accumulationEnabled * done;
@@ -636,24 +698,37 @@ int launchFrames(okrt_renderer* r, uint32_t want, uint32_t& done)
     fp.tilesX = (r->width + kTileW - 1) / kTileW;
     fp.numTiles = fp.tilesX * ((rows + kTileH - 1) / kTileH);
     fp.workCounter = reinterpret_cast<uint32_t*>(r->counters + 3);
-    OKRT_CUDA(cudaMemsetAsync(fp.workCounter, 0, sizeof(unsigned long long), r->stream));
     if (r->opt.pipeline == OKRT_PIPELINE_WAVEFRONT && fp.maxBounces <= kMaxWavefrontBounces) return launchWavefront(r, fp, instrumented);
+    /* the megakernel adds to u1 itself: a serial batch on lane 0, after everything issued so far */
+    BatchLane* lane = nullptr;
+    int rc = beginBatch(r, 1, true, lane);
+    if (rc) return rc;
+    if (r->timingPending) { OKRT_CUDA(cudaEventRecord(r->evStart, lane->stream)); r->timingPending = false; }
+    OKRT_CUDA(cudaMemsetAsync(fp.workCounter, 0, sizeof(unsigned long long), lane->stream));
     const int blocksPerSm = instrumented ? r->blocksPerSmInstrumented : r->blocksPerSmLean;
     const unsigned wantBlocks = (unsigned)((fp.numTiles * (uint32_t)kTilePixels + kBlockThreads - 1) / kBlockThreads);
     const unsigned grid = std::min<unsigned>((unsigned)(r->numSms * blocksPerSm), std::max(1u, wantBlocks));
-    if (instrumented) pathTraceKernel<true><<<grid, kBlockThreads, 0, r->stream>>>(sceneView(r), fp);
-    else pathTraceKernel<false><<<grid, kBlockThreads, 0, r->stream>>>(sceneView(r), fp);
+    if (instrumented) pathTraceKernel<true><<<grid, kBlockThreads, 0, lane->stream>>>(sceneView(r), fp);
+    else pathTraceKernel<false><<<grid, kBlockThreads, 0, lane->stream>>>(sceneView(r), fp);
     r->launches++;
     OKRT_CUDA(cudaGetLastError());
-    return OKRT_OK;
+    return endBatch(r, *lane);
 }
 
-int checkHandle(const okrt_renderer* r, const char* fn)
+/* the steady loop's calls (render, set_render_data, read_result_async, wait_read): queue nothing a batch's chain reads */
+int checkHandleQuiet(const okrt_renderer* r, const char* fn)
 {
     if (!r) { setError(std::string(fn) + ": null renderer"); return OKRT_ERR_INVALID_ARGUMENT; }
     cudaError_t e = cudaSetDevice(r->device);
     if (e != cudaSuccess) { setError(std::string(fn) + ": cudaSetDevice: " + cudaGetErrorString(e)); return OKRT_ERR_CUDA; }
     return OKRT_OK;
+}
+/* every other entry point may queue work on the main stream that the next batch has to see from its first kernel on */
+int checkHandle(const okrt_renderer* r, const char* fn)
+{
+    const int rc = checkHandleQuiet(r, fn);
+    if (!rc) const_cast<okrt_renderer*>(r)->mainTouched = true;
+    return rc;
 }
 
 /* rows of the result this handle owns, as contiguous byte runs of the image (a strided family + extra runs) */
@@ -730,10 +805,8 @@ int okrt_create(int device, uint32_t width, uint32_t height, okrt_renderer** out
     r->rd.textureDims[0] = width; r->rd.textureDims[1] = height;
     cudaError_t e;
     if ((e = cudaStreamCreateWithFlags(&r->stream, cudaStreamNonBlocking)) != cudaSuccess ||
-        (e = cudaStreamCreateWithFlags(&r->stream2, cudaStreamNonBlocking)) != cudaSuccess ||
-        (e = cudaEventCreateWithFlags(&r->evFork, cudaEventDisableTiming)) != cudaSuccess ||
-        (e = cudaEventCreateWithFlags(&r->evJoin, cudaEventDisableTiming)) != cudaSuccess ||
-        (e = cudaMalloc(&r->counts2, kCountWords * sizeof(uint32_t))) != cudaSuccess ||
+        (e = cudaEventCreateWithFlags(&r->evMainFork, cudaEventDisableTiming)) != cudaSuccess ||
+        (e = cudaEventCreateWithFlags(&r->evMainNow, cudaEventDisableTiming)) != cudaSuccess ||
         (e = cudaEventCreate(&r->evStart)) != cudaSuccess || (e = cudaEventCreate(&r->evStop)) != cudaSuccess ||
         (e = cudaMalloc(&r->counters, 4 * sizeof(unsigned long long))) != cudaSuccess ||
         (e = cudaMemsetAsync(r->counters, 0, 4 * sizeof(unsigned long long), r->stream)) != cudaSuccess) {
@@ -775,8 +848,11 @@ void okrt_destroy(okrt_renderer* r)
 {
     if (!r) return;
     cudaSetDevice(r->device);
+    for (BatchLane& l : r->lanes) {
+        if (l.stream) cudaStreamSynchronize(l.stream);
+        if (l.streamBeside) cudaStreamSynchronize(l.streamBeside);
+    }
     if (r->stream) cudaStreamSynchronize(r->stream);
-    if (r->stream2) cudaStreamSynchronize(r->stream2);
     r->triPos.release(); r->triInfo.release(); r->shadeInfo.release(); r->bvhNodes.release(); r->octNodes.release(); r->spheres.release();
     r->instances.release(); r->dirLights.release(); r->pointLights.release(); r->spotLights.release();
     if (r->fastTrisTex) { cudaDestroyTextureObject(r->fastTrisTex); r->fastTrisTex = 0; }
@@ -792,16 +868,21 @@ void okrt_destroy(okrt_renderer* r)
     for (cudaEvent_t e : r->traceEvents) if (e) cudaEventDestroy(e);
     if (r->evStart) cudaEventDestroy(r->evStart);
     if (r->evStop) cudaEventDestroy(r->evStop);
-    if (r->evFork) cudaEventDestroy(r->evFork);
-    if (r->evJoin) cudaEventDestroy(r->evJoin);
-    if (r->counts2) cudaFree(r->counts2);
-    for (int k = 0; k < 2; k++) {
+    if (r->evMainFork) cudaEventDestroy(r->evMainFork);
+    if (r->evMainNow) cudaEventDestroy(r->evMainNow);
+    for (BatchLane& l : r->lanes) {
+        if (l.evFork) cudaEventDestroy(l.evFork);
+        if (l.evJoin) cudaEventDestroy(l.evJoin);
+        if (l.evDone) cudaEventDestroy(l.evDone);
+        if (l.streamBeside) cudaStreamDestroy(l.streamBeside);
+        if (l.stream) cudaStreamDestroy(l.stream);
+    }
+    for (int k = 0; k < OKRT_READ_SLOTS; k++) {
         if (r->snapshot[k]) cudaFree(r->snapshot[k]);
         if (r->evSnapshot[k]) cudaEventDestroy(r->evSnapshot[k]);
         if (r->evCopied[k]) cudaEventDestroy(r->evCopied[k]);
     }
     if (r->streamCopy) { cudaStreamSynchronize(r->streamCopy); cudaStreamDestroy(r->streamCopy); }
-    if (r->stream2) cudaStreamDestroy(r->stream2);
     if (r->stream) cudaStreamDestroy(r->stream);
     delete r;
 }
@@ -812,7 +893,7 @@ int okrt_resize(okrt_renderer* r, uint32_t width, uint32_t height)
     if (!width || !height) { setError("okrt_resize: zero extent"); return OKRT_ERR_INVALID_ARGUMENT; }
     OKRT_CUDA(cudaStreamSynchronize(r->stream));
     if (r->streamCopy) OKRT_CUDA(cudaStreamSynchronize(r->streamCopy));
-    for (int k = 0; k < 2; k++) { if (r->snapshot[k]) cudaFree(r->snapshot[k]); r->snapshot[k] = nullptr; r->copyPending[k] = false; }
+    for (int k = 0; k < OKRT_READ_SLOTS; k++) { if (r->snapshot[k]) cudaFree(r->snapshot[k]); r->snapshot[k] = nullptr; r->copyPending[k] = false; }
     r->width = width; r->height = height;
     r->rd.textureDims[0] = width; r->rd.textureDims[1] = height;
     r->rd.numAccumulationFrames = 0u;                        /* onResize -> resetAccumulation, RayTracer.cpp:494-501 */
@@ -966,18 +1047,20 @@ int okrt_set_options(okrt_renderer* r, const okrt_options* o)
 
 int okrt_render_frames(okrt_renderer* r, uint32_t frames)
 {
-    int rc = checkHandle(r, "okrt_render"); if (rc) return rc;
-    if (r->layoutDirty && (rc = rebuildLayout(r))) return rc;
+    int rc = checkHandleQuiet(r, "okrt_render"); if (rc) return rc;
+    if (r->layoutDirty) { r->mainTouched = true; if ((rc = rebuildLayout(r))) return rc; }
     if (r->refine && (rc = adoptRefined(r, false))) return rc;
-    if (r->opt.writeAov && (rc = ensureAov(r))) return rc;
+    if (r->opt.writeAov && !r->aov) { r->mainTouched = true; if ((rc = ensureAov(r))) return rc; }
+    if ((rc = presizeLanes(r, frames))) return rc;
     r->traceEventsUsed = 0;
-    OKRT_CUDA(cudaEventRecord(r->evStart, r->stream));
+    r->timingPending = true;                                  /* evStart: where the first batch's chain begins */
     for (uint32_t f = 0; f < frames;) {
         uint32_t done = 1u;
         if ((rc = launchFrames(r, frames - f, done))) return rc;
         f += done;
     }
-    OKRT_CUDA(cudaEventRecord(r->evStop, r->stream));
+    if (r->timingPending) { OKRT_CUDA(cudaEventRecord(r->evStart, r->stream)); r->timingPending = false; }   /* nothing was launched */
+    OKRT_CUDA(cudaEventRecord(r->evStop, r->stream));         /* the main stream waits for every batch (endBatch) */
     return OKRT_OK;
 }
 
@@ -1048,12 +1131,12 @@ int okrt_set_shard_bands(okrt_renderer* r, const uint32_t* bands, uint32_t n)
 
 int okrt_read_result_async(okrt_renderer* r, uint8_t* outRgba8, uint64_t* outBytes, uint32_t slot)
 {
-    int rc = checkHandle(r, "okrt_read_result_async"); if (rc) return rc;
-    if (!outRgba8 || slot > 1u) { setError("okrt_read_result_async: bad argument"); return OKRT_ERR_INVALID_ARGUMENT; }
+    int rc = checkHandleQuiet(r, "okrt_read_result_async"); if (rc) return rc;
+    if (!outRgba8 || slot >= OKRT_READ_SLOTS) { setError("okrt_read_result_async: bad argument"); return OKRT_ERR_INVALID_ARGUMENT; }
     const size_t imageBytes = (size_t)r->width * r->height * 4;
     if (!r->streamCopy) {
         OKRT_CUDA(cudaStreamCreateWithFlags(&r->streamCopy, cudaStreamNonBlocking));
-        for (int k = 0; k < 2; k++) {
+        for (int k = 0; k < OKRT_READ_SLOTS; k++) {
             OKRT_CUDA(cudaEventCreateWithFlags(&r->evSnapshot[k], cudaEventDisableTiming));
             OKRT_CUDA(cudaEventCreateWithFlags(&r->evCopied[k], cudaEventDisableTiming));
         }
@@ -1077,8 +1160,8 @@ int okrt_read_result_async(okrt_renderer* r, uint8_t* outRgba8, uint64_t* outByt
 
 int okrt_wait_read(okrt_renderer* r, uint32_t slot)
 {
-    int rc = checkHandle(r, "okrt_wait_read"); if (rc) return rc;
-    if (slot > 1u) { setError("okrt_wait_read: bad slot"); return OKRT_ERR_INVALID_ARGUMENT; }
+    int rc = checkHandleQuiet(r, "okrt_wait_read"); if (rc) return rc;
+    if (slot >= OKRT_READ_SLOTS) { setError("okrt_wait_read: bad slot"); return OKRT_ERR_INVALID_ARGUMENT; }
     if (!r->copyPending[slot]) return OKRT_OK;
     OKRT_CUDA(cudaEventSynchronize(r->evCopied[slot]));
     r->copyPending[slot] = false;
@@ -1434,8 +1517,8 @@ int okrt_get_trace_stats(okrt_renderer* r, uint64_t* out, uint32_t bounces)
     int rc = checkHandle(r, "okrt_get_trace_stats"); if (rc) return rc;
     if (!out || bounces > kMaxWavefrontBounces + 1) { setError("okrt_get_trace_stats: bad argument"); return OKRT_ERR_INVALID_ARGUMENT; }
 #ifdef OKRT_TRACE_STATS
-    if (!r->wb.traceStats) { std::memset(out, 0, (size_t)bounces * 8 * sizeof(uint64_t)); return OKRT_OK; }
-    OKRT_CUDA(cudaMemcpyAsync(out, r->wb.traceStats, (size_t)bounces * 8 * sizeof(uint64_t), cudaMemcpyDeviceToHost, r->stream));
+    if (!r->traceStats) { std::memset(out, 0, (size_t)bounces * 8 * sizeof(uint64_t)); return OKRT_OK; }
+    OKRT_CUDA(cudaMemcpyAsync(out, r->traceStats, (size_t)bounces * 8 * sizeof(uint64_t), cudaMemcpyDeviceToHost, r->stream));
     OKRT_CUDA(cudaStreamSynchronize(r->stream));
     return OKRT_OK;
 #else
@@ -1519,7 +1602,7 @@ int okrt_reset_stats(okrt_renderer* r)
 {
     int rc = checkHandle(r, "okrt_reset_stats"); if (rc) return rc;
     OKRT_CUDA(cudaMemsetAsync(r->counters, 0, 4 * sizeof(unsigned long long), r->stream));
-    if (r->wb.traceStats) OKRT_CUDA(cudaMemsetAsync(r->wb.traceStats, 0, 8 * (kMaxWavefrontBounces + 2) * sizeof(unsigned long long), r->stream));
+    if (r->traceStats) OKRT_CUDA(cudaMemsetAsync(r->traceStats, 0, 8 * (kMaxWavefrontBounces + 2) * sizeof(unsigned long long), r->stream));
     r->launches = 0;
     return OKRT_OK;
 }

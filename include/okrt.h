@@ -242,7 +242,10 @@ typedef struct okrt_options {
     uint32_t frameOffset;         /* sample sharding: seed frame of local frame k (1-based) is */
     uint32_t frameStride;         /*   frameOffset + (k-1)*frameStride + 1; defaults 0 / 1 */
     uint32_t pipeline;            /* OKRT_PIPELINE_*: same results, different kernel organisation */
-    uint32_t reserved[5];
+    uint32_t batchesInFlight;     /* wavefront pipeline: how many batches of frames may be on the device at once, each on its
+                                     own stream with its own path state (1..4; 0 = default 3).  Frames still reach the
+                                     accumulation image in frame order: same images for every value */
+    uint32_t reserved[4];
 } okrt_options;
 
 typedef struct okrt_aov {         /* parity tap, one per pixel (new) */
@@ -480,8 +483,11 @@ OKRT_API int okrt_read_result_owned(okrt_renderer* r, uint8_t* outRgba8, uint64_
 /* Non-blocking form: snapshots the result image as of the frames submitted so far (device-to-device, on the renderer's
  * stream) and starts the device-to-host copy of the rows this handle owns on a second stream; returns at once, so the caller
  * can submit the next okrt_render_frames while the copy runs (the reference's render() is fire-and-forget on the device queue,
- * RayTracer.cpp:219-260).  `slot` (0 or 1) names one of two snapshots; okrt_wait_read(slot) blocks until that copy has landed
- * in outRgba8, which must stay valid (and should be page-locked, okrt_host_register) until then. */
+ * RayTracer.cpp:219-260).  `slot` (0 .. OKRT_READ_SLOTS-1) names one of four snapshots; okrt_wait_read(slot) blocks until that
+ * copy has landed in outRgba8, which must stay valid (and should be page-locked, okrt_host_register) until then.  A loop that
+ * waits for step k-2's image after submitting step k (three slots in turn) keeps three batches on the device
+ * (okrt_options::batchesInFlight). */
+#define OKRT_READ_SLOTS 4
 OKRT_API int okrt_read_result_async(okrt_renderer* r, uint8_t* outRgba8, uint64_t* outBytes, uint32_t slot);
 OKRT_API int okrt_wait_read(okrt_renderer* r, uint32_t slot);
 OKRT_API int okrt_read_accumulation(okrt_renderer* r, float* outRgba32f);

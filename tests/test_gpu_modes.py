@@ -257,31 +257,95 @@ def test_cpp_mirror_on_gpu(okrt, tmp_path):
     test_cpp_mirror_builds_and_runs(okrt, tmp_path)
 
 
-_DUAL_SCRIPT = """
-import importlib, sys, numpy as np
-sys.path.insert(0, {root!r})
-from tests import helpers
-okrt = importlib.import_module("gpu-raytracer_b200")
-rm, sc, info = okrt.scenes.sponza_standin(8000, texture_size=64)
-host = helpers.build_host_side(okrt, rm, sc, info, 160, 90)
-r = helpers.Renderer(okrt, host, 160, 90, envFaces=okrt.scenes.procedural_sky_faces(32))
-r.options(maxBounces=4)
-r.render(host["rd"].copy(), frames=5)
-np.save({out!r}, r.accumulation())
-r.close()
-"""
+def _lanes_run(okrt, host, W, H, env, lanes, calls, read_every_call):
+    """`calls` = frames per okrt_render_frames call; returns u1, the RGBA8 results read after every call, the segment count."""
+    import ctypes
+    r = helpers.Renderer(okrt, host, W, H, envFaces=env)
+    r.options(maxBounces=4, batchesInFlight=lanes)
+    rd = host["rd"].copy()
+    images = []
+    pinned = [np.zeros((H, W, 4), np.uint8) for _ in range(2)]
+    moved = ctypes.c_uint64(0)
+    for k, frames in enumerate(calls):
+        rd[0]["numAccumulationFrames"] = r.L.okrt_get_num_accumulation_frames(r.h)
+        okrt.abi.check(r.L.okrt_set_render_data(r.h, okrt.abi.ptr(rd)))
+        okrt.abi.check(r.L.okrt_render_frames(r.h, frames))
+        if read_every_call:
+            okrt.abi.check(r.L.okrt_read_result_async(r.h, okrt.abi.ptr(pinned[k & 1]), ctypes.byref(moved), k & 1))
+            okrt.abi.check(r.L.okrt_wait_read(r.h, k & 1))
+            images.append(pinned[k & 1].copy())
+    acc = r.accumulation()
+    seg = int(r.stats()["raySegments"])
+    r.close()
+    return acc, images, seg
 
 
-def test_two_stream_halves_bit_identical(okrt, tmp_path):
-    """OKRT_DUAL_MIN_FRAMES (launchWavefront: the batch as two halves on two streams, one frame-ordered accumulate):
-    5 frames (halves of 3 and 2) give the same u1 bits as the single-stream batch."""
-    import os, subprocess, sys
-    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+def test_batches_in_flight_bit_identical(okrt):
+    """okrt_options::batchesInFlight (launchWavefront: consecutive batches on up to four streams, each with its own path state,
+    accumulate stages in frame order): many small calls give the same u1 bits, the same intermediate result images and the same
+    segment count with 1, 2, 3 and 4 batches in flight, and the same u1 as ONE call for all the frames."""
+    rm, sc, info = okrt.scenes.sponza_standin(8000, texture_size=64)
+    W, H = 160, 90
+    host = helpers.build_host_side(okrt, rm, sc, info, W, H)
+    env = okrt.scenes.procedural_sky_faces(32)
+    calls = [1, 2, 1, 3, 1, 1, 2, 5, 1, 1, 1, 4]
+    ref_acc, ref_images, ref_seg = _lanes_run(okrt, host, W, H, env, 1, calls, True)
+    assert ref_acc[..., 3].max() == float(sum(calls))
+    for lanes in (2, 3, 4):
+        acc, images, seg = _lanes_run(okrt, host, W, H, env, lanes, calls, True)
+        assert seg == ref_seg
+        assert np.array_equal(acc.view(np.uint32), ref_acc.view(np.uint32))
+        assert all(np.array_equal(a, b) for a, b in zip(images, ref_images))
+    acc, _, seg = _lanes_run(okrt, host, W, H, env, 0, [sum(calls)], False)
+    assert seg == ref_seg and np.array_equal(acc.view(np.uint32), ref_acc.view(np.uint32))
+
+
+def test_batches_in_flight_with_edits_between_calls(okrt):
+    """A call that changes what the kernels read or write (a light, the accumulation reset, an overwritten accumulation image,
+    an AOV frame) orders the next batch after itself, without a host synchronisation in between: same images with one batch
+    in flight and with four."""
+    rm, sc, info = okrt.scenes.test_scene(with_textures=False)
+    W, H = 160, 90
+    host = helpers.build_host_side(okrt, rm, sc, info, W, H)
+    env = okrt.scenes.procedural_sky_faces(32)
+    abi = okrt.abi
     outs = []
-    for name, val in (("single", "0"), ("dual", "2")):
-        out = str(tmp_path / (name + ".npy"))
-        env = dict(os.environ, OKRT_DUAL_MIN_FRAMES=val)
-        subprocess.run([sys.executable, "-c", _DUAL_SCRIPT.format(root=root, out=out)], check=True, env=env, cwd=root, timeout=300)
-        outs.append(np.load(out))
-    assert outs[0][..., 3].max() == 5.0
-    assert np.array_equal(outs[0].view(np.uint32), outs[1].view(np.uint32))
+    for lanes in (1, 4):
+        r = helpers.Renderer(okrt, host, W, H, envFaces=env)
+        r.options(maxBounces=3, batchesInFlight=lanes)
+        rd = host["rd"].copy()
+
+        def go(frames):
+            rd[0]["numAccumulationFrames"] = r.L.okrt_get_num_accumulation_frames(r.h)
+            abi.check(r.L.okrt_set_render_data(r.h, abi.ptr(rd)))
+            abi.check(r.L.okrt_render_frames(r.h, frames))          # no okrt_sync: the next call is queued behind it
+
+        got = []
+        go(3); go(2); go(1)
+        got.append(r.accumulation())
+        go(2)
+        abi.check(r.L.okrt_reset_accumulation(r.h))
+        go(2); go(1)
+        got.append(r.accumulation()); got.append(r.result())
+        light = np.zeros(1, abi.POINT_LIGHT)
+        light[0]["colour"] = (0.9, 0.2, 0.1); light[0]["intensity"] = 3.0; light[0]["radius"] = 0.5; light[0]["position"] = (0.0, 4.0, 0.0)
+        go(2)
+        r.set_lights(pointLights=light)
+        rd[0]["numPointLights"] = 1
+        go(2); go(2)
+        got.append(r.accumulation())
+        go(1)
+        abi.check(r.L.okrt_write_accumulation(r.h, abi.ptr(got[0]), 6))
+        go(2); go(1)
+        got.append(r.accumulation())
+        r.options(writeAov=1)
+        go(1)
+        got.append(r.aov()["numSegments"].copy())
+        r.options(writeAov=0)
+        go(3)
+        got.append(r.accumulation())
+        r.close()
+        outs.append(got)
+    assert outs[0][0][..., 3].max() == 6.0 and outs[0][1][..., 3].max() == 3.0 and outs[0][4][..., 3].max() == 9.0
+    for a, b in zip(*outs):
+        assert np.array_equal(np.ascontiguousarray(a).view(np.uint8), np.ascontiguousarray(b).view(np.uint8))
