@@ -43,6 +43,7 @@ def _stale(target, deps):
 
 
 OUT_STATS = os.path.join(HERE, "libokrt_stats.so")
+OUT_CHECKS = os.path.join(HERE, "libokrt_checks.so")
 
 
 def build_stats_library(force=False, verbose=False):
@@ -50,6 +51,13 @@ def build_stats_library(force=False, verbose=False):
     (okrt_get_trace_stats).  bench.py renders one step through it to quote the kernel's executed work; the timed arms use
     libokrt.so, which carries no counters."""
     return build_library(force=force, verbose=verbose, extra_nvcc=("-DOKRT_TRACE_STATS",), out=OUT_STATS, obj_dir=OBJ + "_stats")
+
+
+def build_checks_library(force=False, verbose=False):
+    """The same library with -DOKRT_DEBUG_CHECKS: device-side asserts on every traversal-stack push / pop and every node,
+    triangle and instance index the kernels form (OKRT_CHECK).  compute-sanitizer is closed on the GPU pool, so the GPU suite is
+    run once per round against this build instead (OKRT_LIB=.../libokrt_checks.so python -m pytest tests -m gpu)."""
+    return build_library(force=force, verbose=verbose, extra_nvcc=("-DOKRT_DEBUG_CHECKS",), out=OUT_CHECKS, obj_dir=OBJ + "_checks")
 
 
 def build_library(force=False, verbose=False, extra_nvcc=(), out=None, obj_dir=None):

@@ -1208,6 +1208,8 @@ __global__ void __launch_bounds__(128) issueRateKernel(uint32_t iters, float see
 {
     float a0 = seed + threadIdx.x, a1 = a0 + 1.f, a2 = a0 + 2.f, a3 = a0 + 3.f, a4 = a0 + 4.f, a5 = a0 + 5.f, a6 = a0 + 6.f, a7 = a0 + 7.f;
     const float m = 1.0000001f, c = 0.5f;
+    unsigned long long g0, g1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g0));
     const long long t0 = clock64();
     for (uint32_t i = 0; i < iters; i++) {
 #pragma unroll
@@ -1217,9 +1219,11 @@ __global__ void __launch_bounds__(128) issueRateKernel(uint32_t iters, float see
         }
     }
     const long long t1 = clock64();
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g1));
     const float sum = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
     if (sum == 123.456f) *sink = sum;
-    if (blockIdx.x == 0 && threadIdx.x == 0) *cycles = (unsigned long long)(t1 - t0);
+    /* SM clock under this load: block 0's own cycles over its own nanoseconds (the grid runs several waves of blocks) */
+    if (blockIdx.x == 0 && threadIdx.x == 0) { cycles[0] = (unsigned long long)(t1 - t0); cycles[1] = g1 - g0; }
 }
 
 int okrt_measure_unit_peaks(int device, okrt_unit_peaks* out)
@@ -1237,13 +1241,13 @@ int okrt_measure_unit_peaks(int device, okrt_unit_peaks* out)
     if (e == cudaSuccess) e = cudaMemset(data, 1, (size_t)sectors * 32);
     if (e == cudaSuccess) e = cudaMalloc(&sink, 4);
     if (e == cudaSuccess) e = cudaMalloc(&fsink, 4);
-    if (e == cudaSuccess) e = cudaMalloc(&cycles, 8);
+    if (e == cudaSuccess) e = cudaMalloc(&cycles, 16);
     if (e == cudaSuccess) e = cudaEventCreate(&e0);
     if (e == cudaSuccess) e = cudaEventCreate(&e1);
     const unsigned grid = (unsigned)prop.multiProcessorCount * 8u;
     float msSector = 0.f, msSectorL1 = 0.f, msIssue = 0.f;
     const uint32_t sIters = 256u, iIters = 4096u;
-    unsigned long long hCycles = 0;
+    unsigned long long hCycles[2] = {0, 0};
     if (e == cudaSuccess) {
         for (int rep = 0; rep < 3 && e == cudaSuccess; rep++) {     /* the last repetition is the warm one */
             cudaEventRecord(e0);
@@ -1266,7 +1270,7 @@ int okrt_measure_unit_peaks(int device, okrt_unit_peaks* out)
             e = cudaEventSynchronize(e1);
             if (e == cudaSuccess) e = cudaEventElapsedTime(&msIssue, e0, e1);
         }
-        if (e == cudaSuccess) e = cudaMemcpy(&hCycles, cycles, 8, cudaMemcpyDeviceToHost);
+        if (e == cudaSuccess) e = cudaMemcpy(hCycles, cycles, 16, cudaMemcpyDeviceToHost);
     }
     if (data) cudaFree(data); if (sink) cudaFree(sink); if (fsink) cudaFree(fsink); if (cycles) cudaFree(cycles);
     if (e0) cudaEventDestroy(e0); if (e1) cudaEventDestroy(e1);
@@ -1275,7 +1279,7 @@ int okrt_measure_unit_peaks(int device, okrt_unit_peaks* out)
     out->sectorsPerSecond = threads * sIters * 4.0 * 2.0 / (msSector * 1e-3);         /* 4 loads x 2 sectors per trip */
     out->sectorsPerSecondL1 = threads * (sIters * 4.0) * 4.0 * 2.0 / (msSectorL1 * 1e-3);
     out->warpInstructionsPerSecond = (threads / 32.0) * iIters * 64.0 / (msIssue * 1e-3);
-    out->smClockMHz = msIssue > 0.f ? (double)hCycles / (msIssue * 1e-3) / 1e6 : 0.0;
+    out->smClockMHz = hCycles[1] ? (double)hCycles[0] / (double)hCycles[1] * 1e3 : 0.0;
     out->numSms = (uint32_t)prop.multiProcessorCount;
     return OKRT_OK;
 }
