@@ -609,6 +609,18 @@ constexpr uint32_t kTraceTop = 0xFFFFFFFFu;
 #ifndef OKRT_COLD_IN_LOCAL
 #define OKRT_COLD_IN_LOCAL 1
 #endif
+/* OKRT_SMEM_STACK = K > 0 (device code only): stack entries 0..K-1 of a lane live in shared memory, word-interleaved over the
+ * block's 128 threads (entry e of thread t at word e*128 + t: every lane owns its bank, a push or pop is one wavefront whatever
+ * the lanes' depths are), entries K.. stay in local memory.  In local memory lanes at different depths touch different 128-byte
+ * rows: 2-3 wavefronts per push or pop (profiles/r2_j: stack traffic is 28 % of the traversal kernel's L1 wavefronts). */
+#ifndef OKRT_SMEM_STACK
+#define OKRT_SMEM_STACK 0
+#endif
+#if OKRT_SMEM_STACK && defined(__CUDA_ARCH__)
+#define OKRT_SMEM_STACK_ON 1
+#else
+#define OKRT_SMEM_STACK_ON 0
+#endif
 /* OKRT_COLD_IN_LOCAL: the lane's hit record (written once or twice per ray, read when the ray finishes) lives in the slots
  * behind the traversal stack instead of registers, which buys resident warps */
 constexpr uint32_t kColdSlots = 8;
@@ -632,7 +644,18 @@ struct StepLane {
 #endif
     uint32_t inst;           /* instance record inside a generic instance; kTraceTop at the top level */
     uint32_t path;
+#if OKRT_SMEM_STACK_ON
+    uint32_t smBase;         /* shared-window address of this thread's entry 0 */
+#endif
 };
+#if OKRT_SMEM_STACK_ON
+__device__ __forceinline__ void stackSharedStore(uint32_t addr, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" :: "r"(addr), "r"(v) : "memory"); }
+__device__ __forceinline__ uint32_t stackSharedLoad(uint32_t addr) { uint32_t v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory"); return v; }
+#define OKRT_SMEM_STACK_DECLARE(L) __shared__ uint32_t okrtSmemStack[OKRT_SMEM_STACK * 128]; \
+    (L).smBase = (uint32_t)__cvta_generic_to_shared(okrtSmemStack + threadIdx.x);
+#else
+#define OKRT_SMEM_STACK_DECLARE(L)
+#endif
 
 OKRT_HD void stepCandidate(StepLane& L, uint32_t* stack, float t, uint32_t rec, uint32_t tri, float u, float v)
 {
@@ -665,7 +688,10 @@ OKRT_HD void stepEnter(StepLane& L, uint32_t ref)
 OKRT_HD void stackPush(StepLane& L, uint32_t* stack, uint32_t v)
 {
     OKRT_CHECK(L.sp >= 1 && L.sp < (int)kFastStackCapacity);
-#if OKRT_STACK_TOPREG
+#if OKRT_SMEM_STACK_ON
+    if (L.sp < OKRT_SMEM_STACK) stackSharedStore(L.smBase + (uint32_t)L.sp * 512u, v); else stack[L.sp] = v;
+    L.sp++;
+#elif OKRT_STACK_TOPREG
     stack[L.sp++] = L.top; L.top = v;
 #else
     stack[L.sp++] = v;
@@ -674,7 +700,10 @@ OKRT_HD void stackPush(StepLane& L, uint32_t* stack, uint32_t v)
 OKRT_HD uint32_t stackPop(StepLane& L, const uint32_t* stack)
 {
     OKRT_CHECK(L.sp >= 1 && L.sp <= (int)kFastStackCapacity);
-#if OKRT_STACK_TOPREG
+#if OKRT_SMEM_STACK_ON
+    --L.sp;
+    return L.sp < OKRT_SMEM_STACK ? stackSharedLoad(L.smBase + (uint32_t)L.sp * 512u) : stack[L.sp];
+#elif OKRT_STACK_TOPREG
     const uint32_t v = L.top; L.top = stack[--L.sp]; return v;
 #else
     return stack[--L.sp];
@@ -693,6 +722,9 @@ OKRT_HD void stepInit(const DeviceScene& s, StepLane& L, uint32_t* stack, uint32
     L.hitRec = 0x3FFFFFFFu; L.hitTri = 0xFFFFFFFFu; L.hitU = 0.f; L.hitV = 0.f;
 #endif
     stack[0] = kTraceDone; L.sp = 1;
+#if OKRT_SMEM_STACK_ON
+    stackSharedStore(L.smBase, kTraceDone);
+#endif
 #if OKRT_STACK_TOPREG
     L.top = kTraceDone;
 #endif
@@ -907,6 +939,7 @@ OKRT_HD bool traversePairs(const DeviceScene& s, uint32_t numSpheres, V3 o, V3 d
     uint32_t stack[kFastStackCapacity + kColdSlots];
     StepLane L;
     L.path = 0u;
+    OKRT_SMEM_STACK_DECLARE(L)
     stepInit(s, L, stack, numSpheres, o, d);
     while (L.cur != kTraceDone) {
         const uint32_t tag = L.cur & kRefTagMask;

@@ -209,6 +209,10 @@ traceFastKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ F
     StepLane L;
     L.cur = kTraceDone; L.sp = 1; L.path = 0u; L.inst = kTraceTop; L.triNext = 0u;
     stack[0] = kTraceDone;
+    OKRT_SMEM_STACK_DECLARE(L)
+#if OKRT_SMEM_STACK_ON
+    stackSharedStore(L.smBase, kTraceDone);
+#endif
 #if OKRT_STACK_TOPREG
     L.top = kTraceDone;
 #endif
