@@ -161,8 +161,9 @@ def run_reference_arm(args):
 
 
 # ----------------------------------------------------------------------------------------------- legs of the GPU arm
-def run_config(okrt, name, rm, sc, info, width, height, bounces, frames, env, device, steps=3, note=None):
-    """One BASELINE config on one GPU: `steps` timed calls of `frames` progressive frames after one warm-up call."""
+def run_config(okrt, name, rm, sc, info, width, height, bounces, frames, env, device, steps=3, note=None, with_cpu=True):
+    """One BASELINE config on one GPU: `steps` timed calls of `frames` progressive frames after one warm-up call; with_cpu: frame 1
+    by the oracle on all host threads as well (its rate, and the GPU's frame 1 compared with it word for word)."""
     abi = okrt.abi
     t0 = time.perf_counter()
     host = okrt.harness.build_host_side(okrt, rm, sc, info, width, height, spheres=(name == "C1"))
@@ -181,29 +182,51 @@ def run_config(okrt, name, rm, sc, info, width, height, bounces, frames, env, de
         ms += float(r.stats()["lastRenderMs"])
     st = r.stats()
     seg, fb = int(st["raySegments"]), int(st["fallbackSegments"])
+    cpu = parity = None
+    if with_cpu:
+        from oracle import binding as oracle_binding
+        oracle = oracle_binding.load()
+        scene = oracle_binding.oracle_scene(oracle, host, envFaces=env)
+        rd1 = host["rd"].copy()
+        rd1[0]["numAccumulationFrames"] = 1
+        t0 = time.perf_counter()
+        o = oracle.render(scene, rd1, bounces)
+        dt = time.perf_counter() - t0
+        cpu = {"value": o["segments"] / dt / 1e6, "unit": UNIT, "cores": os.cpu_count() or 1, "kind": "port",
+               "sample": "frame 1, %d ray segments in %.1f s" % (o["segments"], dt)}
+        abi.check(r.L.okrt_reset_accumulation(r.h))
+        abi.check(r.L.okrt_reset_stats(r.h))
+        r.render(host["rd"].copy(), frames=1)
+        acc = r.accumulation()
+        bad = np.any(acc.view(np.uint32) != o["accum"].view(np.uint32), axis=2)
+        gseg = int(r.stats()["raySegments"])
+        parity = {"bit_exact": bool(not bad.any()) and gseg == int(o["segments"]), "differing_pixels": int(bad.sum()),
+                  "segments": [gseg, int(o["segments"])]}
     r.close()
     out = {"workload": "%s %dx%d maxBounces=%d, %d frames per call" % (info.get("name", name), width, height, bounces, frames),
            "value": seg / (ms * 1e-3) / 1e6, "unit": UNIT, "ms_per_frame": ms / (steps * frames), "ray_segments": seg,
            "fallback_segments": fb, "triangles": int(len(host["geometry"].trianglesPos)), "stand_in": bool(info.get("stand_in", False)),
            "host_build_s": round(build_s, 2), "first_call_ms": round(first_ms, 1),
            "layout": {"builder": int(lb["builder"]), "device_ms": round(float(lb["deviceMs"]), 2), "refine_ms": round(float(lb["refineMs"]), 1)}}
+    if cpu:
+        out["cpu_baseline"], out["parity"] = cpu, parity
     if note:
         out["note"] = note
     return out
 
 
-def run_single_gpu_configs(okrt, device):
+def run_single_gpu_configs(okrt, device, with_cpu=True):
     sc_mod = okrt.scenes
     configs = {}
     rm, sc, info = sc_mod.test_scene()
-    configs["C1"] = run_config(okrt, "C1", rm, sc, info, 512, 512, 0, 16, None, device,
+    configs["C1"] = run_config(okrt, "C1", rm, sc, info, 512, 512, 0, 16, None, device, with_cpu=with_cpu,
                                note="configs[0]: primary rays only; 512x504 pixels are covered (Dispatch(W/16, H/9), Q9)")
     rm, sc, info = sc_mod.dragon_scene()
-    configs["C2"] = run_config(okrt, "C2", rm, sc, info, 1920, 1080, 4, 16, sc_mod.procedural_sky_faces(256), device,
+    configs["C2"] = run_config(okrt, "C2", rm, sc, info, 1920, 1080, 4, 16, sc_mod.procedural_sky_faces(256), device, with_cpu=with_cpu,
                                note="configs[1]: 871k-triangle displaced knot (stand-in: dragon.obj is not shipped), metallic, sky cube")
     path = os.path.join(ROOT, "tests", "golden", "ikea_glass_mesh.npz")
     rm, sc, info = sc_mod.glass_scene_from_fixture(path) if os.path.exists(path) else sc_mod.glass_scene()
-    configs["C3"] = run_config(okrt, "C3", rm, sc, info, 1920, 1080, 16, 16, sc_mod.procedural_sky_faces(256), device,
+    configs["C3"] = run_config(okrt, "C3", rm, sc, info, 1920, 1080, 16, 16, sc_mod.procedural_sky_faces(256), device, with_cpu=with_cpu,
                                note="configs[2]: the reference's ikea_glass.obj (committed fixture), scale 10, transparency 1, IOR 1.5")
     return configs
 
@@ -569,7 +592,8 @@ def main():
     r.close()
     if not args.no_configs:
         if world == 1 and rank == 0:
-            line["configs"] = run_single_gpu_configs(okrt, local_rank)
+            line["configs"] = run_single_gpu_configs(okrt, local_rank, with_cpu=not args.no_cpu_baseline)
+            failed = failed or any(c.get("parity") and not c["parity"]["bit_exact"] for c in line["configs"].values())
             c5 = run_c5(okrt, scene_parts, env, local_rank, 0, 1, None)
             c5["note"] += "; one GPU: no all-reduce"
             line["configs"]["C5"] = c5
