@@ -21,6 +21,23 @@ def test_band_ownership_partitions_the_image(okrt):
             assert max(len(r) for r in rows) - min(len(r) for r in rows) <= band
 
 
+def test_cost_balanced_band_table(okrt):
+    """okrt_shard_balance (host-only): every band gets one owner, the same table comes out of every call (each rank computes it
+    for itself), and no rank carries more than the ideal share plus one band's cost (longest-processing-time-first)."""
+    rng = np.random.default_rng(5)
+    for bands, world in ((135, 8), (135, 4), (270, 8), (17, 2), (5, 8)):
+        cost = rng.uniform(1.0, 3.0, bands) * np.linspace(0.5, 2.0, bands)
+        owner = okrt.sharding.balanced_bands(cost, world)
+        again = okrt.sharding.balanced_bands(cost.copy(), world)
+        assert owner.shape == (bands,) and owner.max() < world and np.array_equal(owner, again)
+        loads = np.array([cost[owner == k].sum() for k in range(world)])
+        assert abs(loads.sum() - cost.sum()) < 1e-9 * cost.sum()
+        assert loads.max() <= cost.sum() / world + cost.max() + 1e-9
+    seg = np.arange(20 * 4, dtype=np.uint32).reshape(20, 4)
+    per_band = okrt.sharding.band_costs_from_segments(seg, 8)
+    assert per_band.tolist() == [float(seg[0:8].sum()), float(seg[8:16].sum()), float(seg[16:20].sum())]
+
+
 def test_seed_frames_interleave(okrt):
     sh = okrt.sharding
     for world in (1, 2, 8):
