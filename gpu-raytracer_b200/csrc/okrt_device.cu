@@ -19,6 +19,9 @@
 #include <cstring>
 #include <string>
 #include <mutex>
+#include <sys/resource.h>
+#include <sys/syscall.h>
+#include <unistd.h>
 #include <vector>
 
 #include "okrt.h"
@@ -328,6 +331,9 @@ void startRefine(okrt_renderer* r)
     job->tris = r->hTris; job->nodes = r->hNodes; job->instances = r->hInstances; job->oct = r->hOct;
     r->refine = job;
     std::thread([job]() {
+        /* lowest scheduling priority for this thread and the builder threads it starts (they inherit it): the refinement must
+         * not take the cores from the thread that is feeding the GPU */
+        setpriority(PRIO_PROCESS, (id_t)syscall(SYS_gettid), 19);
         const auto t0 = std::chrono::steady_clock::now();
         job->ok = buildFastLayout(job->tris->data(), (uint32_t)job->tris->size(), job->nodes->data(), (uint32_t)job->nodes->size(),
                                   job->instances->data(), (uint32_t)job->instances->size(), job->oct->data(), (uint32_t)job->oct->size(), job->layout, false);
@@ -546,7 +552,7 @@ int launchWavefront(okrt_renderer* r, const FrameParams& fp, bool instrumented)
     generateKernel<<<flatGrid, 128, 0, st>>>(fp, wb);
     r->launches++;
     for (uint32_t b = 0; b <= fp.maxBounces; b++) {
-        const uint32_t* qin = wb.queue[b & 1u];
+        const uint32_t* qin = (b == 0u && fp.allCovered) ? nullptr : wb.queue[b & 1u];
         uint32_t* qout = wb.queue[(b + 1u) & 1u];
         if (fp.traversal == OKRT_TRAVERSAL_EXACT) {
             traceExactKernel<<<flatGrid, 128, 0, st>>>(scene, fp, wb, qin, b);
@@ -697,6 +703,8 @@ int launchFrames(okrt_renderer* r, uint32_t want, uint32_t& done)
     if (rows == 0) return OKRT_OK;
     fp.tilesX = (r->width + kTileW - 1) / kTileW;
     fp.numTiles = fp.tilesX * ((rows + kTileH - 1) / kTileH);
+    /* every slot of the owned tiles is a covered pixel: full tiles in x, and in y the covered extent is the image and ends on a band */
+    fp.allCovered = (fp.coveredW == fp.tilesX * (uint32_t)kTileW && fp.coveredH == r->height && r->height % fp.bandRows == 0u) ? 1u : 0u;
     fp.workCounter = reinterpret_cast<uint32_t*>(r->counters + 3);
     if (r->opt.pipeline == OKRT_PIPELINE_WAVEFRONT && fp.maxBounces <= kMaxWavefrontBounces) return launchWavefront(r, fp, instrumented);
     /* the megakernel adds to u1 itself: a serial batch on lane 0, after everything issued so far */

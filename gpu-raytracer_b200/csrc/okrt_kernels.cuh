@@ -125,6 +125,7 @@ struct FrameParams {
     uint32_t bandRows, shardRank, shardCount; /* tile sharding: row band b belongs to rank b % shardCount */
     const uint32_t* ownedBands;               /* tile sharding with an explicit table (okrt_set_shard_bands): global band of this rank's k-th band */
     uint32_t tilesX, numTiles;                /* 16x8 tiles this launch owns */
+    uint32_t allCovered;                      /* every pixel slot of those tiles is a covered pixel [Q9]: bounce 0 needs no queue */
     uint32_t* workCounter;                    /* next tile to hand out (zeroed before the launch) */
     float4* accumulation;                     /* u1 */
     uchar4* result;                           /* u0 */

@@ -189,9 +189,13 @@ __device__ __forceinline__ float unionArea(const float* a, const float* b)
     return dx * dy + dy * dz + dz * dx;
 }
 
-__global__ void plocNearestKernel(const float* __restrict__ box, const uint32_t* __restrict__ cluster, uint32_t count, uint32_t* __restrict__ nearest)
+/* The clustering rounds keep their state on the device — state[0] = clusters left, state[1] = next free tree node, double
+ * buffered by round parity — so that the host can queue many rounds without reading anything back (a round with one cluster
+ * left changes nothing). */
+__global__ void plocNearestKernel(const float* __restrict__ box, const uint32_t* __restrict__ cluster, const uint32_t* __restrict__ state, uint32_t* __restrict__ nearest)
 {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t count = state[0];
     if (i >= count) return;
     float mine[6];
     const float* b = box + (size_t)cluster[i] * 6;
@@ -206,33 +210,38 @@ __global__ void plocNearestKernel(const float* __restrict__ box, const uint32_t*
     nearest[i] = bestJ;
 }
 
-__global__ void plocFlagsKernel(const uint32_t* __restrict__ nearest, uint32_t count, uint32_t* __restrict__ mergeFlag, uint32_t* __restrict__ keepFlag)
+/* flags[i] = merge | keep << 32 for the clusters left, 0 up to `bound` (what the scan covers) */
+__global__ void plocFlagsKernel(const uint32_t* __restrict__ nearest, const uint32_t* __restrict__ state, uint32_t bound, unsigned long long* __restrict__ flags)
 {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= count) return;
+    if (i >= bound) return;
+    if (i >= state[0]) { flags[i] = 0ull; return; }
     const uint32_t j = nearest[i];
     const bool mutual = j != kNone && nearest[j] == i;
-    mergeFlag[i] = (mutual && i < j) ? 1u : 0u;
-    keepFlag[i] = (mutual && i > j) ? 0u : 1u;
+    const unsigned long long merge = (mutual && i < j) ? 1ull : 0ull, keep = (mutual && i > j) ? 0ull : 1ull;
+    flags[i] = merge | (keep << 32);
 }
 
-__global__ void plocApplyKernel(const uint32_t* __restrict__ nearest, const uint32_t* __restrict__ mergeFlag, const uint32_t* __restrict__ keepFlag,
-                                const uint32_t* __restrict__ mergeIdx, const uint32_t* __restrict__ keepIdx, uint32_t count, uint32_t nextNode,
+__global__ void plocApplyKernel(const uint32_t* __restrict__ nearest, const unsigned long long* __restrict__ flags, const unsigned long long* __restrict__ idx,
+                                const uint32_t* __restrict__ stateIn, uint32_t* __restrict__ stateOut,
                                 const uint32_t* __restrict__ cluster, uint32_t* __restrict__ clusterOut, float* __restrict__ box,
-                                uint32_t* __restrict__ child /* 2 per node */, uint32_t* __restrict__ treeParent, uint32_t* __restrict__ status)
+                                uint32_t* __restrict__ child /* 2 per node */, uint32_t* __restrict__ treeParent)
 {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t count = stateIn[0], nextNode = stateIn[1];
     if (i >= count) return;
-    if (mergeFlag[i]) {
-        const uint32_t id = nextNode + mergeIdx[i], a = cluster[i], b = cluster[nearest[i]];
+    const uint32_t mergeFlag = (uint32_t)(flags[i] & 0xFFFFFFFFull), keepFlag = (uint32_t)(flags[i] >> 32);
+    const uint32_t mergeIdx = (uint32_t)(idx[i] & 0xFFFFFFFFull), keepIdx = (uint32_t)(idx[i] >> 32);
+    if (mergeFlag) {
+        const uint32_t id = nextNode + mergeIdx, a = cluster[i], b = cluster[nearest[i]];
         const float *ba = box + (size_t)a * 6, *bb = box + (size_t)b * 6;
         float* bo = box + (size_t)id * 6;
         for (int k = 0; k < 3; k++) { bo[k] = fminf(ba[k], bb[k]); bo[3 + k] = fmaxf(ba[3 + k], bb[3 + k]); }
         child[2 * (size_t)id] = a; child[2 * (size_t)id + 1] = b;
         treeParent[a] = id; treeParent[b] = id;
-        clusterOut[keepIdx[i]] = id;
-    } else if (keepFlag[i]) clusterOut[keepIdx[i]] = cluster[i];
-    if (i == count - 1u) { status[kStMerged] = mergeIdx[i] + mergeFlag[i]; status[kStKept] = keepIdx[i] + keepFlag[i]; }
+        clusterOut[keepIdx] = id;
+    } else if (keepFlag) clusterOut[keepIdx] = cluster[i];
+    if (i == count - 1u) { stateOut[0] = keepIdx + keepFlag; stateOut[1] = nextNode + mergeIdx + mergeFlag; }
 }
 
 __global__ void emitPairsKernel(const float* __restrict__ box, const uint32_t* __restrict__ child, const uint32_t* __restrict__ sortedPrim,
@@ -337,17 +346,18 @@ int buildFastLayoutDevice(const okrt_triangle* dTris, uint32_t numTris, const ok
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     OKRT_LD_CUDA(cudaEventCreate(&ev0)); OKRT_LD_CUDA(cudaEventCreate(&ev1));
     struct Cleanup { cudaEvent_t a, b; void* scratch; ~Cleanup() { if (a) cudaEventDestroy(a); if (b) cudaEventDestroy(b); if (scratch) cudaFree(scratch); } } cleanup{ev0, ev1, nullptr};
-    OKRT_LD_CUDA(cudaEventRecord(ev0, stream));
     const size_t maxLeaves = numNodes, treeNodes = 2 * maxLeaves;
     size_t selectBytes = 0, sortBytes = 0, scanBytes = 0;
     cub::DeviceSelect::Flagged(nullptr, selectBytes, thrust::counting_iterator<uint32_t>(0), (const uint8_t*)nullptr, (uint32_t*)nullptr, (uint32_t*)nullptr, (int)numNodes, stream);
     cub::DeviceRadixSort::SortPairs(nullptr, sortBytes, (const uint32_t*)nullptr, (uint32_t*)nullptr, (const uint32_t*)nullptr, (uint32_t*)nullptr, (int)maxLeaves, 0, 30, stream);
-    cub::DeviceScan::ExclusiveSum(nullptr, scanBytes, (const uint32_t*)nullptr, (uint32_t*)nullptr, (int)maxLeaves, stream);
+    cub::DeviceScan::ExclusiveSum(nullptr, scanBytes, (const unsigned long long*)nullptr, (unsigned long long*)nullptr, (int)maxLeaves, stream);
     const size_t cubBytes = std::max(selectBytes, std::max(sortBytes, scanBytes));
     Arena ar;
     ar.size = cubBytes + 4096 + (size_t)numNodes * (4 + 1 + 4) + (size_t)numTris * 4 + rootRec.size() * 8 +
               maxLeaves * (4 + 24 + 4 + 4 + 4 + 4 + 4) + treeNodes * (24 + 8 + 4) + maxLeaves * 4 * 7 + 64 * 256;
     OKRT_LD_CUDA(cudaMalloc(&cleanup.scratch, ar.size));
+    OKRT_LD_CUDA(cudaMalloc(&out.tris, (size_t)numTris * kTriQuads * sizeof(float4)));
+    OKRT_LD_CUDA(cudaEventRecord(ev0, stream));                        /* deviceMs: the build, not the two allocations above */
     ar.base = (uint8_t*)cleanup.scratch;
     uint32_t* status = ar.take<uint32_t>(kStWords + 8);                  /* + 6 ordered bound words, + number of leaves */
     uint32_t* bounds = status + kStWords;
@@ -366,8 +376,9 @@ int buildFastLayoutDevice(const okrt_triangle* dTris, uint32_t numTris, const ok
     uint32_t* child = ar.take<uint32_t>(treeNodes * 2);
     uint32_t* treeParent = ar.take<uint32_t>(treeNodes);
     uint32_t *clusterA = ar.take<uint32_t>(maxLeaves), *clusterB = ar.take<uint32_t>(maxLeaves), *nearest = ar.take<uint32_t>(maxLeaves);
-    uint32_t *mergeFlag = ar.take<uint32_t>(maxLeaves), *keepFlag = ar.take<uint32_t>(maxLeaves), *mergeIdx = ar.take<uint32_t>(maxLeaves), *keepIdx = ar.take<uint32_t>(maxLeaves);
-    if (!keepIdx) { setError("device layout: scratch arena too small"); return OKRT_ERR_CAPACITY; }
+    unsigned long long *flags64 = ar.take<unsigned long long>(maxLeaves), *idx64 = ar.take<unsigned long long>(maxLeaves);
+    uint32_t* plocState = ar.take<uint32_t>(4);
+    if (!plocState) { cudaFree(out.tris); out.tris = nullptr; setError("device layout: scratch arena too small"); return OKRT_ERR_CAPACITY; }
 
     const unsigned B = 256;
     auto grid = [&](size_t n) { return (unsigned)((n + B - 1) / B); };
@@ -389,7 +400,6 @@ int buildFastLayoutDevice(const okrt_triangle* dTris, uint32_t numTris, const ok
         OKRT_LD_CUDA(cub::DeviceSelect::Flagged(cubTemp, bytes, thrust::counting_iterator<uint32_t>(0), isLeaf, leafNode, numLeavesDev, (int)numNodes, stream));
     }
     /* the triangle records and the leaf primitives do not need the host to know the leaf count */
-    OKRT_LD_CUDA(cudaMalloc(&out.tris, (size_t)numTris * kTriQuads * sizeof(float4)));
     triangleRecordsKernel<<<grid(numTris), B, 0, stream>>>((const float*)dTris, triOwner, numTris, out.tris);
     leafPrimsKernel<<<grid(maxLeaves), B, 0, stream>>>(dNodes, leafNode, numLeavesDev, primBox, primRef, bounds);
     uint32_t hStatus[kStWords + 8];
@@ -414,23 +424,35 @@ int buildFastLayoutDevice(const okrt_triangle* dTris, uint32_t numTris, const ok
     }
     OKRT_LD_CUDA(cudaMemsetAsync(treeParent, 0xFF, (size_t)2 * n * 4, stream));
     treeLeavesKernel<<<grid(n), B, 0, stream>>>(primBox, sortedPrim, n, box, clusterA);
-    uint32_t count = n, nextNode = n, rounds = 0;
+    uint32_t count = n, nextNode = n, rounds = 0, parity = 0;
     uint32_t *cur = clusterA, *nxt = clusterB;
+    {
+        const uint32_t init[2] = {n, n};
+        OKRT_LD_CUDA(cudaMemcpyAsync(plocState, init, sizeof(init), cudaMemcpyHostToDevice, stream));
+    }
+    /* rounds are queued kPlocChunk at a time; the host reads the state once per chunk (a read per round made the build wait
+     * for the host 50 times, which a busy host stretches to tens of milliseconds) */
+    constexpr uint32_t kPlocChunk = 16;
     while (count > 1u) {
-        plocNearestKernel<<<grid(count), B, 0, stream>>>(box, cur, count, nearest);
-        plocFlagsKernel<<<grid(count), B, 0, stream>>>(nearest, count, mergeFlag, keepFlag);
-        size_t bytes = cubBytes;
-        OKRT_LD_CUDA(cub::DeviceScan::ExclusiveSum(cubTemp, bytes, mergeFlag, mergeIdx, (int)count, stream));
-        bytes = cubBytes;
-        OKRT_LD_CUDA(cub::DeviceScan::ExclusiveSum(cubTemp, bytes, keepFlag, keepIdx, (int)count, stream));
-        plocApplyKernel<<<grid(count), B, 0, stream>>>(nearest, mergeFlag, keepFlag, mergeIdx, keepIdx, count, nextNode, cur, nxt, box, child, treeParent, status);
+        const uint32_t bound = count;
+        for (uint32_t k = 0; k < kPlocChunk; k++) {
+            const uint32_t* in = plocState + 2u * parity;
+            uint32_t* outState = plocState + 2u * (parity ^ 1u);
+            plocNearestKernel<<<grid(bound), B, 0, stream>>>(box, cur, in, nearest);
+            plocFlagsKernel<<<grid(bound), B, 0, stream>>>(nearest, in, bound, flags64);
+            size_t bytes = cubBytes;
+            OKRT_LD_CUDA(cub::DeviceScan::ExclusiveSum(cubTemp, bytes, flags64, idx64, (int)bound, stream));
+            plocApplyKernel<<<grid(bound), B, 0, stream>>>(nearest, flags64, idx64, in, outState, cur, nxt, box, child, treeParent);
+            std::swap(cur, nxt);
+            parity ^= 1u;
+            rounds++;
+        }
         uint32_t two[2];
-        OKRT_LD_CUDA(cudaMemcpyAsync(two, status + kStMerged, 8, cudaMemcpyDeviceToHost, stream));
+        OKRT_LD_CUDA(cudaMemcpyAsync(two, plocState + 2u * parity, 8, cudaMemcpyDeviceToHost, stream));
         OKRT_LD_CUDA(cudaStreamSynchronize(stream));
-        if (two[0] == 0u || two[1] >= count) return giveUp("clustering made no progress (host builder)");
-        nextNode += two[0]; count = two[1];
-        std::swap(cur, nxt);
-        if (++rounds > 4096u) return giveUp("clustering did not finish (host builder)");
+        if (two[0] == 0u || two[0] >= count) return giveUp("clustering made no progress (host builder)");
+        count = two[0]; nextNode = two[1];
+        if (rounds > 4096u) return giveUp("clustering did not finish (host builder)");
     }
     if (n > 1u && nextNode != 2u * n - 1u) return giveUp("clustering lost nodes (host builder)");
 

@@ -76,14 +76,20 @@ generateKernel(const __grid_constant__ FrameParams fp, const WavefrontBuffers wb
     const bool covered = px < fp.coveredW && py < fp.coveredH;
 
     /* path slot = frame * numSlots + pixel slot (so that the final gather can add frames in order); covered
-     * pixels are compacted into queue 0 (keeps tile order inside a warp) */
-    const uint32_t mask = __ballot_sync(0xFFFFFFFFu, covered);
-    uint32_t base = 0u;
-    if ((threadIdx.x & 31u) == 0u && mask) base = atomicAdd(wb.counts + 0, (uint32_t)__popc(mask));
-    base = __shfl_sync(0xFFFFFFFFu, base, 0);
-    if (!covered) return;
+     * pixels are compacted into queue 0 (keeps tile order inside a warp).  When every slot is a covered pixel (1920x1080,
+     * 3840x2160, ...: width a multiple of 16, height of 72) the queue of bounce 0 is the identity: nothing is written, the
+     * kernels of bounce 0 index the paths directly, and the count is stored once (a million same-address atomics less). */
     const uint32_t path = gslot;
-    wb.queue[0][base + __popc(mask & ((1u << (threadIdx.x & 31u)) - 1u))] = path;
+    if (fp.allCovered) {
+        if (gslot == 0u) wb.counts[0] = numSlots * fp.batchFrames;
+    } else {
+        const uint32_t mask = __ballot_sync(0xFFFFFFFFu, covered);
+        uint32_t base = 0u;
+        if ((threadIdx.x & 31u) == 0u && mask) base = atomicAdd(wb.counts + 0, (uint32_t)__popc(mask));
+        base = __shfl_sync(0xFFFFFFFFu, base, 0);
+        if (!covered) return;
+        wb.queue[0][base + __popc(mask & ((1u << (threadIdx.x & 31u)) - 1u))] = path;
+    }
 
     const uint32_t width = rd.textureDims[0];
     uint32_t seed = px + (py + 74813u) * width * ((fp.seedFrame + frame * fp.seedStride) + 1u);
@@ -112,8 +118,7 @@ generateKernel(const __grid_constant__ FrameParams fp, const WavefrontBuffers wb
 
     wb.rayO[path] = make_float4(o.x, o.y, o.z, __uint_as_float(seed));
     wb.rayD[path] = make_float4(d.x, d.y, d.z, __uint_as_float(py * width + px));
-    wb.radiance[path] = make_float4(0.f, 0.f, 0.f, __uint_as_float(0u));
-    wb.throughput[path] = make_float4(1.f, 1.f, 1.f, 0.f);
+    /* radiance (0, 0, 0 | bounce 0) and throughput (1, 1, 1) of a new path are not stored: shadeKernel knows them at bounce 0 */
     if (fp.aov) {
         okrt_aov av;
         av.hitKind = 0u; av.hitIdx = 0xFFFFFFFFu; av.triIdx = 0xFFFFFFFFu; av.baryU = 0.f; av.baryV = 0.f; av.distance = OKRT_FLT_MAX;
@@ -509,7 +514,12 @@ shadeKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ Frame
         hbEarly = wb.hitB[path];
     }
     if (active && (late || hbEarly != kHitPending)) {
-        const float4 ro = wb.rayO[path], rdv = wb.rayD[path], li = wb.radiance[path], th = wb.throughput[path];
+        const float4 ro = wb.rayO[path], rdv = wb.rayD[path];
+        float4 li, th;
+        if (bounce == 0u) {                      /* a new path: light 0, bounce 0, contribution 1 (generateKernel stores neither) */
+            li = make_float4(0.f, 0.f, 0.f, __uint_as_float(0u));
+            th = make_float4(1.f, 1.f, 1.f, late ? wb.throughput[path].w : 0.f);
+        } else { li = wb.radiance[path]; th = wb.throughput[path]; }
         const float4 ha = wb.hitA[path];
         const uint32_t hb = late ? __float_as_uint(th.w) : hbEarly;
         PathState ps;
