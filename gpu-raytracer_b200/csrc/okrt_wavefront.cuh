@@ -509,18 +509,19 @@ shadeKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ Frame
     bool survives = false;
     uint32_t path = 0u;
     uint32_t hbEarly = 0u;
+    float4 ro, rdv, li, th, ha;
     if (active) {
+        /* the whole path record is requested at once, before hitB says whether the path is this launch's to shade (one memory
+         * latency instead of two in a row; a path still with the reference-order kernel is one in ten thousand) */
         path = late ? wb.fallbackQueue[k] : (queueIn ? __ldg(queueIn + k) : k);
         hbEarly = wb.hitB[path];
-    }
-    if (active && (late || hbEarly != kHitPending)) {
-        const float4 ro = wb.rayO[path], rdv = wb.rayD[path];
-        float4 li, th;
+        ro = wb.rayO[path]; rdv = wb.rayD[path]; ha = wb.hitA[path];
         if (bounce == 0u) {                      /* a new path: light 0, bounce 0, contribution 1 (generateKernel stores neither) */
             li = make_float4(0.f, 0.f, 0.f, __uint_as_float(0u));
             th = make_float4(1.f, 1.f, 1.f, late ? wb.throughput[path].w : 0.f);
         } else { li = wb.radiance[path]; th = wb.throughput[path]; }
-        const float4 ha = wb.hitA[path];
+    }
+    if (active && (late || hbEarly != kHitPending)) {
         const uint32_t hb = late ? __float_as_uint(th.w) : hbEarly;
         PathState ps;
         ps.o = v3(ro.x, ro.y, ro.z); ps.seed = __float_as_uint(ro.w);
