@@ -374,25 +374,47 @@ __device__ __forceinline__ V3 bilerp(V3 c00, V3 c10, V3 c01, V3 c11, float fx, f
 /* RaytracerCS.hlsl:133-136 [Q12]: bilinear, WRAP, lod 0.  Four point fetches through the texture
  * unit (uchar4, no hardware filtering) and a float32 lerp: D3D's 8-bit fixed-point filter weights
  * are not reproducible on a CPU, the float lerp is. */
-__device__ __forceinline__ V3 sampleTexture(const DeviceScene& s, uint32_t textureIdx, V2 uv)
+/* the four taps of a uv: every layer of the array has the same size, so all maps of a hit (albedo, roughness, metallic, specular,
+ * normal) share them — computed once per hit, not once per map */
+struct TexTaps { float cx0, cx1, cy0, cy1, fx, fy; };
+__device__ __forceinline__ TexTaps textureTaps(const DeviceScene& s, V2 uv)
 {
-    if (s.texLayers == 0u) return v3(0.f, 0.f, 0.f);
-    const int layer = (int)(textureIdx < s.texLayers ? textureIdx : s.texLayers - 1u);
+    TexTaps t;
     const int N = (int)s.texSize;
     const float u = finitef_(uv.x) ? uv.x : 0.0f, v = finitef_(uv.y) ? uv.y : 0.0f;
     float x = u * (float)N - 0.5f, y = v * (float)N - 0.5f;
     if (!(fabsf(x) < 1.0e9f)) x = 0.0f;
     if (!(fabsf(y) < 1.0e9f)) y = 0.0f;
     const float xf = floorf(x), yf = floorf(y);
-    const float fx = x - xf, fy = y - yf;
+    t.fx = x - xf; t.fy = y - yf;
     const int x0 = wrapIndex(xf, N, s.texInvSize), y0 = wrapIndex(yf, N, s.texInvSize);
     const int x1 = x0 + 1 == N ? 0 : x0 + 1;
     const int y1 = y0 + 1 == N ? 0 : y0 + 1;
-    const uchar4 t00 = tex2DLayered<uchar4>(s.textures, (float)x0 + 0.5f, (float)y0 + 0.5f, layer);
-    const uchar4 t10 = tex2DLayered<uchar4>(s.textures, (float)x1 + 0.5f, (float)y0 + 0.5f, layer);
-    const uchar4 t01 = tex2DLayered<uchar4>(s.textures, (float)x0 + 0.5f, (float)y1 + 0.5f, layer);
-    const uchar4 t11 = tex2DLayered<uchar4>(s.textures, (float)x1 + 0.5f, (float)y1 + 0.5f, layer);
-    return bilerp(texelRgb(t00), texelRgb(t10), texelRgb(t01), texelRgb(t11), fx, fy);
+    t.cx0 = (float)x0 + 0.5f; t.cx1 = (float)x1 + 0.5f; t.cy0 = (float)y0 + 0.5f; t.cy1 = (float)y1 + 0.5f;
+    return t;
+}
+struct TexQuad { uchar4 t00, t10, t01, t11; };
+__device__ __forceinline__ TexQuad fetchQuad(const DeviceScene& s, uint32_t textureIdx, const TexTaps& t)
+{
+    const int layer = (int)(textureIdx < s.texLayers ? textureIdx : s.texLayers - 1u);
+    TexQuad q;
+    q.t00 = tex2DLayered<uchar4>(s.textures, t.cx0, t.cy0, layer);
+    q.t10 = tex2DLayered<uchar4>(s.textures, t.cx1, t.cy0, layer);
+    q.t01 = tex2DLayered<uchar4>(s.textures, t.cx0, t.cy1, layer);
+    q.t11 = tex2DLayered<uchar4>(s.textures, t.cx1, t.cy1, layer);
+    return q;
+}
+__device__ __forceinline__ V3 filterQuad(const TexQuad& q, const TexTaps& t)
+{
+    return bilerp(texelRgb(q.t00), texelRgb(q.t10), texelRgb(q.t01), texelRgb(q.t11), t.fx, t.fy);
+}
+/* RaytracerCS.hlsl:133-136 [Q12]: bilinear, WRAP, lod 0.  Four point fetches through the texture
+ * unit (uchar4, no hardware filtering) and a float32 lerp: D3D's 8-bit fixed-point filter weights
+ * are not reproducible on a CPU, the float lerp is. */
+__device__ __forceinline__ V3 sampleTexture(const DeviceScene& s, uint32_t textureIdx, const TexTaps& t)
+{
+    if (s.texLayers == 0u) return v3(0.f, 0.f, 0.f);
+    return filterQuad(fetchQuad(s, textureIdx, t), t);
 }
 
 /* RaytracerCS.hlsl:86-88 [Q13] */
@@ -967,23 +989,30 @@ namespace okrt {
 
 /* ------------------------------------------------------------ hit resolve
  * RaytracerCS.hlsl:336-392 [Q8] */
-__device__ __forceinline__ void findMaterialTextureColours(const DeviceScene& s, okrt_material& m, V2 uv)   /* :138-165 */
+__device__ __forceinline__ void findMaterialTextureColours(const DeviceScene& s, okrt_material& m, const TexTaps& taps)   /* :138-165 */
 {
+    if (s.texLayers == 0u) {                                   /* no array bound: a map reads as (0, 0, 0) */
+        if (m.albedoTextureIdx != 0xFFFFFFFFu) { m.albedo[0] = 0.f; m.albedo[1] = 0.f; m.albedo[2] = 0.f; }
+        if (m.roughnessTextureIdx != 0xFFFFFFFFu) m.roughness = fminf(fmaxf(0.f, m.roughness), 1.f);
+        if (m.metallicTextureIdx != 0xFFFFFFFFu) m.metallic = fminf(fmaxf(0.f, m.metallic), 1.f);
+        if (m.specularTextureIdx != 0xFFFFFFFFu) m.specular = fminf(fmaxf(0.f, m.specular), 1.f);
+        return;
+    }
     if (m.albedoTextureIdx != 0xFFFFFFFFu) {
-        const V3 t = sampleTexture(s, m.albedoTextureIdx, uv);
+        const V3 t = sampleTexture(s, m.albedoTextureIdx, taps);
         m.albedo[0] = t.x; m.albedo[1] = t.y; m.albedo[2] = t.z;
     }
     if (m.roughnessTextureIdx != 0xFFFFFFFFu)
-        m.roughness = fminf(fmaxf(sampleTexture(s, m.roughnessTextureIdx, uv).x, m.roughness), 1.f);
+        m.roughness = fminf(fmaxf(sampleTexture(s, m.roughnessTextureIdx, taps).x, m.roughness), 1.f);
     if (m.metallicTextureIdx != 0xFFFFFFFFu)
-        m.metallic = fminf(fmaxf(sampleTexture(s, m.metallicTextureIdx, uv).x, m.metallic), 1.f);
+        m.metallic = fminf(fmaxf(sampleTexture(s, m.metallicTextureIdx, taps).x, m.metallic), 1.f);
     if (m.specularTextureIdx != 0xFFFFFFFFu)
-        m.specular = fminf(fmaxf(sampleTexture(s, m.specularTextureIdx, uv).x, m.specular), 1.f);
+        m.specular = fminf(fmaxf(sampleTexture(s, m.specularTextureIdx, taps).x, m.specular), 1.f);
 }
 
-__device__ __forceinline__ V3 sampleNormalMap(const DeviceScene& s, uint32_t textureIdx, V2 uv, V3 normal, V3 tangent, V3 bitangent)   /* :167-175 */
+__device__ __forceinline__ V3 sampleNormalMap(const DeviceScene& s, uint32_t textureIdx, const TexTaps& taps, V3 normal, V3 tangent, V3 bitangent)   /* :167-175 */
 {
-    V3 sn = sampleTexture(s, textureIdx, uv);
+    V3 sn = sampleTexture(s, textureIdx, taps);
     sn = sn * 2.f - v3(1.f, 1.f, 1.f);
     const V3 r = v3((sn.x * tangent.x + sn.y * bitangent.x) + sn.z * normal.x,
                     (sn.x * tangent.y + sn.y * bitangent.y) + sn.z * normal.y,
@@ -1009,12 +1038,13 @@ __device__ __forceinline__ void resolveHit(const DeviceScene& s, V3 o, V3 d, con
         V2 uv;                                                /* normalToUV :77-84 */
         uv.x = okm::atan2_(hitNormal.x, hitNormal.z) / (2 * OKRT_PI) + 0.5f;
         uv.y = hitNormal.y * 0.5f + 0.5f;
+        const TexTaps taps = textureTaps(s, uv);
         if (sf.material.normalMapIdx != 0xFFFFFFFFu) {
             const V3 tangent = normalize(cross(v3(0.f, 1.f, 0.f), hitNormal));
             const V3 bitangent = normalize(cross(tangent, hitNormal));
-            sf.worldNormal = sampleNormalMap(s, sf.material.normalMapIdx, uv, hitNormal, tangent, bitangent);
+            sf.worldNormal = sampleNormalMap(s, sf.material.normalMapIdx, taps, hitNormal, tangent, bitangent);
         } else sf.worldNormal = hitNormal;
-        findMaterialTextureColours(s, sf.material, uv);
+        findMaterialTextureColours(s, sf.material, taps);
     } else {                                                  /* mesh, :364-391 */
         const okrt_mesh_instance& inst = s.instances[hit.idx];
         loadMaterial(sf.material, &inst.material);
@@ -1027,14 +1057,15 @@ __device__ __forceinline__ void resolveHit(const DeviceScene& s, V3 o, V3 d, con
         uv.y = (s1.w * bu + s3.x * bv) + s3.z * bw;
         const V3 n0 = v3(s0.x, s0.y, s0.z), n1 = v3(s1.x, s1.y, s1.z), n2 = v3(s2.x, s2.y, s2.z);
         V3 normal = normalize(mulDir((n0 * bu + n1 * bv) + n2 * bw, inst.transformMatrix));
+        const TexTaps taps = textureTaps(s, uv);
         if (sf.material.normalMapIdx != 0xFFFFFFFFu) {
             const V3 g0 = v3(__ldg(ti + 5), __ldg(ti + 6), __ldg(ti + 7)), g1 = v3(__ldg(ti + 16), __ldg(ti + 17), __ldg(ti + 18)), g2 = v3(__ldg(ti + 27), __ldg(ti + 28), __ldg(ti + 29));
             const V3 b0 = v3(__ldg(ti + 8), __ldg(ti + 9), __ldg(ti + 10)), b1 = v3(__ldg(ti + 19), __ldg(ti + 20), __ldg(ti + 21)), b2 = v3(__ldg(ti + 30), __ldg(ti + 31), __ldg(ti + 32));
             const V3 tangent = normalize(mulDir((g0 * bu + g1 * bv) + g2 * bw, inst.transformMatrix));
             const V3 bitangent = normalize(mulDir((b0 * bu + b1 * bv) + b2 * bw, inst.transformMatrix));
-            sf.worldNormal = sampleNormalMap(s, sf.material.normalMapIdx, uv, normal, tangent, bitangent);
+            sf.worldNormal = sampleNormalMap(s, sf.material.normalMapIdx, taps, normal, tangent, bitangent);
         } else sf.worldNormal = normal;
-        findMaterialTextureColours(s, sf.material, uv);
+        findMaterialTextureColours(s, sf.material, taps);
     }
 }
 
