@@ -575,13 +575,16 @@ int launchWavefront(okrt_renderer* r, const FrameParams& fp, bool instrumented)
         /* The reference-order kernel decides a few hundred rays per launch and lasts one bounded traversal (~100 us of
          * dependent loads): on the lane's second stream it runs BESIDE the main shade launch, which skips its paths (kHitPending);
          * a late shade launch over the fallback queue follows. */
-        OKRT_CUDA(cudaEventRecord(lane.evFork, st));
-        OKRT_CUDA(cudaStreamWaitEvent(lane.streamBeside, lane.evFork, 0));
-        traceFallbackKernel<<<fallbackGrid, 128, 0, lane.streamBeside>>>(scene, fp, wb, b);
-        OKRT_CUDA(cudaEventRecord(lane.evJoin, lane.streamBeside));
+        static const bool beside = [] { const char* e = std::getenv("OKRT_FALLBACK_BESIDE"); return e ? std::atoi(e) != 0 : true; }();
+        if (beside) {
+            OKRT_CUDA(cudaEventRecord(lane.evFork, st));
+            OKRT_CUDA(cudaStreamWaitEvent(lane.streamBeside, lane.evFork, 0));
+            traceFallbackKernel<<<fallbackGrid, 128, 0, lane.streamBeside>>>(scene, fp, wb, b);
+            OKRT_CUDA(cudaEventRecord(lane.evJoin, lane.streamBeside));
+        } else traceFallbackKernel<<<fallbackGrid, 128, 0, st>>>(scene, fp, wb, b);
         if (instrumented) shadeKernel<true><<<shadeGrid, 128, 0, st>>>(scene, fp, wb, qin, qout, b, 0u);
         else shadeKernel<false><<<shadeGrid, 128, 0, st>>>(scene, fp, wb, qin, qout, b, 0u);
-        OKRT_CUDA(cudaStreamWaitEvent(st, lane.evJoin, 0));
+        if (beside) OKRT_CUDA(cudaStreamWaitEvent(st, lane.evJoin, 0));
         if (instrumented) shadeKernel<true><<<fallbackGrid, 128, 0, st>>>(scene, fp, wb, qin, qout, b, 1u);
         else shadeKernel<false><<<fallbackGrid, 128, 0, st>>>(scene, fp, wb, qin, qout, b, 1u);
         r->launches += 4;                                  /* traversal, fallback, main shade, late shade */
