@@ -546,6 +546,7 @@ int launchWavefront(okrt_renderer* r, const FrameParams& fp, bool instrumented)
     const unsigned wideGrid = std::min<unsigned>((unsigned)(r->numSms * std::min(r->blocksPerSmWide, traceBlocksEnv)), std::max(1u, flatGrid));
     unsigned shadeGrid = std::min<unsigned>((unsigned)(r->numSms * OKRT_SHADE_MIN_BLOCKS * (shadeWaves ? std::max(1, std::atoi(shadeWaves)) : 16)), std::max(1u, flatGrid));
     if (shadeBlocksEnv) shadeGrid = std::min<unsigned>((unsigned)(r->numSms * shadeBlocksEnv), std::max(1u, flatGrid));
+    shadeGrid = std::min<unsigned>(shadeGrid, std::max(1u, (flatGrid + kShadePathsPerThread - 1u) / kShadePathsPerThread));
     const unsigned fallbackGrid = std::min<unsigned>((unsigned)(r->numSms * 8), std::max(1u, flatGrid));   /* 4 rays (warps) per block */
     if (r->timingPending) { OKRT_CUDA(cudaEventRecord(r->evStart, st)); r->timingPending = false; }
     OKRT_CUDA(cudaMemsetAsync(wb.counts, 0, kCountWords * sizeof(uint32_t), st));

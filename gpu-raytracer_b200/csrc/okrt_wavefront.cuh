@@ -485,6 +485,12 @@ traceWideKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ F
 #ifndef OKRT_SHADE_MIN_BLOCKS
 #define OKRT_SHADE_MIN_BLOCKS 8
 #endif
+/* paths a thread shades per trip before the block appends its survivors to the next queue (one atomic and two barriers per trip) */
+#ifndef OKRT_SHADE_PATHS_PER_THREAD
+#define OKRT_SHADE_PATHS_PER_THREAD 1
+#endif
+constexpr uint32_t kShadePathsPerThread = OKRT_SHADE_PATHS_PER_THREAD;
+static_assert(kShadePathsPerThread == 1u || kShadePathsPerThread == 2u, "one or two");
 template <bool kInstrumented>
 __global__ void __launch_bounds__(128, OKRT_SHADE_MIN_BLOCKS)
 shadeKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ FrameParams fp, const WavefrontBuffers wb,
@@ -503,11 +509,17 @@ shadeKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ Frame
     }
     /* the grid is sized for the machine, not for the queue (whose length only the device knows): a block walks the
      * queue in grid strides, the trip count is uniform within a block */
-    for (uint32_t first = blockIdx.x * blockDim.x; first < count; first += gridDim.x * blockDim.x) {
-    const uint32_t k = first + threadIdx.x;
+    constexpr uint32_t kSpt = kShadePathsPerThread;
+    for (uint32_t first = blockIdx.x * blockDim.x * kSpt; first < count; first += gridDim.x * blockDim.x * kSpt) {
+    bool survives = false, keep0 = false;
+    uint32_t path = 0u, keepPath0 = 0u;
+#pragma unroll 1
+    for (uint32_t h = 0u; h < kSpt; h++) {
+    if (kSpt == 2u && h == 1u) { keep0 = survives; keepPath0 = path; }
+    const uint32_t k = first + h * blockDim.x + threadIdx.x;
     const bool active = k < count;
-    bool survives = false;
-    uint32_t path = 0u;
+    survives = false;
+    path = 0u;
     uint32_t hbEarly = 0u;
     float4 ro, rdv, li, th, ha;
     if (active) {
@@ -563,22 +575,25 @@ shadeKernel(const __grid_constant__ DeviceScene s, const __grid_constant__ Frame
             survives = true;
         }
     }
+    }
     /* surviving paths -> next queue, one atomic per block (every warp of every block adding to the same counter is
      * half a million same-address atomics per launch) */
     const uint32_t mask = __ballot_sync(0xFFFFFFFFu, survives);
+    const uint32_t mask0 = kSpt == 2u ? __ballot_sync(0xFFFFFFFFu, keep0) : 0u;
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     uint32_t* const ws = warpSurvivors[trip & 1u];
-    if (lane == 0u) ws[warp] = (uint32_t)__popc(mask);
+    if (lane == 0u) ws[warp] = (uint32_t)(__popc(mask) + __popc(mask0));
     __syncthreads();
     if (threadIdx.x == 0u) {
         const uint32_t total = ws[0] + ws[1] + ws[2] + ws[3];
         blockBase[trip & 1u] = total ? atomicAdd(wb.counts + 2u * (bounce + 1u), total) : 0u;
     }
     __syncthreads();
-    if (survives) {
+    if (survives || keep0) {
         uint32_t base = blockBase[trip & 1u];
         for (uint32_t w = 0; w < warp; w++) base += ws[w];
-        queueOut[base + __popc(mask & ((1u << lane) - 1u))] = path;
+        if (keep0) queueOut[base + __popc(mask0 & ((1u << lane) - 1u))] = keepPath0;
+        if (survives) queueOut[base + __popc(mask0) + __popc(mask & ((1u << lane) - 1u))] = path;
     }
     trip++;                          /* the next trip writes the other copy; the one after it is two barriers away */
     }
