@@ -109,3 +109,18 @@ def test_empty_and_degenerate_meshes(okrt):
     assert list(g.meshDescs["numBvhNodes"]) == [1, 1, 1]
     assert g.bvhNodes[0]["triStart"] == 0 and g.bvhNodes[0]["triEnd"] == 0
     assert g.bvhNodes[2]["triEnd"] - g.bvhNodes[2]["triStart"] == 20
+
+
+def test_cmake_lists_every_source_the_in_tree_build_compiles():
+    """CMakeLists.txt and gpu-raytracer_b200/build.py are two descriptions of one library: same translation units."""
+    import importlib.util
+    import os
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("okrt_build_for_test", os.path.join(root, "gpu-raytracer_b200", "build.py"))
+    b = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(b)
+    cmake = open(os.path.join(root, "CMakeLists.txt")).read()
+    listed = set(re.findall(r"\$\{CSRC\}/(\w+\.(?:cu|cpp))", cmake))
+    built = {os.path.basename(s) for s in list(b.HOST_SOURCES) + list(b.DEVICE_SOURCES)}
+    assert listed == built, (sorted(listed), sorted(built))
