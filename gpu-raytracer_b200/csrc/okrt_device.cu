@@ -544,8 +544,15 @@ int launchWavefront(okrt_renderer* r, const FrameParams& fp, bool instrumented)
     const unsigned flatGrid = (unsigned)((paths + 127) / 128);
     /* persistent traversal grid: the whole machine (12 blocks per SM) when batches run one after the other; with several batches
      * in flight a few block slots per SM are left to the other lanes' kernels, which would otherwise wait for this kernel's last
-     * block (measured: 10 per SM +0.1-0.4 % for full-image batches, 8 per SM +1.0-1.1 % for batches of a quarter or an eighth) */
-    const int traceBlocksShared = laneCount(r) > 1 && !instrumented ? (paths <= ((size_t)1 << 23) ? 8 : 10) : r->blocksPerSmTrace;
+     * block (measured: 10 per SM +0.1-0.4 % for full-image batches, 8 per SM +1.0-1.1 % for batches of a quarter or an eighth;
+     * alone, a kernel on 8 or 10 per SM loses 2-6 %) */
+    bool othersInFlight = false;                /* is the previous batch still on the device?  (a caller that synchronises after
+                                                 * every call never has two batches in flight, whatever the lane count) */
+    if (laneCount(r) > 1 && !instrumented && r->lastLane >= 0 && r->lanes[r->lastLane].evDone) {
+        othersInFlight = cudaEventQuery(r->lanes[r->lastLane].evDone) == cudaErrorNotReady;
+        cudaGetLastError();
+    }
+    const int traceBlocksShared = othersInFlight ? (paths <= ((size_t)1 << 23) ? 8 : 10) : r->blocksPerSmTrace;
     const unsigned traceGrid = std::min<unsigned>((unsigned)(r->numSms * std::min(std::min(r->blocksPerSmTrace, traceBlocksShared), traceBlocksEnv)), std::max(1u, flatGrid));
     const unsigned wideGrid = std::min<unsigned>((unsigned)(r->numSms * std::min(r->blocksPerSmWide, traceBlocksEnv)), std::max(1u, flatGrid));
     unsigned shadeGrid = std::min<unsigned>((unsigned)(r->numSms * OKRT_SHADE_MIN_BLOCKS * (shadeWaves ? std::max(1, std::atoi(shadeWaves)) : 16)), std::max(1u, flatGrid));
