@@ -585,6 +585,23 @@ def main():
                               "segments": [gpu_segments, int(o["segments"])],
                               "against": "oracle (CPU restatement of RaytracerCS.hlsl): every RGBA32F accumulation word and the segment count"}
             failed = not ok
+            # the same frame by the reference's own shader text compiled as C++ (oracle/_ref/libokrt_ref_shader.so, when it travelled)
+            try:
+                from oracle import binding as oracle_binding
+                ref_shader = oracle_binding.load_ref_shader()
+            except Exception:
+                ref_shader = None
+            if ref_shader is not None:
+                scene = oracle_binding.oracle_scene(oracle_binding.load(), host, envFaces=env)
+                rd1 = host["rd"].copy()
+                rd1[0]["numAccumulationFrames"] = 1
+                t0 = time.perf_counter()
+                want = ref_shader.render(scene, rd1, MAX_BOUNCES)
+                bad_ref = np.any(acc.view(np.uint32) != want["accum"].view(np.uint32), axis=2)
+                line["parity"]["reference_shader"] = {"bit_exact": bool(not bad_ref.any()), "differing_pixels": int(bad_ref.sum()),
+                                                      "seconds": round(time.perf_counter() - t0, 1),
+                                                      "what": "RaytracerCS.hlsl + GPU-Utilities.hlsli + GPU-Structs.hlsli compiled as C++ (oracle/ref_shader_driver.cpp)"}
+                failed = failed or bool(bad_ref.any())
         if args.traversal == "fast":
             line["roofline"] = trace_roofline(okrt, host, env, local_rank, alone["trace_ms"], alone["trace_launches"], alone["dev_ms"], alone["segments"], peaks)
             line["one_batch_in_flight"] = {"ms_per_step": alone["dev_ms"] / alone["steps"], "value": alone["segments"] / (alone["dev_ms"] * 1e-3) / 1e6,

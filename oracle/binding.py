@@ -13,6 +13,7 @@ ROOT = os.path.dirname(ORACLE_DIR)
 ORACLE_LIB = os.path.join(ORACLE_DIR, "_build", "libokrt_oracle.so")
 REF_LIB = os.path.join(ORACLE_DIR, "_ref", "libokrt_ref.so")
 REF_OCTREE_LIB = os.path.join(ORACLE_DIR, "_ref", "libokrt_ref_octree.so")
+REF_SHADER_LIB = os.path.join(ORACLE_DIR, "_ref", "libokrt_ref_shader.so")
 
 MATH_CANONICAL, MATH_LIBM = 0, 1
 
@@ -35,9 +36,11 @@ def build_oracle(force=False):
 def build_ref():
     """Compiles the reference's BvhBuilder.cpp where /root/reference exists; otherwise keeps the prebuilt file."""
     if os.path.exists("/root/reference/source/Graphics/BvhBuilder.cpp"):
-        shims = [os.path.join(ORACLE_DIR, f) for f in ("ref_shim.cpp", "ref_octree_shim.cpp", "Makefile")]
-        stale = not os.path.exists(REF_LIB) or not os.path.exists(REF_OCTREE_LIB)
-        stale = stale or any(os.path.getmtime(f) > min(os.path.getmtime(REF_LIB), os.path.getmtime(REF_OCTREE_LIB)) for f in shims)
+        shims = [os.path.join(ORACLE_DIR, f) for f in ("ref_shim.cpp", "ref_octree_shim.cpp", "ref_shader_driver.cpp",
+                                                       os.path.join("ref_stubs", "hlsl_shim.h"), "oracle_math.h", "Makefile")]
+        libs = (REF_LIB, REF_OCTREE_LIB, REF_SHADER_LIB)
+        stale = not all(os.path.exists(l) for l in libs)
+        stale = stale or any(os.path.getmtime(f) > min(os.path.getmtime(l) for l in libs) for f in shims)
         if stale:
             subprocess.run(["make", "-s", "-C", ORACLE_DIR, "ref"], check=True)
     return REF_LIB if os.path.exists(REF_LIB) else None
@@ -168,6 +171,43 @@ def load():
     if _oracle is None:
         _oracle = Oracle(ctypes.CDLL(build_oracle()))
     return _oracle
+
+
+class RefShader:
+    """The reference's own compute shader text compiled as C++ (oracle/ref_shader_driver.cpp, oracle/ref_stubs/hlsl_shim.h)."""
+
+    def __init__(self, lib):
+        self.lib = lib
+        lib.ref_shader_render.restype = _U
+        lib.ref_shader_render.argtypes = [ctypes.POINTER(OracleScene), _P, _U, _U, _P, _P, _P, _I]
+        lib.ref_shader_description.restype = ctypes.c_char_p
+
+    def render(self, scene, rd, maxBounces, coverAll=0, accum=None, threads=0):
+        """One RayTracer::render(): rd as uploaded (numAccumulationFrames already advanced).  accum (H, W, 4) float32 is u1, read
+        and written.  Returns dict(accum, result_float, result): result_float is what main() stores into u0 before the UNORM8
+        conversion, result its RGBA8 form."""
+        W, H = int(rd[0]["textureDims"][0]), int(rd[0]["textureDims"][1])
+        if accum is None:
+            accum = np.zeros((H, W, 4), np.float32)
+        result_f = np.zeros((H, W, 4), np.float32)
+        result = np.zeros((H, W, 4), np.uint8)
+        self.lib.ref_shader_render(ctypes.byref(scene), rd.ctypes.data_as(_P), int(maxBounces), int(coverAll),
+                                   accum.ctypes.data_as(_P), result_f.ctypes.data_as(_P), result.ctypes.data_as(_P), int(threads))
+        return dict(accum=accum, result_float=result_f, result=result)
+
+
+_ref_shader = None
+
+
+def load_ref_shader():
+    """None where neither /root/reference nor a prebuilt oracle/_ref/libokrt_ref_shader.so exists."""
+    global _ref_shader
+    if _ref_shader is None:
+        build_ref()
+        if not os.path.exists(REF_SHADER_LIB):
+            return None
+        _ref_shader = RefShader(ctypes.CDLL(REF_SHADER_LIB))
+    return _ref_shader
 
 
 _ref_octree = None
