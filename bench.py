@@ -124,12 +124,32 @@ def oracle_frame(okrt, host, env, threads=0):
     cores = threads if threads > 0 else (os.cpu_count() or 1)
     cpu = {"value": out["segments"] / dt / 1e6, "unit": UNIT, "cores": cores, "kind": "port",
            "sample": "one full 1920x1080 frame, 1 spp, %d ray segments in %.1f s" % (out["segments"], dt)}
+    # where the reference's own shader text compiled as C++ travelled with the snapshot (oracle/_ref/libokrt_ref_shader.so), IT is
+    # the CPU baseline (kind "reference"); the port's rate stays beside it.  Same frame, same paths: the port's segment count.
+    ref_shader = load_reference_shader()
+    if ref_shader is not None:
+        t0 = time.perf_counter()
+        ref_shader.render(scene, rd, MAX_BOUNCES, threads=threads)
+        dtr = time.perf_counter() - t0
+        cpu = {"value": out["segments"] / dtr / 1e6, "unit": UNIT, "cores": cores, "kind": "reference",
+               "sample": "one full 1920x1080 frame, 1 spp, %d ray segments in %.1f s by the reference's RaytracerCS.hlsl compiled as C++" % (out["segments"], dtr),
+               "port_value": out["segments"] / dt / 1e6}
     return cpu, out
 
 
+def load_reference_shader():
+    try:
+        from oracle import binding as oracle_binding
+        return oracle_binding.load_ref_shader()
+    except Exception:
+        return None
+
+
 def run_reference_arm(args):
-    """--impl reference: the reference's CPU-runnable implementation of the path = the oracle port (the HLSL
-    itself needs D3D11: unavailable on this box), all host threads, each step a bounded sample of the workload."""
+    """--impl reference: the reference's own implementation of the path on the host cores — its shader text compiled as C++
+    (oracle/_ref/libokrt_ref_shader.so, kind "reference"; running the HLSL itself needs D3D11: unavailable on this box), or the
+    oracle port where that library did not travel.  All host threads, each step a bounded sample of the workload.  The compiled
+    shader has no segment counter: the port traces the same rows of the same frame outside the timed region (identical paths)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
@@ -142,20 +162,33 @@ def run_reference_arm(args):
     rows = np.array([y for y in range(HEIGHT) if (y // 8) % 8 == 0], np.uint32)     # every 8th 8-row band: 1/8 of the frame
     cores = os.cpu_count() or 1
 
+    ref_shader = load_reference_shader()
+    kind = "reference" if ref_shader is not None else "port"
+
+    def count(frame):
+        rd[0]["numAccumulationFrames"] = frame
+        return oracle.render(scene, rd, MAX_BOUNCES, row_list=rows)["segments"]
+
     def step(frame):
         rd[0]["numAccumulationFrames"] = frame
+        if ref_shader is not None:
+            ref_shader.render(scene, rd, MAX_BOUNCES, row_list=rows)
+            return 0
         return oracle.render(scene, rd, MAX_BOUNCES, row_list=rows)["segments"]
     for w in range(args.warmup):
         step(w + 1)
     t0 = time.perf_counter()
     segments = sum(step(args.warmup + k + 1) for k in range(args.steps))
     dt = time.perf_counter() - t0
+    if ref_shader is not None:
+        segments = sum(count(args.warmup + k + 1) for k in range(args.steps))      # untimed: the same rows of the same frames
     value = segments / dt / 1e6
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dt / max(1, args.steps) * 1e3, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args.gpus),
-            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
-                             "sample": "per step: every 8th 8-row band of the 1080p frame (1/8 of the pixels), 1 spp, %d host threads" % cores},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind,
+                             "sample": "per step: every 8th 8-row band of the 1080p frame (1/8 of the pixels), 1 spp, %d host threads; %s" % (
+                                 cores, "the reference's RaytracerCS.hlsl compiled as C++" if kind == "reference" else "oracle port")},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
     print(json.dumps(line))
 

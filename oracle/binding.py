@@ -180,9 +180,11 @@ class RefShader:
         self.lib = lib
         lib.ref_shader_render.restype = _U
         lib.ref_shader_render.argtypes = [ctypes.POINTER(OracleScene), _P, _U, _U, _P, _P, _P, _I]
+        lib.ref_shader_render_rows.restype = _U
+        lib.ref_shader_render_rows.argtypes = [ctypes.POINTER(OracleScene), _P, _U, _U, _P, _P, _P, _P, _U, _I]
         lib.ref_shader_description.restype = ctypes.c_char_p
 
-    def render(self, scene, rd, maxBounces, coverAll=0, accum=None, threads=0):
+    def render(self, scene, rd, maxBounces, coverAll=0, accum=None, threads=0, row_list=None):
         """One RayTracer::render(): rd as uploaded (numAccumulationFrames already advanced).  accum (H, W, 4) float32 is u1, read
         and written.  Returns dict(accum, result_float, result): result_float is what main() stores into u0 before the UNORM8
         conversion, result its RGBA8 form."""
@@ -191,8 +193,10 @@ class RefShader:
             accum = np.zeros((H, W, 4), np.float32)
         result_f = np.zeros((H, W, 4), np.float32)
         result = np.zeros((H, W, 4), np.uint8)
-        self.lib.ref_shader_render(ctypes.byref(scene), rd.ctypes.data_as(_P), int(maxBounces), int(coverAll),
-                                   accum.ctypes.data_as(_P), result_f.ctypes.data_as(_P), result.ctypes.data_as(_P), int(threads))
+        rl = None if row_list is None else np.ascontiguousarray(row_list, np.uint32)
+        self.lib.ref_shader_render_rows(ctypes.byref(scene), rd.ctypes.data_as(_P), int(maxBounces), int(coverAll),
+                                        accum.ctypes.data_as(_P), result_f.ctypes.data_as(_P), result.ctypes.data_as(_P),
+                                        None if rl is None else rl.ctypes.data_as(_P), 0 if rl is None else len(rl), int(threads))
         return dict(accum=accum, result_float=result_f, result=result)
 
 

@@ -20,10 +20,17 @@
  *     code (BvhBuilder.cpp compiled unmodified + its vendored glm) through
  *     oracle/_ref/libokrt_ref.so — see tests/test_oracle_vs_ref.py and the
  *     committed fixtures under tests/golden/.
- *   - Device path (HLSL): "parity unpinned" — the reference ships no tests, golden
- *     images or known-answer vectors for the shader, and cs_5_0 cannot be compiled
- *     or run without D3D11 (unavailable on this box).  The restatement follows the
- *     shader line by line; each function cites the lines it restates.
+ *   - Oct-tree (createOctTree / loadOctTree / refitOctTreeNode): PINNED against the
+ *     reference's own function text compiled into oracle/_ref/libokrt_ref_octree.so.
+ *   - Device path (HLSL): PINNED against the reference's own shader text compiled as
+ *     C++ (oracle/ref_shader_driver.cpp + oracle/ref_stubs/hlsl_shim.h ->
+ *     oracle/_ref/libokrt_ref_shader.so): oracle_render equals it word for word,
+ *     tests/test_cpu_ref_shader.py, fixtures tests/golden/ref_shader_*.npz.  What
+ *     nothing outside this repository pins: the conventions hlsl_shim.h lists
+ *     (intrinsic math bits, texture filtering, mul's summation order) — D3D11 leaves
+ *     them to the driver or hardware, and cs_5_0 cannot run without D3D11
+ *     (unavailable on this box).  The restatement follows the shader line by line;
+ *     each function cites the lines it restates.
  *
  * Semantics that differ between HLSL and C++ are restated deliberately; see the
  * Q-list in SURVEY.md §8.0 (Q1..Q15), referenced inline as [Qn].

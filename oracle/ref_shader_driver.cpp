@@ -63,8 +63,20 @@ const char* ref_shader_description(void)
  * accum: W*H float4 (u1, read and written); resultF: W*H float4 as main() stores it; result8 (may be NULL): the same as UNORM8.
  * coverAll = 0 runs the reference's thread grid (pixels beyond 16*(W/16) x 9*(H/9) are not touched). */
 extern "C" __attribute__((visibility("default")))
+uint32_t ref_shader_render_rows(const RefShaderScene* s, const void* rd, uint32_t maxBounces, uint32_t coverAll,
+                                float* accum, float* resultF, uint8_t* result8, const uint32_t* rowList, uint32_t numRows, int threads);
+
+extern "C" __attribute__((visibility("default")))
 uint32_t ref_shader_render(const RefShaderScene* s, const void* rd, uint32_t maxBounces, uint32_t coverAll,
                            float* accum, float* resultF, uint8_t* result8, int threads)
+{
+    return ref_shader_render_rows(s, rd, maxBounces, coverAll, accum, resultF, result8, nullptr, 0u, threads);
+}
+
+/* the same for the thread rows in rowList only (NULL: every row): a bounded sample of a frame for timing */
+extern "C" __attribute__((visibility("default")))
+uint32_t ref_shader_render_rows(const RefShaderScene* s, const void* rd, uint32_t maxBounces, uint32_t coverAll,
+                                float* accum, float* resultF, uint8_t* result8, const uint32_t* rowList, uint32_t numRows, int threads)
 {
     using namespace hlslref;
     std::memcpy(&renderData, rd, sizeof(RenderData));
@@ -90,8 +102,10 @@ uint32_t ref_shader_render(const RefShaderScene* s, const void* rd, uint32_t max
     for (unsigned t = 0; t < n; t++)
         pool.emplace_back([&]() {
             for (;;) {
-                const uint32_t y = nextRow.fetch_add(1);
-                if (y >= coveredH) break;
+                const uint32_t k = nextRow.fetch_add(1);
+                if (k >= (rowList ? numRows : coveredH)) break;
+                const uint32_t y = rowList ? rowList[k] : k;
+                if (y >= coveredH) continue;
                 for (uint32_t x = 0; x < coveredW; x++) {
                     uint3 id; id.x = x; id.y = y; id.z = 0u;
                     hlslref::main(id);
@@ -100,12 +114,12 @@ uint32_t ref_shader_render(const RefShaderScene* s, const void* rd, uint32_t max
         });
     for (auto& th : pool) th.join();
     if (result8)
-        for (uint32_t y = 0; y < coveredH; y++)
-            for (uint32_t x = 0; x < coveredW; x++)
+        for (uint32_t k = 0; k < (rowList ? numRows : coveredH); k++)
+            for (uint32_t x = 0, y = rowList ? rowList[k] : k; x < coveredW && y < coveredH; x++)
                 for (int k = 0; k < 4; k++) {
                     const float v = resultF[((size_t)y * W + x) * 4 + k];
                     /* D3D11 float -> UNORM8 [Q14]: saturate, scale by 255, add 0.5, truncate; NaN -> 0 */
                     result8[((size_t)y * W + x) * 4 + k] = (uint8_t)(std::fmin(std::fmax(v, 0.0f), 1.0f) * 255.0f + 0.5f);
                 }
-    return coveredW * coveredH;
+    return coveredW * (rowList ? numRows : coveredH);
 }
