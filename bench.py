@@ -235,6 +235,12 @@ def run_config(okrt, name, rm, sc, info, width, height, bounces, frames, env, de
         gseg = int(r.stats()["raySegments"])
         parity = {"bit_exact": bool(not bad.any()) and gseg == int(o["segments"]), "differing_pixels": int(bad.sum()),
                   "segments": [gseg, int(o["segments"])]}
+        ref_shader = load_reference_shader()
+        if ref_shader is not None:                       # the reference's own shader text compiled as C++, same frame
+            want = ref_shader.render(scene, rd1, bounces)
+            bad_ref = np.any(acc.view(np.uint32) != want["accum"].view(np.uint32), axis=2)
+            parity["reference_shader_bit_exact"] = bool(not bad_ref.any())
+            parity["bit_exact"] = parity["bit_exact"] and parity["reference_shader_bit_exact"]
     r.close()
     out = {"workload": "%s %dx%d maxBounces=%d, %d frames per call" % (info.get("name", name), width, height, bounces, frames),
            "value": seg / (ms * 1e-3) / 1e6, "unit": UNIT, "ms_per_frame": ms / (steps * frames), "ray_segments": seg,
