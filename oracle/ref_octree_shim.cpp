@@ -14,7 +14,9 @@
 #include <chrono>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
+#include <string_view>
 #include <stack>
 #include <vector>
 
@@ -48,7 +50,52 @@ static int okrt_silent_printf(const char*, ...) { return 0; }
 #include "octree_extract.inc"
 #undef printf
 
+/* ---- the reference's own text: RayTracer::loadEnvironmentMap, RayTracer.cpp:343-432 (row a13, the cube part).  stb_image and
+ * the D3D11 device are replaced: stbi_load hands out the caller's cross image, ID3D11Device::CreateTexture2D (ref_stubs/d3d11.h)
+ * passes the six faces the function has cut out of it to the sink below. */
+OkrtTextureSink g_okrtTextureSink = {nullptr};
+namespace Okay { ID3D11Device* getDevice() { static ID3D11Device dev; return &dev; } }
+enum { STBI_rgb_alpha = 4 };
+static const uint8_t* g_crossImage = nullptr;
+static int g_crossW = 0, g_crossH = 0;
+static unsigned char* stbi_load(const char*, int* w, int* h, int*, int channels)
+{
+    if (!g_crossImage) return nullptr;
+    const size_t bytes = (size_t)g_crossW * g_crossH * channels;
+    unsigned char* copy = (unsigned char*)std::malloc(bytes);
+    std::memcpy(copy, g_crossImage, bytes);
+    *w = g_crossW; *h = g_crossH;
+    return copy;
+}
+static void stbi_image_free(void* p) { std::free(p); }
+#include "envmap_extract.inc"
+
 #define REF_API extern "C" __attribute__((visibility("default")))
+
+static uint8_t* g_facesOut = nullptr;
+static uint32_t g_faceW = 0, g_faceH = 0;
+static void takeCubeFaces(const D3D11_TEXTURE2D_DESC* desc, const D3D11_SUBRESOURCE_DATA* data)
+{
+    g_faceW = desc->Width; g_faceH = desc->Height;
+    if (!g_facesOut || desc->ArraySize != 6u) return;
+    for (uint32_t f = 0; f < 6u; f++)
+        for (uint32_t y = 0; y < desc->Height; y++)
+            std::memcpy(g_facesOut + ((size_t)f * desc->Height + y) * desc->Width * 4, (const uint8_t*)data[f].pSysMem + (size_t)y * data[f].SysMemPitch,
+                        (size_t)desc->Width * 4);
+}
+
+/* crossRgba8: imgW x imgH RGBA8 (what stbi_load returns for the cross image); outFaces: 6 x (imgH/3) x (imgW/4) RGBA8 in the
+ * order the reference fills the cube's array slices (+X -X +Y -Y +Z -Z).  Returns faceW << 16 | faceH (0 on failure). */
+REF_API uint32_t ref_environment_cross_to_faces(const uint8_t* crossRgba8, uint32_t imgW, uint32_t imgH, uint8_t* outFaces)
+{
+    g_crossImage = crossRgba8; g_crossW = (int)imgW; g_crossH = (int)imgH;
+    g_facesOut = outFaces; g_faceW = g_faceH = 0;
+    g_okrtTextureSink.take = takeCubeFaces;
+    RayTracer rt;
+    rt.loadEnvironmentMap("cross");
+    g_okrtTextureSink.take = nullptr; g_crossImage = nullptr; g_facesOut = nullptr;
+    return (g_faceW << 16) | g_faceH;
+}
 
 struct ShimMeshEntity { float position[3], rotation[3], scale[3]; Material material; uint32_t meshID; };
 struct ShimSphereEntity { float position[3], rotation[3], scale[3]; Material material; float radius; };

@@ -268,3 +268,31 @@ def test_layout_build_is_deterministic(okrt):
     assert first[0] > 10000                                       # large enough for the parallel subtree path (ranges > 8192)
     for r in runs[1:]:
         assert tuple(r[k] for k in keys) == first
+
+
+def test_environment_cube_equals_reference(okrt, oracle, ref_octree):
+    """Row a13, the cube part: okrt_environment_cross_to_faces and the oracle's restatement against the reference's OWN
+    RayTracer::loadEnvironmentMap (RayTracer.cpp:343-432) compiled from its text (oracle/ref_octree_shim.cpp: stb_image and the
+    D3D11 device replaced, the six faces taken where the function hands them to CreateTexture2D) — random cross images of odd and
+    even sizes (imgW/4, imgH/3 truncate) and the reference's own Skybox2.jpg (down-sampled fixture)."""
+    abi = okrt.abi
+    rng = np.random.default_rng(9)
+    crosses = [rng.integers(0, 256, (h, w, 4), dtype=np.uint8) for (w, h) in ((48, 36), (64, 48), (51, 38), (130, 99), (16, 12))]
+    assets = os.path.join(GOLD, "assets_small.npz")
+    if os.path.exists(assets):
+        z = np.load(assets)
+        key = [k for k in z.files if "cross" in k.lower() or "sky" in k.lower()]
+        if key:
+            crosses.append(np.ascontiguousarray(z[key[0]]))
+    for cross in crosses:
+        H, W = cross.shape[:2]
+        fw, fh = W // 4, H // 3
+        want = np.zeros((6, fh, fw, 4), np.uint8)
+        packed = ref_octree.ref_environment_cross_to_faces(abi.ptr(cross), W, H, abi.ptr(want))
+        assert packed == (fw << 16 | fh)
+        got = np.zeros_like(want)
+        abi.check(abi.lib().okrt_environment_cross_to_faces(abi.ptr(cross), W, H, abi.ptr(got)))
+        assert np.array_equal(got, want)
+        of = np.zeros_like(want)
+        oracle.lib.oracle_environment_cross_to_faces(abi.ptr(cross), W, H, abi.ptr(of))
+        assert np.array_equal(of, want)
