@@ -228,6 +228,8 @@ def load_ref_octree():
         lib = ctypes.CDLL(REF_OCTREE_LIB)
         lib.ref_build_octree.restype = _U
         lib.ref_build_octree.argtypes = [_P, _P, _U, _P, _U, _P, _U, _U, _U, _P, _U, _P, _U, ctypes.POINTER(_U)]
+        lib.ref_render_data_after_projection.restype = None
+        lib.ref_render_data_after_projection.argtypes = [_P, _P, _F, _F, _F, _U, _U, _P]
         lib.ref_environment_cross_to_faces.restype = _U
         lib.ref_environment_cross_to_faces.argtypes = [_P, _U, _U, _P]
         _ref_octree = lib

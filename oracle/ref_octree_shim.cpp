@@ -70,7 +70,30 @@ static unsigned char* stbi_load(const char*, int* w, int* h, int*, int channels)
 static void stbi_image_free(void* p) { std::free(p); }
 #include "envmap_extract.inc"
 
+/* ---- the reference's own text: RayTracer::calculateProjectionData, RayTracer.cpp:268-308 (row a12) */
+#include "projection_extract.inc"
+
 #define REF_API extern "C" __attribute__((visibility("default")))
+
+/* The reference's whole constant buffer (RayTracer::RenderData, 240 bytes: its own default member initialisers plus what
+ * calculateProjectionData writes) for a camera entity with this Transform / Camera and a target of width x height. */
+static_assert(sizeof(RayTracer::RenderData) == 240, "cbuffer");
+REF_API void ref_render_data_after_projection(const float* camPos, const float* camRotDeg, float fov, float nearZ, float farZ,
+                                              uint32_t width, uint32_t height, void* out240)
+{
+    Scene scene;
+    Entity cam = scene.createEntity();
+    Transform& t = cam.getComponent<Transform>();
+    t.position = glm::vec3(camPos[0], camPos[1], camPos[2]);
+    t.rotation = glm::vec3(camRotDeg[0], camRotDeg[1], camRotDeg[2]);
+    Camera& c = cam.addComponent<Camera>(fov, nearZ);
+    c.farZ = farZ;
+    RayTracer rt;
+    rt.setScene(scene);
+    rt.m_renderData.textureDims = glm::uvec2(width, height);
+    rt.calculateProjectionData();
+    std::memcpy(out240, &rt.m_renderData, 240);
+}
 
 static uint8_t* g_facesOut = nullptr;
 static uint32_t g_faceW = 0, g_faceH = 0;

@@ -296,3 +296,33 @@ def test_environment_cube_equals_reference(okrt, oracle, ref_octree):
         of = np.zeros_like(want)
         oracle.lib.oracle_environment_cross_to_faces(abi.ptr(cross), W, H, abi.ptr(of))
         assert np.array_equal(of, want)
+
+
+def test_projection_data_equals_reference_text(okrt, oracle, ref_octree):
+    """Row a12: okrt_calculate_projection_data (and the oracle's) against the reference's OWN RayTracer::calculateProjectionData
+    text (RayTracer.cpp:268-308) compiled as a member of its own class with its own Scene / EnTT / glm
+    (oracle/ref_octree_shim.cpp).  The whole 240-byte constant buffer is compared: what the function writes AND the default
+    member initialisers of RayTracer::RenderData (RayTracer.h:129-157) against okrt_render_data_default."""
+    abi = okrt.abi
+    rng = np.random.default_rng(31)
+    sizes = [(1920, 1080), (3840, 2160), (512, 512), (320, 180), (1600, 900), (33, 77)]
+    for it in range(60):
+        pos = rng.uniform(-80, 80, 3).astype(np.float32)
+        rot = (rng.uniform(-180, 180, 3) if it % 5 else np.array([0.0, 90.0 * (it // 5), 0.0])).astype(np.float32)
+        fov, nz, fz = float(np.float32(rng.uniform(20, 110))), float(np.float32(rng.uniform(0.01, 1.0))), 1000.0
+        W, H = sizes[it % len(sizes)]
+        want = np.zeros(1, abi.RENDER_DATA)
+        ref_octree.ref_render_data_after_projection(abi.ptr(pos), abi.ptr(rot), fov, nz, fz, W, H, abi.ptr(want))
+        cam = np.zeros(1, abi.CAMERA)
+        cam[0]["position"], cam[0]["rotation"], cam[0]["fov"], cam[0]["nearZ"], cam[0]["farZ"] = pos, rot, fov, nz, fz
+        rd = abi.default_render_data()
+        rd[0]["textureDims"] = (W, H)                      # an input of the function (RayTracer::onResize sets it)
+        abi.check(abi.lib().okrt_calculate_projection_data(abi.ptr(cam), W, H, abi.ptr(rd)))
+        ro = abi.default_render_data()
+        ro[0]["textureDims"] = (W, H)
+        oracle.lib.oracle_calculate_projection_data(abi.ptr(pos), abi.ptr(rot), fov, nz, fz, W, H, abi.ptr(ro))
+        for f in abi.RENDER_DATA.names:
+            if f == "pad0":
+                continue                                   # uninitialised in the reference's struct
+            assert np.array_equal(rd[0][f], want[0][f]), (f, rd[0][f], want[0][f])
+            assert np.array_equal(ro[0][f], want[0][f]), ("oracle", f)
