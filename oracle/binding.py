@@ -230,6 +230,8 @@ def load_ref_octree():
         lib.ref_build_octree.argtypes = [_P, _P, _U, _P, _U, _P, _U, _U, _U, _P, _U, _P, _U, ctypes.POINTER(_U)]
         lib.ref_render_data_after_projection.restype = None
         lib.ref_render_data_after_projection.argtypes = [_P, _P, _F, _F, _F, _U, _U, _P]
+        lib.ref_load_mesh_and_bvh.restype = _U
+        lib.ref_load_mesh_and_bvh.argtypes = [_P, _U, _U, _U, _P, _P, _U, _P, _U, _P, ctypes.POINTER(_U)]
         lib.ref_environment_cross_to_faces.restype = _U
         lib.ref_environment_cross_to_faces.argtypes = [_P, _U, _U, _P]
         _ref_octree = lib

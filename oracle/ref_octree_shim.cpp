@@ -15,6 +15,7 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
+#include <map>
 #include <cstring>
 #include <string_view>
 #include <stack>
@@ -38,6 +39,14 @@ void updateBuffer(ID3D11Buffer*, const void*, size_t) {}
 GPUStorage::GPUStorage() : m_pBuffer(nullptr), m_pSRV(nullptr), m_capacity(0), m_elementByteWidth(0) {}
 GPUStorage::~GPUStorage() {}
 void GPUStorage::updateRaw(uint32_t, const void*) {}
+/* initiate keeps the initial data a caller hands over (RayTracer::loadMeshAndBvhData's triangle arrays); no buffer is created */
+static std::map<const GPUStorage*, std::vector<uint8_t>> g_storageData;
+void GPUStorage::initiate(uint32_t elementByteWidth, uint32_t capacity, const void* pData)
+{
+    std::vector<uint8_t>& v = g_storageData[this];
+    v.clear();
+    if (pData) v.assign((const uint8_t*)pData, (const uint8_t*)pData + (size_t)elementByteWidth * capacity);
+}
 RenderTexture::RenderTexture() {}
 RenderTexture::~RenderTexture() {}
 RayTracer::RayTracer() : m_pScene(nullptr), m_pResourceManager(nullptr), m_pTargetTexture(nullptr), m_pRenderDataBuffer(nullptr),
@@ -73,6 +82,13 @@ static void stbi_image_free(void* p) { std::free(p); }
 /* ---- the reference's own text: RayTracer::calculateProjectionData, RayTracer.cpp:268-308 (row a12) */
 #include "projection_extract.inc"
 
+/* ---- the reference's own text: RayTracer::loadMeshAndBvhData, RayTracer.cpp:120-217 (row a10: the flattening of the per-mesh
+ * trees into t0 / t1 / t2 and the mesh descriptors); BvhBuilder.cpp is compiled into this library unmodified */
+#include "Graphics/BvhBuilder.h"
+#define printf okrt_silent_printf
+#include "meshload_extract.inc"
+#undef printf
+
 #define REF_API extern "C" __attribute__((visibility("default")))
 
 /* The reference's whole constant buffer (RayTracer::RenderData, 240 bytes: its own default member initialisers plus what
@@ -93,6 +109,52 @@ REF_API void ref_render_data_after_projection(const float* camPos, const float* 
     rt.m_renderData.textureDims = glm::uvec2(width, height);
     rt.calculateProjectionData();
     std::memcpy(out240, &rt.m_renderData, 240);
+}
+
+struct ShimMeshView { const float* trianglesPos; const float* trianglesInfo; uint32_t numTriangles; float bounds[6]; };
+static_assert(sizeof(Okay::Triangle) == 36 && sizeof(Okay::TriangleInfo) == 132 && sizeof(GPUNode) == 36 && sizeof(MeshDesc) == 16, "wire structs");
+
+/* views: as okrt_mesh_view (include/okrt.h).  Outputs: t0 (36 B per triangle), t1 (132 B), t2 (36 B per node), 16-byte mesh
+ * descriptors.  Returns the node count (~0u if a capacity is too small); *outNumTris = triangles written. */
+REF_API uint32_t ref_load_mesh_and_bvh(const ShimMeshView* views, uint32_t numMeshes, uint32_t maxDepth, uint32_t maxLeafTriangles,
+                                       void* outTriPos, void* outTriInfo, uint32_t triCapacity, void* outNodes, uint32_t nodeCapacity,
+                                       void* outDescs, uint32_t* outNumTris)
+{
+    ResourceManager rm;
+    for (uint32_t m = 0; m < numMeshes; m++) {
+        const uint32_t nv = views[m].numTriangles * 3u;
+        MeshData md;
+        md.positions.resize(nv); md.normals.resize(nv); md.uvs.resize(nv); md.tangents.resize(nv); md.bitangents.resize(nv);
+        for (uint32_t v = 0; v < nv; v++) {
+            const float* p = views[m].trianglesPos + (size_t)v * 3;
+            const float* q = views[m].trianglesInfo + (size_t)v * 11;
+            md.positions[v] = glm::vec3(p[0], p[1], p[2]);
+            md.normals[v] = glm::vec3(q[0], q[1], q[2]);
+            md.uvs[v] = glm::vec2(q[3], q[4]);
+            md.tangents[v] = glm::vec3(q[5], q[6], q[7]);
+            md.bitangents[v] = glm::vec3(q[8], q[9], q[10]);
+        }
+        md.boundingBox.min = glm::vec3(views[m].bounds[0], views[m].bounds[1], views[m].bounds[2]);
+        md.boundingBox.max = glm::vec3(views[m].bounds[3], views[m].bounds[4], views[m].bounds[5]);
+        rm.m_meshes.emplace_back(md, "shim");
+    }
+    RayTracer rt;
+    rt.m_pResourceManager = &rm;
+    rt.loadMeshAndBvhData(maxDepth, maxLeafTriangles);
+    const std::vector<uint8_t>& pos = g_storageData[&rt.m_trianglePositions];
+    const std::vector<uint8_t>& info = g_storageData[&rt.m_triangleInfo];
+    const uint32_t numTris = (uint32_t)(pos.size() / sizeof(Okay::Triangle));
+    uint32_t result = (uint32_t)rt.m_bvhTreeNodes.size();
+    if (numTris > triCapacity || rt.m_bvhTreeNodes.size() > nodeCapacity) result = ~0u;
+    else {
+        std::memcpy(outTriPos, pos.data(), pos.size());
+        std::memcpy(outTriInfo, info.data(), info.size());
+        std::memcpy(outNodes, rt.m_bvhTreeNodes.data(), rt.m_bvhTreeNodes.size() * sizeof(GPUNode));
+        std::memcpy(outDescs, rt.m_meshDescs.data(), rt.m_meshDescs.size() * sizeof(MeshDesc));
+        *outNumTris = numTris;
+    }
+    g_storageData.erase(&rt.m_trianglePositions); g_storageData.erase(&rt.m_triangleInfo); g_storageData.erase(&rt.m_bvhTree);
+    return result;
 }
 
 static uint8_t* g_facesOut = nullptr;

@@ -326,3 +326,34 @@ def test_projection_data_equals_reference_text(okrt, oracle, ref_octree):
                 continue                                   # uninitialised in the reference's struct
             assert np.array_equal(rd[0][f], want[0][f]), (f, rd[0][f], want[0][f])
             assert np.array_equal(ro[0][f], want[0][f]), ("oracle", f)
+
+
+def test_geometry_build_equals_reference_text(okrt, ref_octree):
+    """Row a10 end to end: okrt_geometry_build (per-mesh SAH trees flattened into t0 / t1 / t2 + mesh descriptors) against the
+    reference's OWN RayTracer::loadMeshAndBvhData text (RayTracer.cpp:120-217) compiled as a member of its class, with its own
+    BvhBuilder.cpp, Mesh and ResourceManager (oracle/ref_octree_shim.cpp); the arrays it hands to GPUStorage::initiate are taken
+    there.  Every byte of the four arrays."""
+    abi = okrt.abi
+    cases = [(okrt.scenes.test_scene(with_textures=True), (30, 5)), (okrt.scenes.sponza_standin(5000, texture_size=16), (30, 5)),
+             (okrt.scenes.sponza_standin(3000, texture_size=16), (4, 2)), (okrt.scenes.glass_scene(segments=16, rings=10), (12, 1))]
+    for (rm, sc, info), (depth, leaf) in cases:
+        meshes = rm.meshes
+        geo = okrt.Geometry(meshes, depth, leaf)
+        views = (abi.MeshView * len(meshes))()
+        for i, m in enumerate(meshes):
+            views[i].trianglesPos = m.trianglesPos.ctypes.data
+            views[i].trianglesInfo = m.trianglesInfo.ctypes.data
+            views[i].numTriangles = len(m.trianglesPos)
+            for k in range(3):
+                views[i].boundingBox[k] = float(m.boundingBox[0][k])
+                views[i].boundingBox[3 + k] = float(m.boundingBox[1][k])
+        nt = sum(len(m.trianglesPos) for m in meshes)
+        pos = np.zeros(nt, abi.TRIANGLE); inf = np.zeros(nt, abi.TRIANGLE_INFO)
+        nodes = np.zeros(2 * nt + 16, abi.BVH_NODE); descs = np.zeros(len(meshes), abi.MESH_DESC)
+        got_tris = ctypes.c_uint32(0)
+        nn = ref_octree.ref_load_mesh_and_bvh(ctypes.cast(views, ctypes.c_void_p), len(meshes), depth, leaf, abi.ptr(pos), abi.ptr(inf), nt,
+                                              abi.ptr(nodes), len(nodes), abi.ptr(descs), ctypes.byref(got_tris))
+        assert nn == len(geo.bvhNodes) and got_tris.value == nt == len(geo.trianglesPos)
+        assert nodes[:nn].tobytes() == geo.bvhNodes.tobytes()
+        assert pos.tobytes() == geo.trianglesPos.tobytes() and inf.tobytes() == geo.trianglesInfo.tobytes()
+        assert descs.tobytes() == geo.meshDescs.tobytes()
